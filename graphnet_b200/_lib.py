@@ -1,0 +1,95 @@
+"""ctypes binding of the C ABI declared in include/graphnet_b200.h.
+
+The shared library is built in-tree by `__graft_entry__.build()` (plain nvcc,
+sm_100a).  There is NO fallback: if the library is missing, importing any
+compute entry point raises, and every wrapper refuses non-CUDA tensors.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libgraphnet_b200.so")
+
+GN_OK = 0
+ACT = {"none": 0, "relu": 1, "gelu": 2}
+AGGR = {"add": 0, "sum": 0, "mean": 1, "max": 2, "min": 3}
+POOL = {"min": 0, "max": 1, "sum": 2, "mean": 3}
+DTYPE_F32, DTYPE_BF16 = 0, 1
+HEAD = {
+    "IdentityTask": 0,
+    "EnergyReconstruction": 1,
+    "DirectionReconstructionWithKappa": 2,
+    "ZenithReconstruction": 3,
+    "ZenithReconstructionWithKappa": 4,
+    "AzimuthReconstructionWithKappa": 5,
+}
+FLAG_UNSORTED_BATCH, FLAG_UNSORTED_TARGETS, FLAG_INDEX_OUT_OF_RANGE = 1, 2, 4
+
+
+class GnGraph(C.Structure):
+    _fields_ = [
+        ("col", C.c_void_p),
+        ("deg", C.c_void_p),
+        ("rowptr", C.c_void_p),
+        ("ell_stride", C.c_int32),
+    ]
+
+
+_p, _i64, _i32, _int, _sz = C.c_void_p, C.c_int64, C.c_int32, C.c_int, C.c_size_t
+_gp = C.POINTER(GnGraph)
+_hp = C.POINTER(C.c_int32)  # host int32 array
+
+# name -> (restype, argtypes); must list every symbol of include/graphnet_b200.h
+SIGNATURES = {
+    "gn_last_error": (C.c_char_p, []),
+    "gn_version": (_int, []),
+    "gn_launch_count": (C.c_uint64, []),
+    "gn_batch_to_ptr": (_int, [_p, _i64, _i64, _p, _p, _p]),
+    "gn_knn_graph": (_int, [_p, _i64, _hp, _int, _p, _i64, _i64, _int, _int, _p, _i32, _p, _p]),
+    "gn_scan_scratch_bytes": (_sz, [_i64]),
+    "gn_ell_row_offsets": (_int, [_p, _i64, _p, _p, _sz, _p]),
+    "gn_ell_to_coo": (_int, [_p, _i32, _p, _p, _i64, _i64, _p, _p]),
+    "gn_coo_to_csr": (_int, [_p, _i64, _i64, _p, _p, _p, _p, _p]),
+    "gn_global_variables": (_int, [_p, _i64, _int, _gp, _p, _p, _i64, _i64, _p, _p, _i64, _int, _int, _p]),
+    "gn_segment_pool": (_int, [_p, _int, _i64, _int, _p, _i64, _hp, _int, _p, _i64, _p]),
+    "gn_linear_f32": (_int, [_p, _i64, _p, _p, _p, _i64, _i64, _int, _int, _int, _p]),
+    "gn_edgeconv_prepare_f32": (_int, [_p, _p, _int, _int, _int, _p, _p, _p]),
+    "gn_edgeconv_f32": (_int, [_p, _i64, _int, _gp, _i64, _p, _p, _int, _p, _p, _int, _int, _int, _p, _p, _i64, _p]),
+    "gn_task_head": (_int, [_p, _i64, _int, _int, _p, _p]),
+}
+
+_lib: Optional[C.CDLL] = None
+
+
+class GraphnetB200Error(RuntimeError):
+    """Raised when a C-ABI call returns a non-zero status."""
+
+
+def load() -> C.CDLL:
+    """Load (once) and return the shared library; raise loudly if absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"graphnet_b200: CUDA library not built ({LIB_PATH} missing). "
+            "Run `python -c 'import __graft_entry__ as g; g.build()'` in the repo root. "
+            "There is no CPU fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str) -> None:
+    if status != GN_OK:
+        msg = load().gn_last_error().decode("utf-8", "replace")
+        raise GraphnetB200Error(f"{what} failed with status {status}: {msg}")

@@ -1,0 +1,465 @@
+// Segmented per-event kNN graph construction and graph-layout conversions.
+//
+// Replaces torch_cluster.knn / torch_geometric.nn.knn_graph as reached from the
+// reference at data_representation/graphs/edges/edges.py:78-82 and
+// models/components/layers.py:70-74.  See include/graphnet_b200.h for the contract.
+//
+// Kernel shape (HBM-bound integer/float work, no tensor cores): one CTA per event.
+// The event's coordinates are staged once in shared memory as SoA; every thread owns
+// one query at a time and scans the candidates in index order (shared-memory
+// broadcast reads), keeping the best k+1 in a register-resident sorted list.  The
+// (distance^2, index) total order falls out of the scan order plus a strict '<'
+// insertion.  Distances use __fsub_rn/__fmul_rn/__fadd_rn so nvcc cannot contract
+// them into FMAs: the rounding is that of the CPU reference.
+#include "common.cuh"
+
+namespace gn {
+
+// ---------------------------------------------------------------- batch -> ptr
+__global__ void batch_to_ptr_kernel(const int64_t* __restrict__ batch, int64_t N, int64_t B,
+                                    int32_t* __restrict__ ptr, int32_t* __restrict__ flags) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > N) return;
+  int64_t cur = (i < N) ? batch[i] : B;
+  int64_t prev = (i > 0) ? batch[i - 1] : -1;
+  if (i < N && (cur < 0 || cur >= B)) {
+    atomicOr(flags, GN_FLAG_INDEX_OUT_OF_RANGE);
+    return;
+  }
+  if (i > 0 && (prev < 0 || prev >= B)) return;
+  if (cur < prev) {
+    atomicOr(flags, GN_FLAG_UNSORTED_BATCH);
+    return;
+  }
+  for (int64_t e = prev + 1; e <= cur; ++e) ptr[e] = (int32_t)i;
+}
+
+// ------------------------------------------------------------------------ kNN
+constexpr int KNN_MAX_DIMS = 16;
+constexpr int KNN_THREADS = 128;
+constexpr int KNN_SMEM_FLOATS = 8192;  // 32 KB of staged coordinates per CTA
+
+struct KnnParams {
+  const float* x;
+  int64_t ldx;
+  int cols[KNN_MAX_DIMS];
+  int dims;
+  const int32_t* ptr;
+  int kk;    // neighbours kept before dropping self: k + (loop ? 0 : 1)
+  int loop;
+  int32_t* nbr;
+  int32_t stride;
+  int32_t* deg;
+  int chunk;  // candidates staged per pass (multiple of 32)
+};
+
+// Sorted list of the CAP best (distance, index) pairs seen so far.
+template <int CAP>
+struct TopList {
+  float d[CAP];
+  int idx[CAP];
+  int m;
+  __device__ __forceinline__ void init() {
+#pragma unroll
+    for (int s = 0; s < CAP; ++s) { d[s] = __int_as_float(0x7f800000); idx[s] = -1; }
+    m = 0;
+  }
+  // Candidates arrive in ascending index order; an equal distance never displaces
+  // an earlier entry, so ties rank by index.
+  __device__ __forceinline__ void push(float cd, int ci) {
+    if (m == CAP && !(cd < d[CAP - 1])) return;
+    bool ins = false;
+#pragma unroll
+    for (int s = 0; s < CAP; ++s) {
+      bool sw = ins | (s >= m) | (cd < d[s]);
+      float td = d[s];
+      int ti = idx[s];
+      d[s] = sw ? cd : td;
+      idx[s] = sw ? ci : ti;
+      cd = sw ? td : cd;
+      ci = sw ? ti : ci;
+      ins = sw;
+    }
+    m = min(m + 1, CAP);
+  }
+};
+
+template <int CAP, int DIMS>  // DIMS == 0: runtime p.dims
+__global__ void __launch_bounds__(KNN_THREADS) knn_kernel(KnnParams p) {
+  extern __shared__ float s_coord[];  // [dims][chunk]
+  const int dims = DIMS > 0 ? DIMS : p.dims;
+  const int e = blockIdx.x;
+  const int lo = p.ptr[e];
+  const int n = p.ptr[e + 1] - lo;
+  if (n <= 0) return;
+  const int chunk = p.chunk;
+  const int tid = threadIdx.x;
+
+  for (int qbase = 0; qbase < n; qbase += KNN_THREADS) {
+    const int q = qbase + tid;
+    const bool active = q < n;
+    float qc[DIMS > 0 ? DIMS : KNN_MAX_DIMS];
+#pragma unroll
+    for (int t = 0; t < (DIMS > 0 ? DIMS : KNN_MAX_DIMS); ++t)
+      qc[t] = (active && t < dims) ? p.x[(int64_t)(lo + q) * p.ldx + p.cols[t]] : 0.f;
+    TopList<CAP> top;
+    top.init();
+
+    for (int cbase = 0; cbase < n; cbase += chunk) {
+      const int cn = min(chunk, n - cbase);
+      if (n > chunk || qbase == 0) {
+        __syncthreads();
+        for (int t = 0; t < dims; ++t)
+          for (int c = tid; c < cn; c += KNN_THREADS)
+            s_coord[t * chunk + c] = p.x[(int64_t)(lo + cbase + c) * p.ldx + p.cols[t]];
+        __syncthreads();
+      }
+      if (active) {
+        for (int c = 0; c < cn; ++c) {
+          float d = 0.f;
+#pragma unroll
+          for (int t = 0; t < (DIMS > 0 ? DIMS : KNN_MAX_DIMS); ++t) {
+            if (t < dims) {
+              float diff = __fsub_rn(qc[t], s_coord[t * chunk + c]);
+              d = __fadd_rn(d, __fmul_rn(diff, diff));
+            }
+          }
+          top.push(d, cbase + c);
+        }
+      }
+    }
+
+    if (active) {
+      const int keep = min(top.m, p.kk);
+      int32_t* row = p.nbr + (int64_t)(lo + q) * p.stride;
+      int cnt = 0;
+#pragma unroll
+      for (int s = 0; s < CAP; ++s) {
+        if (s < keep) {
+          int j = top.idx[s];
+          if (p.loop || j != q) row[cnt++] = lo + j;
+        }
+      }
+      p.deg[lo + q] = cnt;
+      for (int r = cnt; r < p.stride; ++r) row[r] = -1;
+    }
+  }
+}
+
+// Runtime-capacity variant for large k (k+1 > 33): the list lives in local memory.
+constexpr int KNN_MAX_KK = 128;
+template <int DIMS>
+__global__ void __launch_bounds__(KNN_THREADS) knn_kernel_bigk(KnnParams p) {
+  extern __shared__ float s_coord[];
+  const int dims = DIMS > 0 ? DIMS : p.dims;
+  const int e = blockIdx.x;
+  const int lo = p.ptr[e];
+  const int n = p.ptr[e + 1] - lo;
+  if (n <= 0) return;
+  const int chunk = p.chunk;
+  const int tid = threadIdx.x;
+  const int cap = p.kk;
+  for (int qbase = 0; qbase < n; qbase += KNN_THREADS) {
+    const int q = qbase + tid;
+    const bool active = q < n;
+    float qc[KNN_MAX_DIMS];
+    for (int t = 0; t < dims; ++t)
+      qc[t] = active ? p.x[(int64_t)(lo + q) * p.ldx + p.cols[t]] : 0.f;
+    float bd[KNN_MAX_KK];
+    int bi[KNN_MAX_KK];
+    int m = 0;
+    for (int cbase = 0; cbase < n; cbase += chunk) {
+      const int cn = min(chunk, n - cbase);
+      if (n > chunk || qbase == 0) {
+        __syncthreads();
+        for (int t = 0; t < dims; ++t)
+          for (int c = tid; c < cn; c += KNN_THREADS)
+            s_coord[t * chunk + c] = p.x[(int64_t)(lo + cbase + c) * p.ldx + p.cols[t]];
+        __syncthreads();
+      }
+      if (active) {
+        for (int c = 0; c < cn; ++c) {
+          float d = 0.f;
+          for (int t = 0; t < dims; ++t) {
+            float diff = __fsub_rn(qc[t], s_coord[t * chunk + c]);
+            d = __fadd_rn(d, __fmul_rn(diff, diff));
+          }
+          if (m == cap && !(d < bd[cap - 1])) continue;
+          int s = (m < cap) ? m : cap - 1;  // slot that is freed / appended
+          while (s > 0 && d < bd[s - 1]) { bd[s] = bd[s - 1]; bi[s] = bi[s - 1]; --s; }
+          bd[s] = d;
+          bi[s] = cbase + c;
+          if (m < cap) ++m;
+        }
+      }
+    }
+    if (active) {
+      int32_t* row = p.nbr + (int64_t)(lo + q) * p.stride;
+      int cnt = 0;
+      for (int s = 0; s < m; ++s) {
+        int j = bi[s];
+        if (p.loop || j != q) row[cnt++] = lo + j;
+      }
+      p.deg[lo + q] = cnt;
+      for (int r = cnt; r < p.stride; ++r) row[r] = -1;
+    }
+  }
+}
+
+template <int CAP>
+static int launch_knn(const KnnParams& p, int64_t B, cudaStream_t st) {
+  size_t smem = (size_t)p.dims * p.chunk * sizeof(float);
+  dim3 grid((unsigned)B), block(KNN_THREADS);
+  switch (p.dims) {
+    case 1: knn_kernel<CAP, 1><<<grid, block, smem, st>>>(p); break;
+    case 2: knn_kernel<CAP, 2><<<grid, block, smem, st>>>(p); break;
+    case 3: knn_kernel<CAP, 3><<<grid, block, smem, st>>>(p); break;
+    case 4: knn_kernel<CAP, 4><<<grid, block, smem, st>>>(p); break;
+    default: knn_kernel<CAP, 0><<<grid, block, smem, st>>>(p); break;
+  }
+  return GN_OK;
+}
+
+// ------------------------------------------------------- exclusive scan (int32)
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 4;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;  // 1024 values per block
+
+__device__ __forceinline__ int64_t block_exclusive_scan(int64_t v, int64_t* total) {
+  // exclusive scan of one value per thread over a SCAN_THREADS block
+  __shared__ int64_t warp_sums[SCAN_THREADS / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int64_t incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int64_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int64_t w = (lane < SCAN_THREADS / 32) ? warp_sums[lane] : 0;
+    int64_t wi = w;
+#pragma unroll
+    for (int o = 1; o < SCAN_THREADS / 32; o <<= 1) {
+      int64_t t = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane >= o) wi += t;
+    }
+    if (lane < SCAN_THREADS / 32) warp_sums[lane] = wi - w;  // exclusive warp offsets
+    if (lane == SCAN_THREADS / 32 - 1) *total = wi;
+  }
+  __syncthreads();
+  int64_t r = warp_sums[warp] + incl - v;
+  __syncthreads();
+  return r;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums_kernel(
+    const int32_t* __restrict__ in, int64_t n, int64_t* __restrict__ block_sums) {
+  __shared__ int64_t total;
+  int64_t base = (int64_t)blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+  int64_t s = 0;
+#pragma unroll
+  for (int t = 0; t < SCAN_ITEMS; ++t)
+    if (base + t < n) s += in[base + t];
+  block_exclusive_scan(s, &total);
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+// one block turns the per-block sums into exclusive block offsets, in place
+__global__ void __launch_bounds__(SCAN_THREADS) scan_offsets_kernel(int64_t* __restrict__ block_sums,
+                                                                   int64_t nblocks) {
+  __shared__ int64_t total;
+  int64_t carry = 0;
+  for (int64_t base = 0; base < nblocks; base += SCAN_THREADS) {
+    int64_t i = base + threadIdx.x;
+    int64_t v = (i < nblocks) ? block_sums[i] : 0;
+    int64_t ex = block_exclusive_scan(v, &total);
+    if (i < nblocks) block_sums[i] = carry + ex;
+    carry += total;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(
+    const int32_t* __restrict__ in, int64_t n, const int64_t* __restrict__ block_offsets,
+    int64_t* __restrict__ out) {
+  __shared__ int64_t total;
+  int64_t base = (int64_t)blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+  int32_t v[SCAN_ITEMS];
+  int64_t s = 0;
+#pragma unroll
+  for (int t = 0; t < SCAN_ITEMS; ++t) {
+    v[t] = (base + t < n) ? in[base + t] : 0;
+    s += v[t];
+  }
+  int64_t ex = block_exclusive_scan(s, &total) + block_offsets[blockIdx.x];
+#pragma unroll
+  for (int t = 0; t < SCAN_ITEMS; ++t) {
+    if (base + t < n) out[base + t] = ex;
+    ex += v[t];
+  }
+  // out[n] = grand total, written by the thread that owns the last element
+  if (base <= n - 1 && n - 1 < base + SCAN_ITEMS) out[n] = ex;
+}
+
+__global__ void ell_to_coo_kernel(const int32_t* __restrict__ nbr, int32_t stride,
+                                  const int32_t* __restrict__ deg,
+                                  const int64_t* __restrict__ rowptr, int64_t N, int64_t E,
+                                  int64_t* __restrict__ ei) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  int64_t o = rowptr[i];
+  int d = deg[i];
+  for (int r = 0; r < d; ++r) {
+    ei[o + r] = nbr[i * stride + r];
+    ei[E + o + r] = i;
+  }
+}
+
+// ------------------------------------------------------------------ COO -> CSR
+__global__ void coo_to_csr_kernel(const int64_t* __restrict__ ei, int64_t E, int64_t N,
+                                  int32_t* __restrict__ rowptr, int32_t* __restrict__ col,
+                                  int32_t* __restrict__ flags) {
+  int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e > E) return;
+  const int64_t* src = ei;
+  const int64_t* dst = ei + E;
+  int64_t cur = (e < E) ? dst[e] : N;
+  int64_t prev = (e > 0) ? dst[e - 1] : -1;
+  if (e < E) {
+    int64_t s = src[e];
+    if (s < 0 || s >= N || cur < 0 || cur >= N) {
+      atomicOr(flags, GN_FLAG_INDEX_OUT_OF_RANGE);
+      col[e] = 0;
+      return;
+    }
+    col[e] = (int32_t)s;
+  }
+  if (e > 0 && (prev < 0 || prev >= N)) return;
+  if (cur < prev) {
+    atomicOr(flags, GN_FLAG_UNSORTED_TARGETS);
+    return;
+  }
+  for (int64_t v = prev + 1; v <= cur; ++v) rowptr[v] = (int32_t)e;
+}
+
+__global__ void max_degree_kernel(const int32_t* __restrict__ rowptr, int64_t N,
+                                  int32_t* __restrict__ max_degree) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int d = (i < N) ? rowptr[i + 1] - rowptr[i] : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) d = max(d, __shfl_xor_sync(0xffffffffu, d, o));
+  if ((threadIdx.x & 31) == 0 && d > 0) atomicMax(max_degree, d);
+}
+
+}  // namespace gn
+
+using namespace gn;
+
+extern "C" int gn_batch_to_ptr(const int64_t* batch, int64_t N, int64_t B, int32_t* ptr,
+                               int32_t* flags, void* stream) {
+  GN_CHECK_ARG(N >= 0 && B >= 0 && ptr && flags, "gn_batch_to_ptr: bad arguments");
+  GN_CHECK_ARG(N == 0 || batch, "gn_batch_to_ptr: batch is null");
+  GN_CHECK_ARG(N < INT32_MAX, "gn_batch_to_ptr: N must fit int32");
+  int threads = 256;
+  batch_to_ptr_kernel<<<(unsigned)ceil_div(N + 1, threads), threads, 0, as_stream(stream)>>>(
+      batch, N, B, ptr, flags);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_knn_graph(const float* x, int64_t ldx, const int32_t* cols, int dims,
+                            const int32_t* ptr, int64_t N, int64_t B, int k, int loop,
+                            int32_t* nbr, int32_t stride, int32_t* deg, void* stream) {
+  GN_CHECK_ARG(dims >= 1 && dims <= KNN_MAX_DIMS, "gn_knn_graph: dims=%d not in [1,%d]", dims,
+               KNN_MAX_DIMS);
+  GN_CHECK_ARG(k >= 1, "gn_knn_graph: k=%d must be >= 1", k);
+  const int kk = k + (loop ? 0 : 1);
+  GN_CHECK_ARG(kk <= KNN_MAX_KK, "gn_knn_graph: k=%d too large (max %d)", k, KNN_MAX_KK - 1);
+  GN_CHECK_ARG(stride >= kk, "gn_knn_graph: stride=%d < k+1=%d", stride, kk);
+  GN_CHECK_ARG(N >= 0 && B >= 0 && N < INT32_MAX, "gn_knn_graph: bad sizes");
+  if (N == 0 || B == 0) return GN_OK;
+  GN_CHECK_ARG(x && cols && ptr && nbr && deg, "gn_knn_graph: null pointer");
+  KnnParams p;
+  p.x = x; p.ldx = ldx; p.dims = dims; p.ptr = ptr; p.kk = kk; p.loop = loop;
+  p.nbr = nbr; p.stride = stride; p.deg = deg;
+  for (int t = 0; t < KNN_MAX_DIMS; ++t) p.cols[t] = t < dims ? cols[t] : 0;
+  for (int t = 0; t < dims; ++t)
+    GN_CHECK_ARG(cols[t] >= 0 && cols[t] < ldx, "gn_knn_graph: column %d out of range", cols[t]);
+  p.chunk = (KNN_SMEM_FLOATS / dims) & ~31;
+  cudaStream_t st = as_stream(stream);
+  if (kk <= 9) launch_knn<9>(p, B, st);
+  else if (kk <= 17) launch_knn<17>(p, B, st);
+  else if (kk <= 33) launch_knn<33>(p, B, st);
+  else {
+    size_t smem = (size_t)dims * p.chunk * sizeof(float);
+    knn_kernel_bigk<0><<<(unsigned)B, KNN_THREADS, smem, st>>>(p);
+  }
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" size_t gn_scan_scratch_bytes(int64_t n) {
+  return (size_t)(ceil_div(n > 0 ? n : 1, SCAN_TILE)) * sizeof(int64_t);
+}
+
+namespace gn {
+int exclusive_scan_i32(const int32_t* in, int64_t n, int64_t* out, int64_t* block_sums,
+                       cudaStream_t st) {
+  int64_t nblocks = ceil_div(n, SCAN_TILE);
+  scan_block_sums_kernel<<<(unsigned)nblocks, SCAN_THREADS, 0, st>>>(in, n, block_sums);
+  GN_LAUNCH_CHECK();
+  scan_offsets_kernel<<<1, SCAN_THREADS, 0, st>>>(block_sums, nblocks);
+  GN_LAUNCH_CHECK();
+  scan_apply_kernel<<<(unsigned)nblocks, SCAN_THREADS, 0, st>>>(in, n, block_sums, out);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+}  // namespace gn
+
+extern "C" int gn_ell_row_offsets(const int32_t* deg, int64_t N, int64_t* rowptr, void* scratch,
+                                  size_t scratch_bytes, void* stream) {
+  GN_CHECK_ARG(N >= 0 && rowptr, "gn_ell_row_offsets: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (N == 0) {
+    GN_CUDA(cudaMemsetAsync(rowptr, 0, sizeof(int64_t), st));
+    return GN_OK;
+  }
+  GN_CHECK_ARG(deg && scratch, "gn_ell_row_offsets: null pointer");
+  GN_CHECK_ARG(scratch_bytes >= gn_scan_scratch_bytes(N),
+               "gn_ell_row_offsets: scratch too small (%zu < %zu)", scratch_bytes,
+               gn_scan_scratch_bytes(N));
+  return exclusive_scan_i32(deg, N, rowptr, reinterpret_cast<int64_t*>(scratch), st);
+}
+
+extern "C" int gn_ell_to_coo(const int32_t* nbr, int32_t stride, const int32_t* deg,
+                             const int64_t* rowptr, int64_t N, int64_t E, int64_t* edge_index,
+                             void* stream) {
+  GN_CHECK_ARG(N >= 0 && E >= 0, "gn_ell_to_coo: bad sizes");
+  if (N == 0 || E == 0) return GN_OK;
+  GN_CHECK_ARG(nbr && deg && rowptr && edge_index && stride > 0, "gn_ell_to_coo: null pointer");
+  ell_to_coo_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, as_stream(stream)>>>(
+      nbr, stride, deg, rowptr, N, E, edge_index);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_coo_to_csr(const int64_t* edge_index, int64_t E, int64_t N, int32_t* rowptr,
+                             int32_t* col, int32_t* flags, int32_t* max_degree, void* stream) {
+  GN_CHECK_ARG(E >= 0 && N >= 0 && rowptr && flags, "gn_coo_to_csr: bad arguments");
+  GN_CHECK_ARG(E < INT32_MAX && N < INT32_MAX, "gn_coo_to_csr: sizes must fit int32");
+  GN_CHECK_ARG(E == 0 || (edge_index && col), "gn_coo_to_csr: null pointer");
+  cudaStream_t st = as_stream(stream);
+  coo_to_csr_kernel<<<(unsigned)ceil_div(E + 1, 256), 256, 0, st>>>(edge_index, E, N, rowptr, col,
+                                                                    flags);
+  GN_LAUNCH_CHECK();
+  if (max_degree) {
+    GN_CUDA(cudaMemsetAsync(max_degree, 0, sizeof(int32_t), st));
+    if (N > 0) {
+      max_degree_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(rowptr, N, max_degree);
+      GN_LAUNCH_CHECK();
+    }
+  }
+  return GN_OK;
+}

@@ -1,0 +1,292 @@
+// Per-event (segmented) reductions: global variables + homophily + "distribute",
+// and global min/max/sum/mean pooling.
+//
+// Replaces torch_scatter.scatter_{min,max,sum,mean} and
+// torch_geometric.utils.homophily as reached from the reference at
+// models/gnn/dynedge.py:252-265, :267-294, :309-320 and models/utils.py:17-33.
+// Both kernels are HBM-bound streaming reductions: rows of one event are
+// contiguous, threads map to feature columns (coalesced, 128-bit where aligned),
+// every input element is read exactly once and all requested statistics are
+// produced in the same pass.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace gn {
+
+// --------------------------------------------------------- global variables
+constexpr int GV_THREADS = 128;
+constexpr int GV_MAX_F = 64;
+
+template <typename OutT>
+__device__ __forceinline__ OutT to_out(float v);
+template <>
+__device__ __forceinline__ float to_out<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 to_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+template <typename OutT>
+__global__ void __launch_bounds__(GV_THREADS) global_variables_kernel(
+    const float* __restrict__ x, int64_t ldx, int F, GraphView g, const int32_t* __restrict__ ptr,
+    const int32_t* __restrict__ n_pulses, float* __restrict__ gv, OutT* __restrict__ x0,
+    int64_t ldx0, int x0_cols) {
+  __shared__ float s_part[GV_THREADS];
+  __shared__ float s_gv[GV_MAX_F + 5];
+  __shared__ int s_cnt[5];
+  const int e = blockIdx.x;
+  const int lo = ptr[e];
+  const int n = ptr[e + 1] - lo;
+  const int tid = threadIdx.x;
+  const int G = F + 5;
+  if (tid < 5) s_cnt[tid] = 0;
+
+  // column sums: thread (r, c) walks rows r, r + rpp, ...
+  const int rpp = GV_THREADS / F;
+  const int r0 = tid / F, c0 = tid % F;
+  float s = 0.f;
+  if (r0 < rpp)
+    for (int r = r0; r < n; r += rpp) s += x[(int64_t)(lo + r) * ldx + c0];
+  s_part[tid] = s;
+  __syncthreads();
+  if (tid < F) {
+    float tot = 0.f;
+    for (int r = 0; r < rpp; ++r) tot += s_part[r * F + tid];
+    float cnt = (float)max(n, 1);
+    s_gv[tid] = tot / cnt;
+  }
+
+  // homophily of columns 0..3 over the in-edges of this event's nodes
+  int eq[4] = {0, 0, 0, 0};
+  int ne = 0;
+  for (int r = tid; r < n; r += GV_THREADS) {
+    const int64_t i = lo + r;
+    int64_t start;
+    int cnt;
+    graph_row(g, i, start, cnt);
+    const float xi0 = x[i * ldx + 0], xi1 = x[i * ldx + 1], xi2 = x[i * ldx + 2],
+                xi3 = x[i * ldx + 3];
+    for (int t = 0; t < cnt; ++t) {
+      const int64_t j = g.col[start + t];
+      eq[0] += (x[j * ldx + 0] == xi0);
+      eq[1] += (x[j * ldx + 1] == xi1);
+      eq[2] += (x[j * ldx + 2] == xi2);
+      eq[3] += (x[j * ldx + 3] == xi3);
+    }
+    ne += cnt;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) eq[c] += __shfl_xor_sync(0xffffffffu, eq[c], o);
+    ne += __shfl_xor_sync(0xffffffffu, ne, o);
+  }
+  if ((tid & 31) == 0) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) atomicAdd(&s_cnt[c], eq[c]);
+    atomicAdd(&s_cnt[4], ne);
+  }
+  __syncthreads();
+  if (tid < 4) {
+    const int tot = s_cnt[4];
+    s_gv[F + tid] = tot > 0 ? (float)s_cnt[tid] / (float)tot : 0.f;
+  }
+  if (tid == 4) s_gv[F + 4] = log10f((float)n_pulses[e]);
+  __syncthreads();
+  for (int c = tid; c < G; c += GV_THREADS) gv[(int64_t)e * G + c] = s_gv[c];
+
+  if (x0 != nullptr) {
+    const int64_t total = (int64_t)n * x0_cols;
+    for (int64_t idx = tid; idx < total; idx += GV_THREADS) {
+      const int r = (int)(idx / x0_cols), c = (int)(idx % x0_cols);
+      float v = 0.f;
+      if (c < F) v = x[(int64_t)(lo + r) * ldx + c];
+      else if (c < F + G) v = s_gv[c - F];
+      x0[(int64_t)(lo + r) * ldx0 + c] = to_out<OutT>(v);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ pooling
+constexpr int POOL_COLS = 64;   // column-threads per CTA (x4 columns each when vectorised)
+constexpr int POOL_ROWG = 4;    // row groups per CTA
+
+struct PoolSchemes {
+  int n;
+  int s[8];
+};
+
+template <typename T, int VEC>
+__device__ __forceinline__ void load_vec(const T* p, float (&v)[VEC]);
+template <>
+__device__ __forceinline__ void load_vec<float, 4>(const float* p, float (&v)[4]) {
+  float4 t = *reinterpret_cast<const float4*>(p);
+  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+template <>
+__device__ __forceinline__ void load_vec<float, 1>(const float* p, float (&v)[1]) { v[0] = *p; }
+template <>
+__device__ __forceinline__ void load_vec<__nv_bfloat16, 4>(const __nv_bfloat16* p, float (&v)[4]) {
+  uint2 t = *reinterpret_cast<const uint2*>(p);
+  v[0] = __uint_as_float(t.x << 16); v[1] = __uint_as_float(t.x & 0xffff0000u);
+  v[2] = __uint_as_float(t.y << 16); v[3] = __uint_as_float(t.y & 0xffff0000u);
+}
+template <>
+__device__ __forceinline__ void load_vec<__nv_bfloat16, 1>(const __nv_bfloat16* p, float (&v)[1]) {
+  v[0] = __bfloat162float(*p);
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(POOL_COLS * POOL_ROWG) segment_pool_kernel(
+    const T* __restrict__ x, int64_t ldx, int C, const int32_t* __restrict__ ptr,
+    PoolSchemes sch, float* __restrict__ out, int64_t ldo) {
+  __shared__ float s_min[POOL_ROWG][POOL_COLS * VEC];
+  __shared__ float s_max[POOL_ROWG][POOL_COLS * VEC];
+  __shared__ float s_sum[POOL_ROWG][POOL_COLS * VEC];
+  const int e = blockIdx.x;
+  const int lo = ptr[e];
+  const int n = ptr[e + 1] - lo;
+  const int ct = threadIdx.x % POOL_COLS;
+  const int rg = threadIdx.x / POOL_COLS;
+  const int c = (blockIdx.y * POOL_COLS + ct) * VEC;
+  const bool col_ok = c < C;
+  float mn[VEC], mx[VEC], sm[VEC];
+#pragma unroll
+  for (int v = 0; v < VEC; ++v) {
+    mn[v] = __int_as_float(0x7f800000);
+    mx[v] = __int_as_float(0xff800000);
+    sm[v] = 0.f;
+  }
+  if (col_ok) {
+    const T* base = x + (int64_t)lo * ldx + c;
+    int r = rg;
+    for (; r + 3 * POOL_ROWG < n; r += 4 * POOL_ROWG) {
+      float a0[VEC], a1[VEC], a2[VEC], a3[VEC];
+      load_vec<T, VEC>(base + (int64_t)r * ldx, a0);
+      load_vec<T, VEC>(base + (int64_t)(r + POOL_ROWG) * ldx, a1);
+      load_vec<T, VEC>(base + (int64_t)(r + 2 * POOL_ROWG) * ldx, a2);
+      load_vec<T, VEC>(base + (int64_t)(r + 3 * POOL_ROWG) * ldx, a3);
+#pragma unroll
+      for (int v = 0; v < VEC; ++v) {
+        mn[v] = fminf(fminf(mn[v], a0[v]), fminf(a1[v], fminf(a2[v], a3[v])));
+        mx[v] = fmaxf(fmaxf(mx[v], a0[v]), fmaxf(a1[v], fmaxf(a2[v], a3[v])));
+        sm[v] += a0[v]; sm[v] += a1[v]; sm[v] += a2[v]; sm[v] += a3[v];
+      }
+    }
+    for (; r < n; r += POOL_ROWG) {
+      float a0[VEC];
+      load_vec<T, VEC>(base + (int64_t)r * ldx, a0);
+#pragma unroll
+      for (int v = 0; v < VEC; ++v) {
+        mn[v] = fminf(mn[v], a0[v]);
+        mx[v] = fmaxf(mx[v], a0[v]);
+        sm[v] += a0[v];
+      }
+    }
+  }
+#pragma unroll
+  for (int v = 0; v < VEC; ++v) {
+    s_min[rg][ct * VEC + v] = mn[v];
+    s_max[rg][ct * VEC + v] = mx[v];
+    s_sum[rg][ct * VEC + v] = sm[v];
+  }
+  __syncthreads();
+  if (rg == 0 && col_ok) {
+    const float cnt = (float)max(n, 1);
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) {
+      float a = s_min[0][ct * VEC + v], b = s_max[0][ct * VEC + v], s = s_sum[0][ct * VEC + v];
+#pragma unroll
+      for (int g2 = 1; g2 < POOL_ROWG; ++g2) {
+        a = fminf(a, s_min[g2][ct * VEC + v]);
+        b = fmaxf(b, s_max[g2][ct * VEC + v]);
+        s += s_sum[g2][ct * VEC + v];
+      }
+      if (n == 0) { a = 0.f; b = 0.f; }  // torch_scatter: empty segment -> 0
+      if (c + v < C) {
+        for (int k = 0; k < sch.n; ++k) {
+          float r = sch.s[k] == GN_POOL_MIN ? a
+                  : sch.s[k] == GN_POOL_MAX ? b
+                  : sch.s[k] == GN_POOL_SUM ? s : s / cnt;
+          out[(int64_t)e * ldo + (int64_t)k * C + c + v] = r;
+        }
+      }
+    }
+  }
+}
+
+}  // namespace gn
+
+using namespace gn;
+
+extern "C" int gn_global_variables(const float* x, int64_t ldx, int F, const gn_graph* graph,
+                                   const int32_t* ptr, const int32_t* n_pulses, int64_t N,
+                                   int64_t B, float* gv, void* x0, int64_t ldx0, int x0_cols,
+                                   int x0_dtype, void* stream) {
+  GN_CHECK_ARG(F >= 4 && F <= GV_MAX_F,
+               "gn_global_variables: F=%d not in [4,%d] (columns 0..3 must be x,y,z,t)", F,
+               GV_MAX_F);
+  GN_CHECK_ARG(N >= 0 && B >= 0 && ldx >= F, "gn_global_variables: bad sizes");
+  if (B == 0) return GN_OK;
+  GN_CHECK_ARG(x && ptr && n_pulses && gv, "gn_global_variables: null pointer");
+  GraphView g;
+  int rc = make_graph_view(graph, &g);
+  if (rc != GN_OK) return rc;
+  if (x0) {
+    GN_CHECK_ARG(x0_cols >= F + F + 5 && ldx0 >= x0_cols,
+                 "gn_global_variables: x0 needs >= 2F+5 columns");
+  }
+  cudaStream_t st = as_stream(stream);
+  if (x0_dtype == GN_BF16) {
+    global_variables_kernel<__nv_bfloat16><<<(unsigned)B, GV_THREADS, 0, st>>>(
+        x, ldx, F, g, ptr, n_pulses, gv, reinterpret_cast<__nv_bfloat16*>(x0), ldx0, x0_cols);
+  } else {
+    GN_CHECK_ARG(x0_dtype == GN_F32, "gn_global_variables: bad x0_dtype");
+    global_variables_kernel<float><<<(unsigned)B, GV_THREADS, 0, st>>>(
+        x, ldx, F, g, ptr, n_pulses, gv, reinterpret_cast<float*>(x0), ldx0, x0_cols);
+  }
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_segment_pool(const void* x, int x_dtype, int64_t ldx, int C, const int32_t* ptr,
+                               int64_t B, const int32_t* schemes, int n_schemes, float* out,
+                               int64_t ldo, void* stream) {
+  GN_CHECK_ARG(C >= 1 && n_schemes >= 1 && n_schemes <= 8, "gn_segment_pool: bad sizes");
+  GN_CHECK_ARG(ldo >= (int64_t)C * n_schemes, "gn_segment_pool: ldo too small");
+  if (B == 0) return GN_OK;
+  GN_CHECK_ARG(x && ptr && schemes && out, "gn_segment_pool: null pointer");
+  PoolSchemes sch;
+  sch.n = n_schemes;
+  for (int k = 0; k < n_schemes; ++k) {
+    GN_CHECK_ARG(schemes[k] >= GN_POOL_MIN && schemes[k] <= GN_POOL_MEAN,
+                 "gn_segment_pool: unknown scheme %d", schemes[k]);
+    sch.s[k] = schemes[k];
+  }
+  cudaStream_t st = as_stream(stream);
+  const int threads = POOL_COLS * POOL_ROWG;
+  if (x_dtype == GN_F32) {
+    const float* xf = reinterpret_cast<const float*>(x);
+    bool vec = (C % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+    if (vec) {
+      dim3 grid((unsigned)B, (unsigned)ceil_div(C, POOL_COLS * 4));
+      segment_pool_kernel<float, 4><<<grid, threads, 0, st>>>(xf, ldx, C, ptr, sch, out, ldo);
+    } else {
+      dim3 grid((unsigned)B, (unsigned)ceil_div(C, POOL_COLS));
+      segment_pool_kernel<float, 1><<<grid, threads, 0, st>>>(xf, ldx, C, ptr, sch, out, ldo);
+    }
+  } else if (x_dtype == GN_BF16) {
+    const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+    bool vec = (C % 4 == 0) && (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 7) == 0);
+    if (vec) {
+      dim3 grid((unsigned)B, (unsigned)ceil_div(C, POOL_COLS * 4));
+      segment_pool_kernel<__nv_bfloat16, 4><<<grid, threads, 0, st>>>(xb, ldx, C, ptr, sch, out, ldo);
+    } else {
+      dim3 grid((unsigned)B, (unsigned)ceil_div(C, POOL_COLS));
+      segment_pool_kernel<__nv_bfloat16, 1><<<grid, threads, 0, st>>>(xb, ldx, C, ptr, sch, out, ldo);
+    }
+  } else {
+    GN_CHECK_ARG(false, "gn_segment_pool: bad x_dtype %d", x_dtype);
+  }
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}

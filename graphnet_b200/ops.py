@@ -1,0 +1,302 @@
+"""Tensor-level wrappers over the C ABI (device memory and streams via PyTorch).
+
+PyTorch is plumbing here: it owns device memory (outputs and scratch come from
+its caching allocator) and the current CUDA stream; all arithmetic happens in
+the sm_100a kernels of `csrc/` reached through `include/graphnet_b200.h`.
+Every wrapper refuses CPU tensors - there is no CPU path.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple, Union
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from ._lib import ACT, AGGR, DTYPE_BF16, DTYPE_F32, HEAD, POOL, GnGraph, check
+
+
+def _require_cuda(*tensors: Optional[Tensor]) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError(
+                "graphnet_b200 operates on CUDA tensors only (no CPU fallback); "
+                f"got a tensor on {t.device}"
+            )
+        dev = t.device if dev is None else dev
+        if t.device != dev:
+            raise RuntimeError("graphnet_b200: tensors on different devices")
+    assert dev is not None
+    return dev
+
+
+def _stream(dev: torch.device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def _ptr(t: Optional[Tensor]) -> C.c_void_p:
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _host_i32(vals: Sequence[int]):
+    return (C.c_int32 * len(vals))(*[int(v) for v in vals])
+
+
+@dataclass
+class Graph:
+    """In-edges grouped by target node (ELL from our kNN, or CSR from user COO)."""
+
+    col: Tensor  # int32
+    deg: Optional[Tensor]  # int32 [N]   (ELL)
+    rowptr: Optional[Tensor]  # int32 [N+1] (CSR)
+    ell_stride: int
+    num_nodes: int
+    flags: Optional[Tensor] = None  # int32[1], device
+    max_degree: Optional[Tensor] = None  # int32[1], device
+
+    def c_struct(self) -> GnGraph:
+        return GnGraph(
+            col=self.col.data_ptr(),
+            deg=0 if self.deg is None else self.deg.data_ptr(),
+            rowptr=0 if self.rowptr is None else self.rowptr.data_ptr(),
+            ell_stride=self.ell_stride,
+        )
+
+
+# ------------------------------------------------------------------ graph build
+def batch_to_ptr(batch: Tensor, num_events: int) -> Tuple[Tensor, Tensor]:
+    """Event offsets `ptr` [B+1] (int32) from the sorted `batch` vector, plus flags."""
+    dev = _require_cuda(batch)
+    batch = batch.contiguous()
+    if batch.dtype != torch.int64:
+        batch = batch.long()
+    ptr = torch.empty(num_events + 1, dtype=torch.int32, device=dev)
+    flags = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_batch_to_ptr(_ptr(batch), batch.shape[0], num_events, _ptr(ptr),
+                                          _ptr(flags), _stream(dev)), "gn_batch_to_ptr")
+    return ptr, flags
+
+
+def _columns(features_subset: Union[slice, Sequence[int], None], width: int) -> List[int]:
+    if features_subset is None:
+        return list(range(width))
+    if isinstance(features_subset, slice):
+        return list(range(width))[features_subset]
+    return [int(c) if c >= 0 else width + int(c) for c in features_subset]
+
+
+def knn_graph_ell(x: Tensor, k: int, ptr: Tensor, columns: Sequence[int], loop: bool = False,
+                  stride: Optional[int] = None) -> Graph:
+    """kNN graph of `x[:, columns]` per event in ELL layout (device only, no sync)."""
+    dev = _require_cuda(x, ptr)
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    N = x.shape[0]
+    B = ptr.shape[0] - 1
+    kk = k + (0 if loop else 1)
+    stride = kk if stride is None else stride
+    nbr = torch.empty((N, stride), dtype=torch.int32, device=dev)
+    deg = torch.empty(N, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_knn_graph(_ptr(x), x.stride(0), _host_i32(columns), len(columns),
+                                       _ptr(ptr), N, B, k, int(loop), _ptr(nbr), stride,
+                                       _ptr(deg), _stream(dev)), "gn_knn_graph")
+    return Graph(col=nbr, deg=deg, rowptr=None, ell_stride=stride, num_nodes=N)
+
+
+def ell_to_coo(g: Graph) -> Tensor:
+    """int64 `edge_index` [2, E] from an ELL graph (one host sync for E)."""
+    assert g.ell_stride > 0 and g.deg is not None
+    dev = g.col.device
+    N = g.num_nodes
+    lib = _lib.load()
+    rowptr = torch.empty(N + 1, dtype=torch.int64, device=dev)
+    nbytes = lib.gn_scan_scratch_bytes(N)
+    scratch = torch.empty(max(nbytes, 8), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gn_ell_row_offsets(_ptr(g.deg), N, _ptr(rowptr), _ptr(scratch), nbytes,
+                                     _stream(dev)), "gn_ell_row_offsets")
+        E = int(rowptr[N].item())
+        ei = torch.empty((2, E), dtype=torch.int64, device=dev)
+        check(lib.gn_ell_to_coo(_ptr(g.col), g.ell_stride, _ptr(g.deg), _ptr(rowptr), N, E,
+                                _ptr(ei), _stream(dev)), "gn_ell_to_coo")
+    return ei
+
+
+def knn_graph(x: Tensor, k: int, batch: Optional[Tensor] = None, loop: bool = False,
+              num_events: Optional[int] = None) -> Tensor:
+    """Drop-in for `torch_geometric.nn.knn_graph(x, k, batch, loop)` on CUDA tensors.
+
+    Reference call sites: graphs/edges/edges.py:78-82, components/layers.py:70-74.
+    Returns int64 COO [2, E] (row 0 = neighbour j, row 1 = query i), ordered by
+    query, then ascending (distance^2, index).
+    """
+    dev = _require_cuda(x, batch)
+    x = x.float().contiguous()
+    N = x.shape[0]
+    if N == 0:
+        return torch.zeros((2, 0), dtype=torch.int64, device=dev)
+    if batch is None:
+        ptr = torch.tensor([0, N], dtype=torch.int32, device=dev)
+    else:
+        if num_events is None:
+            num_events = int(batch.max().item()) + 1
+        ptr, flags = batch_to_ptr(batch, num_events)
+        if int(flags.item()) != 0:
+            raise ValueError("knn_graph: `batch` must be sorted with ids in [0, num_events)")
+    g = knn_graph_ell(x, k, ptr, list(range(x.shape[1])), loop=loop)
+    return ell_to_coo(g)
+
+
+def coo_to_csr(edge_index: Tensor, num_nodes: int) -> Graph:
+    """User `edge_index` [2, E] (int64, targets non-decreasing) -> CSR by target."""
+    dev = _require_cuda(edge_index)
+    assert edge_index.dim() == 2 and edge_index.shape[0] == 2
+    ei = edge_index.contiguous()
+    if ei.dtype != torch.int64:
+        ei = ei.long()
+    E = ei.shape[1]
+    rowptr = torch.empty(num_nodes + 1, dtype=torch.int32, device=dev)
+    col = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
+    flags = torch.zeros(1, dtype=torch.int32, device=dev)
+    maxdeg = torch.empty(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_coo_to_csr(_ptr(ei), E, num_nodes, _ptr(rowptr), _ptr(col),
+                                        _ptr(flags), _ptr(maxdeg), _stream(dev)), "gn_coo_to_csr")
+    return Graph(col=col, deg=None, rowptr=rowptr, ell_stride=0, num_nodes=num_nodes,
+                 flags=flags, max_degree=maxdeg)
+
+
+# ----------------------------------------------------------- per-event features
+def global_variables(x: Tensor, graph: Graph, ptr: Tensor, n_pulses: Tensor,
+                     x0: Optional[Tensor] = None, x0_cols: int = 0) -> Tensor:
+    """gv [B, F+5]; if `x0` is given also writes x0[:, :x0_cols] = [x, gv[batch], 0...]."""
+    dev = _require_cuda(x, ptr, n_pulses, x0)
+    assert x.dtype == torch.float32 and x.stride(1) == 1
+    N, F = x.shape
+    B = ptr.shape[0] - 1
+    n_pulses = n_pulses.to(torch.int32).contiguous()
+    assert n_pulses.shape[0] == B, "n_pulses must have one entry per event"
+    gv = torch.empty((B, F + 5), dtype=torch.float32, device=dev)
+    gs = graph.c_struct()
+    if x0 is not None:
+        assert x0.stride(1) == 1 and x0.shape[0] == N
+        dt = DTYPE_BF16 if x0.dtype == torch.bfloat16 else DTYPE_F32
+        ld0 = x0.stride(0)
+    else:
+        dt, ld0 = DTYPE_F32, 0
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_global_variables(_ptr(x), x.stride(0), F, C.byref(gs), _ptr(ptr),
+                                              _ptr(n_pulses), N, B, _ptr(gv), _ptr(x0), ld0,
+                                              x0_cols, dt, _stream(dev)), "gn_global_variables")
+    return gv
+
+
+def segment_pool(x: Tensor, ptr: Tensor, schemes: Sequence[str],
+                 out: Optional[Tensor] = None) -> Tensor:
+    """Per-event min/max/sum/mean of `x` [N, C], concatenated per scheme -> [B, C*P]."""
+    dev = _require_cuda(x, ptr, out)
+    assert x.stride(1) == 1
+    C_ = x.shape[1]
+    B = ptr.shape[0] - 1
+    P = len(schemes)
+    if out is None:
+        out = torch.empty((B, C_ * P), dtype=torch.float32, device=dev)
+    assert out.dtype == torch.float32 and out.stride(1) == 1
+    dt = DTYPE_BF16 if x.dtype == torch.bfloat16 else DTYPE_F32
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_segment_pool(_ptr(x), dt, x.stride(0), C_, _ptr(ptr), B,
+                                          _host_i32([POOL[s] for s in schemes]), P, _ptr(out),
+                                          out.stride(0), _stream(dev)), "gn_segment_pool")
+    return out
+
+
+# ------------------------------------------------------------------ dense, fp32
+def linear_f32(A: Tensor, W: Tensor, bias: Optional[Tensor], act: str = "none",
+               out: Optional[Tensor] = None) -> Tensor:
+    """act(A W^T + bias) with torch.nn.Linear's weight layout [N, K]."""
+    dev = _require_cuda(A, W, bias, out)
+    assert A.dtype == torch.float32 and A.stride(1) == 1
+    W = W.detach().contiguous()
+    M, K = A.shape
+    Nout = W.shape[0]
+    assert W.shape[1] == K
+    if out is None:
+        out = torch.empty((M, Nout), dtype=torch.float32, device=dev)
+    assert out.stride(1) == 1 and out.shape[0] == M and out.shape[1] >= Nout
+    b = None if bias is None else bias.detach().contiguous()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_linear_f32(_ptr(A), A.stride(0), _ptr(W), _ptr(b), _ptr(out),
+                                        out.stride(0), M, Nout, K, ACT[act], _stream(dev)),
+              "gn_linear_f32")
+    return out
+
+
+def edgeconv_prepare_f32(W1: Tensor, W2: Optional[Tensor]) -> Tuple[Tensor, Optional[Tensor]]:
+    """Repack an EdgeConv MLP's weights: Wpq [2a, d], W2T [a, b]."""
+    dev = _require_cuda(W1, W2)
+    W1 = W1.detach().float().contiguous()
+    a, d2 = W1.shape
+    assert d2 % 2 == 0
+    d = d2 // 2
+    Wpq = torch.empty((2 * a, d), dtype=torch.float32, device=dev)
+    if W2 is not None:
+        W2 = W2.detach().float().contiguous()
+        b = W2.shape[0]
+        assert W2.shape[1] == a
+        W2T = torch.empty((a, b), dtype=torch.float32, device=dev)
+    else:
+        b, W2T = a, None
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_edgeconv_prepare_f32(_ptr(W1), _ptr(W2), d, a, b, _ptr(Wpq),
+                                                  _ptr(W2T), _stream(dev)),
+              "gn_edgeconv_prepare_f32")
+    return Wpq, W2T
+
+
+def edgeconv_f32(x: Tensor, graph: Graph, Wpq: Tensor, b1: Optional[Tensor],
+                 W2T: Optional[Tensor], b2: Optional[Tensor], act: str = "relu",
+                 aggr: str = "add", out: Optional[Tensor] = None) -> Tensor:
+    """Fused EdgeConv forward (fp32): out[i] = aggr_j act(W2 act(W1 [x_i, x_j-x_i] + b1) + b2)."""
+    dev = _require_cuda(x, Wpq, W2T, out)
+    assert x.dtype == torch.float32 and x.stride(1) == 1
+    N, d = x.shape
+    a = Wpq.shape[0] // 2
+    assert Wpq.shape[1] == d
+    b = a if W2T is None else W2T.shape[1]
+    if out is None:
+        out = torch.empty((N, b), dtype=torch.float32, device=dev)
+    assert out.stride(1) == 1 and out.shape[0] == N and out.shape[1] >= b
+    pq = torch.empty((N, 2 * a), dtype=torch.float32, device=dev)
+    zeros = None
+    if b1 is None:
+        b1 = torch.zeros(a, dtype=torch.float32, device=dev)
+    if b2 is None and W2T is not None:
+        b2 = torch.zeros(b, dtype=torch.float32, device=dev)
+    gs = graph.c_struct()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_edgeconv_f32(
+            _ptr(x), x.stride(0), d, C.byref(gs), N, _ptr(Wpq), _ptr(b1.detach().contiguous()), a,
+            _ptr(W2T), _ptr(None if b2 is None else b2.detach().contiguous()), b, ACT[act],
+            AGGR[aggr], _ptr(pq), _ptr(out), out.stride(0), _stream(dev)), "gn_edgeconv_f32")
+    return out
+
+
+def task_head(y: Tensor, kind: str) -> Tensor:
+    """The `_forward` transform of a reconstruction head on the affine output `y`."""
+    dev = _require_cuda(y)
+    y = y.float().contiguous()
+    M, p = y.shape
+    code = HEAD[kind]
+    p_out = 4 if code == 2 else (2 if code in (4, 5) else (1 if code == 3 else p))
+    out = torch.empty((M, p_out), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_task_head(_ptr(y), M, p, code, _ptr(out), _stream(dev)),
+              "gn_task_head")
+    return out

@@ -1,0 +1,112 @@
+"""`StandardModel`: data representation + backbone + task heads.
+
+Mirrors /root/reference/src/graphnet/models/standard_model.py:18-159
+(constructor argument names incl. the deprecated `graph_definition` / `gnn`
+aliases, `forward(Data | List[Data]) -> List[Tensor]`, `compute_loss`,
+`shared_step`) and the `inference()` / `train(mode)` toggling of
+easy_model.py:276-289.  The Lightning trainer glue (`fit`, `predict`) is out of
+scope; `predict` here is a plain loop over an iterable of batches.
+"""
+
+from __future__ import annotations
+
+from typing import Any, Dict, Iterable, List, Optional, Type, Union
+
+import torch
+from torch import Tensor
+
+from .tasks import StandardLearnedTask
+
+
+class StandardModel(torch.nn.Module):
+    def __init__(
+        self,
+        tasks: Union[StandardLearnedTask, List[StandardLearnedTask]],
+        data_representation: Any = None,
+        graph_definition: Any = None,
+        backbone: Optional[torch.nn.Module] = None,
+        gnn: Optional[torch.nn.Module] = None,
+        optimizer_class: Type[torch.optim.Optimizer] = torch.optim.Adam,
+        optimizer_kwargs: Optional[Dict] = None,
+        scheduler_class: Optional[type] = None,
+        scheduler_kwargs: Optional[Dict] = None,
+        scheduler_config: Optional[Dict] = None,
+    ) -> None:
+        super().__init__()
+        if not isinstance(tasks, (list, tuple)):
+            tasks = [tasks]
+        if data_representation is None and graph_definition is not None:
+            data_representation = graph_definition
+        elif data_representation is None and graph_definition is None:
+            raise TypeError("__init__() missing 1 required keyword argument:'data_representation'")
+        if backbone is None and gnn is not None:
+            backbone = gnn
+        elif backbone is None and gnn is None:
+            raise TypeError("__init__() missing 1 required keyword argument:'backbone'")
+        assert isinstance(backbone, torch.nn.Module)
+        self._tasks = torch.nn.ModuleList(tasks)
+        self._data_representation = data_representation
+        self.backbone = backbone
+        self._optimizer_class = optimizer_class
+        self._optimizer_kwargs = optimizer_kwargs or dict()
+        self._scheduler_class = scheduler_class
+        self._scheduler_kwargs = scheduler_kwargs or dict()
+        self._scheduler_config = scheduler_config or dict()
+        for task in self._tasks:
+            assert isinstance(task, StandardLearnedTask)
+
+    @property
+    def target_labels(self) -> List[str]:
+        return [label for task in self._tasks for label in task._target_labels]
+
+    @property
+    def prediction_labels(self) -> List[str]:
+        return [label for task in self._tasks for label in task._prediction_labels]
+
+    def forward(self, data: Any) -> List[Tensor]:
+        """standard_model.py:119-132."""
+        if not isinstance(data, (list, tuple)):
+            data = [data]
+        x_list = [self.backbone(d) for d in data]
+        x = x_list[0] if len(x_list) == 1 else torch.cat(x_list, dim=0)
+        return [task(x) for task in self._tasks]
+
+    def compute_loss(self, preds: List[Tensor], data: Any, verbose: bool = False) -> Tensor:
+        """standard_model.py:94-117."""
+        if not isinstance(data, (list, tuple)):
+            data = [data]
+        data_merged: Dict[str, Tensor] = {}
+        for label in list(set(self.target_labels)):
+            data_merged[label] = torch.cat([d[label] for d in data], dim=0)
+        for task in self._tasks:
+            if task._loss_weight is not None:
+                data_merged[task._loss_weight] = torch.cat(
+                    [d[task._loss_weight] for d in data], dim=0)
+        losses = [task.compute_loss(pred, data_merged) for task, pred in zip(self._tasks, preds)]
+        assert all(loss.dim() == 0 for loss in losses), "Please reduce loss for each task separately"
+        return torch.sum(torch.stack(losses))
+
+    def shared_step(self, batch: Any, batch_idx: int = 0) -> Tensor:
+        preds = self(batch)
+        return self.compute_loss(preds, batch)
+
+    def inference(self) -> None:
+        """easy_model.py:276-279."""
+        for task in self._tasks:
+            task.inference()
+
+    def train(self, mode: bool = True) -> "StandardModel":
+        """easy_model.py:281-289."""
+        super().train(mode)
+        if mode:
+            for task in self._tasks:
+                task.train_eval()
+        return self
+
+    @torch.no_grad()
+    def predict(self, batches: Iterable[Any]) -> List[Tensor]:
+        """easy_model.py:291-321 without the Lightning trainer: cat per task."""
+        self.inference()
+        self.train(False)
+        per_batch = [self(b) for b in batches]
+        return [torch.cat([pb[i] for pb in per_batch], dim=0) for i in range(len(self._tasks))]

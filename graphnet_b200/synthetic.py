@@ -4,9 +4,10 @@ Nothing here reads the reference tree: the detector geometry is generated
 procedurally (a hexagonal string grid with the published IceCube-86 /
 IceCube-Upgrade dimensions), and pulses follow the recipe of SURVEY.md
 section 8(d), C2/C4: pulses per event ~ max(2, Poisson(mean)), sensors drawn
-WITH replacement around a random vertex with probability ~ exp(-r / 150 m)
-(so a sizeable fraction of pulses share a sensor and therefore share xyz
-exactly - the tie structure the kNN must reproduce), time = 1e4 + r/0.3 +
+WITH replacement around a random vertex with probability ~ exp(-r / 40 m)
+(the scale is set so that ~30 % of pulses share a sensor, the ratio measured on
+the reference's bundled oscNext events: 38 unique sensors / 56 pulses; they
+therefore share xyz exactly - the tie structure the kNN must reproduce), time = 1e4 + r/0.3 +
 Exp(300) ns, charge ~ LogNormal(0, 1), rde in {1.0, 1.35}, pmt_area 0.0444.
 Features are standardised with the reference's detector formulas
 (`graphnet_b200.detector`).
@@ -115,7 +116,7 @@ def make_pulse_batch(
     detector: str = "icecube86",
     seed: int = 1234,
     fixed_pulses: Optional[int] = None,
-    scale_m: float = 150.0,
+    scale_m: float = 40.0,
 ) -> PulseBatch:
     """Generate `num_events` standardised events (CPU tensors)."""
     rng = np.random.default_rng(seed)

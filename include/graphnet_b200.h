@@ -1,0 +1,185 @@
+/*
+ * graphnet_b200 - C ABI of the B200 (sm_100a) DynEdge hot path.
+ *
+ * The reference (graphnet-team/graphnet) has no FFI of its own: its DynEdge path
+ * is Python that calls third-party wheels (torch_cluster, torch_scatter,
+ * torch_geometric).  Each entry point below replaces one of those library calls
+ * at the reference call site cited beside it (paths relative to the reference's
+ * src/graphnet/).  Plain pointers and sizes only; all pointers are DEVICE
+ * pointers unless marked "host"; `stream` is a cudaStream_t passed as void*.
+ *
+ * Every function returns GN_OK (0) or a negative GN_ERR_* code and never
+ * aborts; gn_last_error() returns a message for the calling thread's last
+ * failure.  Functions only enqueue work on `stream` (no synchronisation) unless
+ * stated otherwise.  None of them allocates device memory: outputs and scratch
+ * are provided by the caller (sizes via the *_bytes helpers).
+ */
+#ifndef GRAPHNET_B200_H_
+#define GRAPHNET_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GN_OK 0
+#define GN_ERR_INVALID_ARGUMENT (-1)
+#define GN_ERR_CUDA (-2)
+#define GN_ERR_UNSUPPORTED (-3)
+
+/* activation of an MLP layer (models/gnn/dynedge.py:161-168) */
+#define GN_ACT_NONE 0
+#define GN_ACT_RELU 1
+#define GN_ACT_GELU 2
+
+/* aggregation of EdgeConv messages (components/layers.py:33; dynedge.py:208 uses ADD) */
+#define GN_AGGR_ADD 0
+#define GN_AGGR_MEAN 1
+#define GN_AGGR_MAX 2
+#define GN_AGGR_MIN 3
+
+/* global pooling schemes, GLOBAL_POOLINGS in models/gnn/dynedge.py:14-19 */
+#define GN_POOL_MIN 0
+#define GN_POOL_MAX 1
+#define GN_POOL_SUM 2
+#define GN_POOL_MEAN 3
+
+/* element types of activations handed between kernels */
+#define GN_F32 0
+#define GN_BF16 1
+
+/* task heads, models/task/reconstruction.py */
+#define GN_HEAD_IDENTITY 0
+#define GN_HEAD_ENERGY 1             /* EnergyReconstruction :101-112            */
+#define GN_HEAD_DIRECTION_KAPPA 2    /* DirectionReconstructionWithKappa :49-69  */
+#define GN_HEAD_ZENITH 3             /* ZenithReconstruction :72-82              */
+#define GN_HEAD_ZENITH_KAPPA 4       /* ZenithReconstructionWithKappa :85-98     */
+#define GN_HEAD_AZIMUTH_KAPPA 5      /* AzimuthReconstructionWithKappa :11-27    */
+
+/* flag bits written by the graph-conversion kernels */
+#define GN_FLAG_UNSORTED_BATCH 1
+#define GN_FLAG_UNSORTED_TARGETS 2
+#define GN_FLAG_INDEX_OUT_OF_RANGE 4
+
+/*
+ * In-edges grouped by target node.  Two layouts:
+ *   ELL (ell_stride > 0): sources of node i are col[i*ell_stride .. + deg[i])
+ *   CSR (ell_stride == 0): sources of node i are col[rowptr[i] .. rowptr[i+1])
+ * Within a node, sources keep the order of the reference's edge_index
+ * (ascending (distance^2, index) for kNN graphs).
+ */
+typedef struct gn_graph {
+  const int32_t* col;
+  const int32_t* deg;    /* ELL: [N]   */
+  const int32_t* rowptr; /* CSR: [N+1] */
+  int32_t ell_stride;
+} gn_graph;
+
+const char* gn_last_error(void);
+int gn_version(void);
+/* Kernel launches issued by this library in this process so far (diagnostic). */
+uint64_t gn_launch_count(void);
+
+/* ---- graph construction ------------------------------------------------- */
+
+/* Event offsets from the sorted PyG `batch` vector (what torch_cluster derives
+ * internally for knn(x, x, k, batch, batch)).  ptr[e] = first node
+ * of event e, ptr[B] = N.  Sets GN_FLAG_UNSORTED_BATCH / _OUT_OF_RANGE in *flags. */
+int gn_batch_to_ptr(const int64_t* batch, int64_t N, int64_t B, int32_t* ptr,
+                    int32_t* flags, void* stream);
+
+/* torch_geometric.nn.knn_graph(x[:, cols], k, batch, loop) - replaces the call at
+ * data_representation/graphs/edges/edges.py:78-82 and components/layers.py:70-74.
+ * Per event, per query i: candidates ordered by (squared L2 distance in fp32
+ * accumulated dimension by dimension without FMA, index); the first
+ * min(n, k + (loop?0:1)) are kept, (i,i) is dropped unless loop.  Output is ELL:
+ * nbr[i*stride + r] = r-th kept neighbour (global node id), padded with -1;
+ * deg[i] in [0, k+1].  stride >= k+1.  `cols` is a HOST array of `dims` column
+ * indices into the [N, ldx] matrix (dims <= 16). */
+int gn_knn_graph(const float* x, int64_t ldx, const int32_t* cols, int dims,
+                 const int32_t* ptr, int64_t N, int64_t B, int k, int loop,
+                 int32_t* nbr, int32_t stride, int32_t* deg, void* stream);
+
+/* Exclusive scan of the ELL degrees: rowptr[i] = sum(deg[0..i)), rowptr[N] = E.
+ * `scratch` holds the per-block partial sums (gn_scan_scratch_bytes(N) bytes). */
+size_t gn_scan_scratch_bytes(int64_t n);
+int gn_ell_row_offsets(const int32_t* deg, int64_t N, int64_t* rowptr,
+                       void* scratch, size_t scratch_bytes, void* stream);
+
+/* The int64 COO `edge_index` [2, E] the reference API returns (row 0 = source j,
+ * row 1 = target i; ordered by target, then rank) from ELL + its row offsets. */
+int gn_ell_to_coo(const int32_t* nbr, int32_t stride, const int32_t* deg,
+                  const int64_t* rowptr, int64_t N, int64_t E, int64_t* edge_index,
+                  void* stream);
+
+/* A caller-provided PyG `edge_index` [2, E] (int64, targets non-decreasing, as
+ * knn_graph / Batch.from_data_list produce) -> CSR by target.  Sets
+ * GN_FLAG_UNSORTED_TARGETS / GN_FLAG_INDEX_OUT_OF_RANGE in *flags and the
+ * largest in-degree in *max_degree (both device ints, may be read later). */
+int gn_coo_to_csr(const int64_t* edge_index, int64_t E, int64_t N, int32_t* rowptr,
+                  int32_t* col, int32_t* flags, int32_t* max_degree, void* stream);
+
+/* ---- per-event summary features ----------------------------------------- */
+
+/* DynEdge._calculate_global_variables (models/gnn/dynedge.py:267-294) with
+ * calculate_xyzt_homophily (models/utils.py:17-33) and log10(n_pulses) (:303-308):
+ * gv[e] = [mean of each of the F input columns, homophily of columns 0..3 over the
+ * in-edges of the event's nodes (exact float equality, 0 without edges),
+ * log10(n_pulses[e])]  -> [B, F+5].
+ * If x0 != NULL it also performs the "distribute" step and concatenation of
+ * dynedge.py:309-320: x0[i] = [x[i, 0:F], gv[batch[i]]] (row stride ldx0, element
+ * type x0_dtype; columns F+F+5 .. x0_cols are zero-filled). */
+int gn_global_variables(const float* x, int64_t ldx, int F, const gn_graph* graph,
+                        const int32_t* ptr, const int32_t* n_pulses, int64_t N,
+                        int64_t B, float* gv, void* x0, int64_t ldx0, int x0_cols,
+                        int x0_dtype, void* stream);
+
+/* DynEdge._global_pooling (dynedge.py:252-265): torch_scatter.scatter_{min,max,
+ * sum,mean}(x, batch, dim=0) for each scheme in `schemes` (HOST array), results
+ * concatenated along features: out[e, s*C + c].  Empty events give 0. */
+int gn_segment_pool(const void* x, int x_dtype, int64_t ldx, int C, const int32_t* ptr,
+                    int64_t B, const int32_t* schemes, int n_schemes, float* out,
+                    int64_t ldo, void* stream);
+
+/* ---- dense layers, fp32 -------------------------------------------------- */
+
+/* torch.nn.Linear (+ activation): C = act(A W^T + bias).  A [M,K] (row stride
+ * lda), W [N,K] row-major (torch layout), C [M,N] (row stride ldc).  Used for the
+ * post-processing MLP (dynedge.py:222-232, 332), the readout (:244-250, 348) and
+ * the task affine (task/task.py:293). */
+int gn_linear_f32(const float* A, int64_t lda, const float* W, const float* bias,
+                  float* C, int64_t ldc, int64_t M, int N, int K, int act,
+                  void* stream);
+
+/* Repack the two Linear layers of one DynEdgeConv MLP for gn_edgeconv_f32:
+ *   W1 [a, 2d] acting on [x_i, x_j - x_i]  ->  Wpq [2a, d] = [W1a - W1b ; W1b]
+ *   W2 [b, a]                               ->  W2T [a, b]
+ * (W1 [x_i, x_j - x_i] = (W1a - W1b) x_i + W1b x_j).  W2/W2T may be NULL for a
+ * one-layer MLP. */
+int gn_edgeconv_prepare_f32(const float* W1, const float* W2, int d, int a, int b,
+                            float* Wpq, float* W2T, void* stream);
+
+/* torch_geometric EdgeConv forward as called at components/layers.py:67 with the
+ * MLP built at dynedge.py:193-204 (Linear-act[-Linear-act]):
+ *   out[i] = aggr_{j in N(i)} act(W2 act(W1 [x_i, x_j - x_i] + b1) + b2)
+ * fp32 FFMA path.  `pq` is caller scratch [N, 2a] floats.  Nodes without
+ * in-edges give 0.  W2T == NULL: one-layer MLP (then b == a). */
+int gn_edgeconv_f32(const float* x, int64_t ldx, int d, const gn_graph* graph,
+                    int64_t N, const float* Wpq, const float* b1, int a,
+                    const float* W2T, const float* b2, int b, int act, int aggr,
+                    float* pq, float* out, int64_t ldo, void* stream);
+
+/* ---- task heads ----------------------------------------------------------- */
+
+/* The `_forward` of a reconstruction head (models/task/reconstruction.py) applied
+ * to the affine output y [M, p]; out is [M, p_out] (p_out = 4 for
+ * DIRECTION_KAPPA, 2 for *_KAPPA angles, else p). */
+int gn_task_head(const float* y, int64_t M, int p, int kind, float* out,
+                 void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRAPHNET_B200_H_ */

@@ -1,0 +1,67 @@
+"""Shared fixtures.  `-m gpu` tests need a B200; everything else runs on CPU."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+GOLDEN_CASES = ["oscnext5", "upgrade5", "prometheus50", "adversarial", "adversarial_k16_after"]
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def pytest_collection_modifyitems(config, items):
+    if torch.cuda.is_available():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
+def load_golden(name):
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"), allow_pickle=False)
+    out = {}
+    for k in z.files:
+        v = z[k]
+        if v.dtype.kind in "US":
+            out[k] = str(v)
+        else:
+            out[k] = torch.from_numpy(v) if v.ndim > 0 else v.item()
+    out["dyn_kwargs"] = eval(out["dyn_kwargs"], {"__builtins__": {}}, {})  # repr of a plain dict
+    return out
+
+
+@pytest.fixture(params=GOLDEN_CASES)
+def golden(request):
+    return load_golden(request.param)
+
+
+def random_events(num_events, lo, hi, F=7, seed=0, ties=True):
+    """Random events with duplicated xyz rows (same-sensor pulses)."""
+    g = torch.Generator().manual_seed(seed)
+    counts = torch.randint(lo, hi + 1, (num_events,), generator=g)
+    N = int(counts.sum())
+    x = torch.randn(N, F, generator=g)
+    if ties and N > 4:
+        # every ~4th pulse copies the xyz of an earlier pulse of the same event
+        batch = torch.repeat_interleave(torch.arange(num_events), counts)
+        ptr = torch.zeros(num_events + 1, dtype=torch.long)
+        ptr[1:] = counts.cumsum(0)
+        src = torch.randint(0, 1 << 30, (N,), generator=g)
+        for i in range(N):
+            if i % 4 == 3:
+                e = int(batch[i])
+                j = int(ptr[e]) + int(src[i]) % max(1, i - int(ptr[e]))
+                if j < i:
+                    x[i, :3] = x[j, :3]
+    batch = torch.repeat_interleave(torch.arange(num_events), counts)
+    return x.contiguous(), batch, counts.to(torch.int32)

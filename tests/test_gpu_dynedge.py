@@ -1,0 +1,137 @@
+"""GPU: the whole DynEdge forward (fp32 path) against the golden vectors / oracle."""
+import pytest
+import torch
+
+import oracle
+from conftest import load_golden, GOLDEN_CASES
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+FP32_TOL = 1e-4  # BASELINE.json north_star: forward outputs within 1e-4 relative in fp32
+
+
+def rel_l2(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm().clamp(min=1e-30))
+
+
+def _model(g, precision="fp32"):
+    import graphnet_b200 as gb
+    spec = oracle.DynEdgeSpec(nb_inputs=g["x"].shape[1], **g["dyn_kwargs"])
+    sd = oracle.init_dynedge_state_dict(spec, seed=int(g["seed"]))
+    m = gb.DynEdge(g["x"].shape[1], precision=precision, **g["dyn_kwargs"])
+    m.load_state_dict(sd)
+    return m.to(DEV), spec, sd
+
+
+def _data(g):
+    import graphnet_b200 as gb
+    return gb.Data(x=g["x"].to(DEV), edge_index=g["edge_index"].to(DEV), batch=g["batch"].to(DEV),
+                   n_pulses=g["n_pulses"].to(DEV))
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_forward_fp32_matches_golden(name):
+    import graphnet_b200.ops as ops
+    g = load_golden(name)
+    m, spec, sd = _model(g)
+    out, inter = m._forward_f32(_data(g), return_intermediates=True)
+    F = g["x"].shape[1]
+    D0 = spec.nb_conv_inputs
+    skip = inter["skip"].cpu()
+    off = D0
+    for i, sizes in enumerate(spec.dynedge_layer_sizes):
+        b = sizes[-1]
+        conv = skip[:, off:off + b]
+        assert rel_l2(conv, g[f"conv{i}"]) < FP32_TOL, f"conv{i}"
+        # dynamic graph of this layer: identical unless a near-tie flipped; report exactness
+        ei = ops.ell_to_coo(inter["graphs"][i]).cpu()
+        want = g[f"graph{i + 1}"]
+        assert ei.shape == want.shape
+        mismatch = int((ei != want).any(0).sum())
+        assert mismatch <= max(2, ei.shape[1] // 1000), f"graph{i + 1}: {mismatch} edges differ"
+        off += b
+    assert rel_l2(inter["post"].cpu(), g["post"]) < FP32_TOL
+    if "pooled" in g:
+        assert rel_l2(inter["pooled"].cpu(), g["pooled"]) < FP32_TOL
+    assert out.shape == g["out"].shape
+    assert rel_l2(out.cpu(), g["out"]) < FP32_TOL
+    # public call gives the same tensor
+    assert torch.equal(m(_data(g)), out)
+
+
+def test_forward_accepts_unsorted_edges_and_rejects_bad_batch():
+    import graphnet_b200 as gb
+    g = load_golden("oscnext5")
+    m, _, _ = _model(g)
+    d = _data(g)
+    ref = m(d)
+    perm = torch.randperm(d.edge_index.shape[1], generator=torch.Generator().manual_seed(0)).to(DEV)
+    d2 = gb.Data(x=d.x, edge_index=d.edge_index[:, perm], batch=d.batch, n_pulses=d.n_pulses)
+    got = m(d2)
+    assert rel_l2(got.cpu(), ref.cpu()) < 1e-5
+    d3 = gb.Data(x=d.x, edge_index=d.edge_index, batch=d.batch.flip(0), n_pulses=d.n_pulses)
+    with pytest.raises(ValueError):
+        m(d3)
+
+
+def test_standard_model_two_tasks_c5_shape():
+    """Direction + energy heads on one backbone (BASELINE config 5 shape)."""
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    from oracle import tasks as otasks
+    pb = make_pulse_batch(24, 30.0, seed=3)
+    ei = oracle.knn_graph(pb.x[:, :3], 8, pb.batch)
+    pools = ["min", "max", "mean"]
+    torch.manual_seed(5)
+    backbone = gb.DynEdge(7, global_pooling_schemes=pools)
+    tasks = [gb.DirectionReconstructionWithKappa(hidden_size=128, loss_function=gb.VonMisesFisher3DLoss()),
+             gb.EnergyReconstruction(hidden_size=128, loss_function=gb.LogCoshLoss(),
+                                     transform_prediction_and_target=lambda x: torch.log10(x))]
+    model = gb.StandardModel(tasks=tasks, graph_definition=object(), gnn=backbone).to(DEV)
+    data = gb.Data(x=pb.x.to(DEV), edge_index=ei.to(DEV), batch=pb.batch.to(DEV),
+                   n_pulses=pb.n_pulses.to(DEV))
+    preds = model(data)
+    spec = oracle.DynEdgeSpec(nb_inputs=7, global_pooling_schemes=pools)
+    sd = {k: v.cpu() for k, v in backbone.state_dict().items()}
+    y = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
+    w0 = otasks.task_forward("DirectionReconstructionWithKappa", tasks[0]._affine.weight.cpu(),
+                             tasks[0]._affine.bias.cpu(), y)
+    w1 = otasks.task_forward("EnergyReconstruction", tasks[1]._affine.weight.cpu(),
+                             tasks[1]._affine.bias.cpu(), y, transform=torch.log10)
+    assert preds[0].shape == (24, 4) and preds[1].shape == (24, 1)
+    assert rel_l2(preds[0].cpu(), w0) < 1e-3 and rel_l2(preds[1].cpu(), w1) < 1e-3
+    # losses on device agree with the oracle's
+    data.direction = torch.nn.functional.normalize(torch.randn(24, 3), dim=1).to(DEV)
+    data.energy = (torch.rand(24) * 100 + 1).to(DEV)
+    tasks[0]._target_labels = ["direction"]
+    loss_dir = tasks[0]._loss_function(preds[0], data.direction)
+    assert torch.allclose(loss_dir.cpu(), otasks.vmf3d_loss(w0, data.direction.cpu()), rtol=1e-3)
+
+
+def test_knngraph_collate_then_forward():
+    """Device-side graph building after collation feeding the model."""
+    import numpy as np
+    import graphnet_b200 as gb
+    from graphnet_b200.detector import FEATURES_ICECUBE86
+    rng = np.random.default_rng(0)
+    events = []
+    for n in (12, 1, 40, 7):
+        e = rng.normal(size=(n, 7))
+        e[:, :3] *= 300
+        e[:, 3] = 1e4 + rng.exponential(500, n)
+        e[:, 4] = rng.lognormal(0, 1, n)
+        events.append(e)
+    kg = gb.KNNGraph(detector=gb.IceCube86(), nb_nearest_neighbours=8)
+    b = kg.collate(events, FEATURES_ICECUBE86)
+    assert b.n_pulses.tolist() == [12, 40, 7]  # the 1-pulse event is dropped
+    want = oracle.knn_graph(b.x.cpu()[:, :3], 8, b.batch.cpu())
+    assert torch.equal(b.edge_index.cpu(), want)
+    m = gb.DynEdge(7, global_pooling_schemes=["max"]).to(DEV)
+    out = m(b)
+    spec = oracle.DynEdgeSpec(nb_inputs=7, global_pooling_schemes=["max"])
+    y = oracle.dynedge_forward(spec, {k: v.cpu() for k, v in m.state_dict().items()}, b.x.cpu(),
+                               want, b.batch.cpu(), b.n_pulses.cpu())
+    assert rel_l2(out.cpu(), y) < FP32_TOL
+    # single-event call path of the reference (graph_definition.py:127-137)
+    one = kg(events[2], FEATURES_ICECUBE86)
+    assert torch.equal(one.edge_index.cpu(), oracle.knn_graph(one.x.cpu()[:, :3], 8, None))
