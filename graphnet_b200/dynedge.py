@@ -36,7 +36,7 @@ def _act_name(module: torch.nn.Module) -> str:
 
 def _parse_mlp(seq: torch.nn.Module) -> Tuple[List[torch.nn.Linear], str]:
     """Split Sequential(Linear, act[, Linear, act ...]) into its Linears + activation."""
-    mods = list(seq.children()) if isinstance(seq, torch.nn.Sequential) else [seq]
+    mods = list(seq) if isinstance(seq, torch.nn.Sequential) else [seq]  # keeps shared modules
     linears: List[torch.nn.Linear] = []
     act = None
     i = 0

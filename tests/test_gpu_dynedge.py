@@ -14,6 +14,26 @@ def rel_l2(a, b):
     return float((a.double() - b.double()).norm() / b.double().norm().clamp(min=1e-30))
 
 
+def assert_same_graph_up_to_near_ties(ei, want, coords, what, rel=1e-4, max_frac=0.02):
+    """The dynamic graphs are built from latents that carry fp32 rounding noise (a different
+    summation order than the CPU reference), so neighbours at (nearly) equal distance may swap.
+    Same targets and degrees are required; where a source differs, its distance to the target -
+    measured in the REFERENCE latents - must equal the reference neighbour's within `rel`."""
+    assert ei.shape == want.shape, what
+    assert torch.equal(ei[1], want[1]), what
+    diff = (ei[0] != want[0]).nonzero().flatten()
+    if diff.numel() == 0:
+        return
+    assert diff.numel() <= max(2, int(max_frac * ei.shape[1])), f"{what}: {diff.numel()} edges differ"
+    c = coords.double()
+    tgt = want[1][diff]
+    d_mine = ((c[ei[0][diff]] - c[tgt]) ** 2).sum(1)
+    d_want = ((c[want[0][diff]] - c[tgt]) ** 2).sum(1)
+    scale = (c ** 2).sum(1).max()
+    assert bool(((d_mine - d_want).abs() <= rel * (d_want + 1e-6 * scale)).all()), \
+        f"{what}: a differing neighbour is not a near-tie"
+
+
 def _model(g, precision="fp32"):
     import graphnet_b200 as gb
     spec = oracle.DynEdgeSpec(nb_inputs=g["x"].shape[1], **g["dyn_kwargs"])
@@ -94,10 +114,11 @@ def test_standard_model_two_tasks_c5_shape():
     spec = oracle.DynEdgeSpec(nb_inputs=7, global_pooling_schemes=pools)
     sd = {k: v.cpu() for k, v in backbone.state_dict().items()}
     y = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
-    w0 = otasks.task_forward("DirectionReconstructionWithKappa", tasks[0]._affine.weight.cpu(),
-                             tasks[0]._affine.bias.cpu(), y)
-    w1 = otasks.task_forward("EnergyReconstruction", tasks[1]._affine.weight.cpu(),
-                             tasks[1]._affine.bias.cpu(), y, transform=torch.log10)
+    w0 = otasks.task_forward("DirectionReconstructionWithKappa",
+                             tasks[0]._affine.weight.detach().cpu(),
+                             tasks[0]._affine.bias.detach().cpu(), y)
+    w1 = otasks.task_forward("EnergyReconstruction", tasks[1]._affine.weight.detach().cpu(),
+                             tasks[1]._affine.bias.detach().cpu(), y, transform=torch.log10)
     assert preds[0].shape == (24, 4) and preds[1].shape == (24, 1)
     assert rel_l2(preds[0].cpu(), w0) < 1e-3 and rel_l2(preds[1].cpu(), w1) < 1e-3
     # losses on device agree with the oracle's
