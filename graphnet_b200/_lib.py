@@ -59,6 +59,10 @@ SIGNATURES = {
     "gn_linear_f32": (_int, [_p, _i64, _p, _p, _p, _i64, _i64, _int, _int, _int, _p]),
     "gn_edgeconv_prepare_f32": (_int, [_p, _p, _int, _int, _int, _p, _p, _p]),
     "gn_edgeconv_f32": (_int, [_p, _i64, _int, _gp, _i64, _p, _p, _int, _p, _p, _int, _int, _int, _p, _p, _i64, _p]),
+    "gn_tc_linear_bf16": (_int, [_p, _i64, _p, _i64, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),
+    "gn_tc_edge_scratch_bytes": (_sz, [_i64, _int]),
+    "gn_tc_edge_mlp_aggregate": (_int, [_p, _i64, _int, _gp, _i64, _int, _p, _p, _int, _p, _i64,
+                                        _p, _hp, _int, _p, _sz, _p]),
     "gn_task_head": (_int, [_p, _i64, _int, _int, _p, _p]),
 }
 

@@ -1,0 +1,471 @@
+// Fused EdgeConv message + aggregation on tcgen05 / TMEM (bf16 inputs, fp32 accumulate).
+//
+//   out[i] = sum_{j in N(i)} ReLU( W2 ReLU(P_i + Q_j) + b2 )
+//
+// with P = x (W1a-W1b)^T + b1 and Q = x W1b^T produced by the node GEMM (tc_linear.cu), so
+// that W1 [x_i, x_j - x_i] + b1 = P_i + Q_j.  Replaces torch_geometric EdgeConv.propagate +
+// torch_scatter sum as reached from components/layers.py:67 (MLP of dynedge.py:193-204,
+// aggr="add" dynedge.py:208).  The [E, a] hidden tensor and the [E, b] messages never
+// reach HBM: they live in shared memory / TMEM for the lifetime of one 128-edge tile.
+//
+// Persistent kernel, one CTA per SM, 17 warps:
+//   warp 0       tcgen05.mma issuer; owns TMEM (2 x 256 fp32 columns: double-buffered D) and
+//                loads the whole W2 (bf16, K padded, 64B-swizzled) into shared memory once by TMA
+//   warps 1-8    producers: gather P_i / Q_j rows (16-byte chunks, L2 resident), h = ReLU(P+Q)
+//                in packed bf16, written into the 64B-swizzled K-major A stage ring
+//   warps 9-16   epilogue: TMEM -> registers, ReLU, reduce-scatter over the KP edge rows of a
+//                node with warp shuffles, store bf16 row slice (+ fp32 kNN coordinates)
+// Tile rows are ELL slots: row r of tile t is (node t*128/KP + r/KP, slot r%KP); empty slots are
+// all-zero A rows.  b2 is folded into the GEMM: P carries 1.0 in the two pad columns a, a+1 and
+// W2's columns a, a+1 hold b2 split into bf16 hi + lo parts, so an empty slot contributes
+// exactly 0 and the epilogue needs no bias add.  In-edges beyond KP per node are added by
+// edge_overflow_kernel (rare: a node keeps k+1 edges only when >= k+1 coincident pulses precede it).
+#include "tc_common.cuh"
+
+namespace gn {
+namespace tc {
+
+constexpr int EK_ROWS = 128;
+constexpr int EK_KCH = 32;                       // K elements per stage (64-byte rows)
+constexpr int EK_STAGE_BYTES = EK_ROWS * 64;     // 8 KB
+constexpr int EK_STAGES = 5;
+constexpr int EK_MAX_CHUNKS = 11;                // hidden width (padded) <= 352
+constexpr int EK_PROD_WARPS = 8;
+constexpr int EK_EPI_WARPS = 8;
+constexpr int EK_THREADS = 32 * (1 + EK_PROD_WARPS + EK_EPI_WARPS);  // 544
+
+struct __align__(8) EdgeBarriers {
+  uint64_t full[EK_STAGES];
+  uint64_t empty[EK_STAGES];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint64_t w2_full;
+  uint32_t tmem_base;
+};
+
+struct EdgeParams {
+  const __nv_bfloat16* pq;  // [N, ldpq]: P in columns [0, Kp), Q in [Kp, 2Kp)
+  int64_t ldpq;
+  int Kp;                   // padded hidden width, multiple of 32
+  int nch;                  // Kp / 32
+  const int32_t* ell;       // [N, ell_stride] neighbour ids, -1 = empty slot
+  int ell_stride;
+  int64_t N;
+  int bnp;                  // output width padded to a multiple of 16 (UMMA N)
+  int b;                    // valid output columns
+  __nv_bfloat16* out;       // [N, ldo]
+  int64_t ldo;
+  float* coords;            // [N, ncoord] fp32 copy of the columns selected by coord_mask, or null
+  int ncoord;
+  uint32_t coord_mask[8];
+  int64_t num_tiles;
+};
+
+__device__ __forceinline__ uint4 ldg16(const __nv_bfloat16* p) {
+  return __ldg(reinterpret_cast<const uint4*>(p));
+}
+
+__device__ __forceinline__ uint32_t relu_add_bf16x2(uint32_t a, uint32_t b) {
+  __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&a);
+  __nv_bfloat162 y = *reinterpret_cast<__nv_bfloat162*>(&b);
+  __nv_bfloat162 s = __hmax2(__hadd2(x, y), __float2bfloat162_rn(0.f));
+  return *reinterpret_cast<uint32_t*>(&s);
+}
+
+template <int KP>
+__global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
+    const __grid_constant__ CUtensorMap tmW2, const EdgeParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  const int w2_chunk_bytes = p.bnp * 64;
+  uint8_t* w2_smem = smem;
+  uint8_t* a_smem = smem + (size_t)p.nch * w2_chunk_bytes;
+  EdgeBarriers* bars = reinterpret_cast<EdgeBarriers*>(a_smem + EK_STAGES * EK_STAGE_BYTES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int NPT = EK_ROWS / KP;  // nodes per tile
+  const int nch = p.nch;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmW2);
+#pragma unroll
+    for (int s = 0; s < EK_STAGES; ++s) {
+      mbar_init(&bars->full[s], EK_PROD_WARPS);
+      mbar_init(&bars->empty[s], 1);
+    }
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&bars->tmem_full[b], 1);
+      mbar_init(&bars->tmem_empty[b], EK_EPI_WARPS);
+    }
+    mbar_init(&bars->w2_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc<512>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ================================================================ MMA issuer
+    if (elect_one()) {
+      mbar_arrive_expect_tx(&bars->w2_full, (uint32_t)(nch * w2_chunk_bytes));
+      for (int kc = 0; kc < nch; ++kc)
+        tma_load_2d(w2_smem + (size_t)kc * w2_chunk_bytes, &tmW2, &bars->w2_full, kc * EK_KCH, 0);
+    }
+    __syncwarp();
+    mbar_wait(&bars->w2_full, 0);
+    const uint32_t idesc = make_idesc_bf16(EK_ROWS, p.bnp);
+    const uint32_t w2_addr = smem_u32(w2_smem);
+    const uint32_t a_addr = smem_u32(a_smem);
+    uint32_t g = 0;  // running stage counter
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const uint32_t buf = it & 1;
+      mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + buf * 256;
+      for (int kc = 0; kc < nch; ++kc, ++g) {
+        const uint32_t s = g % EK_STAGES;
+        mbar_wait(&bars->full[s], (g / EK_STAGES) & 1);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint64_t adesc = make_kmajor_desc<64>(a_addr + s * EK_STAGE_BYTES);
+          const uint64_t bdesc = make_kmajor_desc<64>(w2_addr + kc * w2_chunk_bytes);
+#pragma unroll
+          for (int k2 = 0; k2 < EK_KCH / 16; ++k2)
+            mma_bf16_ss(tmem_d, adesc + (uint64_t)(k2 * 2), bdesc + (uint64_t)(k2 * 2), idesc,
+                        (kc | k2) != 0);
+          mma_commit(&bars->empty[s]);
+          if (kc == nch - 1) mma_commit(&bars->tmem_full[buf]);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp <= EK_PROD_WARPS) {
+    // ================================================================= producers
+    const int pt = threadIdx.x - 32;       // 0..255
+    const int c = pt & 3;                  // 16-byte chunk inside the 64-byte stage row
+    const int r0 = pt >> 2;                // rows r0 and r0 + 64
+    const uint32_t a_addr = smem_u32(a_smem);
+    uint32_t soff[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int r = r0 + 64 * h;
+      soff[h] = (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4));
+    }
+    // neighbour ids of the first tile
+    int32_t nbr_next[2];
+    {
+      const int64_t tile = blockIdx.x;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int r = r0 + 64 * h;
+        const int64_t node = tile * NPT + r / KP;
+        nbr_next[h] = (tile < p.num_tiles && node < p.N)
+                          ? __ldg(p.ell + node * p.ell_stride + (r % KP)) : -1;
+      }
+    }
+    uint32_t g = 0;
+    for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      const __nv_bfloat16* pp[2];
+      const __nv_bfloat16* qp[2];
+      bool valid[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int r = r0 + 64 * h;
+        const int64_t node = tile * NPT + r / KP;
+        const int32_t j = nbr_next[h];
+        valid[h] = j >= 0;
+        pp[h] = p.pq + (valid[h] ? node : 0) * p.ldpq + c * 8;
+        qp[h] = p.pq + (int64_t)(valid[h] ? j : 0) * p.ldpq + p.Kp + c * 8;
+      }
+      // prefetch the neighbour ids of this CTA's next tile
+      {
+        const int64_t nt = tile + gridDim.x;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int r = r0 + 64 * h;
+          const int64_t node = nt * NPT + r / KP;
+          nbr_next[h] = (nt < p.num_tiles && node < p.N)
+                            ? __ldg(p.ell + node * p.ell_stride + (r % KP)) : -1;
+        }
+      }
+      // two-deep register pipeline over the K chunks of this tile
+      uint4 pa[2], qa[2], pb[2], qb[2];
+      const uint4 zero4 = make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        pa[h] = valid[h] ? ldg16(pp[h]) : zero4;
+        qa[h] = valid[h] ? ldg16(qp[h]) : zero4;
+        pb[h] = (valid[h] && nch > 1) ? ldg16(pp[h] + EK_KCH) : zero4;
+        qb[h] = (valid[h] && nch > 1) ? ldg16(qp[h] + EK_KCH) : zero4;
+      }
+      for (int kc = 0; kc < nch; kc += 2) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int k = kc + half;
+          if (k >= nch) break;
+          const uint32_t s = g % EK_STAGES;
+          mbar_wait(&bars->empty[s], ((g / EK_STAGES) & 1) ^ 1);
+          const uint32_t base = a_addr + s * EK_STAGE_BYTES;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint4 P = half == 0 ? pa[h] : pb[h];
+            const uint4 Q = half == 0 ? qa[h] : qb[h];
+            uint4 H;
+            H.x = relu_add_bf16x2(P.x, Q.x);
+            H.y = relu_add_bf16x2(P.y, Q.y);
+            H.z = relu_add_bf16x2(P.z, Q.z);
+            H.w = relu_add_bf16x2(P.w, Q.w);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(base + soff[h]),
+                         "r"(H.x), "r"(H.y), "r"(H.z), "r"(H.w)
+                         : "memory");
+          }
+          // refill this register slot with chunk k + 2
+          const int kn = k + 2;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const bool ld = valid[h] && kn < nch;
+            const uint4 np = ld ? ldg16(pp[h] + kn * EK_KCH) : zero4;
+            const uint4 nq = ld ? ldg16(qp[h] + kn * EK_KCH) : zero4;
+            if (half == 0) { pa[h] = np; qa[h] = nq; } else { pb[h] = np; qb[h] = nq; }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars->full[s]);
+          ++g;
+        }
+      }
+    }
+  } else {
+    // ================================================================== epilogue
+    const int e = warp - (1 + EK_PROD_WARPS);  // 0..7
+    const int q = warp & 3;                    // TMEM lane quadrant of this warp
+    const int chalf = e >> 2;                  // which 128-column half
+    constexpr int CPL = 32 / KP;               // columns per lane after the reduce-scatter
+    const int coloff = (lane & (KP - 1)) * CPL;
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const uint32_t buf = it & 1;
+      mbar_wait(&bars->tmem_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const int64_t node = tile * NPT + (q * 32 + lane) / KP;
+#pragma unroll 1
+      for (int cc = 0; cc < 4; ++cc) {
+        const int c0 = chalf * 128 + cc * 32;
+        if (c0 >= p.bnp) break;
+        float v[32];
+        tmem_ld_32x32(tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+        // reduce-scatter over the KP lanes (edge rows) of each node
+        int n = 32;
+#pragma unroll
+        for (int mask = KP / 2; mask >= 1; mask >>= 1) {
+          n >>= 1;
+          const bool up = (lane & mask) != 0;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            if (i < n) {
+              const float send = up ? v[i] : v[i + n];
+              const float keep = up ? v[i + n] : v[i];
+              v[i] = keep + __shfl_xor_sync(0xffffffffu, send, mask);
+            }
+          }
+        }
+        if (node < p.N) {
+          const int col = c0 + coloff;
+          __nv_bfloat16* dst = p.out + node * p.ldo + col;
+          if (CPL == 4 && col + 4 <= p.b) {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]);
+            __nv_bfloat162 hi = __floats2bfloat162_rn(v[2], v[3]);
+            uint2 u;
+            u.x = *reinterpret_cast<uint32_t*>(&lo);
+            u.y = *reinterpret_cast<uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(dst) = u;
+          } else {
+#pragma unroll
+            for (int i = 0; i < CPL; ++i)
+              if (col + i < p.b) dst[i] = __float2bfloat16_rn(v[i]);
+          }
+          if (p.coords != nullptr) {
+#pragma unroll
+            for (int i = 0; i < CPL; ++i) {
+              const int cidx = col + i;
+              const uint32_t word = p.coord_mask[cidx >> 5];
+              if (cidx < p.b && ((word >> (cidx & 31)) & 1u)) {
+                int rank = __popc(word & ((1u << (cidx & 31)) - 1u));
+                for (int w = 0; w < (cidx >> 5); ++w) rank += __popc(p.coord_mask[w]);
+                p.coords[node * p.ncoord + rank] = v[i];
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<512>(tmem_base);
+}
+
+struct CoordMask {
+  uint32_t w[8];
+};
+
+// In-edges beyond the KP slots of the main kernel: one CTA walks 8 nodes; for a node with
+// deg > KP every extra edge adds ReLU(W2 ReLU(P_i + Q_j) + b2) (same bf16 operands, fp32
+// accumulate) to the stored row.  W2T is [Kp, ldw] bf16 (k-major, the bias rows included).
+__global__ void __launch_bounds__(256) edge_overflow_kernel(
+    const __nv_bfloat16* __restrict__ pq, int64_t ldpq, int Kp, GraphView g, int KP, int64_t N,
+    const __nv_bfloat16* __restrict__ W2T, int ldw, int b, __nv_bfloat16* __restrict__ out,
+    int64_t ldo, float* __restrict__ coords, int ncoord, const CoordMask cm) {
+  __shared__ float h[EK_MAX_CHUNKS * EK_KCH];
+  __shared__ uint32_t cmask[8];
+  if (threadIdx.x < 8) cmask[threadIdx.x] = cm.w[threadIdx.x];
+  for (int64_t i = (int64_t)blockIdx.x * 8; i < (int64_t)blockIdx.x * 8 + 8 && i < N; ++i) {
+    int64_t start;
+    int cnt;
+    graph_row(g, i, start, cnt);
+    for (int s = KP; s < cnt; ++s) {
+      const int64_t j = g.col[start + s];
+      __syncthreads();
+      for (int k = threadIdx.x; k < Kp; k += 256) {
+        const __nv_bfloat16 hv = __hmax(__hadd(pq[i * ldpq + k], pq[j * ldpq + Kp + k]),
+                                        __float2bfloat16_rn(0.f));
+        h[k] = __bfloat162float(hv);
+      }
+      __syncthreads();
+      const int n = threadIdx.x;
+      if (n < b) {
+        float acc = 0.f;
+        for (int k = 0; k < Kp; ++k) acc = fmaf(h[k], __bfloat162float(W2T[(int64_t)k * ldw + n]), acc);
+        acc = fmaxf(acc, 0.f);
+        const float cur = __bfloat162float(out[i * ldo + n]);
+        out[i * ldo + n] = __float2bfloat16_rn(cur + acc);
+        if (coords != nullptr && ((cmask[n >> 5] >> (n & 31)) & 1u)) {
+          int rank = __popc(cmask[n >> 5] & ((1u << (n & 31)) - 1u));
+          for (int w = 0; w < (n >> 5); ++w) rank += __popc(cmask[w]);
+          coords[i * ncoord + rank] += acc;
+        }
+      }
+    }
+  }
+}
+
+// CSR / ELL graph -> dense ELL with exactly KP slots per node (-1 padded) for the main kernel
+__global__ void graph_to_ell_kernel(GraphView g, int64_t N, int KP, int32_t* __restrict__ ell) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * KP) return;
+  const int64_t i = idx / KP;
+  const int s = (int)(idx % KP);
+  int64_t start;
+  int cnt;
+  graph_row(g, i, start, cnt);
+  ell[idx] = s < cnt ? g.col[start + s] : -1;
+}
+
+}  // namespace tc
+}  // namespace gn
+
+using namespace gn;
+
+extern "C" size_t gn_tc_edge_scratch_bytes(int64_t N, int slots) {
+  return (size_t)(N > 0 ? N : 1) * (size_t)slots * sizeof(int32_t);
+}
+
+extern "C" int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp,
+                                        const gn_graph* graph, int64_t N, int slots,
+                                        const void* W2p, const void* W2Tp, int b, void* out,
+                                        int64_t ldo, float* coords, const int32_t* coord_cols,
+                                        int ncoord, void* scratch, size_t scratch_bytes,
+                                        void* stream) {
+  GN_CHECK_ARG(N >= 0 && b >= 1 && b <= 256, "gn_tc_edge_mlp_aggregate: b=%d not in [1,256]", b);
+  GN_CHECK_ARG(Kp >= 32 && Kp % 32 == 0 && Kp <= tc::EK_MAX_CHUNKS * tc::EK_KCH,
+               "gn_tc_edge_mlp_aggregate: padded hidden width %d not a multiple of 32 in [32,%d]",
+               Kp, tc::EK_MAX_CHUNKS * tc::EK_KCH);
+  GN_CHECK_ARG(slots == 8 || slots == 16 || slots == 32,
+               "gn_tc_edge_mlp_aggregate: slots=%d (must be 8, 16 or 32)", slots);
+  GN_CHECK_ARG(ldpq >= 2 * Kp && ldpq % 8 == 0 && ldo % 4 == 0 && ldo >= b,
+               "gn_tc_edge_mlp_aggregate: bad leading dimensions");
+  GN_CHECK_ARG(ncoord >= 0 && ncoord <= 16, "gn_tc_edge_mlp_aggregate: ncoord=%d", ncoord);
+  if (N == 0) return GN_OK;
+  GN_CHECK_ARG(pq && W2p && W2Tp && out && scratch, "gn_tc_edge_mlp_aggregate: null pointer");
+  GN_CHECK_ARG(scratch_bytes >= gn_tc_edge_scratch_bytes(N, slots),
+               "gn_tc_edge_mlp_aggregate: scratch too small");
+  GN_CHECK_ARG((reinterpret_cast<uintptr_t>(pq) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(out) & 7) == 0,
+               "gn_tc_edge_mlp_aggregate: pq must be 16-byte and out 8-byte aligned");
+  GraphView g;
+  int rc = make_graph_view(graph, &g);
+  if (rc != GN_OK) return rc;
+  cudaStream_t st = as_stream(stream);
+  const int bnp = (b + 15) & ~15;
+
+  tc::EdgeParams p;
+  memset(&p, 0, sizeof(p));
+  for (int t = 0; t < ncoord; ++t) {
+    GN_CHECK_ARG(coord_cols && coord_cols[t] >= 0 && coord_cols[t] < b,
+                 "gn_tc_edge_mlp_aggregate: coordinate column out of range");
+    GN_CHECK_ARG(t == 0 || coord_cols[t] > coord_cols[t - 1],
+                 "gn_tc_edge_mlp_aggregate: coordinate columns must be strictly increasing");
+    p.coord_mask[coord_cols[t] >> 5] |= 1u << (coord_cols[t] & 31);
+  }
+
+  int32_t* ell = reinterpret_cast<int32_t*>(scratch);
+  tc::CoordMask cm;
+  tc::graph_to_ell_kernel<<<(unsigned)ceil_div(N * slots, 256), 256, 0, st>>>(g, N, slots, ell);
+  GN_LAUNCH_CHECK();
+
+  CUtensorMap tmW2;
+  rc = make_tmap_bf16_2d(&tmW2, W2p, (uint64_t)bnp, (uint64_t)Kp, (uint64_t)Kp, (uint32_t)bnp,
+                         tc::EK_KCH, 64);
+  if (rc != GN_OK) return rc;
+
+  p.pq = reinterpret_cast<const __nv_bfloat16*>(pq);
+  p.ldpq = ldpq;
+  p.Kp = Kp;
+  p.nch = Kp / tc::EK_KCH;
+  p.ell = ell;
+  p.ell_stride = slots;
+  p.N = N;
+  p.bnp = bnp;
+  p.b = b;
+  p.out = reinterpret_cast<__nv_bfloat16*>(out);
+  p.ldo = ldo;
+  p.coords = ncoord > 0 ? coords : nullptr;
+  p.ncoord = ncoord;
+  const int npt = tc::EK_ROWS / slots;
+  p.num_tiles = ceil_div(N, npt);
+
+  int dev = 0, sms = 0;
+  GN_CUDA(cudaGetDevice(&dev));
+  GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const size_t smem = (size_t)p.nch * bnp * 64 + tc::EK_STAGES * tc::EK_STAGE_BYTES +
+                      sizeof(tc::EdgeBarriers) + 1024;
+  const unsigned grid = (unsigned)(p.num_tiles < sms ? p.num_tiles : sms);
+#define GN_EDGE_CASE(KP_)                                                                        \
+  {                                                                                              \
+    auto kern = tc::edge_mlp_aggregate_kernel<KP_>;                                              \
+    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    kern<<<grid, tc::EK_THREADS, smem, st>>>(tmW2, p);                                           \
+  }
+  if (slots == 8) GN_EDGE_CASE(8)
+  else if (slots == 16) GN_EDGE_CASE(16)
+  else GN_EDGE_CASE(32)
+#undef GN_EDGE_CASE
+  GN_LAUNCH_CHECK();
+
+  memcpy(cm.w, p.coord_mask, sizeof(cm.w));
+  tc::edge_overflow_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, st>>>(
+      p.pq, ldpq, Kp, g, slots, N, reinterpret_cast<const __nv_bfloat16*>(W2Tp), bnp, b, p.out, ldo,
+      p.coords, ncoord, cm);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}

@@ -1,0 +1,269 @@
+// bf16 tensor-core Linear (+bias, +activation) on tcgen05 / TMEM, operands staged by TMA.
+//
+// C[M,N] = act(A[M,K] W[N,K]^T + bias)   A, W bf16 (K contiguous), fp32 accumulate in TMEM.
+//
+// Used for the node-level GEMMs of the DynEdge path: the factored first layer of every
+// EdgeConv MLP (PQ = x [W1a-W1b ; W1b]^T, reference dynedge.py:193-204 via layers.py:67) and
+// the post-processing MLP (dynedge.py:222-232, 332).
+//
+// One CTA computes one 128 x BN output tile.  Warp roles: warp 0 = TMA producer, warp 1 =
+// tcgen05.mma issuer (also owns the TMEM allocation), warps 2-5 = epilogue (one TMEM lane
+// quadrant each).  A/W tiles travel as 128B-swizzled 64-column boxes through a 4-stage
+// mbarrier ring; rows/columns beyond M, N, K are zero-filled by the TMA unit.
+#include "tc_common.cuh"
+
+namespace gn {
+
+int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
+                      uint64_t ld, uint32_t box_rows, uint32_t box_cols, int swizzle_bytes) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                               const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                               const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = nullptr;
+  if (!encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
+      set_error("cuTensorMapEncodeTiled is not available from the driver");
+      return GN_ERR_CUDA;
+    }
+    encode = reinterpret_cast<EncodeFn>(fn);
+  }
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || ((ld * 2) & 15)) {
+    set_error("TMA operand must be 16-byte aligned with a row stride that is a multiple of 8 "
+              "bf16 elements (base=%p, ld=%llu)", base, (unsigned long long)ld);
+    return GN_ERR_INVALID_ARGUMENT;
+  }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                        : swizzle_bytes == 64  ? CU_TENSOR_MAP_SWIZZLE_64B
+                        : swizzle_bytes == 32  ? CU_TENSOR_MAP_SWIZZLE_32B
+                                               : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims,
+                      strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%llu cols=%llu ld=%llu box=%ux%u)",
+              (int)r, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld,
+              box_rows, box_cols);
+    return GN_ERR_CUDA;
+  }
+  return GN_OK;
+}
+
+namespace tc {
+
+constexpr int LIN_BM = 128;
+constexpr int LIN_BK = 64;        // 64 bf16 = one 128-byte swizzle row
+constexpr int LIN_STAGES = 4;
+constexpr int LIN_THREADS = 192;  // 6 warps
+constexpr int LIN_A_BYTES = LIN_BM * LIN_BK * 2;  // 16 KB
+
+struct __align__(8) LinBarriers {
+  uint64_t full[LIN_STAGES];
+  uint64_t empty[LIN_STAGES];
+  uint64_t tmem_full;
+  uint32_t tmem_base;
+};
+
+template <typename OutT>
+__device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int nvalid);
+
+template <>
+__device__ __forceinline__ void store_row32<float>(float* dst, const float (&v)[32], int nvalid) {
+  if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 4)
+      *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < nvalid) dst[j] = v[j];
+  }
+}
+template <>
+__device__ __forceinline__ void store_row32<__nv_bfloat16>(__nv_bfloat16* dst, const float (&v)[32],
+                                                           int nvalid) {
+  if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(v[j], v[j + 1]);
+      __nv_bfloat162 p1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+      __nv_bfloat162 p2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
+      __nv_bfloat162 p3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+      uint4 u;
+      u.x = *reinterpret_cast<uint32_t*>(&p0);
+      u.y = *reinterpret_cast<uint32_t*>(&p1);
+      u.z = *reinterpret_cast<uint32_t*>(&p2);
+      u.w = *reinterpret_cast<uint32_t*>(&p3);
+      *reinterpret_cast<uint4*>(dst + j) = u;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < nvalid) dst[j] = __float2bfloat16_rn(v[j]);
+  }
+}
+
+template <typename OutT, int ACT>
+__global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
+    const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+    const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
+    int BN) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the 128B swizzle atoms
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  const int b_bytes = BN * LIN_BK * 2;
+  const int stage_bytes = LIN_A_BYTES + b_bytes;
+  LinBarriers* bars = reinterpret_cast<LinBarriers*>(smem + LIN_STAGES * stage_bytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t m0 = (int64_t)blockIdx.x * LIN_BM;
+  const int n0 = blockIdx.y * BN;
+  const int nk = (K + LIN_BK - 1) / LIN_BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+#pragma unroll
+    for (int s = 0; s < LIN_STAGES; ++s) {
+      mbar_init(&bars->full[s], 1);
+      mbar_init(&bars->empty[s], 1);
+    }
+    mbar_init(&bars->tmem_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<256>(&bars->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_d = bars->tmem_base;
+
+  if (warp == 0) {
+    // ---------------------------------------------------------- TMA producer
+    if (elect_one()) {
+      for (int kb = 0; kb < nk; ++kb) {
+        const int s = kb % LIN_STAGES;
+        mbar_wait(&bars->empty[s], ((kb / LIN_STAGES) & 1) ^ 1);
+        uint8_t* a_dst = smem + s * stage_bytes;
+        uint8_t* b_dst = a_dst + LIN_A_BYTES;
+        mbar_arrive_expect_tx(&bars->full[s], (uint32_t)stage_bytes);
+        tma_load_2d(a_dst, &tmA, &bars->full[s], kb * LIN_BK, (int32_t)m0);
+        tma_load_2d(b_dst, &tmW, &bars->full[s], kb * LIN_BK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    const uint32_t idesc = make_idesc_bf16(LIN_BM, BN);
+    for (int kb = 0; kb < nk; ++kb) {
+      const int s = kb % LIN_STAGES;
+      mbar_wait(&bars->full[s], (kb / LIN_STAGES) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
+        const uint32_t b_addr = a_addr + LIN_A_BYTES;
+        const uint64_t adesc = make_kmajor_desc<128>(a_addr);
+        const uint64_t bdesc = make_kmajor_desc<128>(b_addr);
+#pragma unroll
+        for (int k4 = 0; k4 < LIN_BK / 16; ++k4) {
+          // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4) units
+          mma_bf16_ss(tmem_d, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc,
+                      (kb | k4) != 0);
+        }
+        mma_commit(&bars->empty[s]);
+        if (kb == nk - 1) mma_commit(&bars->tmem_full);
+      }
+      __syncwarp();
+    }
+  } else {
+    // -------------------------------------------------------------- epilogue
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    mbar_wait(&bars->tmem_full, 0);
+    tc_fence_after();
+    const int64_t row = m0 + q * 32 + lane;
+    for (int c = 0; c < BN; c += 32) {
+      float v[32];
+      tmem_ld_32x32(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+      const int n = n0 + c;
+      if (n >= N) break;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float b = (bias != nullptr && n + j < N) ? bias[n + j] : 0.f;
+        v[j] = activate<ACT>(v[j] + b);
+      }
+      if (row < M) store_row32<OutT>(C + row * ldc + n, v, min(N - n, BN - c));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<256>(tmem_d);
+}
+
+template <typename OutT>
+static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, const float* bias,
+                            void* C, int64_t ldc, int64_t M, int N, int K, int BN, int act,
+                            cudaStream_t st) {
+  const size_t smem = (size_t)LIN_STAGES * (LIN_A_BYTES + BN * LIN_BK * 2) + sizeof(LinBarriers) + 1024;
+  dim3 grid((unsigned)ceil_div(M, LIN_BM), (unsigned)ceil_div(N, BN));
+#define GN_TC_LIN_CASE(A_)                                                                      \
+  {                                                                                             \
+    auto kern = tc_linear_kernel<OutT, A_>;                                                     \
+    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    kern<<<grid, LIN_THREADS, smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
+                                          K, BN);                                               \
+  }
+  switch (act) {
+    case GN_ACT_NONE: GN_TC_LIN_CASE(ACT_NONE) break;
+    case GN_ACT_RELU: GN_TC_LIN_CASE(ACT_RELU) break;
+    case GN_ACT_GELU: GN_TC_LIN_CASE(ACT_GELU) break;
+    default: set_error("unknown activation %d", act); return GN_ERR_INVALID_ARGUMENT;
+  }
+#undef GN_TC_LIN_CASE
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+}  // namespace tc
+
+int tc_pick_bn(int N) {
+  // largest tile width <= 256 (multiple of 16) that minimises padding
+  int best = 256, best_waste = 1 << 30;
+  for (int bn = 256; bn >= 64; bn -= 16) {
+    int tiles = (N + bn - 1) / bn;
+    int waste = tiles * bn - N;
+    if (waste < best_waste) { best = bn; best_waste = waste; }
+  }
+  return best;
+}
+
+}  // namespace gn
+
+using namespace gn;
+
+extern "C" int gn_tc_linear_bf16(const void* A, int64_t lda, const void* W, int64_t ldw,
+                                 const float* bias, void* C, int64_t ldc, int c_dtype, int64_t M,
+                                 int N, int K, int act, void* stream) {
+  GN_CHECK_ARG(M >= 0 && N >= 1 && K >= 1 && lda >= K && ldw >= K && ldc >= N,
+               "gn_tc_linear_bf16: bad sizes");
+  if (M == 0) return GN_OK;
+  GN_CHECK_ARG(A && W && C, "gn_tc_linear_bf16: null pointer");
+  GN_CHECK_ARG(c_dtype == GN_F32 || c_dtype == GN_BF16, "gn_tc_linear_bf16: bad c_dtype");
+  const int BN = tc_pick_bn(N);
+  CUtensorMap tmA, tmW;
+  int rc = make_tmap_bf16_2d(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, tc::LIN_BM,
+                             tc::LIN_BK, 128);
+  if (rc != GN_OK) return rc;
+  rc = make_tmap_bf16_2d(&tmW, W, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)BN,
+                         tc::LIN_BK, 128);
+  if (rc != GN_OK) return rc;
+  cudaStream_t st = as_stream(stream);
+  if (c_dtype == GN_F32)
+    return tc::launch_tc_linear<float>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, st);
+  return tc::launch_tc_linear<__nv_bfloat16>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, st);
+}

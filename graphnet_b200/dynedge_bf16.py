@@ -1,0 +1,230 @@
+"""bf16 tensor-core forward of DynEdge (tcgen05 / TMEM / TMA kernels).
+
+Same computation as `DynEdge._forward_f32` (reference dynedge.py:296-350) with
+bf16 GEMM operands and fp32 accumulation / aggregation; outputs agree with the
+fp32 reference within 2e-2 relative (BASELINE.json north_star).  Weight
+repacking (padding, bf16 conversion, bias folding) happens once per parameter
+version on the device with torch ops - plumbing, not the timed path.
+"""
+
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import ops
+from .dynedge import _act_name, _parse_mlp, _WeightCache
+
+
+def _round_up(v: int, m: int) -> int:
+    return (v + m - 1) // m * m
+
+
+def _slots(k: int) -> int:
+    s = 8
+    while s < k and s < 32:
+        s *= 2
+    return s
+
+
+class _ConvPack:
+    """Repacked weights of one DynEdgeConv MLP for the tensor-core kernels."""
+
+    def __init__(self, l1: torch.nn.Linear, l2: torch.nn.Linear):
+        dev = l1.weight.device
+        a, d2 = l1.weight.shape
+        d = d2 // 2
+        b = l2.weight.shape[0]
+        Kp = _round_up(a + 2, 32)
+        if Kp > 352 or b > 256:
+            raise NotImplementedError(
+                f"bf16 EdgeConv kernel supports hidden <= 350 and output <= 256 (got {a}, {b}); "
+                "use precision='fp32' for this architecture")
+        Kd = _round_up(d, 8)
+        b16 = _round_up(b, 16)
+        W1 = l1.weight.detach().float()
+        Wpq = torch.zeros((2 * Kp, Kd), dtype=torch.float32, device=dev)
+        Wpq[:a, :d] = W1[:, :d] - W1[:, d:]
+        Wpq[Kp:Kp + a, :d] = W1[:, d:]
+        bias = torch.zeros(2 * Kp, dtype=torch.float32, device=dev)
+        bias[:a] = l1.bias.detach().float() if l1.bias is not None else 0.0
+        bias[a] = 1.0      # the two "ones" columns that carry b2 through the second GEMM
+        bias[a + 1] = 1.0
+        W2p = torch.zeros((b16, Kp), dtype=torch.float32, device=dev)
+        W2p[:b, :a] = l2.weight.detach().float()
+        W2p = W2p.to(torch.bfloat16)
+        if l2.bias is not None:
+            b2 = l2.bias.detach().float()
+            hi = b2.to(torch.bfloat16)
+            lo = (b2 - hi.float()).to(torch.bfloat16)
+            W2p[:b, a] = hi
+            W2p[:b, a + 1] = lo
+        self.d, self.a, self.b, self.Kp, self.Kd, self.b16 = d, a, b, Kp, Kd, b16
+        self.Wpq = Wpq.to(torch.bfloat16).contiguous()
+        self.bias_pq = bias
+        self.W2p = W2p.contiguous()
+        self.W2Tp = W2p.t().contiguous()
+
+
+def _conv_pack(conv) -> _ConvPack:
+    linears, act = conv._mlp()
+    if act != "relu" or len(linears) != 2:
+        raise NotImplementedError(
+            "precision='bf16' supports Linear-ReLU-Linear-ReLU EdgeConv MLPs; use precision='fp32'")
+    if conv.aggr not in ("add", "sum"):
+        raise NotImplementedError("precision='bf16' supports aggr='add'; use precision='fp32'")
+    if not hasattr(conv, "_cache_bf16"):
+        conv._cache_bf16 = _WeightCache()
+    l1, l2 = linears
+    params = [p for p in (l1.weight, l1.bias, l2.weight, l2.bias) if p is not None]
+    return conv._cache_bf16.get(params, lambda: _ConvPack(l1, l2))
+
+
+def _skip_layout(model) -> Tuple[int, List[int], List[int], int]:
+    """Column layout of the bf16 skip-cat buffer: [x0 | pad | conv1 | pad | ...]."""
+    D0 = model._nb_conv_inputs
+    widths = [conv.out_features for conv in model._conv_layers]
+    offs, off = [], _round_up(D0, 8)
+    for w in widths:
+        offs.append(off)
+        off += _round_up(w, 8)
+    return D0, widths, offs, off
+
+
+def _post_pack(model, total: int, D0: int, widths: List[int], offs: List[int]):
+    if not hasattr(model, "_cache_post_bf16"):
+        model._cache_post_bf16 = _WeightCache()
+    linears, act = _parse_mlp(model._post_processing)
+    if act != "relu":
+        raise NotImplementedError("precision='bf16' supports ReLU; use precision='fp32'")
+    params = [p for lin in linears for p in (lin.weight, lin.bias) if p is not None]
+
+    def build():
+        packs = []
+        dev = linears[0].weight.device
+        for i, lin in enumerate(linears):
+            W = lin.weight.detach().float()
+            n, k = W.shape
+            if i == 0:  # scatter the columns to the padded skip layout
+                Wp = torch.zeros((n, total), dtype=torch.float32, device=dev)
+                Wp[:, :D0] = W[:, :D0]
+                src = D0
+                for w, o in zip(widths, offs):
+                    Wp[:, o:o + w] = W[:, src:src + w]
+                    src += w
+                K = total
+            else:
+                K = k
+                Wp = torch.zeros((n, _round_up(k, 8)), dtype=torch.float32, device=dev)
+                Wp[:, :k] = W
+            bias = None if lin.bias is None else lin.bias.detach().float().contiguous()
+            packs.append((Wp.to(torch.bfloat16).contiguous(), bias, n, K))
+        return packs
+    return model._cache_post_bf16.get(params, build)
+
+
+def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
+                 return_intermediates: bool = False):
+    x, n_pulses, ptr, graph, N, B = model._graph_inputs(data, edge_index)
+    model._last_flags = graph.flags
+    dev = x.device
+    F = model._nb_inputs
+    assert x.shape[1] == F, f"expected {F} input features, got {x.shape[1]}"
+    D0, widths, offs, total = _skip_layout(model)
+    needs_zero = any(w % 8 for w in widths)
+    skip = (torch.zeros if needs_zero else torch.empty)((N, total), dtype=torch.bfloat16, device=dev)
+    x0w = offs[0]
+    if model._add_global_variables_after_pooling:
+        gv = ops.global_variables(x, graph, ptr, n_pulses)
+        skip[:, :x0w] = 0
+        skip[:, :F] = x
+    else:
+        gv = ops.global_variables(x, graph, ptr, n_pulses, x0=skip, x0_cols=x0w)
+    inter: Dict[str, Any] = {"global_variables": gv, "graphs": []}
+
+    off_in, d_in = 0, D0
+    convs = list(model._conv_layers)
+    for li, conv in enumerate(convs):
+        pk = _conv_pack(conv)
+        assert pk.d == d_in
+        pq = torch.empty((N, 2 * pk.Kp), dtype=torch.bfloat16, device=dev)
+        ops.tc_linear_bf16(skip[:, off_in:], pk.Wpq, pk.bias_pq, pq, K=d_in, act="none")
+        last = li + 1 == len(convs)
+        need_graph = (not last) or return_intermediates
+        cols = sorted(ops._columns(conv.features_subset, pk.b))
+        coords = (torch.empty((N, len(cols)), dtype=torch.float32, device=dev)
+                  if need_graph else None)
+        ops.tc_edge_mlp_aggregate(pq, pk.Kp, graph, _slots(conv.nb_neighbors), pk.W2p, pk.W2Tp,
+                                  pk.b, skip[:, offs[li]:], coords, cols)
+        if need_graph:
+            graph = ops.knn_graph_ell(coords, conv.nb_neighbors, ptr, list(range(len(cols))))
+            if return_intermediates:
+                inter["graphs"].append(graph)
+                inter.setdefault("coords", []).append(coords)
+        off_in, d_in = offs[li], pk.b
+
+    packs = _post_pack(model, total, D0, widths, offs)
+    h = skip
+    for i, (Wp, bias, n, K) in enumerate(packs):
+        lastp = i + 1 == len(packs)
+        out = torch.empty((N, n if lastp else _round_up(n, 8)),
+                          dtype=torch.float32 if lastp else torch.bfloat16, device=dev)
+        ops.tc_linear_bf16(h, Wp, bias, out, K=K, act="relu")
+        h = out
+    inter["post"] = h
+
+    if not model._skip_readout:
+        if model._global_pooling_schemes:
+            P = len(model._global_pooling_schemes)
+            C_ = h.shape[1]
+            extra = model._nb_global_variables if model._add_global_variables_after_pooling else 0
+            pooled = torch.empty((B, C_ * P + extra), dtype=torch.float32, device=dev)
+            ops.segment_pool(h, ptr, model._global_pooling_schemes, out=pooled)
+            if extra:
+                pooled[:, C_ * P:] = gv
+            inter["pooled"] = pooled
+            h = pooled
+        ro, ract = _parse_mlp(model._readout)
+        for lin in ro:
+            h = ops.linear_f32(h, lin.weight, lin.bias, act=ract)
+    if return_intermediates:
+        inter["skip"] = skip
+        inter["skip_offsets"] = offs
+        return h, inter
+    return h
+
+
+def time_edge_kernel(model, data: Any, flush_buf: Tensor, layer: int = 1, reps: int = 10):
+    """CUDA-event time of the fused edge kernel of conv `layer` alone (for bench.py's roofline)."""
+    x, n_pulses, ptr, graph, N, B = model._graph_inputs(data, None)
+    dev = x.device
+    conv = model._conv_layers[layer]
+    pk = _conv_pack(conv)
+    g = torch.Generator(device=dev).manual_seed(0)
+    pq = (torch.randn((N, 2 * pk.Kp), generator=g, device=dev) * 0.5).to(torch.bfloat16)
+    out = torch.empty((N, pk.b), dtype=torch.bfloat16, device=dev)
+    coords = torch.empty((N, 3), dtype=torch.float32, device=dev)
+    ell = ops.knn_graph_ell(x, conv.nb_neighbors, ptr, [0, 1, 2])
+    slots = _slots(conv.nb_neighbors)
+
+    def run():
+        ops.tc_edge_mlp_aggregate(pq, pk.Kp, ell, slots, pk.W2p, pk.W2Tp, pk.b, out, coords,
+                                  [0, 1, 2])
+    for _ in range(3):
+        run()
+    s = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+    e = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+    for i in range(reps):
+        flush_buf.fill_(i)
+        s[i].record()
+        run()
+        e[i].record()
+    torch.cuda.synchronize(dev)
+    ms = sum(a.elapsed_time(b_) for a, b_ in zip(s, e)) / reps
+    E = int(ell.deg.sum().item())
+    executed = 2.0 * (N * slots) * pk.Kp * pk.b16
+    name = ("gn::tc::edge_mlp_aggregate_kernel<8> (+ graph_to_ell, edge_overflow; "
+            "tcgen05 bf16, timed as one C-ABI call)")
+    return ms, executed, name

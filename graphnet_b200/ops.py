@@ -300,3 +300,40 @@ def task_head(y: Tensor, kind: str) -> Tensor:
         check(_lib.load().gn_task_head(_ptr(y), M, p, code, _ptr(out), _stream(dev)),
               "gn_task_head")
     return out
+
+
+# ------------------------------------------------- dense, bf16 tensor cores
+def tc_linear_bf16(A: Tensor, W: Tensor, bias: Optional[Tensor], out: Tensor, K: int,
+                   act: str = "none") -> Tensor:
+    """out[:, :N] = act(A[:, :K] W[:, :K]^T + bias); A, W bf16; out bf16 or fp32 (tcgen05)."""
+    dev = _require_cuda(A, W, bias, out)
+    assert A.dtype == torch.bfloat16 and W.dtype == torch.bfloat16
+    assert A.stride(1) == 1 and W.stride(1) == 1 and out.stride(1) == 1
+    M = A.shape[0]
+    Nout = W.shape[0]
+    assert out.shape[0] == M and out.shape[1] >= Nout and A.shape[1] >= K and W.shape[1] >= K
+    dt = DTYPE_BF16 if out.dtype == torch.bfloat16 else DTYPE_F32
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_tc_linear_bf16(_ptr(A), A.stride(0), _ptr(W), W.stride(0),
+                                            _ptr(bias), _ptr(out), out.stride(0), dt, M, Nout, K,
+                                            ACT[act], _stream(dev)), "gn_tc_linear_bf16")
+    return out
+
+
+def tc_edge_mlp_aggregate(pq: Tensor, Kp: int, graph: Graph, slots: int, W2p: Tensor,
+                          W2Tp: Tensor, b: int, out: Tensor, coords: Optional[Tensor],
+                          coord_cols: Sequence[int]) -> Tensor:
+    """out[i] = sum_j ReLU(W2 ReLU(P_i + Q_j) + b2) on tcgen05 (see include/graphnet_b200.h)."""
+    dev = _require_cuda(pq, W2p, W2Tp, out, coords)
+    N = pq.shape[0]
+    lib = _lib.load()
+    nbytes = lib.gn_tc_edge_scratch_bytes(N, slots)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    gs = graph.c_struct()
+    ncoord = 0 if coords is None else len(coord_cols)
+    with torch.cuda.device(dev):
+        check(lib.gn_tc_edge_mlp_aggregate(
+            _ptr(pq), pq.stride(0), Kp, C.byref(gs), N, slots, _ptr(W2p), _ptr(W2Tp), b,
+            _ptr(out), out.stride(0), _ptr(coords), _host_i32(coord_cols) if ncoord else None,
+            ncoord, _ptr(scratch), nbytes, _stream(dev)), "gn_tc_edge_mlp_aggregate")
+    return out

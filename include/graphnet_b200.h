@@ -171,6 +171,33 @@ int gn_edgeconv_f32(const float* x, int64_t ldx, int d, const gn_graph* graph,
                     const float* W2T, const float* b2, int b, int act, int aggr,
                     float* pq, float* out, int64_t ldo, void* stream);
 
+/* ---- dense layers, bf16 tensor cores (tcgen05 / TMEM / TMA) ------------------- */
+
+/* torch.nn.Linear (+ activation) with bf16 operands and fp32 accumulation:
+ * C = act(A W^T + bias).  A [M,K] bf16 (row stride lda), W [N,K] bf16 (row stride ldw),
+ * both 16-byte aligned with strides that are multiples of 8 elements; bias fp32 or NULL;
+ * C [M,N] of c_dtype (GN_F32 / GN_BF16, row stride ldc).  Same reference call sites as
+ * gn_linear_f32 plus the first (factored) Linear of each EdgeConv MLP. */
+int gn_tc_linear_bf16(const void* A, int64_t lda, const void* W, int64_t ldw,
+                      const float* bias, void* C, int64_t ldc, int c_dtype, int64_t M,
+                      int N, int K, int act, void* stream);
+
+/* Second half of the fused EdgeConv (components/layers.py:67, aggr="add"):
+ *   out[i] = sum_{j in N(i)} ReLU(W2 ReLU(P_i + Q_j) + b2)
+ * pq [N, ldpq] bf16 holds P in columns [0,Kp) and Q in [Kp,2Kp) (Kp = hidden width a
+ * padded to a multiple of 32 with >= 2 pad columns; P[:,a] = P[:,a+1] = 1, Q pads = 0).
+ * W2p [b16, Kp] bf16 row-major (b16 = b rounded up to 16; columns a, a+1 hold b2 split
+ * into bf16 hi/lo parts, remaining pads 0); W2Tp [Kp, b16] is its transpose (used for
+ * in-edges beyond `slots` per node).  slots in {8,16,32} >= the usual in-degree.
+ * out [N, ldo] bf16.  If ncoord > 0, the fp32 (unrounded) values of the columns listed in
+ * the HOST array coord_cols (strictly increasing) are also written to coords [N, ncoord]
+ * for the next kNN.  scratch: gn_tc_edge_scratch_bytes(N, slots) bytes. */
+size_t gn_tc_edge_scratch_bytes(int64_t N, int slots);
+int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp, const gn_graph* graph,
+                             int64_t N, int slots, const void* W2p, const void* W2Tp, int b,
+                             void* out, int64_t ldo, float* coords, const int32_t* coord_cols,
+                             int ncoord, void* scratch, size_t scratch_bytes, void* stream);
+
 /* ---- task heads ----------------------------------------------------------- */
 
 /* The `_forward` of a reconstruction head (models/task/reconstruction.py) applied
