@@ -18,7 +18,7 @@ GN_OK = 0
 ACT = {"none": 0, "relu": 1, "gelu": 2}
 AGGR = {"add": 0, "sum": 0, "mean": 1, "max": 2, "min": 3}
 POOL = {"min": 0, "max": 1, "sum": 2, "mean": 3}
-DTYPE_F32, DTYPE_BF16 = 0, 1
+DTYPE_F32, DTYPE_BF16, DTYPE_F16 = 0, 1, 2
 HEAD = {
     "IdentityTask": 0,
     "EnergyReconstruction": 1,
@@ -36,6 +36,7 @@ class GnGraph(C.Structure):
         ("deg", C.c_void_p),
         ("rowptr", C.c_void_p),
         ("ell_stride", C.c_int32),
+        ("num_edges", C.c_int64),
     ]
 
 
@@ -54,14 +55,15 @@ SIGNATURES = {
     "gn_ell_row_offsets": (_int, [_p, _i64, _p, _p, _sz, _p]),
     "gn_ell_to_coo": (_int, [_p, _i32, _p, _p, _i64, _i64, _p, _p]),
     "gn_coo_to_csr": (_int, [_p, _i64, _i64, _p, _p, _p, _p, _p]),
-    "gn_global_variables": (_int, [_p, _i64, _int, _gp, _p, _p, _i64, _i64, _p, _p, _i64, _int, _int, _p]),
+    "gn_global_variables": (_int, [_p, _i64, _int, _gp, _p, _p, _i64, _i64, _p, _p, _i64, _int, _int,
+                                   _p, _i64, _int, _int, _p]),
     "gn_segment_pool": (_int, [_p, _int, _i64, _int, _p, _i64, _hp, _int, _p, _i64, _p]),
-    "gn_linear_f32": (_int, [_p, _i64, _p, _p, _p, _i64, _i64, _int, _int, _int, _p]),
+    "gn_linear_f32": (_int, [_p, _i64, _p, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),
     "gn_edgeconv_prepare_f32": (_int, [_p, _p, _int, _int, _int, _p, _p, _p]),
     "gn_edgeconv_f32": (_int, [_p, _i64, _int, _gp, _i64, _p, _p, _int, _p, _p, _int, _int, _int, _p, _p, _i64, _p]),
-    "gn_tc_linear_bf16": (_int, [_p, _i64, _p, _i64, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),
-    "gn_tc_edge_scratch_bytes": (_sz, [_i64, _int]),
-    "gn_tc_edge_mlp_aggregate": (_int, [_p, _i64, _int, _gp, _i64, _int, _p, _p, _int, _p, _i64,
+    "gn_tc_linear": (_int, [_p, _i64, _p, _i64, _int, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),
+    "gn_tc_edge_scratch_bytes": (_sz, [_gp, _i64, _int]),
+    "gn_tc_edge_mlp_aggregate": (_int, [_p, _i64, _int, _gp, _i64, _int, _p, _int, _p, _i64, _int,
                                         _p, _hp, _int, _p, _sz, _p]),
     "gn_task_head": (_int, [_p, _i64, _int, _int, _p, _p]),
 }

@@ -13,65 +13,87 @@
 //        D     = H W2^T                              (register-tiled FFMA)
 //        acc  (+)= act(D + b2)  for rows with s < deg(i_r)
 //   3. out[i] = acc   (sum / mean / max / min over the node's in-edges)
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace gn {
 
 // ------------------------------------------------------------------- linear
-constexpr int LIN_TM = 64, LIN_TN = 64, LIN_TK = 16, LIN_THREADS = 256;
+constexpr int LIN_TK = 16, LIN_THREADS = 256;
 
-template <int ACT>
+template <typename OutT>
+__device__ __forceinline__ OutT cvt_out(float v);
+template <>
+__device__ __forceinline__ float cvt_out<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 cvt_out<__nv_bfloat16>(float v) {
+  return __float2bfloat16_rn(v);
+}
+template <>
+__device__ __forceinline__ __half cvt_out<__half>(float v) {  // saturating
+  return __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+}
+
+// TM x TN output tile per CTA, (TM/16) x (TN/16) outputs per thread.
+template <int ACT, int TM, int TN, typename OutT>
 __global__ void __launch_bounds__(LIN_THREADS) linear_f32_kernel(
     const float* __restrict__ A, int64_t lda, const float* __restrict__ W,
-    const float* __restrict__ bias, float* __restrict__ C, int64_t ldc, int64_t M, int N, int K) {
-  __shared__ float As[LIN_TK][LIN_TM + 4];
-  __shared__ float Ws[LIN_TK][LIN_TN + 4];
+    const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K) {
+  constexpr int RM = TM / 16, RN = TN / 16;
+  __shared__ __align__(16) float As[LIN_TK][TM + 4];
+  __shared__ __align__(16) float Ws[LIN_TK][TN + 4];
   const int tid = threadIdx.x;
-  const int64_t m0 = (int64_t)blockIdx.x * LIN_TM;
-  const int n0 = blockIdx.y * LIN_TN;
-  const int ty = tid / 16, tx = tid % 16;  // 4x4 outputs per thread
-  float acc[4][4];
+  const int64_t m0 = (int64_t)blockIdx.x * TM;
+  const int n0 = blockIdx.y * TN;
+  const int ty = tid / 16, tx = tid % 16;
+  float acc[RM][RN];
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < RM; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < RN; ++j) acc[i][j] = 0.f;
 
-  // loader mapping: 64 rows x 16 k = 1024 elements, 4 per thread, k fastest
-  const int lr = tid / 4;         // 0..63
-  const int lk = (tid % 4) * 4;   // 0,4,8,12
   for (int k0 = 0; k0 < K; k0 += LIN_TK) {
+    // TM x 16 and TN x 16 elements, k fastest within a row
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
-      const int k = k0 + lk + t;
-      const int64_t m = m0 + lr;
-      As[lk + t][lr] = (m < M && k < K) ? A[m * lda + k] : 0.f;
-      const int n = n0 + lr;
-      Ws[lk + t][lr] = (n < N && k < K) ? W[(int64_t)n * K + k] : 0.f;
+    for (int t = 0; t < RM; ++t) {
+      const int idx = tid + t * LIN_THREADS;
+      const int r = idx / LIN_TK, kk = idx % LIN_TK;
+      const int64_t m = m0 + r;
+      As[kk][r] = (m < M && k0 + kk < K) ? A[m * lda + k0 + kk] : 0.f;
+    }
+#pragma unroll
+    for (int t = 0; t < RN; ++t) {
+      const int idx = tid + t * LIN_THREADS;
+      const int r = idx / LIN_TK, kk = idx % LIN_TK;
+      const int n = n0 + r;
+      Ws[kk][r] = (n < N && k0 + kk < K) ? W[(int64_t)n * K + k0 + kk] : 0.f;
     }
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < LIN_TK; ++k) {
-      float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
-      float4 w = *reinterpret_cast<const float4*>(&Ws[k][tx * 4]);
-      const float av[4] = {a.x, a.y, a.z, a.w};
-      const float wv[4] = {w.x, w.y, w.z, w.w};
+      float av[RM], wv[RN];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < RM; ++i) av[i] = As[k][ty * RM + i];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], wv[j], acc[i][j]);
+      for (int j = 0; j < RN; ++j) wv[j] = Ws[k][tx * RN + j];
+#pragma unroll
+      for (int i = 0; i < RM; ++i)
+#pragma unroll
+        for (int j = 0; j < RN; ++j) acc[i][j] = fmaf(av[i], wv[j], acc[i][j]);
     }
     __syncthreads();
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int64_t m = m0 + ty * 4 + i;
+  for (int i = 0; i < RM; ++i) {
+    const int64_t m = m0 + ty * RM + i;
     if (m >= M) continue;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int n = n0 + tx * 4 + j;
+    for (int j = 0; j < RN; ++j) {
+      const int n = n0 + tx * RN + j;
       if (n < N) {
         float v = acc[i][j] + (bias ? bias[n] : 0.f);
-        C[m * ldc + n] = activate<ACT>(v);
+        C[m * ldc + n] = cvt_out<OutT>(activate<ACT>(v));
       }
     }
   }
@@ -278,25 +300,45 @@ __global__ void edgeconv1_f32_kernel(const float* __restrict__ pq, int a, GraphV
   }
 }
 
-template <int ACT>
-static int launch_linear(const float* A, int64_t lda, const float* W, const float* bias, float* C,
+template <int ACT, typename OutT>
+static int launch_linear(const float* A, int64_t lda, const float* W, const float* bias, void* C,
                          int64_t ldc, int64_t M, int N, int K, cudaStream_t st) {
-  dim3 grid((unsigned)ceil_div(M, LIN_TM), (unsigned)ceil_div(N, LIN_TN));
-  linear_f32_kernel<ACT><<<grid, LIN_THREADS, 0, st>>>(A, lda, W, bias, C, ldc, M, N, K);
+  // small problems (readout, heads): 32x32 tiles so that the grid still covers the SMs
+  const int64_t big_ctas = ceil_div(M, 64) * ceil_div(N, 64);
+  if (big_ctas >= 256) {
+    dim3 grid((unsigned)ceil_div(M, 64), (unsigned)ceil_div(N, 64));
+    linear_f32_kernel<ACT, 64, 64, OutT><<<grid, LIN_THREADS, 0, st>>>(
+        A, lda, W, bias, reinterpret_cast<OutT*>(C), ldc, M, N, K);
+  } else {
+    dim3 grid((unsigned)ceil_div(M, 32), (unsigned)ceil_div(N, 32));
+    linear_f32_kernel<ACT, 32, 32, OutT><<<grid, LIN_THREADS, 0, st>>>(
+        A, lda, W, bias, reinterpret_cast<OutT*>(C), ldc, M, N, K);
+  }
   return GN_OK;
 }
 
-int linear_f32(const float* A, int64_t lda, const float* W, const float* bias, float* C,
-               int64_t ldc, int64_t M, int N, int K, int act, cudaStream_t st) {
-  if (M == 0) return GN_OK;
+template <typename OutT>
+static int linear_f32_t(const float* A, int64_t lda, const float* W, const float* bias, void* C,
+                        int64_t ldc, int64_t M, int N, int K, int act, cudaStream_t st) {
   switch (act) {
-    case GN_ACT_NONE: launch_linear<ACT_NONE>(A, lda, W, bias, C, ldc, M, N, K, st); break;
-    case GN_ACT_RELU: launch_linear<ACT_RELU>(A, lda, W, bias, C, ldc, M, N, K, st); break;
-    case GN_ACT_GELU: launch_linear<ACT_GELU>(A, lda, W, bias, C, ldc, M, N, K, st); break;
+    case GN_ACT_NONE: launch_linear<ACT_NONE, OutT>(A, lda, W, bias, C, ldc, M, N, K, st); break;
+    case GN_ACT_RELU: launch_linear<ACT_RELU, OutT>(A, lda, W, bias, C, ldc, M, N, K, st); break;
+    case GN_ACT_GELU: launch_linear<ACT_GELU, OutT>(A, lda, W, bias, C, ldc, M, N, K, st); break;
     default: set_error("unknown activation %d", act); return GN_ERR_INVALID_ARGUMENT;
   }
   GN_LAUNCH_CHECK();
   return GN_OK;
+}
+
+int linear_f32(const float* A, int64_t lda, const float* W, const float* bias, void* C,
+               int64_t ldc, int c_dtype, int64_t M, int N, int K, int act, cudaStream_t st) {
+  if (M == 0) return GN_OK;
+  if (c_dtype == GN_F32) return linear_f32_t<float>(A, lda, W, bias, C, ldc, M, N, K, act, st);
+  if (c_dtype == GN_BF16)
+    return linear_f32_t<__nv_bfloat16>(A, lda, W, bias, C, ldc, M, N, K, act, st);
+  if (c_dtype == GN_F16) return linear_f32_t<__half>(A, lda, W, bias, C, ldc, M, N, K, act, st);
+  set_error("unknown output dtype %d", c_dtype);
+  return GN_ERR_INVALID_ARGUMENT;
 }
 
 template <int ACT, int AGGR>
@@ -342,11 +384,11 @@ static int dispatch_aggr(int aggr, const float* pq, int a, const GraphView& g, i
 using namespace gn;
 
 extern "C" int gn_linear_f32(const float* A, int64_t lda, const float* W, const float* bias,
-                             float* C, int64_t ldc, int64_t M, int N, int K, int act,
+                             void* C, int64_t ldc, int c_dtype, int64_t M, int N, int K, int act,
                              void* stream) {
   GN_CHECK_ARG(M >= 0 && N >= 1 && K >= 1 && lda >= K && ldc >= N, "gn_linear_f32: bad sizes");
   GN_CHECK_ARG(M == 0 || (A && W && C), "gn_linear_f32: null pointer");
-  return linear_f32(A, lda, W, bias, C, ldc, M, N, K, act, as_stream(stream));
+  return linear_f32(A, lda, W, bias, C, ldc, c_dtype, M, N, K, act, as_stream(stream));
 }
 
 extern "C" int gn_edgeconv_prepare_f32(const float* W1, const float* W2, int d, int a, int b,
@@ -376,9 +418,10 @@ extern "C" int gn_edgeconv_f32(const float* x, int64_t ldx, int d, const gn_grap
   if (rc != GN_OK) return rc;
   cudaStream_t st = as_stream(stream);
   // 1. node GEMM: pq[:, 0:a] = x (W1a-W1b)^T + b1 ; pq[:, a:2a] = x W1b^T
-  rc = linear_f32(x, ldx, Wpq, b1, pq, 2 * a, N, a, d, GN_ACT_NONE, st);
+  rc = linear_f32(x, ldx, Wpq, b1, pq, 2 * a, GN_F32, N, a, d, GN_ACT_NONE, st);
   if (rc != GN_OK) return rc;
-  rc = linear_f32(x, ldx, Wpq + (int64_t)a * d, nullptr, pq + a, 2 * a, N, a, d, GN_ACT_NONE, st);
+  rc = linear_f32(x, ldx, Wpq + (int64_t)a * d, nullptr, pq + a, 2 * a, GN_F32, N, a, d,
+                  GN_ACT_NONE, st);
   if (rc != GN_OK) return rc;
   // 2./3. gather + second layer + aggregation
   switch (act) {

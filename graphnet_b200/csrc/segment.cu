@@ -8,6 +8,7 @@
 // contiguous, threads map to feature columns (coalesced, 128-bit where aligned),
 // every input element is read exactly once and all requested statistics are
 // produced in the same pass.
+#include <cuda_fp16.h>
 #include <math.h>
 
 #include "common.cuh"
@@ -18,18 +19,25 @@ namespace gn {
 constexpr int GV_THREADS = 128;
 constexpr int GV_MAX_F = 64;
 
-template <typename OutT>
-__device__ __forceinline__ OutT to_out(float v);
-template <>
-__device__ __forceinline__ float to_out<float>(float v) { return v; }
-template <>
-__device__ __forceinline__ __nv_bfloat16 to_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+struct X0Out {
+  void* ptr;      // [N, ld] or null
+  int64_t ld;
+  int cols;       // columns written: [x | gv[batch] | zeros]
+  int dtype;      // GN_F32 / GN_BF16 / GN_F16
+};
 
-template <typename OutT>
+__device__ __forceinline__ void store_x0(const X0Out& o, int64_t row, int c, float v) {
+  if (o.dtype == GN_F32) reinterpret_cast<float*>(o.ptr)[row * o.ld + c] = v;
+  else if (o.dtype == GN_BF16)
+    reinterpret_cast<__nv_bfloat16*>(o.ptr)[row * o.ld + c] = __float2bfloat16_rn(v);
+  else
+    reinterpret_cast<__half*>(o.ptr)[row * o.ld + c] =
+        __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+}
+
 __global__ void __launch_bounds__(GV_THREADS) global_variables_kernel(
     const float* __restrict__ x, int64_t ldx, int F, GraphView g, const int32_t* __restrict__ ptr,
-    const int32_t* __restrict__ n_pulses, float* __restrict__ gv, OutT* __restrict__ x0,
-    int64_t ldx0, int x0_cols) {
+    const int32_t* __restrict__ n_pulses, float* __restrict__ gv, X0Out o0, X0Out o1) {
   __shared__ float s_part[GV_THREADS];
   __shared__ float s_gv[GV_MAX_F + 5];
   __shared__ int s_cnt[5];
@@ -94,14 +102,17 @@ __global__ void __launch_bounds__(GV_THREADS) global_variables_kernel(
   __syncthreads();
   for (int c = tid; c < G; c += GV_THREADS) gv[(int64_t)e * G + c] = s_gv[c];
 
-  if (x0 != nullptr) {
-    const int64_t total = (int64_t)n * x0_cols;
+#pragma unroll
+  for (int w = 0; w < 2; ++w) {
+    const X0Out& o = w == 0 ? o0 : o1;
+    if (o.ptr == nullptr) continue;
+    const int64_t total = (int64_t)n * o.cols;
     for (int64_t idx = tid; idx < total; idx += GV_THREADS) {
-      const int r = (int)(idx / x0_cols), c = (int)(idx % x0_cols);
+      const int r = (int)(idx / o.cols), c = (int)(idx % o.cols);
       float v = 0.f;
       if (c < F) v = x[(int64_t)(lo + r) * ldx + c];
       else if (c < F + G) v = s_gv[c - F];
-      x0[(int64_t)(lo + r) * ldx0 + c] = to_out<OutT>(v);
+      store_x0(o, lo + r, c, v);
     }
   }
 }
@@ -221,7 +232,8 @@ using namespace gn;
 extern "C" int gn_global_variables(const float* x, int64_t ldx, int F, const gn_graph* graph,
                                    const int32_t* ptr, const int32_t* n_pulses, int64_t N,
                                    int64_t B, float* gv, void* x0, int64_t ldx0, int x0_cols,
-                                   int x0_dtype, void* stream) {
+                                   int x0_dtype, void* x0b, int64_t ldx0b, int x0b_cols,
+                                   int x0b_dtype, void* stream) {
   GN_CHECK_ARG(F >= 4 && F <= GV_MAX_F,
                "gn_global_variables: F=%d not in [4,%d] (columns 0..3 must be x,y,z,t)", F,
                GV_MAX_F);
@@ -231,19 +243,16 @@ extern "C" int gn_global_variables(const float* x, int64_t ldx, int F, const gn_
   GraphView g;
   int rc = make_graph_view(graph, &g);
   if (rc != GN_OK) return rc;
-  if (x0) {
-    GN_CHECK_ARG(x0_cols >= F + F + 5 && ldx0 >= x0_cols,
+  X0Out o0{x0, ldx0, x0_cols, x0_dtype}, o1{x0b, ldx0b, x0b_cols, x0b_dtype};
+  for (const X0Out* o : {&o0, &o1}) {
+    if (!o->ptr) continue;
+    GN_CHECK_ARG(o->cols >= F + F + 5 && o->ld >= o->cols,
                  "gn_global_variables: x0 needs >= 2F+5 columns");
+    GN_CHECK_ARG(o->dtype == GN_F32 || o->dtype == GN_BF16 || o->dtype == GN_F16,
+                 "gn_global_variables: bad x0 dtype");
   }
-  cudaStream_t st = as_stream(stream);
-  if (x0_dtype == GN_BF16) {
-    global_variables_kernel<__nv_bfloat16><<<(unsigned)B, GV_THREADS, 0, st>>>(
-        x, ldx, F, g, ptr, n_pulses, gv, reinterpret_cast<__nv_bfloat16*>(x0), ldx0, x0_cols);
-  } else {
-    GN_CHECK_ARG(x0_dtype == GN_F32, "gn_global_variables: bad x0_dtype");
-    global_variables_kernel<float><<<(unsigned)B, GV_THREADS, 0, st>>>(
-        x, ldx, F, g, ptr, n_pulses, gv, reinterpret_cast<float*>(x0), ldx0, x0_cols);
-  }
+  global_variables_kernel<<<(unsigned)B, GV_THREADS, 0, as_stream(stream)>>>(
+      x, ldx, F, g, ptr, n_pulses, gv, o0, o1);
   GN_LAUNCH_CHECK();
   return GN_OK;
 }

@@ -1,4 +1,4 @@
-// Fused EdgeConv message + aggregation on tcgen05 / TMEM (bf16 inputs, fp32 accumulate).
+// Fused EdgeConv message + aggregation on tcgen05 / TMEM (fp16 hidden layer, fp32 accumulate).
 //
 //   out[i] = sum_{j in N(i)} ReLU( W2 ReLU(P_i + Q_j) + b2 )
 //
@@ -18,8 +18,18 @@
 // Tile rows are ELL slots: row r of tile t is (node t*128/KP + r/KP, slot r%KP); empty slots are
 // all-zero A rows.  b2 is folded into the GEMM: P carries 1.0 in the two pad columns a, a+1 and
 // W2's columns a, a+1 hold b2 split into bf16 hi + lo parts, so an empty slot contributes
-// exactly 0 and the epilogue needs no bias add.  In-edges beyond KP per node are added by
-// edge_overflow_kernel (rare: a node keeps k+1 edges only when >= k+1 coincident pulses precede it).
+// exactly 0 and the epilogue needs no bias add.
+//
+// The hidden layer (P, Q, h, W2) is IEEE fp16 rather than bf16: same tensor-core rate, 3 more
+// mantissa bits, which matters because P_i + Q_j cancels (W1b (x_j - x_i) is small for near
+// neighbours); pre-activations are bounded by the weights, so fp16's range is ample (the node
+// GEMM saturates at +-65504).  Layer inputs/outputs stay bf16.
+//
+// In-edges beyond the KP slots of a node (a node keeps k+1 edges when >= k+1 coincident pulses
+// precede it; user graphs may have any degree) are handled by a second pass of the SAME kernel
+// over a compacted list of (node, slot base) groups, accumulating with red.global.add.
+#include <cuda_fp16.h>
+
 #include "tc_common.cuh"
 
 namespace gn {
@@ -44,32 +54,59 @@ struct __align__(8) EdgeBarriers {
 };
 
 struct EdgeParams {
-  const __nv_bfloat16* pq;  // [N, ldpq]: P in columns [0, Kp), Q in [Kp, 2Kp)
+  const __half* pq;         // [N, ldpq]: P in columns [0, Kp), Q in [Kp, 2Kp)
   int64_t ldpq;
   int Kp;                   // padded hidden width, multiple of 32
   int nch;                  // Kp / 32
-  const int32_t* ell;       // [N, ell_stride] neighbour ids, -1 = empty slot
-  int ell_stride;
+  const int32_t* ell;       // [groups, KP] neighbour ids, -1 = empty slot
+  const int32_t* group_node;  // target node of each group, or null: group g is node g
+  const int32_t* group_count; // device int: number of groups, or null: N groups
+  int accumulate;           // 0: store, 1: red.add into out / coords (overflow pass)
   int64_t N;
   int bnp;                  // output width padded to a multiple of 16 (UMMA N)
   int b;                    // valid output columns
-  __nv_bfloat16* out;       // [N, ldo]
+  void* out;                // [N, ldo] bf16 or fp16
+  int out_f16;              // 0: bf16, 1: fp16 (saturated)
   int64_t ldo;
   float* coords;            // [N, ncoord] fp32 copy of the columns selected by coord_mask, or null
   int ncoord;
   uint32_t coord_mask[8];
-  int64_t num_tiles;
 };
 
-__device__ __forceinline__ uint4 ldg16(const __nv_bfloat16* p) {
+__device__ __forceinline__ uint4 ldg16(const __half* p) {
   return __ldg(reinterpret_cast<const uint4*>(p));
 }
 
-__device__ __forceinline__ uint32_t relu_add_bf16x2(uint32_t a, uint32_t b) {
-  __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&a);
-  __nv_bfloat162 y = *reinterpret_cast<__nv_bfloat162*>(&b);
-  __nv_bfloat162 s = __hmax2(__hadd2(x, y), __float2bfloat162_rn(0.f));
+__device__ __forceinline__ uint32_t relu_add_f16x2(uint32_t a, uint32_t b) {
+  __half2 x = *reinterpret_cast<__half2*>(&a);
+  __half2 y = *reinterpret_cast<__half2*>(&b);
+  __half2 s = __hmax2(__hadd2(x, y), __float2half2_rn(0.f));
   return *reinterpret_cast<uint32_t*>(&s);
+}
+
+__device__ __forceinline__ uint32_t pack2_16(float a, float b, bool f16) {
+  if (f16) {
+    __half2 h = __floats2half2_rn(fminf(a, 65504.f), fminf(b, 65504.f));  // inputs are >= 0
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint16_t pack1_16(float a, bool f16) {
+  if (f16) {
+    __half h = __float2half_rn(fminf(a, 65504.f));
+    return *reinterpret_cast<uint16_t*>(&h);
+  }
+  __nv_bfloat16 h = __float2bfloat16_rn(a);
+  return *reinterpret_cast<uint16_t*>(&h);
+}
+__device__ __forceinline__ void red_add2_16(void* dst, float a, float b, bool f16) {
+  if (f16) atomicAdd(reinterpret_cast<__half2*>(dst), __floats2half2_rn(fminf(a, 65504.f), fminf(b, 65504.f)));
+  else atomicAdd(reinterpret_cast<__nv_bfloat162*>(dst), __floats2bfloat162_rn(a, b));
+}
+__device__ __forceinline__ void red_add1_16(void* dst, float a, bool f16) {
+  if (f16) atomicAdd(reinterpret_cast<__half*>(dst), __float2half_rn(fminf(a, 65504.f)));
+  else atomicAdd(reinterpret_cast<__nv_bfloat16*>(dst), __float2bfloat16_rn(a));
 }
 
 template <int KP>
@@ -84,8 +121,11 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
   EdgeBarriers* bars = reinterpret_cast<EdgeBarriers*>(a_smem + EK_STAGES * EK_STAGE_BYTES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  constexpr int NPT = EK_ROWS / KP;  // nodes per tile
+  constexpr int NPT = EK_ROWS / KP;  // groups (nodes) per tile
   const int nch = p.nch;
+  const int64_t num_groups = p.group_count ? (int64_t)__ldg(p.group_count) : p.N;
+  const int64_t num_tiles = (num_groups + NPT - 1) / NPT;
+  if ((int64_t)blockIdx.x >= num_tiles) return;  // uniform per CTA, before any barrier
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmW2);
@@ -117,12 +157,12 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
     }
     __syncwarp();
     mbar_wait(&bars->w2_full, 0);
-    const uint32_t idesc = make_idesc_bf16(EK_ROWS, p.bnp);
+    const uint32_t idesc = make_idesc_f16(EK_ROWS, p.bnp);
     const uint32_t w2_addr = smem_u32(w2_smem);
     const uint32_t a_addr = smem_u32(a_smem);
     uint32_t g = 0;  // running stage counter
     uint32_t it = 0;
-    for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const uint32_t buf = it & 1;
       mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
       tc_fence_after();
@@ -156,30 +196,29 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
       const int r = r0 + 64 * h;
       soff[h] = (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4));
     }
-    // neighbour ids of the first tile
-    int32_t nbr_next[2];
+    // neighbour ids (and target nodes) of the first tile
+    int32_t nbr_next[2], node_next[2];
     {
       const int64_t tile = blockIdx.x;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const int r = r0 + 64 * h;
-        const int64_t node = tile * NPT + r / KP;
-        nbr_next[h] = (tile < p.num_tiles && node < p.N)
-                          ? __ldg(p.ell + node * p.ell_stride + (r % KP)) : -1;
+        const int64_t grp = tile * NPT + r / KP;
+        const bool ok = tile < num_tiles && grp < num_groups;
+        nbr_next[h] = ok ? __ldg(p.ell + grp * KP + (r % KP)) : -1;
+        node_next[h] = ok ? (p.group_node ? __ldg(p.group_node + grp) : (int32_t)grp) : 0;
       }
     }
     uint32_t g = 0;
-    for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-      const __nv_bfloat16* pp[2];
-      const __nv_bfloat16* qp[2];
+    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const __half* pp[2];
+      const __half* qp[2];
       bool valid[2];
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        const int r = r0 + 64 * h;
-        const int64_t node = tile * NPT + r / KP;
         const int32_t j = nbr_next[h];
         valid[h] = j >= 0;
-        pp[h] = p.pq + (valid[h] ? node : 0) * p.ldpq + c * 8;
+        pp[h] = p.pq + (int64_t)(valid[h] ? node_next[h] : 0) * p.ldpq + c * 8;
         qp[h] = p.pq + (int64_t)(valid[h] ? j : 0) * p.ldpq + p.Kp + c * 8;
       }
       // prefetch the neighbour ids of this CTA's next tile
@@ -188,9 +227,10 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int r = r0 + 64 * h;
-          const int64_t node = nt * NPT + r / KP;
-          nbr_next[h] = (nt < p.num_tiles && node < p.N)
-                            ? __ldg(p.ell + node * p.ell_stride + (r % KP)) : -1;
+          const int64_t grp = nt * NPT + r / KP;
+          const bool ok = nt < num_tiles && grp < num_groups;
+          nbr_next[h] = ok ? __ldg(p.ell + grp * KP + (r % KP)) : -1;
+          node_next[h] = ok ? (p.group_node ? __ldg(p.group_node + grp) : (int32_t)grp) : 0;
         }
       }
       // two-deep register pipeline over the K chunks of this tile
@@ -216,10 +256,10 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
             const uint4 P = half == 0 ? pa[h] : pb[h];
             const uint4 Q = half == 0 ? qa[h] : qb[h];
             uint4 H;
-            H.x = relu_add_bf16x2(P.x, Q.x);
-            H.y = relu_add_bf16x2(P.y, Q.y);
-            H.z = relu_add_bf16x2(P.z, Q.z);
-            H.w = relu_add_bf16x2(P.w, Q.w);
+            H.x = relu_add_f16x2(P.x, Q.x);
+            H.y = relu_add_f16x2(P.y, Q.y);
+            H.z = relu_add_f16x2(P.z, Q.z);
+            H.w = relu_add_f16x2(P.w, Q.w);
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(base + soff[h]),
                          "r"(H.x), "r"(H.y), "r"(H.z), "r"(H.w)
                          : "memory");
@@ -248,11 +288,13 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
     constexpr int CPL = 32 / KP;               // columns per lane after the reduce-scatter
     const int coloff = (lane & (KP - 1)) * CPL;
     uint32_t it = 0;
-    for (int64_t tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const uint32_t buf = it & 1;
       mbar_wait(&bars->tmem_full[buf], (it >> 1) & 1);
       tc_fence_after();
-      const int64_t node = tile * NPT + (q * 32 + lane) / KP;
+      const int64_t grp = tile * NPT + (q * 32 + lane) / KP;
+      const bool grp_ok = grp < num_groups;
+      const int64_t node = grp_ok ? (p.group_node ? (int64_t)__ldg(p.group_node + grp) : grp) : 0;
 #pragma unroll 1
       for (int cc = 0; cc < 4; ++cc) {
         const int c0 = chalf * 128 + cc * 32;
@@ -276,20 +318,44 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
             }
           }
         }
-        if (node < p.N) {
+        const bool f16 = p.out_f16 != 0;
+        if (grp_ok && p.accumulate) {
           const int col = c0 + coloff;
-          __nv_bfloat16* dst = p.out + node * p.ldo + col;
+          uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + node * p.ldo + col;
+#pragma unroll
+          for (int i = 0; i < CPL; i += 2) {
+            if (CPL >= 2 && col + i + 2 <= p.b) {
+              red_add2_16(dst + i, v[i], v[i + 1 < CPL ? i + 1 : i], f16);
+            } else {
+              if (col + i < p.b) red_add1_16(dst + i, v[i], f16);
+              if (i + 1 < CPL && col + i + 1 < p.b)
+                red_add1_16(dst + i + 1, v[i + 1 < CPL ? i + 1 : i], f16);
+            }
+          }
+          if (p.coords != nullptr) {
+#pragma unroll
+            for (int i = 0; i < CPL; ++i) {
+              const int cidx = col + i;
+              const uint32_t word = p.coord_mask[cidx >> 5];
+              if (cidx < p.b && ((word >> (cidx & 31)) & 1u)) {
+                int rank = __popc(word & ((1u << (cidx & 31)) - 1u));
+                for (int w = 0; w < (cidx >> 5); ++w) rank += __popc(p.coord_mask[w]);
+                atomicAdd(p.coords + node * p.ncoord + rank, v[i]);
+              }
+            }
+          }
+        } else if (grp_ok) {
+          const int col = c0 + coloff;
+          uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + node * p.ldo + col;
           if (CPL == 4 && col + 4 <= p.b) {
-            __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]);
-            __nv_bfloat162 hi = __floats2bfloat162_rn(v[2], v[3]);
             uint2 u;
-            u.x = *reinterpret_cast<uint32_t*>(&lo);
-            u.y = *reinterpret_cast<uint32_t*>(&hi);
+            u.x = pack2_16(v[0], v[1], f16);
+            u.y = pack2_16(v[2], v[3], f16);
             *reinterpret_cast<uint2*>(dst) = u;
           } else {
 #pragma unroll
             for (int i = 0; i < CPL; ++i)
-              if (col + i < p.b) dst[i] = __float2bfloat16_rn(v[i]);
+              if (col + i < p.b) dst[i] = pack1_16(v[i], f16);
           }
           if (p.coords != nullptr) {
 #pragma unroll
@@ -315,52 +381,15 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
   if (warp == 0) tmem_dealloc<512>(tmem_base);
 }
 
-struct CoordMask {
-  uint32_t w[8];
-};
-
-// In-edges beyond the KP slots of the main kernel: one CTA walks 8 nodes; for a node with
-// deg > KP every extra edge adds ReLU(W2 ReLU(P_i + Q_j) + b2) (same bf16 operands, fp32
-// accumulate) to the stored row.  W2T is [Kp, ldw] bf16 (k-major, the bias rows included).
-__global__ void __launch_bounds__(256) edge_overflow_kernel(
-    const __nv_bfloat16* __restrict__ pq, int64_t ldpq, int Kp, GraphView g, int KP, int64_t N,
-    const __nv_bfloat16* __restrict__ W2T, int ldw, int b, __nv_bfloat16* __restrict__ out,
-    int64_t ldo, float* __restrict__ coords, int ncoord, const CoordMask cm) {
-  __shared__ float h[EK_MAX_CHUNKS * EK_KCH];
-  __shared__ uint32_t cmask[8];
-  if (threadIdx.x < 8) cmask[threadIdx.x] = cm.w[threadIdx.x];
-  for (int64_t i = (int64_t)blockIdx.x * 8; i < (int64_t)blockIdx.x * 8 + 8 && i < N; ++i) {
-    int64_t start;
-    int cnt;
-    graph_row(g, i, start, cnt);
-    for (int s = KP; s < cnt; ++s) {
-      const int64_t j = g.col[start + s];
-      __syncthreads();
-      for (int k = threadIdx.x; k < Kp; k += 256) {
-        const __nv_bfloat16 hv = __hmax(__hadd(pq[i * ldpq + k], pq[j * ldpq + Kp + k]),
-                                        __float2bfloat16_rn(0.f));
-        h[k] = __bfloat162float(hv);
-      }
-      __syncthreads();
-      const int n = threadIdx.x;
-      if (n < b) {
-        float acc = 0.f;
-        for (int k = 0; k < Kp; ++k) acc = fmaf(h[k], __bfloat162float(W2T[(int64_t)k * ldw + n]), acc);
-        acc = fmaxf(acc, 0.f);
-        const float cur = __bfloat162float(out[i * ldo + n]);
-        out[i * ldo + n] = __float2bfloat16_rn(cur + acc);
-        if (coords != nullptr && ((cmask[n >> 5] >> (n & 31)) & 1u)) {
-          int rank = __popc(cmask[n >> 5] & ((1u << (n & 31)) - 1u));
-          for (int w = 0; w < (n >> 5); ++w) rank += __popc(cmask[w]);
-          coords[i * ncoord + rank] += acc;
-        }
-      }
-    }
-  }
-}
-
-// CSR / ELL graph -> dense ELL with exactly KP slots per node (-1 padded) for the main kernel
-__global__ void graph_to_ell_kernel(GraphView g, int64_t N, int KP, int32_t* __restrict__ ell) {
+// Graph (CSR or ELL) -> the group lists the main kernel consumes:
+//   ell[N, KP]            slots 0..KP-1 of every node (-1 padded)          (pass 1, group = node)
+//   ovf_node[], ovf_ell[] one entry per further block of KP in-edges of a node  (pass 2)
+// ovf_count is a device counter (zeroed by the caller); entries are appended with atomicAdd,
+// their order does not affect the result (pass 2 accumulates with red.add).
+__global__ void graph_to_groups_kernel(GraphView g, int64_t N, int KP, int32_t* __restrict__ ell,
+                                       int32_t* __restrict__ ovf_node,
+                                       int32_t* __restrict__ ovf_ell,
+                                       int32_t* __restrict__ ovf_count, int64_t ovf_cap) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= N * KP) return;
   const int64_t i = idx / KP;
@@ -369,6 +398,18 @@ __global__ void graph_to_ell_kernel(GraphView g, int64_t N, int KP, int32_t* __r
   int cnt;
   graph_row(g, i, start, cnt);
   ell[idx] = s < cnt ? g.col[start + s] : -1;
+  if (s == 0 && cnt > KP) {
+    const int extra = (cnt - 1) / KP;  // further blocks of KP edges
+    const int base = atomicAdd(ovf_count, extra);
+    for (int e = 0; e < extra; ++e) {
+      if (base + e >= ovf_cap) break;  // cannot happen when the caller sized the scratch right
+      ovf_node[base + e] = (int32_t)i;
+      for (int t = 0; t < KP; ++t) {
+        const int slot = (e + 1) * KP + t;
+        ovf_ell[(int64_t)(base + e) * KP + t] = slot < cnt ? g.col[start + slot] : -1;
+      }
+    }
+  }
 }
 
 }  // namespace tc
@@ -376,16 +417,27 @@ __global__ void graph_to_ell_kernel(GraphView g, int64_t N, int KP, int32_t* __r
 
 using namespace gn;
 
-extern "C" size_t gn_tc_edge_scratch_bytes(int64_t N, int slots) {
-  return (size_t)(N > 0 ? N : 1) * (size_t)slots * sizeof(int32_t);
+static int64_t edge_overflow_cap(const gn_graph* graph, int64_t N, int slots) {
+  if (graph->ell_stride > 0) return N * ((graph->ell_stride + slots - 1) / slots - 1);
+  return graph->num_edges / slots + 1;
+}
+
+extern "C" size_t gn_tc_edge_scratch_bytes(const gn_graph* graph, int64_t N, int slots) {
+  if (!graph || slots <= 0) return 0;
+  const int64_t n = N > 0 ? N : 1;
+  const int64_t cap = edge_overflow_cap(graph, n, slots);
+  // ell [N, slots] + ovf_ell [cap, slots] + ovf_node [cap] + counter (16-byte padded)
+  return (size_t)(n * slots + cap * slots + cap + 4) * sizeof(int32_t);
 }
 
 extern "C" int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp,
                                         const gn_graph* graph, int64_t N, int slots,
-                                        const void* W2p, const void* W2Tp, int b, void* out,
-                                        int64_t ldo, float* coords, const int32_t* coord_cols,
-                                        int ncoord, void* scratch, size_t scratch_bytes,
-                                        void* stream) {
+                                        const void* W2p, int b, void* out, int64_t ldo,
+                                        int out_dtype, float* coords,
+                                        const int32_t* coord_cols, int ncoord, void* scratch,
+                                        size_t scratch_bytes, void* stream) {
+  GN_CHECK_ARG(out_dtype == GN_BF16 || out_dtype == GN_F16,
+               "gn_tc_edge_mlp_aggregate: out_dtype must be GN_BF16 or GN_F16");
   GN_CHECK_ARG(N >= 0 && b >= 1 && b <= 256, "gn_tc_edge_mlp_aggregate: b=%d not in [1,256]", b);
   GN_CHECK_ARG(Kp >= 32 && Kp % 32 == 0 && Kp <= tc::EK_MAX_CHUNKS * tc::EK_KCH,
                "gn_tc_edge_mlp_aggregate: padded hidden width %d not a multiple of 32 in [32,%d]",
@@ -396,11 +448,12 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp,
                "gn_tc_edge_mlp_aggregate: bad leading dimensions");
   GN_CHECK_ARG(ncoord >= 0 && ncoord <= 16, "gn_tc_edge_mlp_aggregate: ncoord=%d", ncoord);
   if (N == 0) return GN_OK;
-  GN_CHECK_ARG(pq && W2p && W2Tp && out && scratch, "gn_tc_edge_mlp_aggregate: null pointer");
-  GN_CHECK_ARG(scratch_bytes >= gn_tc_edge_scratch_bytes(N, slots),
+  GN_CHECK_ARG(pq && W2p && out && scratch && graph, "gn_tc_edge_mlp_aggregate: null pointer");
+  GN_CHECK_ARG(scratch_bytes >= gn_tc_edge_scratch_bytes(graph, N, slots),
                "gn_tc_edge_mlp_aggregate: scratch too small");
   GN_CHECK_ARG((reinterpret_cast<uintptr_t>(pq) & 15) == 0 &&
-               (reinterpret_cast<uintptr_t>(out) & 7) == 0,
+               (reinterpret_cast<uintptr_t>(out) & 7) == 0 &&
+               (reinterpret_cast<uintptr_t>(scratch) & 3) == 0,
                "gn_tc_edge_mlp_aggregate: pq must be 16-byte and out 8-byte aligned");
   GraphView g;
   int rc = make_graph_view(graph, &g);
@@ -417,55 +470,68 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp,
                  "gn_tc_edge_mlp_aggregate: coordinate columns must be strictly increasing");
     p.coord_mask[coord_cols[t] >> 5] |= 1u << (coord_cols[t] & 31);
   }
-
+  const int64_t cap = edge_overflow_cap(graph, N, slots);
   int32_t* ell = reinterpret_cast<int32_t*>(scratch);
-  tc::CoordMask cm;
-  tc::graph_to_ell_kernel<<<(unsigned)ceil_div(N * slots, 256), 256, 0, st>>>(g, N, slots, ell);
+  int32_t* ovf_ell = ell + N * slots;
+  int32_t* ovf_node = ovf_ell + cap * slots;
+  int32_t* ovf_count = ovf_node + cap;
+  GN_CUDA(cudaMemsetAsync(ovf_count, 0, sizeof(int32_t), st));
+  tc::graph_to_groups_kernel<<<(unsigned)ceil_div(N * slots, 256), 256, 0, st>>>(
+      g, N, slots, ell, ovf_node, ovf_ell, ovf_count, cap);
   GN_LAUNCH_CHECK();
 
   CUtensorMap tmW2;
-  rc = make_tmap_bf16_2d(&tmW2, W2p, (uint64_t)bnp, (uint64_t)Kp, (uint64_t)Kp, (uint32_t)bnp,
-                         tc::EK_KCH, 64);
+  rc = make_tmap_f16_2d(&tmW2, W2p, (uint64_t)bnp, (uint64_t)Kp, (uint64_t)Kp, (uint32_t)bnp,
+                        tc::EK_KCH, 64);
   if (rc != GN_OK) return rc;
 
-  p.pq = reinterpret_cast<const __nv_bfloat16*>(pq);
+  p.pq = reinterpret_cast<const __half*>(pq);
   p.ldpq = ldpq;
   p.Kp = Kp;
   p.nch = Kp / tc::EK_KCH;
-  p.ell = ell;
-  p.ell_stride = slots;
   p.N = N;
   p.bnp = bnp;
   p.b = b;
-  p.out = reinterpret_cast<__nv_bfloat16*>(out);
+  p.out = out;
+  p.out_f16 = out_dtype == GN_F16;
   p.ldo = ldo;
   p.coords = ncoord > 0 ? coords : nullptr;
   p.ncoord = ncoord;
   const int npt = tc::EK_ROWS / slots;
-  p.num_tiles = ceil_div(N, npt);
 
   int dev = 0, sms = 0;
   GN_CUDA(cudaGetDevice(&dev));
   GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const size_t smem = (size_t)p.nch * bnp * 64 + tc::EK_STAGES * tc::EK_STAGE_BYTES +
                       sizeof(tc::EdgeBarriers) + 1024;
-  const unsigned grid = (unsigned)(p.num_tiles < sms ? p.num_tiles : sms);
+  for (int pass = 0; pass < 2; ++pass) {
+    int64_t max_tiles;
+    if (pass == 0) {
+      p.ell = ell;
+      p.group_node = nullptr;
+      p.group_count = nullptr;
+      p.accumulate = 0;
+      max_tiles = ceil_div(N, npt);
+    } else {
+      if (cap <= 0) break;
+      p.ell = ovf_ell;
+      p.group_node = ovf_node;
+      p.group_count = ovf_count;
+      p.accumulate = 1;
+      max_tiles = ceil_div(cap, npt);
+    }
+    const unsigned grid = (unsigned)(max_tiles < sms ? max_tiles : sms);
 #define GN_EDGE_CASE(KP_)                                                                        \
   {                                                                                              \
     auto kern = tc::edge_mlp_aggregate_kernel<KP_>;                                              \
     GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, tc::EK_THREADS, smem, st>>>(tmW2, p);                                           \
   }
-  if (slots == 8) GN_EDGE_CASE(8)
-  else if (slots == 16) GN_EDGE_CASE(16)
-  else GN_EDGE_CASE(32)
+    if (slots == 8) GN_EDGE_CASE(8)
+    else if (slots == 16) GN_EDGE_CASE(16)
+    else GN_EDGE_CASE(32)
 #undef GN_EDGE_CASE
-  GN_LAUNCH_CHECK();
-
-  memcpy(cm.w, p.coord_mask, sizeof(cm.w));
-  tc::edge_overflow_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, st>>>(
-      p.pq, ldpq, Kp, g, slots, N, reinterpret_cast<const __nv_bfloat16*>(W2Tp), bnp, b, p.out, ldo,
-      p.coords, ncoord, cm);
-  GN_LAUNCH_CHECK();
+    GN_LAUNCH_CHECK();
+  }
   return GN_OK;
 }

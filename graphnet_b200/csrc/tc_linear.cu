@@ -6,16 +6,20 @@
 // EdgeConv MLP (PQ = x [W1a-W1b ; W1b]^T, reference dynedge.py:193-204 via layers.py:67) and
 // the post-processing MLP (dynedge.py:222-232, 332).
 //
-// One CTA computes one 128 x BN output tile.  Warp roles: warp 0 = TMA producer, warp 1 =
-// tcgen05.mma issuer (also owns the TMEM allocation), warps 2-5 = epilogue (one TMEM lane
-// quadrant each).  A/W tiles travel as 128B-swizzled 64-column boxes through a 4-stage
-// mbarrier ring; rows/columns beyond M, N, K are zero-filled by the TMA unit.
+// Persistent kernel, one CTA per SM walking 128 x BN output tiles.  Warp roles: warp 0 = TMA
+// producer, warp 1 = tcgen05.mma issuer (owns the TMEM allocation: two 256-column fp32
+// accumulators, so the epilogue of tile i overlaps the main loop of tile i+1), warps 2-5 =
+// epilogue (one TMEM lane quadrant each).  A/W tiles travel as 128B-swizzled 64-column boxes
+// through a 4-stage mbarrier ring; rows/columns beyond M, N, K are zero-filled by the TMA unit.
+#include <cuda_fp16.h>
+
 #include "tc_common.cuh"
 
 namespace gn {
 
-int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
-                      uint64_t ld, uint32_t box_rows, uint32_t box_cols, int swizzle_bytes) {
+static int make_tmap_16bit_2d(CUtensorMap* map, CUtensorMapDataType dt, const void* base,
+                              uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                              uint32_t box_cols, int swizzle_bytes) {
   typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -44,7 +48,7 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_
                         : swizzle_bytes == 64  ? CU_TENSOR_MAP_SWIZZLE_64B
                         : swizzle_bytes == 32  ? CU_TENSOR_MAP_SWIZZLE_32B
                                                : CU_TENSOR_MAP_SWIZZLE_NONE;
-  CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims,
+  CUresult r = encode(map, dt, 2, const_cast<void*>(base), dims,
                       strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                       CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -56,6 +60,17 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_
   return GN_OK;
 }
 
+int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
+                      uint64_t ld, uint32_t box_rows, uint32_t box_cols, int swizzle_bytes) {
+  return make_tmap_16bit_2d(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, base, rows, cols, ld, box_rows,
+                            box_cols, swizzle_bytes);
+}
+int make_tmap_f16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
+                     uint64_t ld, uint32_t box_rows, uint32_t box_cols, int swizzle_bytes) {
+  return make_tmap_16bit_2d(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, base, rows, cols, ld, box_rows,
+                            box_cols, swizzle_bytes);
+}
+
 namespace tc {
 
 constexpr int LIN_BM = 128;
@@ -64,10 +79,13 @@ constexpr int LIN_STAGES = 4;
 constexpr int LIN_THREADS = 192;  // 6 warps
 constexpr int LIN_A_BYTES = LIN_BM * LIN_BK * 2;  // 16 KB
 
+constexpr int LIN_EPI_WARPS = 4;
+
 struct __align__(8) LinBarriers {
   uint64_t full[LIN_STAGES];
   uint64_t empty[LIN_STAGES];
-  uint64_t tmem_full;
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
   uint32_t tmem_base;
 };
 
@@ -110,11 +128,38 @@ __device__ __forceinline__ void store_row32<__nv_bfloat16>(__nv_bfloat16* dst, c
   }
 }
 
+// fp16 output, saturated to the finite range (feeds the fp16 hidden layer of the edge kernel)
+template <>
+__device__ __forceinline__ void store_row32<__half>(__half* dst, const float (&v)[32], int nvalid) {
+  float c[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) c[j] = fminf(fmaxf(v[j], -65504.f), 65504.f);
+  if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+      __half2 p0 = __floats2half2_rn(c[j], c[j + 1]);
+      __half2 p1 = __floats2half2_rn(c[j + 2], c[j + 3]);
+      __half2 p2 = __floats2half2_rn(c[j + 4], c[j + 5]);
+      __half2 p3 = __floats2half2_rn(c[j + 6], c[j + 7]);
+      uint4 u;
+      u.x = *reinterpret_cast<uint32_t*>(&p0);
+      u.y = *reinterpret_cast<uint32_t*>(&p1);
+      u.z = *reinterpret_cast<uint32_t*>(&p2);
+      u.w = *reinterpret_cast<uint32_t*>(&p3);
+      *reinterpret_cast<uint4*>(dst + j) = u;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < nvalid) dst[j] = __float2half_rn(c[j]);
+  }
+}
+
 template <typename OutT, int ACT>
 __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
-    int BN) {
+    int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -124,8 +169,6 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
   LinBarriers* bars = reinterpret_cast<LinBarriers*>(smem + LIN_STAGES * stage_bytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t m0 = (int64_t)blockIdx.x * LIN_BM;
-  const int n0 = blockIdx.y * BN;
   const int nk = (K + LIN_BK - 1) / LIN_BK;
 
   if (warp == 0 && lane == 0) {
@@ -136,87 +179,120 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
       mbar_init(&bars->full[s], 1);
       mbar_init(&bars->empty[s], 1);
     }
-    mbar_init(&bars->tmem_full, 1);
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&bars->tmem_full[b], 1);
+      mbar_init(&bars->tmem_empty[b], LIN_EPI_WARPS);
+    }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc<256>(&bars->tmem_base);
+  if (warp == 1) tmem_alloc<512>(&bars->tmem_base);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_d = bars->tmem_base;
+  const uint32_t tmem_base = bars->tmem_base;
 
+  // Persistent: this CTA walks tiles blockIdx.x, +gridDim.x, ...; consecutive tile ids share the
+  // A row block (n fastest), so concurrently running CTAs hit the same A tile in L2.
   if (warp == 0) {
     // ---------------------------------------------------------- TMA producer
     if (elect_one()) {
-      for (int kb = 0; kb < nk; ++kb) {
-        const int s = kb % LIN_STAGES;
-        mbar_wait(&bars->empty[s], ((kb / LIN_STAGES) & 1) ^ 1);
-        uint8_t* a_dst = smem + s * stage_bytes;
-        uint8_t* b_dst = a_dst + LIN_A_BYTES;
-        mbar_arrive_expect_tx(&bars->full[s], (uint32_t)stage_bytes);
-        tma_load_2d(a_dst, &tmA, &bars->full[s], kb * LIN_BK, (int32_t)m0);
-        tma_load_2d(b_dst, &tmW, &bars->full[s], kb * LIN_BK, n0);
+      uint32_t g = 0;
+      for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int32_t m0 = (int32_t)((t / num_n_tiles) * LIN_BM);
+        const int32_t n0 = (int32_t)(t % num_n_tiles) * BN;
+        for (int kb = 0; kb < nk; ++kb, ++g) {
+          const uint32_t s = g % LIN_STAGES;
+          mbar_wait(&bars->empty[s], ((g / LIN_STAGES) & 1) ^ 1);
+          uint8_t* a_dst = smem + s * stage_bytes;
+          uint8_t* b_dst = a_dst + LIN_A_BYTES;
+          mbar_arrive_expect_tx(&bars->full[s], (uint32_t)stage_bytes);
+          tma_load_2d(a_dst, &tmA, &bars->full[s], kb * LIN_BK, m0);
+          tma_load_2d(b_dst, &tmW, &bars->full[s], kb * LIN_BK, n0);
+        }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    const uint32_t idesc = make_idesc_bf16(LIN_BM, BN);
-    for (int kb = 0; kb < nk; ++kb) {
-      const int s = kb % LIN_STAGES;
-      mbar_wait(&bars->full[s], (kb / LIN_STAGES) & 1);
+    uint32_t g = 0, it = 0;
+    for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      const uint32_t buf = it & 1;
+      mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
       tc_fence_after();
-      if (elect_one()) {
-        const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
-        const uint32_t b_addr = a_addr + LIN_A_BYTES;
-        const uint64_t adesc = make_kmajor_desc<128>(a_addr);
-        const uint64_t bdesc = make_kmajor_desc<128>(b_addr);
+      const uint32_t tmem_d = tmem_base + buf * 256;
+      for (int kb = 0; kb < nk; ++kb, ++g) {
+        const uint32_t s = g % LIN_STAGES;
+        mbar_wait(&bars->full[s], (g / LIN_STAGES) & 1);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
+          const uint32_t b_addr = a_addr + LIN_A_BYTES;
+          const uint64_t adesc = make_kmajor_desc<128>(a_addr);
+          const uint64_t bdesc = make_kmajor_desc<128>(b_addr);
 #pragma unroll
-        for (int k4 = 0; k4 < LIN_BK / 16; ++k4) {
-          // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4) units
-          mma_bf16_ss(tmem_d, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc,
-                      (kb | k4) != 0);
+          for (int k4 = 0; k4 < LIN_BK / 16; ++k4) {
+            // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4) units
+            mma_bf16_ss(tmem_d, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc,
+                        (kb | k4) != 0);
+          }
+          mma_commit(&bars->empty[s]);
+          if (kb == nk - 1) mma_commit(&bars->tmem_full[buf]);
         }
-        mma_commit(&bars->empty[s]);
-        if (kb == nk - 1) mma_commit(&bars->tmem_full);
+        __syncwarp();
       }
-      __syncwarp();
     }
   } else {
     // -------------------------------------------------------------- epilogue
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
-    mbar_wait(&bars->tmem_full, 0);
-    tc_fence_after();
-    const int64_t row = m0 + q * 32 + lane;
-    for (int c = 0; c < BN; c += 32) {
-      float v[32];
-      tmem_ld_32x32(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-      const int n = n0 + c;
-      if (n >= N) break;
+    uint32_t it = 0;
+    for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      const uint32_t buf = it & 1;
+      const int64_t m0 = (t / num_n_tiles) * LIN_BM;
+      const int n0 = (int)(t % num_n_tiles) * BN;
+      mbar_wait(&bars->tmem_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const int64_t row = m0 + q * 32 + lane;
+      for (int c = 0; c < BN; c += 32) {
+        const int n = n0 + c;
+        if (n >= N) break;
+        float v[32];
+        tmem_ld_32x32(tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float b = (bias != nullptr && n + j < N) ? bias[n + j] : 0.f;
-        v[j] = activate<ACT>(v[j] + b);
+        for (int j = 0; j < 32; ++j) {
+          const float b = (bias != nullptr && n + j < N) ? __ldg(bias + n + j) : 0.f;
+          v[j] = activate<ACT>(v[j] + b);
+        }
+        if (row < M) store_row32<OutT>(C + row * ldc + n, v, min(N - n, BN - c));
       }
-      if (row < M) store_row32<OutT>(C + row * ldc + n, v, min(N - n, BN - c));
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<256>(tmem_d);
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
 template <typename OutT>
 static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, const float* bias,
                             void* C, int64_t ldc, int64_t M, int N, int K, int BN, int act,
-                            cudaStream_t st) {
+                            int ab_dtype, cudaStream_t st) {
+  const uint32_t idesc =
+      ab_dtype == GN_F16 ? make_idesc_f16(LIN_BM, BN) : make_idesc_bf16(LIN_BM, BN);
   const size_t smem = (size_t)LIN_STAGES * (LIN_A_BYTES + BN * LIN_BK * 2) + sizeof(LinBarriers) + 1024;
-  dim3 grid((unsigned)ceil_div(M, LIN_BM), (unsigned)ceil_div(N, BN));
+  const int num_n_tiles = (int)ceil_div(N, BN);
+  const int64_t num_tiles = ceil_div(M, LIN_BM) * num_n_tiles;
+  int dev = 0, sms = 0;
+  GN_CUDA(cudaGetDevice(&dev));
+  GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const unsigned grid = (unsigned)(num_tiles < sms ? num_tiles : sms);
 #define GN_TC_LIN_CASE(A_)                                                                      \
   {                                                                                             \
     auto kern = tc_linear_kernel<OutT, A_>;                                                     \
     GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, LIN_THREADS, smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
-                                          K, BN);                                               \
+                                          K, BN, num_n_tiles, num_tiles, idesc);                       \
   }
   switch (act) {
     case GN_ACT_NONE: GN_TC_LIN_CASE(ACT_NONE) break;
@@ -246,24 +322,28 @@ int tc_pick_bn(int N) {
 
 using namespace gn;
 
-extern "C" int gn_tc_linear_bf16(const void* A, int64_t lda, const void* W, int64_t ldw,
-                                 const float* bias, void* C, int64_t ldc, int c_dtype, int64_t M,
-                                 int N, int K, int act, void* stream) {
+extern "C" int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t ldw, int ab_dtype,
+                            const float* bias, void* C, int64_t ldc, int c_dtype, int64_t M,
+                            int N, int K, int act, void* stream) {
   GN_CHECK_ARG(M >= 0 && N >= 1 && K >= 1 && lda >= K && ldw >= K && ldc >= N,
-               "gn_tc_linear_bf16: bad sizes");
+               "gn_tc_linear: bad sizes");
   if (M == 0) return GN_OK;
-  GN_CHECK_ARG(A && W && C, "gn_tc_linear_bf16: null pointer");
-  GN_CHECK_ARG(c_dtype == GN_F32 || c_dtype == GN_BF16, "gn_tc_linear_bf16: bad c_dtype");
+  GN_CHECK_ARG(A && W && C, "gn_tc_linear: null pointer");
+  GN_CHECK_ARG(ab_dtype == GN_BF16 || ab_dtype == GN_F16, "gn_tc_linear: bad ab_dtype");
+  GN_CHECK_ARG(c_dtype == GN_F32 || c_dtype == GN_BF16 || c_dtype == GN_F16,
+               "gn_tc_linear: bad c_dtype");
   const int BN = tc_pick_bn(N);
   CUtensorMap tmA, tmW;
-  int rc = make_tmap_bf16_2d(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, tc::LIN_BM,
-                             tc::LIN_BK, 128);
+  auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
+  int rc = mk(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, tc::LIN_BM, tc::LIN_BK, 128);
   if (rc != GN_OK) return rc;
-  rc = make_tmap_bf16_2d(&tmW, W, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)BN,
-                         tc::LIN_BK, 128);
+  rc = mk(&tmW, W, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)BN, tc::LIN_BK, 128);
   if (rc != GN_OK) return rc;
   cudaStream_t st = as_stream(stream);
   if (c_dtype == GN_F32)
-    return tc::launch_tc_linear<float>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, st);
-  return tc::launch_tc_linear<__nv_bfloat16>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, st);
+    return tc::launch_tc_linear<float>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype, st);
+  if (c_dtype == GN_F16)
+    return tc::launch_tc_linear<__half>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype, st);
+  return tc::launch_tc_linear<__nv_bfloat16>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype,
+                                             st);
 }

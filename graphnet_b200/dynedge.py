@@ -148,8 +148,8 @@ class DynEdge(torch.nn.Module):
 
     Same constructor arguments, parameter names and output as the reference.
     `precision` is the one addition: "fp32" (default; FFMA kernels, outputs
-    within 1e-4 relative of the reference) or "bf16" (tcgen05 tensor-core
-    kernels, 2e-2).
+    within 1e-4 relative of the reference), or "bf16" / "fp16" (tcgen05
+    tensor-core kernels with bf16 / fp16 activations, 2e-2).
     """
 
     def __init__(
@@ -218,8 +218,8 @@ class DynEdge(torch.nn.Module):
             activation = torch.nn.GELU()
         else:
             raise ValueError(f"Activation layer {activation_layer} not supported.")
-        if precision not in ("fp32", "bf16"):
-            raise ValueError(f"precision {precision!r} not supported (fp32 | bf16)")
+        if precision not in ("fp32", "bf16", "fp16"):
+            raise ValueError(f"precision {precision!r} not supported (fp32 | bf16 | fp16)")
 
         self._activation = activation
         self._nb_inputs = nb_inputs
@@ -320,9 +320,10 @@ class DynEdge(torch.nn.Module):
         return out
 
     validate_inputs: bool = True
+    _last_flags: Optional[Tensor] = None
 
     def _dispatch(self, data: Any, edge_index: Optional[Tensor]) -> Tensor:
-        if self.precision == "bf16":
+        if self.precision in ("bf16", "fp16"):
             from .dynedge_bf16 import forward_bf16
             return forward_bf16(self, data, edge_index)
         return self._forward_f32(data, edge_index=edge_index)

@@ -1,9 +1,15 @@
-"""bf16 tensor-core forward of DynEdge (tcgen05 / TMEM / TMA kernels).
+"""16-bit tensor-core forward of DynEdge (tcgen05 / TMEM / TMA kernels).
 
 Same computation as `DynEdge._forward_f32` (reference dynedge.py:296-350) with
-bf16 GEMM operands and fp32 accumulation / aggregation; outputs agree with the
-fp32 reference within 2e-2 relative (BASELINE.json north_star).  Weight
-repacking (padding, bf16 conversion, bias folding) happens once per parameter
+16-bit GEMM operands and fp32 accumulation / aggregation; outputs agree with the
+fp32 reference within 2e-2 relative (BASELINE.json north_star).
+
+precision="bf16": layer inputs/outputs (the skip-cat buffer) and the node-GEMM /
+post-processing weights are bf16; precision="fp16": the same tensors are IEEE
+fp16 (3 more mantissa bits, conversions saturate at +-65504).  In both modes the
+raw input features enter the first EdgeConv in fp32 (K = 2F+5 is tiny) and the
+hidden layer of every EdgeConv MLP (P, Q, h, W2) is fp16 - see csrc/tc_edge.cu.
+Weight repacking (padding, conversion, bias folding) happens once per parameter
 version on the device with torch ops - plumbing, not the timed path.
 """
 
@@ -32,7 +38,8 @@ def _slots(k: int) -> int:
 class _ConvPack:
     """Repacked weights of one DynEdgeConv MLP for the tensor-core kernels."""
 
-    def __init__(self, l1: torch.nn.Linear, l2: torch.nn.Linear):
+    def __init__(self, l1: torch.nn.Linear, l2: torch.nn.Linear, io_dtype: torch.dtype,
+                 first: bool):
         dev = l1.weight.device
         a, d2 = l1.weight.shape
         d = d2 // 2
@@ -42,7 +49,7 @@ class _ConvPack:
             raise NotImplementedError(
                 f"bf16 EdgeConv kernel supports hidden <= 350 and output <= 256 (got {a}, {b}); "
                 "use precision='fp32' for this architecture")
-        Kd = _round_up(d, 8)
+        Kd = d if first else _round_up(d, 8)
         b16 = _round_up(b, 16)
         W1 = l1.weight.detach().float()
         Wpq = torch.zeros((2 * Kp, Kd), dtype=torch.float32, device=dev)
@@ -54,32 +61,38 @@ class _ConvPack:
         bias[a + 1] = 1.0
         W2p = torch.zeros((b16, Kp), dtype=torch.float32, device=dev)
         W2p[:b, :a] = l2.weight.detach().float()
-        W2p = W2p.to(torch.bfloat16)
+        W2p = W2p.to(torch.float16)  # the hidden layer runs in fp16 (see csrc/tc_edge.cu)
         if l2.bias is not None:
             b2 = l2.bias.detach().float()
-            hi = b2.to(torch.bfloat16)
-            lo = (b2 - hi.float()).to(torch.bfloat16)
+            hi = b2.to(torch.float16)
+            lo = (b2 - hi.float()).to(torch.float16)
             W2p[:b, a] = hi
             W2p[:b, a + 1] = lo
         self.d, self.a, self.b, self.Kp, self.Kd, self.b16 = d, a, b, Kp, Kd, b16
-        self.Wpq = Wpq.to(torch.bfloat16).contiguous()
+        # first layer: fp32 FFMA node GEMM on the fp32 input features; later layers: tcgen05
+        self.first = first
+        self.Wpq = Wpq.contiguous() if first else Wpq.to(io_dtype).contiguous()
         self.bias_pq = bias
         self.W2p = W2p.contiguous()
-        self.W2Tp = W2p.t().contiguous()
 
 
-def _conv_pack(conv) -> _ConvPack:
+def _io_dtype(model) -> torch.dtype:
+    return torch.float16 if model.precision == "fp16" else torch.bfloat16
+
+
+def _conv_pack(conv, io_dtype: torch.dtype, first: bool) -> _ConvPack:
     linears, act = conv._mlp()
     if act != "relu" or len(linears) != 2:
         raise NotImplementedError(
             "precision='bf16' supports Linear-ReLU-Linear-ReLU EdgeConv MLPs; use precision='fp32'")
     if conv.aggr not in ("add", "sum"):
         raise NotImplementedError("precision='bf16' supports aggr='add'; use precision='fp32'")
-    if not hasattr(conv, "_cache_bf16"):
-        conv._cache_bf16 = _WeightCache()
+    key = f"_cache_tc_{io_dtype}_{first}"
+    if not hasattr(conv, key):
+        setattr(conv, key, _WeightCache())
     l1, l2 = linears
     params = [p for p in (l1.weight, l1.bias, l2.weight, l2.bias) if p is not None]
-    return conv._cache_bf16.get(params, lambda: _ConvPack(l1, l2))
+    return getattr(conv, key).get(params, lambda: _ConvPack(l1, l2, io_dtype, first))
 
 
 def _skip_layout(model) -> Tuple[int, List[int], List[int], int]:
@@ -93,9 +106,11 @@ def _skip_layout(model) -> Tuple[int, List[int], List[int], int]:
     return D0, widths, offs, off
 
 
-def _post_pack(model, total: int, D0: int, widths: List[int], offs: List[int]):
-    if not hasattr(model, "_cache_post_bf16"):
-        model._cache_post_bf16 = _WeightCache()
+def _post_pack(model, total: int, D0: int, widths: List[int], offs: List[int],
+               io_dtype: torch.dtype):
+    key = f"_cache_post_{io_dtype}"
+    if not hasattr(model, key):
+        setattr(model, key, _WeightCache())
     linears, act = _parse_mlp(model._post_processing)
     if act != "relu":
         raise NotImplementedError("precision='bf16' supports ReLU; use precision='fp32'")
@@ -120,9 +135,9 @@ def _post_pack(model, total: int, D0: int, widths: List[int], offs: List[int]):
                 Wp = torch.zeros((n, _round_up(k, 8)), dtype=torch.float32, device=dev)
                 Wp[:, :k] = W
             bias = None if lin.bias is None else lin.bias.detach().float().contiguous()
-            packs.append((Wp.to(torch.bfloat16).contiguous(), bias, n, K))
+            packs.append((Wp.to(io_dtype).contiguous(), bias, n, K))
         return packs
-    return model._cache_post_bf16.get(params, build)
+    return getattr(model, key).get(params, build)
 
 
 def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
@@ -132,32 +147,39 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
     dev = x.device
     F = model._nb_inputs
     assert x.shape[1] == F, f"expected {F} input features, got {x.shape[1]}"
+    io = _io_dtype(model)
     D0, widths, offs, total = _skip_layout(model)
     needs_zero = any(w % 8 for w in widths)
-    skip = (torch.zeros if needs_zero else torch.empty)((N, total), dtype=torch.bfloat16, device=dev)
+    skip = (torch.zeros if needs_zero else torch.empty)((N, total), dtype=io, device=dev)
     x0w = offs[0]
     if model._add_global_variables_after_pooling:
         gv = ops.global_variables(x, graph, ptr, n_pulses)
         skip[:, :x0w] = 0
         skip[:, :F] = x
+        x0 = x
     else:
-        gv = ops.global_variables(x, graph, ptr, n_pulses, x0=skip, x0_cols=x0w)
+        x0 = torch.empty((N, D0), dtype=torch.float32, device=dev)
+        gv = ops.global_variables(x, graph, ptr, n_pulses, x0=x0, x0_cols=D0,
+                                  x0b=skip, x0b_cols=x0w)
     inter: Dict[str, Any] = {"global_variables": gv, "graphs": []}
 
     off_in, d_in = 0, D0
     convs = list(model._conv_layers)
     for li, conv in enumerate(convs):
-        pk = _conv_pack(conv)
+        pk = _conv_pack(conv, io, first=(li == 0))
         assert pk.d == d_in
-        pq = torch.empty((N, 2 * pk.Kp), dtype=torch.bfloat16, device=dev)
-        ops.tc_linear_bf16(skip[:, off_in:], pk.Wpq, pk.bias_pq, pq, K=d_in, act="none")
+        pq = torch.empty((N, 2 * pk.Kp), dtype=torch.float16, device=dev)
+        if li == 0:
+            ops.linear_f32(x0, pk.Wpq, pk.bias_pq, act="none", out=pq)
+        else:
+            ops.tc_linear_bf16(skip[:, off_in:], pk.Wpq, pk.bias_pq, pq, K=d_in, act="none")
         last = li + 1 == len(convs)
         need_graph = (not last) or return_intermediates
         cols = sorted(ops._columns(conv.features_subset, pk.b))
         coords = (torch.empty((N, len(cols)), dtype=torch.float32, device=dev)
                   if need_graph else None)
-        ops.tc_edge_mlp_aggregate(pq, pk.Kp, graph, _slots(conv.nb_neighbors), pk.W2p, pk.W2Tp,
-                                  pk.b, skip[:, offs[li]:], coords, cols)
+        ops.tc_edge_mlp_aggregate(pq, pk.Kp, graph, _slots(conv.nb_neighbors), pk.W2p, pk.b,
+                                  skip[:, offs[li]:], coords, cols)
         if need_graph:
             graph = ops.knn_graph_ell(coords, conv.nb_neighbors, ptr, list(range(len(cols))))
             if return_intermediates:
@@ -165,12 +187,12 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
                 inter.setdefault("coords", []).append(coords)
         off_in, d_in = offs[li], pk.b
 
-    packs = _post_pack(model, total, D0, widths, offs)
+    packs = _post_pack(model, total, D0, widths, offs, io)
     h = skip
     for i, (Wp, bias, n, K) in enumerate(packs):
         lastp = i + 1 == len(packs)
         out = torch.empty((N, n if lastp else _round_up(n, 8)),
-                          dtype=torch.float32 if lastp else torch.bfloat16, device=dev)
+                          dtype=torch.float32 if lastp else io, device=dev)
         ops.tc_linear_bf16(h, Wp, bias, out, K=K, act="relu")
         h = out
     inter["post"] = h
@@ -201,17 +223,16 @@ def time_edge_kernel(model, data: Any, flush_buf: Tensor, layer: int = 1, reps: 
     x, n_pulses, ptr, graph, N, B = model._graph_inputs(data, None)
     dev = x.device
     conv = model._conv_layers[layer]
-    pk = _conv_pack(conv)
+    pk = _conv_pack(conv, _io_dtype(model), first=(layer == 0))
     g = torch.Generator(device=dev).manual_seed(0)
-    pq = (torch.randn((N, 2 * pk.Kp), generator=g, device=dev) * 0.5).to(torch.bfloat16)
-    out = torch.empty((N, pk.b), dtype=torch.bfloat16, device=dev)
+    pq = (torch.randn((N, 2 * pk.Kp), generator=g, device=dev) * 0.5).to(torch.float16)
+    out = torch.empty((N, pk.b), dtype=_io_dtype(model), device=dev)
     coords = torch.empty((N, 3), dtype=torch.float32, device=dev)
     ell = ops.knn_graph_ell(x, conv.nb_neighbors, ptr, [0, 1, 2])
     slots = _slots(conv.nb_neighbors)
 
     def run():
-        ops.tc_edge_mlp_aggregate(pq, pk.Kp, ell, slots, pk.W2p, pk.W2Tp, pk.b, out, coords,
-                                  [0, 1, 2])
+        ops.tc_edge_mlp_aggregate(pq, pk.Kp, ell, slots, pk.W2p, pk.b, out, coords, [0, 1, 2])
     for _ in range(3):
         run()
     s = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
@@ -225,6 +246,6 @@ def time_edge_kernel(model, data: Any, flush_buf: Tensor, layer: int = 1, reps: 
     ms = sum(a.elapsed_time(b_) for a, b_ in zip(s, e)) / reps
     E = int(ell.deg.sum().item())
     executed = 2.0 * (N * slots) * pk.Kp * pk.b16
-    name = ("gn::tc::edge_mlp_aggregate_kernel<8> (+ graph_to_ell, edge_overflow; "
-            "tcgen05 bf16, timed as one C-ABI call)")
+    name = ("gn::tc::edge_mlp_aggregate_kernel<8> x2 passes + graph_to_groups "
+            "(tcgen05 kind::f16, timed as one C-ABI call)")
     return ms, executed, name

@@ -16,7 +16,7 @@ import torch
 from torch import Tensor
 
 from . import _lib
-from ._lib import ACT, AGGR, DTYPE_BF16, DTYPE_F32, HEAD, POOL, GnGraph, check
+from ._lib import ACT, AGGR, DTYPE_BF16, DTYPE_F16, DTYPE_F32, HEAD, POOL, GnGraph, check
 
 
 def _require_cuda(*tensors: Optional[Tensor]) -> torch.device:
@@ -66,6 +66,7 @@ class Graph:
             deg=0 if self.deg is None else self.deg.data_ptr(),
             rowptr=0 if self.rowptr is None else self.rowptr.data_ptr(),
             ell_stride=self.ell_stride,
+            num_edges=0 if self.rowptr is None else int(self.col.shape[0]),
         )
 
 
@@ -174,10 +175,14 @@ def coo_to_csr(edge_index: Tensor, num_nodes: int) -> Graph:
 
 
 # ----------------------------------------------------------- per-event features
+_DT = {torch.float32: DTYPE_F32, torch.bfloat16: DTYPE_BF16, torch.float16: DTYPE_F16}
+
+
 def global_variables(x: Tensor, graph: Graph, ptr: Tensor, n_pulses: Tensor,
-                     x0: Optional[Tensor] = None, x0_cols: int = 0) -> Tensor:
-    """gv [B, F+5]; if `x0` is given also writes x0[:, :x0_cols] = [x, gv[batch], 0...]."""
-    dev = _require_cuda(x, ptr, n_pulses, x0)
+                     x0: Optional[Tensor] = None, x0_cols: int = 0,
+                     x0b: Optional[Tensor] = None, x0b_cols: int = 0) -> Tensor:
+    """gv [B, F+5]; if `x0` (/`x0b`) is given also writes [:, :cols] = [x, gv[batch], 0...]."""
+    dev = _require_cuda(x, ptr, n_pulses, x0, x0b)
     assert x.dtype == torch.float32 and x.stride(1) == 1
     N, F = x.shape
     B = ptr.shape[0] - 1
@@ -185,16 +190,18 @@ def global_variables(x: Tensor, graph: Graph, ptr: Tensor, n_pulses: Tensor,
     assert n_pulses.shape[0] == B, "n_pulses must have one entry per event"
     gv = torch.empty((B, F + 5), dtype=torch.float32, device=dev)
     gs = graph.c_struct()
-    if x0 is not None:
-        assert x0.stride(1) == 1 and x0.shape[0] == N
-        dt = DTYPE_BF16 if x0.dtype == torch.bfloat16 else DTYPE_F32
-        ld0 = x0.stride(0)
-    else:
-        dt, ld0 = DTYPE_F32, 0
+    outs = []
+    for t in (x0, x0b):
+        if t is not None:
+            assert t.stride(1) == 1 and t.shape[0] == N
+            outs.append((_DT[t.dtype], t.stride(0)))
+        else:
+            outs.append((DTYPE_F32, 0))
     with torch.cuda.device(dev):
-        check(_lib.load().gn_global_variables(_ptr(x), x.stride(0), F, C.byref(gs), _ptr(ptr),
-                                              _ptr(n_pulses), N, B, _ptr(gv), _ptr(x0), ld0,
-                                              x0_cols, dt, _stream(dev)), "gn_global_variables")
+        check(_lib.load().gn_global_variables(
+            _ptr(x), x.stride(0), F, C.byref(gs), _ptr(ptr), _ptr(n_pulses), N, B, _ptr(gv),
+            _ptr(x0), outs[0][1], x0_cols, outs[0][0], _ptr(x0b), outs[1][1], x0b_cols,
+            outs[1][0], _stream(dev)), "gn_global_variables")
     return gv
 
 
@@ -231,9 +238,10 @@ def linear_f32(A: Tensor, W: Tensor, bias: Optional[Tensor], act: str = "none",
         out = torch.empty((M, Nout), dtype=torch.float32, device=dev)
     assert out.stride(1) == 1 and out.shape[0] == M and out.shape[1] >= Nout
     b = None if bias is None else bias.detach().contiguous()
+    dt = {torch.bfloat16: DTYPE_BF16, torch.float16: DTYPE_F16, torch.float32: DTYPE_F32}[out.dtype]
     with torch.cuda.device(dev):
         check(_lib.load().gn_linear_f32(_ptr(A), A.stride(0), _ptr(W), _ptr(b), _ptr(out),
-                                        out.stride(0), M, Nout, K, ACT[act], _stream(dev)),
+                                        out.stride(0), dt, M, Nout, K, ACT[act], _stream(dev)),
               "gn_linear_f32")
     return out
 
@@ -305,35 +313,38 @@ def task_head(y: Tensor, kind: str) -> Tensor:
 # ------------------------------------------------- dense, bf16 tensor cores
 def tc_linear_bf16(A: Tensor, W: Tensor, bias: Optional[Tensor], out: Tensor, K: int,
                    act: str = "none") -> Tensor:
-    """out[:, :N] = act(A[:, :K] W[:, :K]^T + bias); A, W bf16; out bf16 or fp32 (tcgen05)."""
+    """out[:, :N] = act(A[:, :K] W[:, :K]^T + bias); A, W bf16 or fp16; fp32 accumulate (tcgen05)."""
     dev = _require_cuda(A, W, bias, out)
-    assert A.dtype == torch.bfloat16 and W.dtype == torch.bfloat16
+    assert A.dtype == W.dtype and A.dtype in (torch.bfloat16, torch.float16)
     assert A.stride(1) == 1 and W.stride(1) == 1 and out.stride(1) == 1
     M = A.shape[0]
     Nout = W.shape[0]
     assert out.shape[0] == M and out.shape[1] >= Nout and A.shape[1] >= K and W.shape[1] >= K
-    dt = DTYPE_BF16 if out.dtype == torch.bfloat16 else DTYPE_F32
+    dt = {torch.bfloat16: DTYPE_BF16, torch.float16: DTYPE_F16, torch.float32: DTYPE_F32}[out.dtype]
     with torch.cuda.device(dev):
-        check(_lib.load().gn_tc_linear_bf16(_ptr(A), A.stride(0), _ptr(W), W.stride(0),
-                                            _ptr(bias), _ptr(out), out.stride(0), dt, M, Nout, K,
-                                            ACT[act], _stream(dev)), "gn_tc_linear_bf16")
+        check(_lib.load().gn_tc_linear(_ptr(A), A.stride(0), _ptr(W), W.stride(0), _DT[A.dtype],
+                                       _ptr(bias), _ptr(out), out.stride(0), dt, M, Nout, K,
+                                       ACT[act], _stream(dev)), "gn_tc_linear")
     return out
 
 
-def tc_edge_mlp_aggregate(pq: Tensor, Kp: int, graph: Graph, slots: int, W2p: Tensor,
-                          W2Tp: Tensor, b: int, out: Tensor, coords: Optional[Tensor],
+def tc_edge_mlp_aggregate(pq: Tensor, Kp: int, graph: Graph, slots: int, W2p: Tensor, b: int,
+                          out: Tensor, coords: Optional[Tensor],
                           coord_cols: Sequence[int]) -> Tensor:
     """out[i] = sum_j ReLU(W2 ReLU(P_i + Q_j) + b2) on tcgen05 (see include/graphnet_b200.h)."""
-    dev = _require_cuda(pq, W2p, W2Tp, out, coords)
+    dev = _require_cuda(pq, W2p, out, coords)
+    assert pq.dtype == torch.float16 and W2p.dtype == torch.float16
+    assert out.dtype in (torch.bfloat16, torch.float16)
     N = pq.shape[0]
     lib = _lib.load()
-    nbytes = lib.gn_tc_edge_scratch_bytes(N, slots)
-    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     gs = graph.c_struct()
+    nbytes = lib.gn_tc_edge_scratch_bytes(C.byref(gs), N, slots)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     ncoord = 0 if coords is None else len(coord_cols)
     with torch.cuda.device(dev):
         check(lib.gn_tc_edge_mlp_aggregate(
-            _ptr(pq), pq.stride(0), Kp, C.byref(gs), N, slots, _ptr(W2p), _ptr(W2Tp), b,
-            _ptr(out), out.stride(0), _ptr(coords), _host_i32(coord_cols) if ncoord else None,
+            _ptr(pq), pq.stride(0), Kp, C.byref(gs), N, slots, _ptr(W2p), b,
+            _ptr(out), out.stride(0), _DT[out.dtype], _ptr(coords),
+            _host_i32(coord_cols) if ncoord else None,
             ncoord, _ptr(scratch), nbytes, _stream(dev)), "gn_tc_edge_mlp_aggregate")
     return out

@@ -49,6 +49,7 @@ extern "C" {
 /* element types of activations handed between kernels */
 #define GN_F32 0
 #define GN_BF16 1
+#define GN_F16 2
 
 /* task heads, models/task/reconstruction.py */
 #define GN_HEAD_IDENTITY 0
@@ -75,6 +76,7 @@ typedef struct gn_graph {
   const int32_t* deg;    /* ELL: [N]   */
   const int32_t* rowptr; /* CSR: [N+1] */
   int32_t ell_stride;
+  int64_t num_edges;     /* CSR: E (length of col); ignored for ELL */
 } gn_graph;
 
 const char* gn_last_error(void);
@@ -130,11 +132,13 @@ int gn_coo_to_csr(const int64_t* edge_index, int64_t E, int64_t N, int32_t* rowp
  * log10(n_pulses[e])]  -> [B, F+5].
  * If x0 != NULL it also performs the "distribute" step and concatenation of
  * dynedge.py:309-320: x0[i] = [x[i, 0:F], gv[batch[i]]] (row stride ldx0, element
- * type x0_dtype; columns F+F+5 .. x0_cols are zero-filled). */
+ * type x0_dtype; columns F+F+5 .. x0_cols are zero-filled).  x0b is an optional second
+ * copy in another element type (the 16-bit skip-cat buffer of the tensor-core path). */
 int gn_global_variables(const float* x, int64_t ldx, int F, const gn_graph* graph,
                         const int32_t* ptr, const int32_t* n_pulses, int64_t N,
                         int64_t B, float* gv, void* x0, int64_t ldx0, int x0_cols,
-                        int x0_dtype, void* stream);
+                        int x0_dtype, void* x0b, int64_t ldx0b, int x0b_cols, int x0b_dtype,
+                        void* stream);
 
 /* DynEdge._global_pooling (dynedge.py:252-265): torch_scatter.scatter_{min,max,
  * sum,mean}(x, batch, dim=0) for each scheme in `schemes` (HOST array), results
@@ -145,12 +149,14 @@ int gn_segment_pool(const void* x, int x_dtype, int64_t ldx, int C, const int32_
 
 /* ---- dense layers, fp32 -------------------------------------------------- */
 
-/* torch.nn.Linear (+ activation): C = act(A W^T + bias).  A [M,K] (row stride
- * lda), W [N,K] row-major (torch layout), C [M,N] (row stride ldc).  Used for the
- * post-processing MLP (dynedge.py:222-232, 332), the readout (:244-250, 348) and
- * the task affine (task/task.py:293). */
+/* torch.nn.Linear (+ activation): C = act(A W^T + bias).  A [M,K] fp32 (row stride
+ * lda), W [N,K] fp32 row-major (torch layout), fp32 FFMA accumulate; C [M,N] of c_dtype
+ * (GN_F32, or GN_BF16 / GN_F16 when it feeds a tensor-core kernel; row stride ldc).  Used
+ * for the post-processing MLP (dynedge.py:222-232, 332), the readout (:244-250, 348),
+ * the task affine (task/task.py:293) and the first EdgeConv's node GEMM (input features
+ * stay fp32). */
 int gn_linear_f32(const float* A, int64_t lda, const float* W, const float* bias,
-                  float* C, int64_t ldc, int64_t M, int N, int K, int act,
+                  void* C, int64_t ldc, int c_dtype, int64_t M, int N, int K, int act,
                   void* stream);
 
 /* Repack the two Linear layers of one DynEdgeConv MLP for gn_edgeconv_f32:
@@ -173,30 +179,32 @@ int gn_edgeconv_f32(const float* x, int64_t ldx, int d, const gn_graph* graph,
 
 /* ---- dense layers, bf16 tensor cores (tcgen05 / TMEM / TMA) ------------------- */
 
-/* torch.nn.Linear (+ activation) with bf16 operands and fp32 accumulation:
- * C = act(A W^T + bias).  A [M,K] bf16 (row stride lda), W [N,K] bf16 (row stride ldw),
- * both 16-byte aligned with strides that are multiples of 8 elements; bias fp32 or NULL;
- * C [M,N] of c_dtype (GN_F32 / GN_BF16, row stride ldc).  Same reference call sites as
+/* torch.nn.Linear (+ activation) with 16-bit operands and fp32 accumulation:
+ * C = act(A W^T + bias).  A [M,K] and W [N,K] of ab_dtype (GN_BF16 or GN_F16; row strides
+ * lda, ldw), both 16-byte aligned with strides that are multiples of 8 elements; bias fp32 or NULL;
+ * C [M,N] of c_dtype (GN_F32 / GN_BF16 / GN_F16 saturated, row stride ldc).  Same reference call sites as
  * gn_linear_f32 plus the first (factored) Linear of each EdgeConv MLP. */
-int gn_tc_linear_bf16(const void* A, int64_t lda, const void* W, int64_t ldw,
-                      const float* bias, void* C, int64_t ldc, int c_dtype, int64_t M,
-                      int N, int K, int act, void* stream);
+int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t ldw, int ab_dtype,
+                 const float* bias, void* C, int64_t ldc, int c_dtype, int64_t M, int N, int K,
+                 int act, void* stream);
 
 /* Second half of the fused EdgeConv (components/layers.py:67, aggr="add"):
  *   out[i] = sum_{j in N(i)} ReLU(W2 ReLU(P_i + Q_j) + b2)
- * pq [N, ldpq] bf16 holds P in columns [0,Kp) and Q in [Kp,2Kp) (Kp = hidden width a
- * padded to a multiple of 32 with >= 2 pad columns; P[:,a] = P[:,a+1] = 1, Q pads = 0).
- * W2p [b16, Kp] bf16 row-major (b16 = b rounded up to 16; columns a, a+1 hold b2 split
- * into bf16 hi/lo parts, remaining pads 0); W2Tp [Kp, b16] is its transpose (used for
- * in-edges beyond `slots` per node).  slots in {8,16,32} >= the usual in-degree.
- * out [N, ldo] bf16.  If ncoord > 0, the fp32 (unrounded) values of the columns listed in
+ * pq [N, ldpq] fp16 (as written by gn_tc_linear / gn_linear_f32 with c_dtype GN_F16) holds P in columns
+ * [0,Kp) and Q in [Kp,2Kp) (Kp = hidden width a padded to a multiple of 32 with >= 2 pad
+ * columns; P[:,a] = P[:,a+1] = 1, Q pads = 0).  W2p [b16, Kp] fp16 row-major (b16 = b rounded
+ * up to 16; columns a, a+1 hold b2 split into fp16 hi/lo parts, remaining pads 0).
+ * `slots` in {8,16,32}: in-edges per node handled in the first pass (>= the usual in-degree);
+ * further in-edges are handled by a second pass over a compacted list, any degree is correct.
+ * out [N, ldo] of out_dtype (GN_BF16 / GN_F16).  If ncoord > 0, the fp32 (unrounded) values of the columns listed in
  * the HOST array coord_cols (strictly increasing) are also written to coords [N, ncoord]
- * for the next kNN.  scratch: gn_tc_edge_scratch_bytes(N, slots) bytes. */
-size_t gn_tc_edge_scratch_bytes(int64_t N, int slots);
+ * for the next kNN.  scratch: gn_tc_edge_scratch_bytes(graph, N, slots) bytes (graph lists). */
+size_t gn_tc_edge_scratch_bytes(const gn_graph* graph, int64_t N, int slots);
 int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp, const gn_graph* graph,
-                             int64_t N, int slots, const void* W2p, const void* W2Tp, int b,
-                             void* out, int64_t ldo, float* coords, const int32_t* coord_cols,
-                             int ncoord, void* scratch, size_t scratch_bytes, void* stream);
+                             int64_t N, int slots, const void* W2p, int b, void* out,
+                             int64_t ldo, int out_dtype, float* coords,
+                             const int32_t* coord_cols, int ncoord, void* scratch,
+                             size_t scratch_bytes, void* stream);
 
 /* ---- task heads ----------------------------------------------------------- */
 

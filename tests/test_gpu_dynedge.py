@@ -66,13 +66,14 @@ def test_forward_fp32_matches_golden(name):
         # dynamic graph of this layer: identical unless a near-tie flipped; report exactness
         ei = ops.ell_to_coo(inter["graphs"][i]).cpu()
         want = g[f"graph{i + 1}"]
-        assert ei.shape == want.shape
-        mismatch = int((ei != want).any(0).sum())
-        assert mismatch <= max(2, ei.shape[1] // 1000), f"graph{i + 1}: {mismatch} edges differ"
+        assert_same_graph_up_to_near_ties(ei, want, g[f"conv{i}"][:, :3], f"graph{i + 1}")
         off += b
     assert rel_l2(inter["post"].cpu(), g["post"]) < FP32_TOL
     if "pooled" in g:
-        assert rel_l2(inter["pooled"].cpu(), g["pooled"]) < FP32_TOL
+        C = g["pooled"].shape[1]
+        assert rel_l2(inter["pooled"].cpu()[:, :C], g["pooled"]) < FP32_TOL
+        if spec.add_global_variables_after_pooling:
+            assert torch.equal(inter["pooled"][:, C:], inter["global_variables"])
     assert out.shape == g["out"].shape
     assert rel_l2(out.cpu(), g["out"]) < FP32_TOL
     # public call gives the same tensor
