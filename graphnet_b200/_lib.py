@@ -63,7 +63,7 @@ SIGNATURES = {
     "gn_edgeconv_f32": (_int, [_p, _i64, _int, _gp, _i64, _p, _p, _int, _p, _p, _int, _int, _int, _p, _p, _i64, _p]),
     "gn_tc_linear": (_int, [_p, _i64, _p, _i64, _int, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),
     "gn_tc_edge_scratch_bytes": (_sz, [_gp, _i64, _int]),
-    "gn_tc_edge_mlp_aggregate": (_int, [_p, _i64, _int, _gp, _i64, _int, _p, _int, _p, _i64, _int,
+    "gn_tc_edge_mlp_aggregate": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _int, _p, _int, _p, _i64, _int,
                                         _p, _hp, _int, _p, _sz, _p]),
     "gn_task_head": (_int, [_p, _i64, _int, _int, _p, _p]),
 }

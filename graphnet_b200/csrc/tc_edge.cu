@@ -8,12 +8,13 @@
 // aggr="add" dynedge.py:208).  The [E, a] hidden tensor and the [E, b] messages never
 // reach HBM: they live in shared memory / TMEM for the lifetime of one 128-edge tile.
 //
-// Persistent kernel, one CTA per SM, 17 warps:
+// Persistent kernel, one CTA per SM, 19 warps:
 //   warp 0       tcgen05.mma issuer; owns TMEM (2 x 256 fp32 columns: double-buffered D) and
 //                loads the whole W2 (bf16, K padded, 64B-swizzled) into shared memory once by TMA
-//   warps 1-8    producers: gather P_i / Q_j rows (16-byte chunks, L2 resident), h = ReLU(P+Q)
-//                in packed bf16, written into the 64B-swizzled K-major A stage ring
-//   warps 9-16   epilogue: TMEM -> registers, ReLU, reduce-scatter over the KP edge rows of a
+//   warps 1-10   producers: gather P_i / Q_j rows (16-byte chunks, L2 resident), h = ReLU(P+Q)
+//                in packed fp16, written into the 64B-swizzled K-major A stage ring; one warp
+//                pair per stage, so five K-chunks are being gathered at any time
+//   warps 11-18  epilogue: TMEM -> registers, ReLU, reduce-scatter over the KP edge rows of a
 //                node with warp shuffles, store bf16 row slice (+ fp32 kNN coordinates)
 // Tile rows are ELL slots: row r of tile t is (node t*128/KP + r/KP, slot r%KP); empty slots are
 // all-zero A rows.  b2 is folded into the GEMM: P carries 1.0 in the two pad columns a, a+1 and
@@ -40,7 +41,7 @@ constexpr int EK_KCH = 32;                       // K elements per stage (64-byt
 constexpr int EK_STAGE_BYTES = EK_ROWS * 64;     // 8 KB
 constexpr int EK_STAGES = 5;
 constexpr int EK_MAX_CHUNKS = 11;                // hidden width (padded) <= 352
-constexpr int EK_PROD_WARPS = 8;
+constexpr int EK_PROD_WARPS = 2 * EK_STAGES;     // a pair of producer warps owns each stage
 constexpr int EK_EPI_WARPS = 8;
 constexpr int EK_THREADS = 32 * (1 + EK_PROD_WARPS + EK_EPI_WARPS);  // 544
 
@@ -54,8 +55,10 @@ struct __align__(8) EdgeBarriers {
 };
 
 struct EdgeParams {
-  const __half* pq;         // [N, ldpq]: P in columns [0, Kp), Q in [Kp, 2Kp)
-  int64_t ldpq;
+  const __half* pmat;       // [N, ldp]: P = x (W1a-W1b)^T + b1  (+ the two "ones" columns)
+  int64_t ldp;
+  const __half* qmat;       // [N, ldq]: Q = x W1b^T   (the gathered operand, kept L2 resident)
+  int64_t ldq;
   int Kp;                   // padded hidden width, multiple of 32
   int nch;                  // Kp / 32
   const int32_t* ell;       // [groups, KP] neighbour ids, -1 = empty slot
@@ -75,6 +78,20 @@ struct EdgeParams {
 
 __device__ __forceinline__ uint4 ldg16(const __half* p) {
   return __ldg(reinterpret_cast<const uint4*>(p));
+}
+// Q rows are gathered ~k times each: ask L2 to keep them (evict_last) while the streamed
+// operands (P, outputs) pass through with normal priority.
+__device__ __forceinline__ uint64_t policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint4 ldg16_keep(const __half* p, uint64_t pol) {
+  uint4 r;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.b32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p), "l"(pol));
+  return r;
 }
 
 __device__ __forceinline__ uint32_t relu_add_f16x2(uint32_t a, uint32_t b) {
@@ -131,7 +148,7 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
     tma_prefetch_desc(&tmW2);
 #pragma unroll
     for (int s = 0; s < EK_STAGES; ++s) {
-      mbar_init(&bars->full[s], EK_PROD_WARPS);
+      mbar_init(&bars->full[s], 2);  // the pair of producer warps that owns the stage
       mbar_init(&bars->empty[s], 1);
     }
 #pragma unroll
@@ -186,99 +203,88 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
     }
   } else if (warp <= EK_PROD_WARPS) {
     // ================================================================= producers
-    const int pt = threadIdx.x - 32;       // 0..255
-    const int c = pt & 3;                  // 16-byte chunk inside the 64-byte stage row
-    const int r0 = pt >> 2;                // rows r0 and r0 + 64
+    // Stage s of the A ring is owned by the producer warp pair (2s, 2s+1): each warp builds 64
+    // of its 128 rows, and the five pairs work on five consecutive K-chunks concurrently.
+    // (fence.proxy.async waits for the issuing thread's outstanding global loads, so a warp
+    // cannot prefetch across its own fence - the overlap that hides the gather latency comes
+    // from the other pairs.  A pair only ever waits for the consumption of its own previous
+    // item, which keeps the mbarrier parity protocol one phase deep.)  Lane l owns the 16-byte
+    // chunk c = l & 3 of rows 64 half + (l >> 2) + 8 t, t = 0..7; rows are processed two at a
+    // time with the next pair's loads in flight.  The 8 rows of one load instruction belong to
+    // one node (KP = 8), so the P chunk is fetched once per instruction; Q rows are the gather.
+    const int pw = warp - 1;          // 0..9
+    const int owner = pw >> 1;        // stage owned by this warp's pair
+    const int half = pw & 1;
+    const int c = lane & 3;
+    const int rq = half * 64 + (lane >> 2);
     const uint32_t a_addr = smem_u32(a_smem);
-    uint32_t soff[2];
+    const int64_t my_tiles = (num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    const uint32_t total = (uint32_t)(my_tiles * nch);
+    const uint4 zero4 = make_uint4(0, 0, 0, 0);
+    const uint64_t pol = policy_evict_last();
+    const int64_t ell_len = num_groups * KP;
+    const uint32_t base = a_addr + owner * EK_STAGE_BYTES;
+
+    int32_t ids[8];       // neighbour ids of my 8 rows for the current item's tile
+    int32_t ids_nx[8];    // ... for my next item (prefetched)
+    auto fetch_ids = [&](uint32_t g, int32_t (&dst)[8]) {
+      const int64_t tile = blockIdx.x + (int64_t)(g / nch) * gridDim.x;
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int r = r0 + 64 * h;
-      soff[h] = (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4));
-    }
-    // neighbour ids (and target nodes) of the first tile
-    int32_t nbr_next[2], node_next[2];
-    {
-      const int64_t tile = blockIdx.x;
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int r = r0 + 64 * h;
-        const int64_t grp = tile * NPT + r / KP;
-        const bool ok = tile < num_tiles && grp < num_groups;
-        nbr_next[h] = ok ? __ldg(p.ell + grp * KP + (r % KP)) : -1;
-        node_next[h] = ok ? (p.group_node ? __ldg(p.group_node + grp) : (int32_t)grp) : 0;
+      for (int t = 0; t < 8; ++t) {
+        const int64_t e = tile * EK_ROWS + rq + 8 * t;
+        dst[t] = (g < total && e < ell_len) ? __ldg(p.ell + e) : -1;
       }
-    }
-    uint32_t g = 0;
-    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const __half* pp[2];
-      const __half* qp[2];
-      bool valid[2];
+    };
+    fetch_ids(owner, ids_nx);
+
+    for (uint32_t g = owner; g < total; g += EK_STAGES) {
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int32_t j = nbr_next[h];
-        valid[h] = j >= 0;
-        pp[h] = p.pq + (int64_t)(valid[h] ? node_next[h] : 0) * p.ldpq + c * 8;
-        qp[h] = p.pq + (int64_t)(valid[h] ? j : 0) * p.ldpq + p.Kp + c * 8;
-      }
-      // prefetch the neighbour ids of this CTA's next tile
-      {
-        const int64_t nt = tile + gridDim.x;
+      for (int t = 0; t < 8; ++t) ids[t] = ids_nx[t];
+      fetch_ids(g + EK_STAGES, ids_nx);
+      const int64_t tile = blockIdx.x + (int64_t)(g / nch) * gridDim.x;
+      const int kc = g % nch;
+      const __half* pbase = p.pmat + kc * EK_KCH + c * 8;
+      const __half* qbase = p.qmat + kc * EK_KCH + c * 8;
+
+      uint4 Pb[2][2], Qb[2][2];
+#define GN_EK_LOAD(BUF, S)                                                                 \
+  {                                                                                        \
+    _Pragma("unroll") for (int tt = 0; tt < 2; ++tt) {                                     \
+      const int t = 2 * (S) + tt;                                                          \
+      const int32_t j = ids[t];                                                            \
+      if (j >= 0) {                                                                        \
+        const int64_t grp = tile * NPT + (rq + 8 * t) / KP;                                \
+        const int64_t node = p.group_node ? (int64_t)__ldg(p.group_node + grp) : grp;      \
+        Pb[BUF][tt] = ldg16(pbase + node * p.ldp);                                         \
+        Qb[BUF][tt] = ldg16_keep(qbase + (int64_t)j * p.ldq, pol);                         \
+      } else {                                                                             \
+        Pb[BUF][tt] = zero4;                                                               \
+        Qb[BUF][tt] = zero4;                                                               \
+      }                                                                                    \
+    }                                                                                      \
+  }
+      GN_EK_LOAD(0, 0)
+      mbar_wait(&bars->empty[owner], ((g / EK_STAGES) & 1) ^ 1);
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int r = r0 + 64 * h;
-          const int64_t grp = nt * NPT + r / KP;
-          const bool ok = nt < num_tiles && grp < num_groups;
-          nbr_next[h] = ok ? __ldg(p.ell + grp * KP + (r % KP)) : -1;
-          node_next[h] = ok ? (p.group_node ? __ldg(p.group_node + grp) : (int32_t)grp) : 0;
+      for (int sb = 0; sb < 4; ++sb) {
+        if (sb + 1 < 4) {
+          if ((sb & 1) == 0) GN_EK_LOAD(1, sb + 1) else GN_EK_LOAD(0, sb + 1)
+        }
+#pragma unroll
+        for (int tt = 0; tt < 2; ++tt) {
+          const uint4 P = Pb[sb & 1][tt], Q = Qb[sb & 1][tt];
+          const int r = rq + 8 * (2 * sb + tt);
+          const uint32_t dst = base + (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4));
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst),
+                       "r"(relu_add_f16x2(P.x, Q.x)), "r"(relu_add_f16x2(P.y, Q.y)),
+                       "r"(relu_add_f16x2(P.z, Q.z)), "r"(relu_add_f16x2(P.w, Q.w))
+                       : "memory");
         }
       }
-      // two-deep register pipeline over the K chunks of this tile
-      uint4 pa[2], qa[2], pb[2], qb[2];
-      const uint4 zero4 = make_uint4(0, 0, 0, 0);
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        pa[h] = valid[h] ? ldg16(pp[h]) : zero4;
-        qa[h] = valid[h] ? ldg16(qp[h]) : zero4;
-        pb[h] = (valid[h] && nch > 1) ? ldg16(pp[h] + EK_KCH) : zero4;
-        qb[h] = (valid[h] && nch > 1) ? ldg16(qp[h] + EK_KCH) : zero4;
-      }
-      for (int kc = 0; kc < nch; kc += 2) {
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          const int k = kc + half;
-          if (k >= nch) break;
-          const uint32_t s = g % EK_STAGES;
-          mbar_wait(&bars->empty[s], ((g / EK_STAGES) & 1) ^ 1);
-          const uint32_t base = a_addr + s * EK_STAGE_BYTES;
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const uint4 P = half == 0 ? pa[h] : pb[h];
-            const uint4 Q = half == 0 ? qa[h] : qb[h];
-            uint4 H;
-            H.x = relu_add_f16x2(P.x, Q.x);
-            H.y = relu_add_f16x2(P.y, Q.y);
-            H.z = relu_add_f16x2(P.z, Q.z);
-            H.w = relu_add_f16x2(P.w, Q.w);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(base + soff[h]),
-                         "r"(H.x), "r"(H.y), "r"(H.z), "r"(H.w)
-                         : "memory");
-          }
-          // refill this register slot with chunk k + 2
-          const int kn = k + 2;
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const bool ld = valid[h] && kn < nch;
-            const uint4 np = ld ? ldg16(pp[h] + kn * EK_KCH) : zero4;
-            const uint4 nq = ld ? ldg16(qp[h] + kn * EK_KCH) : zero4;
-            if (half == 0) { pa[h] = np; qa[h] = nq; } else { pb[h] = np; qb[h] = nq; }
-          }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&bars->full[s]);
-          ++g;
-        }
-      }
+#undef GN_EK_LOAD
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->full[owner]);
     }
   } else {
     // ================================================================== epilogue
@@ -430,8 +436,8 @@ extern "C" size_t gn_tc_edge_scratch_bytes(const gn_graph* graph, int64_t N, int
   return (size_t)(n * slots + cap * slots + cap + 4) * sizeof(int32_t);
 }
 
-extern "C" int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp,
-                                        const gn_graph* graph, int64_t N, int slots,
+extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t ldq,
+                                        int Kp, const gn_graph* graph, int64_t N, int slots,
                                         const void* W2p, int b, void* out, int64_t ldo,
                                         int out_dtype, float* coords,
                                         const int32_t* coord_cols, int ncoord, void* scratch,
@@ -444,17 +450,19 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp,
                Kp, tc::EK_MAX_CHUNKS * tc::EK_KCH);
   GN_CHECK_ARG(slots == 8 || slots == 16 || slots == 32,
                "gn_tc_edge_mlp_aggregate: slots=%d (must be 8, 16 or 32)", slots);
-  GN_CHECK_ARG(ldpq >= 2 * Kp && ldpq % 8 == 0 && ldo % 4 == 0 && ldo >= b,
+  GN_CHECK_ARG(ldp >= Kp && ldq >= Kp && ldp % 8 == 0 && ldq % 8 == 0 && ldo % 4 == 0 && ldo >= b,
                "gn_tc_edge_mlp_aggregate: bad leading dimensions");
   GN_CHECK_ARG(ncoord >= 0 && ncoord <= 16, "gn_tc_edge_mlp_aggregate: ncoord=%d", ncoord);
   if (N == 0) return GN_OK;
-  GN_CHECK_ARG(pq && W2p && out && scratch && graph, "gn_tc_edge_mlp_aggregate: null pointer");
+  GN_CHECK_ARG(P && Q && W2p && out && scratch && graph,
+               "gn_tc_edge_mlp_aggregate: null pointer");
   GN_CHECK_ARG(scratch_bytes >= gn_tc_edge_scratch_bytes(graph, N, slots),
                "gn_tc_edge_mlp_aggregate: scratch too small");
-  GN_CHECK_ARG((reinterpret_cast<uintptr_t>(pq) & 15) == 0 &&
+  GN_CHECK_ARG((reinterpret_cast<uintptr_t>(P) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(Q) & 15) == 0 &&
                (reinterpret_cast<uintptr_t>(out) & 7) == 0 &&
                (reinterpret_cast<uintptr_t>(scratch) & 3) == 0,
-               "gn_tc_edge_mlp_aggregate: pq must be 16-byte and out 8-byte aligned");
+               "gn_tc_edge_mlp_aggregate: P, Q must be 16-byte and out 8-byte aligned");
   GraphView g;
   int rc = make_graph_view(graph, &g);
   if (rc != GN_OK) return rc;
@@ -485,8 +493,10 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp,
                         tc::EK_KCH, 64);
   if (rc != GN_OK) return rc;
 
-  p.pq = reinterpret_cast<const __half*>(pq);
-  p.ldpq = ldpq;
+  p.pmat = reinterpret_cast<const __half*>(P);
+  p.ldp = ldp;
+  p.qmat = reinterpret_cast<const __half*>(Q);
+  p.ldq = ldq;
   p.Kp = Kp;
   p.nch = Kp / tc::EK_KCH;
   p.N = N;

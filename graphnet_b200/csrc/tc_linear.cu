@@ -76,12 +76,12 @@ namespace tc {
 constexpr int LIN_BM = 128;
 constexpr int LIN_BK = 64;        // 64 bf16 = one 128-byte swizzle row
 constexpr int LIN_STAGES = 4;
-constexpr int LIN_THREADS = 192;  // 6 warps
+constexpr int LIN_EPI_WARPS = 8;
+constexpr int LIN_THREADS = 32 * (2 + LIN_EPI_WARPS);  // TMA + MMA + 8 epilogue warps
+constexpr int LIN_MAX_N = 2048;   // bias staged in shared memory
 constexpr int LIN_A_BYTES = LIN_BM * LIN_BK * 2;  // 16 KB
 
-constexpr int LIN_EPI_WARPS = 4;
-
-struct __align__(8) LinBarriers {
+struct __align__(16) LinBarriers {
   uint64_t full[LIN_STAGES];
   uint64_t empty[LIN_STAGES];
   uint64_t tmem_full[2];
@@ -90,68 +90,55 @@ struct __align__(8) LinBarriers {
 };
 
 template <typename OutT>
-__device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int nvalid);
-
+__device__ __forceinline__ uint32_t pack2(float a, float b);
 template <>
-__device__ __forceinline__ void store_row32<float>(float* dst, const float (&v)[32], int nvalid) {
-  if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-#pragma unroll
-    for (int j = 0; j < 32; j += 4)
-      *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-  } else {
-#pragma unroll
-    for (int j = 0; j < 32; ++j)
-      if (j < nvalid) dst[j] = v[j];
-  }
+__device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
+  __nv_bfloat162 p = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&p);
 }
 template <>
-__device__ __forceinline__ void store_row32<__nv_bfloat16>(__nv_bfloat16* dst, const float (&v)[32],
-                                                           int nvalid) {
-  if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+__device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {  // saturating
+  __half2 p = __floats2half2_rn(fminf(fmaxf(a, -65504.f), 65504.f),
+                                fminf(fmaxf(b, -65504.f), 65504.f));
+  return *reinterpret_cast<uint32_t*>(&p);
+}
+
+// one thread stores 32 consecutive columns of its row; 16-byte vector stores for every full
+// group of 8 (16-bit) / 4 (fp32) columns, scalar stores only for a ragged tail
+template <typename OutT>
+__device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int nvalid) {
+  const bool aligned = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+  if constexpr (sizeof(OutT) == 4) {
 #pragma unroll
-    for (int j = 0; j < 32; j += 8) {
-      __nv_bfloat162 p0 = __floats2bfloat162_rn(v[j], v[j + 1]);
-      __nv_bfloat162 p1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-      __nv_bfloat162 p2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
-      __nv_bfloat162 p3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-      uint4 u;
-      u.x = *reinterpret_cast<uint32_t*>(&p0);
-      u.y = *reinterpret_cast<uint32_t*>(&p1);
-      u.z = *reinterpret_cast<uint32_t*>(&p2);
-      u.w = *reinterpret_cast<uint32_t*>(&p3);
-      *reinterpret_cast<uint4*>(dst + j) = u;
+    for (int j = 0; j < 32; j += 4) {
+      if (aligned && j + 4 <= nvalid) {
+        *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      } else {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+          if (j + t < nvalid) dst[j + t] = v[j + t];
+      }
     }
   } else {
 #pragma unroll
-    for (int j = 0; j < 32; ++j)
-      if (j < nvalid) dst[j] = __float2bfloat16_rn(v[j]);
-  }
-}
-
-// fp16 output, saturated to the finite range (feeds the fp16 hidden layer of the edge kernel)
-template <>
-__device__ __forceinline__ void store_row32<__half>(__half* dst, const float (&v)[32], int nvalid) {
-  float c[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) c[j] = fminf(fmaxf(v[j], -65504.f), 65504.f);
-  if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-#pragma unroll
     for (int j = 0; j < 32; j += 8) {
-      __half2 p0 = __floats2half2_rn(c[j], c[j + 1]);
-      __half2 p1 = __floats2half2_rn(c[j + 2], c[j + 3]);
-      __half2 p2 = __floats2half2_rn(c[j + 4], c[j + 5]);
-      __half2 p3 = __floats2half2_rn(c[j + 6], c[j + 7]);
-      uint4 u;
-      u.x = *reinterpret_cast<uint32_t*>(&p0);
-      u.y = *reinterpret_cast<uint32_t*>(&p1);
-      u.z = *reinterpret_cast<uint32_t*>(&p2);
-      u.w = *reinterpret_cast<uint32_t*>(&p3);
-      *reinterpret_cast<uint4*>(dst + j) = u;
-    }
-  } else {
+      if (aligned && j + 8 <= nvalid) {
+        uint4 u;
+        u.x = pack2<OutT>(v[j], v[j + 1]);
+        u.y = pack2<OutT>(v[j + 2], v[j + 3]);
+        u.z = pack2<OutT>(v[j + 4], v[j + 5]);
+        u.w = pack2<OutT>(v[j + 6], v[j + 7]);
+        *reinterpret_cast<uint4*>(dst + j) = u;
+      } else {
 #pragma unroll
-    for (int j = 0; j < 32; ++j)
-      if (j < nvalid) dst[j] = __float2half_rn(c[j]);
+        for (int t = 0; t < 8; t += 2) {
+          const uint32_t pr = pack2<OutT>(v[j + t], v[j + t + 1]);
+          uint16_t* d16 = reinterpret_cast<uint16_t*>(dst);
+          if (j + t < nvalid) d16[j + t] = (uint16_t)(pr & 0xffffu);
+          if (j + t + 1 < nvalid) d16[j + t + 1] = (uint16_t)(pr >> 16);
+        }
+      }
+    }
   }
 }
 
@@ -167,9 +154,12 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
   const int b_bytes = BN * LIN_BK * 2;
   const int stage_bytes = LIN_A_BYTES + b_bytes;
   LinBarriers* bars = reinterpret_cast<LinBarriers*>(smem + LIN_STAGES * stage_bytes);
+  float* s_bias = reinterpret_cast<float*>(bars + 1);  // [num_n_tiles * BN]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = (K + LIN_BK - 1) / LIN_BK;
+  for (int n = threadIdx.x; n < num_n_tiles * BN; n += LIN_THREADS)
+    s_bias[n] = (bias != nullptr && n < N) ? bias[n] : 0.f;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -244,6 +234,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
   } else {
     // -------------------------------------------------------------- epilogue
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    const int par = (warp - 2) >> 2;  // the two warps of a quadrant take alternate 32-col chunks
     uint32_t it = 0;
     for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
       const uint32_t buf = it & 1;
@@ -252,15 +243,19 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
       mbar_wait(&bars->tmem_full[buf], (it >> 1) & 1);
       tc_fence_after();
       const int64_t row = m0 + q * 32 + lane;
-      for (int c = 0; c < BN; c += 32) {
+      for (int c = par * 32; c < BN; c += 64) {
         const int n = n0 + c;
         if (n >= N) break;
         float v[32];
         tmem_ld_32x32(tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+        const float4* b4 = reinterpret_cast<const float4*>(s_bias + n);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float b = (bias != nullptr && n + j < N) ? __ldg(bias + n + j) : 0.f;
-          v[j] = activate<ACT>(v[j] + b);
+        for (int j = 0; j < 32; j += 4) {
+          const float4 b = b4[j >> 2];  // same address in every lane: one broadcast wavefront
+          v[j] = activate<ACT>(v[j] + b.x);
+          v[j + 1] = activate<ACT>(v[j + 1] + b.y);
+          v[j + 2] = activate<ACT>(v[j + 2] + b.z);
+          v[j + 3] = activate<ACT>(v[j + 3] + b.w);
         }
         if (row < M) store_row32<OutT>(C + row * ldc + n, v, min(N - n, BN - c));
       }
@@ -280,8 +275,9 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
                             int ab_dtype, cudaStream_t st) {
   const uint32_t idesc =
       ab_dtype == GN_F16 ? make_idesc_f16(LIN_BM, BN) : make_idesc_bf16(LIN_BM, BN);
-  const size_t smem = (size_t)LIN_STAGES * (LIN_A_BYTES + BN * LIN_BK * 2) + sizeof(LinBarriers) + 1024;
   const int num_n_tiles = (int)ceil_div(N, BN);
+  const size_t smem = (size_t)LIN_STAGES * (LIN_A_BYTES + BN * LIN_BK * 2) + sizeof(LinBarriers) +
+                      (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024;
   const int64_t num_tiles = ceil_div(M, LIN_BM) * num_n_tiles;
   int dev = 0, sms = 0;
   GN_CUDA(cudaGetDevice(&dev));
@@ -330,6 +326,7 @@ extern "C" int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
   if (M == 0) return GN_OK;
   GN_CHECK_ARG(A && W && C, "gn_tc_linear: null pointer");
   GN_CHECK_ARG(ab_dtype == GN_BF16 || ab_dtype == GN_F16, "gn_tc_linear: bad ab_dtype");
+  GN_CHECK_ARG(N <= tc::LIN_MAX_N, "gn_tc_linear: N=%d exceeds %d", N, tc::LIN_MAX_N);
   GN_CHECK_ARG(c_dtype == GN_F32 || c_dtype == GN_BF16 || c_dtype == GN_F16,
                "gn_tc_linear: bad c_dtype");
   const int BN = tc_pick_bn(N);

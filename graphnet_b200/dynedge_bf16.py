@@ -71,8 +71,9 @@ class _ConvPack:
         self.d, self.a, self.b, self.Kp, self.Kd, self.b16 = d, a, b, Kp, Kd, b16
         # first layer: fp32 FFMA node GEMM on the fp32 input features; later layers: tcgen05
         self.first = first
-        self.Wpq = Wpq.contiguous() if first else Wpq.to(io_dtype).contiguous()
-        self.bias_pq = bias
+        Wpq = Wpq.contiguous() if first else Wpq.to(io_dtype).contiguous()
+        self.Wp, self.Wq = Wpq[:Kp], Wpq[Kp:]   # P = x Wp^T + bias_p ; Q = x Wq^T
+        self.bias_p = bias[:Kp].contiguous()
         self.W2p = W2p.contiguous()
 
 
@@ -168,17 +169,21 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
     for li, conv in enumerate(convs):
         pk = _conv_pack(conv, io, first=(li == 0))
         assert pk.d == d_in
-        pq = torch.empty((N, 2 * pk.Kp), dtype=torch.float16, device=dev)
+        # P and Q live in separate dense arrays: Q is the gathered operand and stays L2 resident
+        P = torch.empty((N, pk.Kp), dtype=torch.float16, device=dev)
+        Q = torch.empty((N, pk.Kp), dtype=torch.float16, device=dev)
         if li == 0:
-            ops.linear_f32(x0, pk.Wpq, pk.bias_pq, act="none", out=pq)
+            ops.linear_f32(x0, pk.Wp, pk.bias_p, act="none", out=P)
+            ops.linear_f32(x0, pk.Wq, None, act="none", out=Q)
         else:
-            ops.tc_linear_bf16(skip[:, off_in:], pk.Wpq, pk.bias_pq, pq, K=d_in, act="none")
+            ops.tc_linear_bf16(skip[:, off_in:], pk.Wp, pk.bias_p, P, K=d_in, act="none")
+            ops.tc_linear_bf16(skip[:, off_in:], pk.Wq, None, Q, K=d_in, act="none")
         last = li + 1 == len(convs)
         need_graph = (not last) or return_intermediates
         cols = sorted(ops._columns(conv.features_subset, pk.b))
         coords = (torch.empty((N, len(cols)), dtype=torch.float32, device=dev)
                   if need_graph else None)
-        ops.tc_edge_mlp_aggregate(pq, pk.Kp, graph, _slots(conv.nb_neighbors), pk.W2p, pk.b,
+        ops.tc_edge_mlp_aggregate(P, Q, pk.Kp, graph, _slots(conv.nb_neighbors), pk.W2p, pk.b,
                                   skip[:, offs[li]:], coords, cols)
         if need_graph:
             graph = ops.knn_graph_ell(coords, conv.nb_neighbors, ptr, list(range(len(cols))))
@@ -225,14 +230,15 @@ def time_edge_kernel(model, data: Any, flush_buf: Tensor, layer: int = 1, reps: 
     conv = model._conv_layers[layer]
     pk = _conv_pack(conv, _io_dtype(model), first=(layer == 0))
     g = torch.Generator(device=dev).manual_seed(0)
-    pq = (torch.randn((N, 2 * pk.Kp), generator=g, device=dev) * 0.5).to(torch.float16)
+    P = (torch.randn((N, pk.Kp), generator=g, device=dev) * 0.5).to(torch.float16)
+    Q = (torch.randn((N, pk.Kp), generator=g, device=dev) * 0.5).to(torch.float16)
     out = torch.empty((N, pk.b), dtype=_io_dtype(model), device=dev)
     coords = torch.empty((N, 3), dtype=torch.float32, device=dev)
     ell = ops.knn_graph_ell(x, conv.nb_neighbors, ptr, [0, 1, 2])
     slots = _slots(conv.nb_neighbors)
 
     def run():
-        ops.tc_edge_mlp_aggregate(pq, pk.Kp, ell, slots, pk.W2p, pk.b, out, coords, [0, 1, 2])
+        ops.tc_edge_mlp_aggregate(P, Q, pk.Kp, ell, slots, pk.W2p, pk.b, out, coords, [0, 1, 2])
     for _ in range(3):
         run()
     s = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]

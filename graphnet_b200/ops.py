@@ -328,14 +328,15 @@ def tc_linear_bf16(A: Tensor, W: Tensor, bias: Optional[Tensor], out: Tensor, K:
     return out
 
 
-def tc_edge_mlp_aggregate(pq: Tensor, Kp: int, graph: Graph, slots: int, W2p: Tensor, b: int,
-                          out: Tensor, coords: Optional[Tensor],
+def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: int, W2p: Tensor,
+                          b: int, out: Tensor, coords: Optional[Tensor],
                           coord_cols: Sequence[int]) -> Tensor:
     """out[i] = sum_j ReLU(W2 ReLU(P_i + Q_j) + b2) on tcgen05 (see include/graphnet_b200.h)."""
-    dev = _require_cuda(pq, W2p, out, coords)
-    assert pq.dtype == torch.float16 and W2p.dtype == torch.float16
+    dev = _require_cuda(P, Q, W2p, out, coords)
+    assert P.dtype == torch.float16 and Q.dtype == torch.float16 and W2p.dtype == torch.float16
     assert out.dtype in (torch.bfloat16, torch.float16)
-    N = pq.shape[0]
+    assert P.stride(1) == 1 and Q.stride(1) == 1 and P.shape[0] == Q.shape[0]
+    N = P.shape[0]
     lib = _lib.load()
     gs = graph.c_struct()
     nbytes = lib.gn_tc_edge_scratch_bytes(C.byref(gs), N, slots)
@@ -343,7 +344,7 @@ def tc_edge_mlp_aggregate(pq: Tensor, Kp: int, graph: Graph, slots: int, W2p: Te
     ncoord = 0 if coords is None else len(coord_cols)
     with torch.cuda.device(dev):
         check(lib.gn_tc_edge_mlp_aggregate(
-            _ptr(pq), pq.stride(0), Kp, C.byref(gs), N, slots, _ptr(W2p), b,
+            _ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp, C.byref(gs), N, slots, _ptr(W2p), b,
             _ptr(out), out.stride(0), _DT[out.dtype], _ptr(coords),
             _host_i32(coord_cols) if ncoord else None,
             ncoord, _ptr(scratch), nbytes, _stream(dev)), "gn_tc_edge_mlp_aggregate")

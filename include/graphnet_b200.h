@@ -190,9 +190,10 @@ int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t ldw, int ab_
 
 /* Second half of the fused EdgeConv (components/layers.py:67, aggr="add"):
  *   out[i] = sum_{j in N(i)} ReLU(W2 ReLU(P_i + Q_j) + b2)
- * pq [N, ldpq] fp16 (as written by gn_tc_linear / gn_linear_f32 with c_dtype GN_F16) holds P in columns
- * [0,Kp) and Q in [Kp,2Kp) (Kp = hidden width a padded to a multiple of 32 with >= 2 pad
- * columns; P[:,a] = P[:,a+1] = 1, Q pads = 0).  W2p [b16, Kp] fp16 row-major (b16 = b rounded
+ * P [N, ldp] and Q [N, ldq] are fp16 (as written by gn_tc_linear / gn_linear_f32 with c_dtype
+ * GN_F16), Kp columns each (Kp = hidden width a padded to a multiple of 32 with >= 2 pad
+ * columns; P[:,a] = P[:,a+1] = 1, Q pads = 0).  Q is the gathered operand: keeping it in its
+ * own dense array lets it stay L2 resident.  W2p [b16, Kp] fp16 row-major (b16 = b rounded
  * up to 16; columns a, a+1 hold b2 split into fp16 hi/lo parts, remaining pads 0).
  * `slots` in {8,16,32}: in-edges per node handled in the first pass (>= the usual in-degree);
  * further in-edges are handled by a second pass over a compacted list, any degree is correct.
@@ -200,8 +201,9 @@ int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t ldw, int ab_
  * the HOST array coord_cols (strictly increasing) are also written to coords [N, ncoord]
  * for the next kNN.  scratch: gn_tc_edge_scratch_bytes(graph, N, slots) bytes (graph lists). */
 size_t gn_tc_edge_scratch_bytes(const gn_graph* graph, int64_t N, int slots);
-int gn_tc_edge_mlp_aggregate(const void* pq, int64_t ldpq, int Kp, const gn_graph* graph,
-                             int64_t N, int slots, const void* W2p, int b, void* out,
+int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t ldq, int Kp,
+                             const gn_graph* graph, int64_t N, int slots, const void* W2p, int b,
+                             void* out,
                              int64_t ldo, int out_dtype, float* coords,
                              const int32_t* coord_cols, int ncoord, void* scratch,
                              size_t scratch_bytes, void* stream);

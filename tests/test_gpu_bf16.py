@@ -78,7 +78,7 @@ def test_tc_edge_mlp_aggregate(k, a, b):
     out = torch.full((N, b + 4), -3.0, dtype=torch.bfloat16, device=DEV)
     cols = [0, 1, 2] if b >= 200 else [1, 5, 33]
     coords = torch.empty(N, 3, device=DEV)
-    ops.tc_edge_mlp_aggregate(pq.to(DEV), Kp, ell, _slots(k), W2p.to(DEV), b, out, coords, cols)
+    ops.tc_edge_mlp_aggregate(pq.to(DEV)[:, :Kp], pq.to(DEV)[:, Kp:], Kp, ell, _slots(k), W2p.to(DEV), b, out, coords, cols)
     want = _edge_reference(pq, Kp, ei, W2p, b, N)
     got = out.float().cpu()
     assert bool((got[:, b:] == -3.0).all())
@@ -104,7 +104,7 @@ def test_tc_edge_csr_graph_with_large_degrees():
     pq = pq.to(torch.float16)
     W2p = (torch.randn(b, Kp, generator=g) / 8).to(torch.float16)
     out = torch.empty((N, b), dtype=torch.bfloat16, device=DEV)
-    ops.tc_edge_mlp_aggregate(pq.to(DEV), Kp, ops.coo_to_csr(ei.to(DEV), N), 8, W2p.to(DEV), b,
+    ops.tc_edge_mlp_aggregate(pq.to(DEV)[:, :Kp], pq.to(DEV)[:, Kp:], Kp, ops.coo_to_csr(ei.to(DEV), N), 8, W2p.to(DEV), b,
                               out, None, [])
     want = _edge_reference(pq, Kp, ei, W2p, b, N)
     assert float((out.float().cpu() - want).abs().max() / want.abs().max()) < 2e-2
