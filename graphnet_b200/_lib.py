@@ -53,6 +53,7 @@ SIGNATURES = {
     "gn_knn_graph": (_int, [_p, _i64, _hp, _int, _p, _i64, _i64, _int, _int, _p, _i32, _p, _p]),
     "gn_scan_scratch_bytes": (_sz, [_i64]),
     "gn_ell_row_offsets": (_int, [_p, _i64, _p, _p, _sz, _p]),
+    "gn_ell_row_offsets_noalloc": (_int, [_p, _i64, _p, _p]),
     "gn_ell_to_coo": (_int, [_p, _i32, _p, _p, _i64, _i64, _p, _p]),
     "gn_coo_to_csr": (_int, [_p, _i64, _i64, _p, _p, _p, _p, _p]),
     "gn_global_variables": (_int, [_p, _i64, _int, _gp, _p, _p, _i64, _i64, _p, _p, _i64, _int, _int,

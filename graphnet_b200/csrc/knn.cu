@@ -433,6 +433,55 @@ extern "C" int gn_ell_row_offsets(const int32_t* deg, int64_t N, int64_t* rowptr
   return exclusive_scan_i32(deg, N, rowptr, reinterpret_cast<int64_t*>(scratch), st);
 }
 
+// ------------------------------------------------ row offsets without caller scratch
+// Some hosts of this library are not allowed to allocate device memory once they are running:
+// an online filter process at the detector is started with a fixed GPU memory budget and must
+// not grow it per event, and a process that has handed the whole device to another framework's
+// memory pool would see cudaMalloc fail.  For them the per-block partial sums of the scan live
+// in this fixed array instead of in caller-provided scratch.  It is part of the library image:
+// every GPU that loads the library holds these 32 KiB until the process exits.
+constexpr int64_t STATIC_SCAN_MAX_N = 4194304;  // nodes per call (4096 blocks of 1024)
+constexpr int64_t STATIC_SCAN_MAX_BLOCKS = STATIC_SCAN_MAX_N / gn::SCAN_TILE;
+static __device__ __align__(256) int64_t g_static_scan_sums[STATIC_SCAN_MAX_BLOCKS];
+
+// `g_static_scan_sums` is only a host-side handle in host code; the device address has to be
+// asked for, once per device, with that device current.
+static int static_scan_scratch(int64_t** out) {
+  constexpr int MAX_DEVICES = 64;
+  static int64_t* addr[MAX_DEVICES] = {nullptr};
+  int dev = 0;
+  GN_CUDA(cudaGetDevice(&dev));
+  GN_CHECK_ARG(dev >= 0 && dev < MAX_DEVICES, "device ordinal %d not supported", dev);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    GN_CUDA(cudaGetSymbolAddress(&p, g_static_scan_sums));
+    addr[dev] = reinterpret_cast<int64_t*>(p);
+  }
+  *out = addr[dev];
+  return GN_OK;
+}
+
+extern "C" int gn_ell_row_offsets_noalloc(const int32_t* deg, int64_t N, int64_t* rowptr,
+                                          void* stream) {
+  GN_CHECK_ARG(N >= 0 && rowptr, "gn_ell_row_offsets_noalloc: bad arguments");
+  GN_CHECK_ARG(N <= STATIC_SCAN_MAX_N,
+               "gn_ell_row_offsets_noalloc: N=%lld exceeds the built-in scratch (max %lld nodes "
+               "per call); use gn_ell_row_offsets with caller-provided scratch",
+               (long long)N, (long long)STATIC_SCAN_MAX_N);
+  cudaStream_t st = as_stream(stream);
+  if (N == 0) {
+    GN_CUDA(cudaMemsetAsync(rowptr, 0, sizeof(int64_t), st));
+    return GN_OK;
+  }
+  GN_CHECK_ARG(deg, "gn_ell_row_offsets_noalloc: null pointer");
+  int64_t* sums = nullptr;
+  int rc = static_scan_scratch(&sums);
+  if (rc != GN_OK) return rc;
+  // every slot of `sums` that the apply pass reads is first written by the block-sum pass of
+  // this same call, so nothing has to be cleared between calls
+  return exclusive_scan_i32(deg, N, rowptr, sums, st);
+}
+
 extern "C" int gn_ell_to_coo(const int32_t* nbr, int32_t stride, const int32_t* deg,
                              const int64_t* rowptr, int64_t N, int64_t E, int64_t* edge_index,
                              void* stream) {

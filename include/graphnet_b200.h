@@ -110,6 +110,18 @@ size_t gn_scan_scratch_bytes(int64_t n);
 int gn_ell_row_offsets(const int32_t* deg, int64_t N, int64_t* rowptr,
                        void* scratch, size_t scratch_bytes, void* stream);
 
+/* Same result as gn_ell_row_offsets, for callers that may not allocate device memory while
+ * running (an online filter process with a fixed GPU memory budget; a host whose device
+ * memory all belongs to another framework's pool, where cudaMalloc fails): the partial sums
+ * live in a 32 KiB array built into the library instead of in caller scratch, so the call
+ * needs only its input and output.  No counterpart in the reference.
+ * Limit: N <= 4194304 nodes per call (larger N is rejected with GN_ERR_INVALID_ARGUMENT).
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress);
+ * make that first call before starting any stream capture.  All calls on a device share the
+ * array: calls whose kernels can overlap on the GPU (different streams) race - serialise them.
+ * Nothing needs clearing between calls. */
+int gn_ell_row_offsets_noalloc(const int32_t* deg, int64_t N, int64_t* rowptr, void* stream);
+
 /* The int64 COO `edge_index` [2, E] the reference API returns (row 0 = source j,
  * row 1 = target i; ordered by target, then rank) from ELL + its row offsets. */
 int gn_ell_to_coo(const int32_t* nbr, int32_t stride, const int32_t* deg,
