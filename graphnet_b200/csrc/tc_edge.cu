@@ -30,6 +30,7 @@
 // precede it; user graphs may have any degree) are handled by a second pass of the SAME kernel
 // over a compacted list of (node, slot base) groups, accumulating with red.global.add.
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include "tc_common.cuh"
 
@@ -74,6 +75,8 @@ struct EdgeParams {
   float* coords;            // [N, ncoord] fp32 copy of the columns selected by coord_mask, or null
   int ncoord;
   uint32_t coord_mask[8];
+  const void* w2;           // W2p [bnp, Kp] fp16 row-major (second-generation kernel reads it directly)
+  void* dbg;                // optional 8 x uint64 wait-time counters (GN_EDGE_DEBUG), else null
 };
 
 __device__ __forceinline__ uint4 ldg16(const __half* p) {
@@ -387,6 +390,12 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
   if (warp == 0) tmem_dealloc<512>(tmem_base);
 }
 
+}  // namespace tc
+}  // namespace gn
+#include "tc_edge2.cuh"
+namespace gn {
+namespace tc {
+
 // Graph (CSR or ELL) -> the group lists the main kernel consumes:
 //   ell[N, KP]            slots 0..KP-1 of every node (-1 padded)          (pass 1, group = node)
 //   ovf_node[], ovf_ell[] one entry per further block of KP in-edges of a node  (pass 2)
@@ -428,8 +437,29 @@ static int64_t edge_overflow_cap(const gn_graph* graph, int64_t N, int slots) {
   return graph->num_edges / slots + 1;
 }
 
+static __device__ unsigned long long g_edge_dbg[8];
+
+// diagnostic only (not part of include/graphnet_b200.h): copy out and clear the counters
+extern "C" int gn_debug_edge_counters(unsigned long long* host8) {
+  GN_CUDA(cudaDeviceSynchronize());
+  GN_CUDA(cudaMemcpyFromSymbol(host8, g_edge_dbg, sizeof(g_edge_dbg)));
+  unsigned long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  GN_CUDA(cudaMemcpyToSymbol(g_edge_dbg, zero, sizeof(zero)));
+  return GN_OK;
+}
+
+static bool edge_use_v1() {
+  static const bool v = getenv("GN_EDGE_V1") != nullptr;  // first-generation kernel (A/B runs)
+  return v;
+}
+// an ELL graph whose stride is a supported slot count is consumed in place: no lists, no 2nd pass
+static bool edge_direct_ell(const gn_graph* graph) {
+  return !edge_use_v1() && graph->ell_stride > 0 && tc::edge2_supported_slots(graph->ell_stride);
+}
+
 extern "C" size_t gn_tc_edge_scratch_bytes(const gn_graph* graph, int64_t N, int slots) {
   if (!graph || slots <= 0) return 0;
+  if (edge_direct_ell(graph)) return 16;
   const int64_t n = N > 0 ? N : 1;
   const int64_t cap = edge_overflow_cap(graph, n, slots);
   // ell [N, slots] + ovf_ell [cap, slots] + ovf_node [cap] + counter (16-byte padded)
@@ -448,8 +478,10 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
   GN_CHECK_ARG(Kp >= 32 && Kp % 32 == 0 && Kp <= tc::EK_MAX_CHUNKS * tc::EK_KCH,
                "gn_tc_edge_mlp_aggregate: padded hidden width %d not a multiple of 32 in [32,%d]",
                Kp, tc::EK_MAX_CHUNKS * tc::EK_KCH);
-  GN_CHECK_ARG(slots == 8 || slots == 16 || slots == 32,
-               "gn_tc_edge_mlp_aggregate: slots=%d (must be 8, 16 or 32)", slots);
+  GN_CHECK_ARG(tc::edge2_supported_slots(slots),
+               "gn_tc_edge_mlp_aggregate: slots=%d (must be 8, 9, 16, 17 or 32)", slots);
+  GN_CHECK_ARG(!edge_use_v1() || slots == 8 || slots == 16 || slots == 32,
+               "gn_tc_edge_mlp_aggregate: the first-generation kernel takes 8, 16 or 32 slots");
   GN_CHECK_ARG(ldp >= Kp && ldq >= Kp && ldp % 8 == 0 && ldq % 8 == 0 && ldo % 4 == 0 && ldo >= b,
                "gn_tc_edge_mlp_aggregate: bad leading dimensions");
   GN_CHECK_ARG(ncoord >= 0 && ncoord <= 16, "gn_tc_edge_mlp_aggregate: ncoord=%d", ncoord);
@@ -478,21 +510,33 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
                  "gn_tc_edge_mlp_aggregate: coordinate columns must be strictly increasing");
     p.coord_mask[coord_cols[t] >> 5] |= 1u << (coord_cols[t] & 31);
   }
-  const int64_t cap = edge_overflow_cap(graph, N, slots);
+  const bool direct = edge_direct_ell(graph);
+  if (direct) slots = graph->ell_stride;
+  const int64_t cap = direct ? 0 : edge_overflow_cap(graph, N, slots);
   int32_t* ell = reinterpret_cast<int32_t*>(scratch);
   int32_t* ovf_ell = ell + N * slots;
   int32_t* ovf_node = ovf_ell + cap * slots;
   int32_t* ovf_count = ovf_node + cap;
-  GN_CUDA(cudaMemsetAsync(ovf_count, 0, sizeof(int32_t), st));
-  tc::graph_to_groups_kernel<<<(unsigned)ceil_div(N * slots, 256), 256, 0, st>>>(
-      g, N, slots, ell, ovf_node, ovf_ell, ovf_count, cap);
-  GN_LAUNCH_CHECK();
+  if (!direct) {
+    GN_CUDA(cudaMemsetAsync(ovf_count, 0, sizeof(int32_t), st));
+    tc::graph_to_groups_kernel<<<(unsigned)ceil_div(N * slots, 256), 256, 0, st>>>(
+        g, N, slots, ell, ovf_node, ovf_ell, ovf_count, cap);
+    GN_LAUNCH_CHECK();
+  }
 
   CUtensorMap tmW2;
-  rc = make_tmap_f16_2d(&tmW2, W2p, (uint64_t)bnp, (uint64_t)Kp, (uint64_t)Kp, (uint32_t)bnp,
-                        tc::EK_KCH, 64);
-  if (rc != GN_OK) return rc;
+  if (edge_use_v1()) {
+    rc = make_tmap_f16_2d(&tmW2, W2p, (uint64_t)bnp, (uint64_t)Kp, (uint64_t)Kp, (uint32_t)bnp,
+                          tc::EK_KCH, 64);
+    if (rc != GN_OK) return rc;
+  }
 
+  p.w2 = W2p;
+  // GN_EDGE_DEBUG=1: the second-generation kernel accumulates wait-time counters (tc_edge2.cuh)
+  // into g_edge_dbg, read back with the undeclared diagnostic export gn_debug_edge_counters()
+  static const bool dbg_on = getenv("GN_EDGE_DEBUG") != nullptr;
+  p.dbg = nullptr;
+  if (dbg_on) GN_CUDA(cudaGetSymbolAddress(&p.dbg, g_edge_dbg));
   p.pmat = reinterpret_cast<const __half*>(P);
   p.ldp = ldp;
   p.qmat = reinterpret_cast<const __half*>(Q);
@@ -507,17 +551,19 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
   p.ldo = ldo;
   p.coords = ncoord > 0 ? coords : nullptr;
   p.ncoord = ncoord;
-  const int npt = tc::EK_ROWS / slots;
+  const bool use_v1 = edge_use_v1();
+  const int npt = (use_v1 ? tc::EK_ROWS : tc::E2_ROWS) / slots;
 
   int dev = 0, sms = 0;
   GN_CUDA(cudaGetDevice(&dev));
   GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const size_t smem = (size_t)p.nch * bnp * 64 + tc::EK_STAGES * tc::EK_STAGE_BYTES +
-                      sizeof(tc::EdgeBarriers) + 1024;
+  const size_t smem1 = (size_t)p.nch * bnp * 64 + tc::EK_STAGES * tc::EK_STAGE_BYTES +
+                       sizeof(tc::EdgeBarriers) + 1024;
+  const size_t smem2 = tc::edge2_smem_bytes(Kp, slots);
   for (int pass = 0; pass < 2; ++pass) {
     int64_t max_tiles;
     if (pass == 0) {
-      p.ell = ell;
+      p.ell = direct ? graph->col : ell;
       p.group_node = nullptr;
       p.group_count = nullptr;
       p.accumulate = 0;
@@ -531,15 +577,43 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
       max_tiles = ceil_div(cap, npt);
     }
     const unsigned grid = (unsigned)(max_tiles < sms ? max_tiles : sms);
-#define GN_EDGE_CASE(KP_)                                                                        \
+#define GN_EDGE_CASE1(KP_)                                                                       \
   {                                                                                              \
     auto kern = tc::edge_mlp_aggregate_kernel<KP_>;                                              \
-    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    kern<<<grid, tc::EK_THREADS, smem, st>>>(tmW2, p);                                           \
+    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1)); \
+    kern<<<grid, tc::EK_THREADS, smem1, st>>>(tmW2, p);                                          \
   }
-    if (slots == 8) GN_EDGE_CASE(8)
-    else if (slots == 16) GN_EDGE_CASE(16)
-    else GN_EDGE_CASE(32)
+#define GN_EDGE_LAUNCH2(KP_, ACC_, F16_)                                                         \
+  {                                                                                              \
+    auto kern = tc::edge_mlp_aggregate_v2_kernel<KP_, ACC_, F16_>;                               \
+    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2)); \
+    kern<<<grid, tc::E2_THREADS, smem2, st>>>(p);                                                \
+  }
+#define GN_EDGE_CASE2(KP_)                                                                       \
+  {                                                                                              \
+    if (p.accumulate) {                                                                          \
+      if (p.out_f16) GN_EDGE_LAUNCH2(KP_, true, true) else GN_EDGE_LAUNCH2(KP_, true, false)     \
+    } else {                                                                                     \
+      if (p.out_f16) GN_EDGE_LAUNCH2(KP_, false, true) else GN_EDGE_LAUNCH2(KP_, false, false)   \
+    }                                                                                            \
+  }
+    if (use_v1) {
+      if (slots == 8) GN_EDGE_CASE1(8)
+      else if (slots == 16) GN_EDGE_CASE1(16)
+      else GN_EDGE_CASE1(32)
+    } else {
+      switch (slots) {
+        case 8: GN_EDGE_CASE2(8) break;
+        case 9: GN_EDGE_CASE2(9) break;
+        case 16: GN_EDGE_CASE2(16) break;
+        case 17: GN_EDGE_CASE2(17) break;
+        default: GN_EDGE_CASE2(32) break;
+      }
+    }
+#undef GN_EDGE_CASE1
+#undef GN_EDGE_CASE2
+#undef GN_EDGE_LAUNCH2
+#define GN_EDGE_CASE(x)
 #undef GN_EDGE_CASE
     GN_LAUNCH_CHECK();
   }

@@ -1,0 +1,466 @@
+// Fused EdgeConv message + aggregation, second generation ("transposed" formulation).
+//
+//   D^T[ch, e] = sum_k W2[ch, k] * h[e, k],   h[e] = ReLU(P_i(e) + Q_j(e))
+//   out[i, ch] = sum_{e in N(i)} ReLU(D^T[ch, e])
+//
+// W2 is the A operand and lives in TENSOR MEMORY for the whole kernel (written once with
+// tcgen05.st: lane = output channel, 32-bit column = two consecutive k), so shared memory holds
+// no weights at all.  The 64-edge tile h is the B operand (N = 64) in the 64B-swizzled K-major
+// layout.  What this buys over the first generation (tc_edge.cu, W2 resident in smem):
+//   * shared memory is free for a DEEP ASYNCHRONOUS GATHER: eight gather warps copy the neighbour
+//     rows Q_j (and node rows P_i) with 16-byte cp.async into a 4-deep ring of 32-row stages that
+//     complete on mbarriers; the gather latency (L2 / HBM) is hidden by the ring, not by registers
+//     (one cp.async.bulk per 704-byte row was tried first: the per-copy cost of the TMA unit made
+//     it slower than the first-generation kernel);
+//   * edges are COLUMNS of the accumulator: a thread owns one output channel, so the per-node
+//     sum over its KP edges is a plain in-register reduction (no shuffles), and the 32 lanes of
+//     a warp write 32 consecutive channels of a node (coalesced);
+//   * tensor-core operand traffic from shared memory drops from 96 to 64 B/clk.
+//     - and KP need not be a power of two: with KP = k+1 = 9 slots per node a kNN graph needs
+//     no overflow pass at all;
+// Tile = 64 ELL rows = floor(64/KP) nodes.  Warp roles (17 warps): 0-7 epilogue (warp>>2 =
+// channel block of 128, warp&3 = TMEM lane quadrant), 8-11 h builders (16 rows each), 12-15
+// gather warps (one per ring stage), 16 tcgen05.mma issuer.  TMEM columns: [0,Kp/2) W2 block 0, [176,176+Kp/2) W2 block 1,
+// [352,416) D block 0, [416,480) D block 1 - the epilogue of one channel block overlaps the
+// MMAs of the other.
+#pragma once
+
+namespace gn {
+namespace tc {
+
+constexpr int E2_ROWS = 64;          // edge rows (accumulator columns) per tile
+constexpr int E2_HALF = 32;          // rows per gather stage
+constexpr int E2_QSTAGES = 4;        // gather ring depth (half tiles): 2 tiles of lookahead
+constexpr int E2_HBUFS = 2;          // h tiles (B operand) in shared memory
+constexpr int E2_EPI_WARPS = 8;      // (channel block, TMEM lane quadrant)
+constexpr int E2_BLD_WARPS = 4;      // h builders: 16 tile rows per warp
+constexpr int E2_GAT_WARPS = E2_QSTAGES;  // one gather warp owns each ring stage
+constexpr int E2_MMA_WARP = E2_EPI_WARPS + E2_BLD_WARPS + E2_GAT_WARPS;  // warp 16
+constexpr int E2_THREADS = 32 * (E2_MMA_WARP + 1);                       // 544
+constexpr int E2_TMEM_A1 = 176;      // column offset of W2 block 1
+constexpr int E2_TMEM_D0 = 352;
+constexpr int E2_TMEM_D1 = 416;
+
+__host__ __device__ constexpr int e2_pmax(int KP) { return E2_HALF / KP + 2; }  // P rows per stage
+
+struct __align__(16) Edge2Shared {
+  uint64_t q_full[E2_QSTAGES];
+  uint64_t q_empty[E2_QSTAGES];
+  uint64_t h_full[2];
+  uint64_t h_empty[2];
+  uint64_t d_full[2];
+  uint64_t d_empty[2];
+  uint32_t tmem_base;
+  uint32_t pad_;
+  uint8_t row_valid[E2_QSTAGES][E2_HALF];
+};
+
+// 16-byte asynchronous global -> shared copy (LDGSTS), L2 only
+__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+// the mbarrier receives one arrival when all cp.async issued so far by this thread have landed
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+
+__device__ __forceinline__ void tmem_st_32x32_x16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+      "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]^T  (A: lane = row m, 32-bit column = 2 consecutive k)
+__device__ __forceinline__ void mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc,
+                                           uint32_t idesc, bool accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"((uint32_t)accumulate)
+      : "memory");
+}
+
+// the same with the accumulate flag fixed at compile time (no predicate set-up per MMA)
+template <bool ACC>
+__device__ __forceinline__ void mma_f16_ts_c(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc,
+                                             uint32_t idesc) {
+  if (ACC) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.eq.u32 p, 0, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(bdesc), "r"(idesc)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, 0, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(bdesc), "r"(idesc)
+        : "memory");
+  }
+}
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"(addr));
+  return r;
+}
+
+// mbar_wait that also accumulates the cycles spent waiting (profiling builds only)
+template <bool RELAXED = false>
+__device__ __forceinline__ void mbar_wait_t(uint64_t* bar, uint32_t parity, long long& acc,
+                                            bool timed) {
+  const long long t0 = timed ? clock64() : 0;
+  if (RELAXED) mbar_wait_relaxed(bar, parity);
+  else mbar_wait(bar, parity);
+  if (timed) acc += clock64() - t0;
+}
+
+// ACC: second pass (group lists, red.add into out); F16: output element type (else bf16)
+template <int KP, bool ACC, bool F16>
+__global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(const EdgeParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  constexpr int NPT = E2_ROWS / KP;    // nodes (groups) per tile; KP need not be a power of two
+  constexpr int USED = NPT * KP;       // tile rows that carry slots (the rest stay zero)
+  constexpr int PMAX = e2_pmax(KP);    // node rows a 32-row stage can touch
+  const int nch = p.nch;
+  const int rowbytes = p.Kp * 2;
+  const int htile_bytes = nch * (E2_ROWS * 64);           // [kc][64 rows][64 B]
+  const int qstage_bytes = (E2_HALF + PMAX) * rowbytes;   // 32 Q rows then PMAX P rows
+  uint8_t* h_smem = smem;                                 // 2 tiles
+  uint8_t* q_smem = smem + E2_HBUFS * htile_bytes;        // E2_QSTAGES stages
+  Edge2Shared* sh = reinterpret_cast<Edge2Shared*>(q_smem + E2_QSTAGES * qstage_bytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t num_groups = p.group_count ? (int64_t)__ldg(p.group_count) : p.N;
+  const int64_t num_tiles = (num_groups + NPT - 1) / NPT;
+  if ((int64_t)blockIdx.x >= num_tiles) return;  // uniform per CTA, before any barrier
+  const int nblk = p.bnp > 128 ? 2 : 1;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < E2_QSTAGES; ++s) {
+      mbar_init(&sh->q_full[s], 32 + 1);              // the stage's gather warp
+      mbar_init(&sh->q_empty[s], E2_BLD_WARPS / 2);
+    }
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&sh->h_full[b], E2_BLD_WARPS);
+      mbar_init(&sh->h_empty[b], 1);
+      mbar_init(&sh->d_full[b], 1);
+      mbar_init(&sh->d_empty[b], E2_EPI_WARPS / 2);
+    }
+    fence_mbar_init();
+  }
+  if (warp == E2_MMA_WARP) tmem_alloc<512>(&sh->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sh->tmem_base;
+
+  // ---- W2 -> tensor memory (once): epilogue warp (blk, q) writes lanes 32q.. of block blk;
+  // each lane reads its own weight row with 16-byte loads
+  if (warp < E2_EPI_WARPS) {
+    const int blk = warp >> 2, q = warp & 3;
+    if (blk < nblk) {
+      const int ch = blk * 128 + q * 32 + lane;
+      const uint4* wrow = reinterpret_cast<const uint4*>(
+          reinterpret_cast<const __half*>(p.w2) + (int64_t)ch * p.Kp);
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (blk ? E2_TMEM_A1 : 0);
+      for (int cc = 0; cc < nch; ++cc) {  // 4 x 16 bytes = 32 fp16 = one K chunk = 16 columns
+        uint32_t r[16];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const uint4 w = ch < p.bnp ? __ldg(wrow + cc * 4 + t) : make_uint4(0, 0, 0, 0);
+          r[4 * t] = w.x; r[4 * t + 1] = w.y; r[4 * t + 2] = w.z; r[4 * t + 3] = w.w;
+        }
+        tmem_st_32x32_x16(taddr + cc * 16, r);
+      }
+      tmem_st_wait();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+
+  const int64_t my_tiles = (num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+  const uint32_t total_halves = (uint32_t)(2 * my_tiles);
+  // optional wait-time accounting: dbg[0..7] = cycles waited on q_empty (gather), q_full and
+  // h_empty (builders), h_full and d_empty (MMA), d_full (epilogue), total cycles, tiles
+  const bool timed = p.dbg != nullptr;
+  long long w0 = 0, w1 = 0;
+  const long long t_start = clock64();
+
+  if (warp >= E2_EPI_WARPS + E2_BLD_WARPS && warp < E2_MMA_WARP) {
+    // ================================================================ gather warps
+    // Stage s of the ring belongs to gather warp s; half-stage g2 (= 2*tile_iter + half) lives
+    // in stage g2 % 4, so a warp only ever waits for the release of its own previous use.  A stage holds the 32 Q rows of the half tile, then the P rows of the nodes it
+    // touches, Kp fp16 each, filled with 16-byte cp.async pieces (one row per warp iteration,
+    // lanes = consecutive pieces).  Every thread makes the stage's mbarrier count one arrival
+    // when its copies have landed; one plain arrive per warp publishes the row-valid flags.
+    const int so = warp - (E2_EPI_WARPS + E2_BLD_WARPS);  // the stage this warp owns
+    const int ppr = rowbytes / 16;                        // 16-byte pieces per row (<= 44)
+    const bool two = lane + 32 < ppr;
+    const uint32_t stage = smem_u32(q_smem) + so * qstage_bytes + lane * 16;
+    int32_t j_nx = -1, pn_nx = -1;
+    auto fetch_ids = [&](uint32_t g2) {
+      j_nx = -1;
+      pn_nx = -1;
+      if (g2 >= total_halves) return;
+      const int64_t tile = blockIdx.x + (int64_t)(g2 >> 1) * gridDim.x;
+      const int hs = g2 & 1;
+      const int rt = hs * E2_HALF + lane;                 // row in tile
+      const int64_t grp = tile * NPT + rt / KP;
+      if (rt < USED && grp < num_groups) j_nx = __ldg(p.ell + tile * USED + rt);
+      const int nfirst = (hs * E2_HALF) / KP;
+      const int64_t pg = tile * NPT + nfirst + lane;
+      if (lane < PMAX && nfirst + lane < NPT && pg < num_groups)
+        pn_nx = p.group_node ? __ldg(p.group_node + pg) : (int32_t)pg;
+    };
+    fetch_ids(so);
+    for (uint32_t g2 = so; g2 < total_halves; g2 += E2_QSTAGES) {
+      const int32_t j = j_nx, pn = pn_nx;
+      fetch_ids(g2 + E2_QSTAGES);  // ids of this pair's next half-stage, in flight meanwhile
+      mbar_wait_t<true>(&sh->q_empty[so], ((g2 / E2_QSTAGES) & 1) ^ 1, w0, timed);
+      sh->row_valid[so][lane] = j >= 0 ? 1 : 0;
+      // four rows per step (independent address chains); lanes = consecutive 16-byte pieces
+#pragma unroll 1
+      for (int r0 = 0; r0 < E2_HALF; r0 += 4) {
+        int32_t src[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) src[i] = __shfl_sync(0xffffffffu, j, r0 + i);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (src[i] >= 0) {
+            const __half* g = p.qmat + (int64_t)src[i] * p.ldq + lane * 8;
+            const uint32_t d = stage + (uint32_t)((r0 + i) * rowbytes);
+            if (lane < ppr) cp_async16(d, g);
+            if (two) cp_async16(d + 512, g + 256);
+          }
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < PMAX; ++r) {
+        const int32_t src = __shfl_sync(0xffffffffu, pn, r);
+        if (src >= 0) {
+          const __half* g = p.pmat + (int64_t)src * p.ldp + lane * 8;
+          const uint32_t d = stage + (uint32_t)((E2_HALF + r) * rowbytes);
+          if (lane < ppr) cp_async16(d, g);
+          if (two) cp_async16(d + 512, g + 256);
+        }
+      }
+      cp_async_arrive_noinc(&sh->q_full[so]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sh->q_full[so]);
+    }
+  } else if (warp == E2_MMA_WARP) {
+    // =================================================================== MMA issuer
+    const uint32_t idesc = make_idesc_f16(128, E2_ROWS);
+    const uint32_t h_addr = smem_u32(h_smem);
+    for (int64_t it = 0; it < my_tiles; ++it) {
+      const uint32_t hb = (uint32_t)(it % E2_HBUFS);
+      mbar_wait_t(&sh->h_full[hb], (uint32_t)((it / E2_HBUFS) & 1), w0, timed);
+      for (int blk = 0; blk < nblk; ++blk) {
+        mbar_wait_t(&sh->d_empty[blk], (uint32_t)(it & 1) ^ 1, w1, timed);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t d_addr = tmem_base + (blk ? E2_TMEM_D1 : E2_TMEM_D0);
+          const uint32_t a_addr = tmem_base + (blk ? E2_TMEM_A1 : 0);
+          // tight issue loop: one descriptor per tile, then constant increments
+          // (K chunk = 4096 B of B -> +256 in descriptor units, = 16 TMEM columns of A;
+          //  half chunk (16 k) = 32 B -> +2, = 8 columns)
+          uint64_t bdesc = make_kmajor_desc<64>(h_addr + hb * htile_bytes);
+          uint32_t a = a_addr;
+          mma_f16_ts_c<false>(d_addr, a, bdesc, idesc);
+          mma_f16_ts_c<true>(d_addr, a + 8, bdesc + 2, idesc);
+#pragma unroll 1
+          for (int kc = 1; kc < nch; ++kc) {
+            bdesc += (E2_ROWS * 64) >> 4;
+            a += 16;
+            mma_f16_ts_c<true>(d_addr, a, bdesc, idesc);
+            mma_f16_ts_c<true>(d_addr, a + 8, bdesc + 2, idesc);
+          }
+          mma_commit(&sh->d_full[blk]);
+          if (blk == nblk - 1) mma_commit(&sh->h_empty[hb]);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= E2_EPI_WARPS) {
+    // ==================================================================== h builders
+    // warp bw owns rows 16 bw .. 16 bw + 15 of the tile; lane = (row rr = lane >> 2, 16-byte
+    // piece c4 = lane & 3 of the 64-byte K chunk), two rows per lane (rr and rr + 8).
+    // Quarter-warps touch 2 rows x 64 B: conflict free.
+    const int bw = warp - E2_EPI_WARPS;  // 0..3
+    const int hs = bw >> 1;              // which gather stage of the tile
+    const int rr = lane >> 2, c4 = lane & 3;
+    const uint32_t q_addr = smem_u32(q_smem);
+    const uint32_t h_addr = smem_u32(h_smem);
+    const int nfirst = (hs * E2_HALF) / KP;
+    int srow[2];
+    uint32_t dst_off[2], q_off[2], p_off[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int row = bw * 16 + rr + 8 * u;           // row in tile
+      srow[u] = (bw & 1) * 16 + rr + 8 * u;           // row in stage
+      dst_off[u] = (uint32_t)(row * 64 + ((c4 ^ ((row >> 1) & 3)) << 4));
+      q_off[u] = (uint32_t)(srow[u] * rowbytes + c4 * 16);
+      const int pslot = row < USED ? row / KP - nfirst : 0;
+      p_off[u] = (uint32_t)((E2_HALF + pslot) * rowbytes + c4 * 16);
+    }
+    for (int64_t it = 0; it < my_tiles; ++it) {
+      const uint32_t g2 = (uint32_t)(2 * it + hs);
+      const uint32_t s = g2 % E2_QSTAGES;
+      const uint32_t hb = (uint32_t)(it % E2_HBUFS);
+      mbar_wait_t(&sh->q_full[s], (g2 / E2_QSTAGES) & 1, w0, timed);
+      const bool valid0 = sh->row_valid[s][srow[0]] != 0;
+      const bool valid1 = sh->row_valid[s][srow[1]] != 0;
+      mbar_wait_t(&sh->h_empty[hb], (uint32_t)((it / E2_HBUFS) & 1) ^ 1, w1, timed);
+      const uint32_t sbase = q_addr + s * qstage_bytes;
+      const uint32_t dbase = h_addr + hb * htile_bytes;
+      // four K chunks per step: all eight loads are issued before the first use
+#pragma unroll 1
+      for (int kc0 = 0; kc0 < nch; kc0 += 4) {
+        uint4 Q[4][2], P[4][2];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const bool ld = (u == 0 ? valid0 : valid1) && kc0 + i < nch;
+            Q[i][u] = ld ? lds128(sbase + q_off[u] + (kc0 + i) * 64) : make_uint4(0, 0, 0, 0);
+            P[i][u] = ld ? lds128(sbase + p_off[u] + (kc0 + i) * 64) : make_uint4(0, 0, 0, 0);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (kc0 + i < nch) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              // empty slots: P = Q = 0 -> h = 0 (the "ones" columns included)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(
+                               dbase + dst_off[u] + (kc0 + i) * (E2_ROWS * 64)),
+                           "r"(relu_add_f16x2(P[i][u].x, Q[i][u].x)),
+                           "r"(relu_add_f16x2(P[i][u].y, Q[i][u].y)),
+                           "r"(relu_add_f16x2(P[i][u].z, Q[i][u].z)),
+                           "r"(relu_add_f16x2(P[i][u].w, Q[i][u].w))
+                           : "memory");
+            }
+          }
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&sh->h_full[hb]);
+        mbar_arrive(&sh->q_empty[s]);
+      }
+    }
+  } else {
+    // ====================================================================== epilogue
+    // warp (blk, q) reads TMEM lanes 32q.. of channel block blk: lane = output channel, the 64
+    // columns are the tile's edge rows, KP consecutive columns per node -> plain in-register
+    // sums; the 32 lanes store 32 consecutive channels of a node (coalesced)
+    const int blk = warp >> 2, q = warp & 3;
+    if (blk < nblk) {
+      const int ch = blk * 128 + q * 32 + lane;
+      const bool ch_ok = ch < p.b;
+      int crank = -1;  // position of this channel among the kNN coordinate columns
+      if (p.coords != nullptr && ch_ok && ((p.coord_mask[ch >> 5] >> (ch & 31)) & 1u)) {
+        crank = __popc(p.coord_mask[ch >> 5] & ((1u << (ch & 31)) - 1u));
+        for (int w = 0; w < (ch >> 5); ++w) crank += __popc(p.coord_mask[w]);
+      }
+      const uint32_t d_addr =
+          tmem_base + ((uint32_t)(q * 32) << 16) + (blk ? E2_TMEM_D1 : E2_TMEM_D0);
+      uint16_t* const out_ch = reinterpret_cast<uint16_t*>(p.out) + ch;
+      for (int64_t it = 0; it < my_tiles; ++it) {
+        const int64_t tile = blockIdx.x + it * gridDim.x;
+        const int64_t grp0 = tile * NPT;
+        const int nvalid = (int)min((int64_t)NPT, num_groups - grp0);  // groups of this tile
+        mbar_wait_t<true>(&sh->d_full[blk], (uint32_t)(it & 1), w0, timed);
+        tc_fence_after();
+        float v0[32], v1[32];
+        tmem_ld_32x32(d_addr, v0);
+        tmem_ld_32x32(d_addr + 32, v1);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sh->d_empty[blk]);  // values are in registers now
+        float sums[NPT];
+#pragma unroll
+        for (int n = 0; n < NPT; ++n) {
+          // two interleaved partial sums shorten the dependent FADD chain
+          float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+          for (int t = 0; t < KP; ++t) {
+            const int col = n * KP + t;
+            const float r = fmaxf(col < 32 ? v0[col & 31] : v1[col & 31], 0.f);
+            if (t & 1) s1 += r; else s0 += r;
+          }
+          sums[n] = s0 + s1;
+        }
+        if (ch_ok) {
+          if (!ACC) {
+            // pass 1: group g is node g -> consecutive rows of `out`
+            uint16_t* dst = out_ch + grp0 * p.ldo;
+#pragma unroll
+            for (int n = 0; n < NPT; ++n) {
+              if (n < nvalid) dst[(int64_t)n * p.ldo] = pack1_16(sums[n], F16);
+            }
+            if (crank >= 0) {
+#pragma unroll
+              for (int n = 0; n < NPT; ++n)
+                if (n < nvalid) p.coords[(grp0 + n) * p.ncoord + crank] = sums[n];
+            }
+          } else {
+#pragma unroll
+            for (int n = 0; n < NPT; ++n) {
+              if (n < nvalid) {
+                const int64_t node = __ldg(p.group_node + grp0 + n);
+                red_add1_16(out_ch + node * p.ldo, sums[n], F16);
+                if (crank >= 0) atomicAdd(p.coords + node * p.ncoord + crank, sums[n]);
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  if (timed && lane == 0) {
+    unsigned long long* d = reinterpret_cast<unsigned long long*>(p.dbg);
+    if (warp >= E2_EPI_WARPS + E2_BLD_WARPS && warp < E2_MMA_WARP) {
+      atomicAdd(d + 0, (unsigned long long)w0);
+    } else if (warp == E2_MMA_WARP) {
+      atomicAdd(d + 3, (unsigned long long)w0);
+      atomicAdd(d + 4, (unsigned long long)w1);
+      atomicAdd(d + 6, (unsigned long long)(clock64() - t_start));
+      atomicAdd(d + 7, (unsigned long long)my_tiles);
+    } else if (warp >= E2_EPI_WARPS) {
+      atomicAdd(d + 1, (unsigned long long)w0);
+      atomicAdd(d + 2, (unsigned long long)w1);
+    } else {
+      atomicAdd(d + 5, (unsigned long long)w0);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == E2_MMA_WARP) tmem_dealloc<512>(tmem_base);
+}
+
+inline size_t edge2_smem_bytes(int Kp, int slots) {
+  const int nch = Kp / 32;
+  return (size_t)E2_HBUFS * nch * (E2_ROWS * 64) +
+         (size_t)E2_QSTAGES * (E2_HALF + e2_pmax(slots)) * (Kp * 2) + sizeof(Edge2Shared) + 1024;
+}
+inline bool edge2_supported_slots(int s) { return s == 8 || s == 9 || s == 16 || s == 17 || s == 32; }
+
+}  // namespace tc
+}  // namespace gn

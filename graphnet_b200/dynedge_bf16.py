@@ -29,10 +29,12 @@ def _round_up(v: int, m: int) -> int:
 
 
 def _slots(k: int) -> int:
-    s = 8
-    while s < k and s < 32:
-        s *= 2
-    return s
+    """Slots per node of the edge kernel: the smallest supported count >= k+1 (in-degree of a
+    kNN graph is at most k+1), so no second pass is needed."""
+    for s in (8, 9, 16, 17, 32):
+        if s >= k + 1:
+            return s
+    return 32
 
 
 class _ConvPack:

@@ -207,8 +207,9 @@ int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t ldw, int ab_
  * columns; P[:,a] = P[:,a+1] = 1, Q pads = 0).  Q is the gathered operand: keeping it in its
  * own dense array lets it stay L2 resident.  W2p [b16, Kp] fp16 row-major (b16 = b rounded
  * up to 16; columns a, a+1 hold b2 split into fp16 hi/lo parts, remaining pads 0).
- * `slots` in {8,16,32}: in-edges per node handled in the first pass (>= the usual in-degree);
+ * `slots` in {8,9,16,17,32}: in-edges per node handled in the first pass (k+1 for a kNN graph);
  * further in-edges are handled by a second pass over a compacted list, any degree is correct.
+ * An ELL graph whose stride is one of those values is consumed in place (slots = stride).
  * out [N, ldo] of out_dtype (GN_BF16 / GN_F16).  If ncoord > 0, the fp32 (unrounded) values of the columns listed in
  * the HOST array coord_cols (strictly increasing) are also written to coords [N, ncoord]
  * for the next kNN.  scratch: gn_tc_edge_scratch_bytes(graph, N, slots) bytes (graph lists). */

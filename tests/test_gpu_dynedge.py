@@ -53,32 +53,70 @@ def _data(g):
 
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_conv_layers_teacher_forced_fp32(name):
+    """Every EdgeConv layer on the GOLDEN inputs and the GOLDEN graph of that layer: isolates the
+    kernels from the (chaotic) effect of near-tie flips in the dynamic graphs.  Strict: 1e-5."""
+    import graphnet_b200.ops as ops
+    g = load_golden(name)
+    m, spec, sd = _model(g)
+    N = g["x"].shape[0]
+    x_in = torch.cat([g["x"], g["global_variables"][g["batch"]]], 1) \
+        if not spec.add_global_variables_after_pooling else g["x"]
+    graphs = [g["edge_index"]] + [g[f"graph{i}"] for i in range(1, len(spec.dynedge_layer_sizes))]
+    for i, conv in enumerate(m._conv_layers):
+        out = conv._conv_f32(x_in.to(DEV).contiguous(), ops.coo_to_csr(graphs[i].to(DEV), N)).cpu()
+        assert rel_l2(out, g[f"conv{i}"]) < 1e-5, f"conv{i}"
+        # and the graph rebuilt from the golden latents is bit-exact
+        ptr, _ = ops.batch_to_ptr(g["batch"].to(DEV), g["n_pulses"].shape[0])
+        ell = ops.knn_graph_ell(g[f"conv{i}"].to(DEV).contiguous(), conv.nb_neighbors, ptr, [0, 1, 2])
+        assert torch.equal(ops.ell_to_coo(ell).cpu(), g[f"graph{i + 1}"])
+        x_in = g[f"conv{i}"]
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
 def test_forward_fp32_matches_golden(name):
+    """Free-running forward.  The dynamic graphs are rebuilt from latents that differ from the CPU
+    run by fp32 summation order (~3e-7), so a handful of near-tied neighbours swap; rows whose
+    whole history is swap-free must agree to 1e-4, the rest (and everything downstream of them)
+    is bounded more loosely and every swap is verified to be a near-tie."""
     import graphnet_b200.ops as ops
     g = load_golden(name)
     m, spec, sd = _model(g)
     out, inter = m._forward_f32(_data(g), return_intermediates=True)
-    F = g["x"].shape[1]
+    N = g["x"].shape[0]
     D0 = spec.nb_conv_inputs
     skip = inter["skip"].cpu()
     off = D0
+    affected = torch.zeros(N, dtype=torch.bool)   # rows of the current layer input that may differ
+    graph_in = g["edge_index"]
+    any_flip = False
     for i, sizes in enumerate(spec.dynedge_layer_sizes):
         b = sizes[-1]
         conv = skip[:, off:off + b]
-        assert rel_l2(conv, g[f"conv{i}"]) < FP32_TOL, f"conv{i}"
-        # dynamic graph of this layer: identical unless a near-tie flipped; report exactness
+        # conv_i[t] depends on x[t] and x[j] for in-neighbours j (golden graph == ours on clean rows)
+        hit = affected.clone()
+        hit[graph_in[1][affected[graph_in[0]]]] = True
+        clean = ~hit
+        assert rel_l2(conv[clean], g[f"conv{i}"][clean]) < FP32_TOL, f"conv{i} (swap-free rows)"
+        assert rel_l2(conv, g[f"conv{i}"]) < 2e-3, f"conv{i} (all rows)"
         ei = ops.ell_to_coo(inter["graphs"][i]).cpu()
         want = g[f"graph{i + 1}"]
         assert_same_graph_up_to_near_ties(ei, want, g[f"conv{i}"][:, :3], f"graph{i + 1}")
+        flipped = (ei[0] != want[0])
+        any_flip |= bool(flipped.any())
+        affected = hit.clone()
+        affected[want[1][flipped]] = True  # these rows aggregate over a different neighbour set
+        graph_in = want
         off += b
-    assert rel_l2(inter["post"].cpu(), g["post"]) < FP32_TOL
+    tol = FP32_TOL if not any_flip else 2e-3
+    assert rel_l2(inter["post"].cpu(), g["post"]) < tol
     if "pooled" in g:
         C = g["pooled"].shape[1]
-        assert rel_l2(inter["pooled"].cpu()[:, :C], g["pooled"]) < FP32_TOL
+        assert rel_l2(inter["pooled"].cpu()[:, :C], g["pooled"]) < tol
         if spec.add_global_variables_after_pooling:
             assert torch.equal(inter["pooled"][:, C:], inter["global_variables"])
     assert out.shape == g["out"].shape
-    assert rel_l2(out.cpu(), g["out"]) < FP32_TOL
+    assert rel_l2(out.cpu(), g["out"]) < tol
     # public call gives the same tensor
     assert torch.equal(m(_data(g)), out)
 
