@@ -15,6 +15,8 @@
 //   3. out[i] = acc   (sum / mean / max / min over the node's in-edges)
 #include <cuda_fp16.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace gn {
@@ -88,14 +90,72 @@ __global__ void __launch_bounds__(LIN_THREADS) linear_f32_kernel(
   for (int i = 0; i < RM; ++i) {
     const int64_t m = m0 + ty * RM + i;
     if (m >= M) continue;
+    const int nb = n0 + tx * RN;
+    OutT* dst = C + m * ldc + nb;
+    if (RN == 4 && sizeof(OutT) == 2 && nb + 4 <= N &&
+        (reinterpret_cast<uintptr_t>(dst) & 7) == 0) {
+      // four consecutive 16-bit outputs: one 8-byte store
+      OutT o[4];
 #pragma unroll
-    for (int j = 0; j < RN; ++j) {
-      const int n = n0 + tx * RN + j;
-      if (n < N) {
-        float v = acc[i][j] + (bias ? bias[n] : 0.f);
-        C[m * ldc + n] = cvt_out<OutT>(activate<ACT>(v));
+      for (int j = 0; j < 4; ++j)
+        o[j] = cvt_out<OutT>(activate<ACT>(acc[i][j] + (bias ? bias[nb + j] : 0.f)));
+      *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(o);
+    } else {
+#pragma unroll
+      for (int j = 0; j < RN; ++j) {
+        const int n = nb + j;
+        if (n < N) {
+          float v = acc[i][j] + (bias ? bias[n] : 0.f);
+          C[m * ldc + n] = cvt_out<OutT>(activate<ACT>(v));
+        }
       }
     }
+  }
+}
+
+// Small-K variant (K <= 32, 16-bit output): the first EdgeConv's node GEMM has K = 2F+5 = 19
+// and is store bound (N*Kp*2 bytes out).  One thread owns one input row (K values in
+// registers) and walks the output columns 8 at a time; W^T (K x N) sits in shared memory and is
+// read with warp-uniform addresses (broadcast, one wavefront per load); one 16-byte store per
+// 8 outputs.
+constexpr int SK_MAXK = 32;
+template <typename OutT, int KMAX>
+__global__ void __launch_bounds__(128) linear_smallk_kernel(
+    const float* __restrict__ A, int64_t lda, const float* __restrict__ W,
+    const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K) {
+  extern __shared__ __align__(16) float s_wt[];  // [K][N] then bias [N]
+  float* s_b = s_wt + (size_t)K * N;
+  for (int i = threadIdx.x; i < N * K; i += blockDim.x) {
+    const int n = i / K, k = i - n * K;
+    s_wt[k * N + n] = W[i];
+  }
+  for (int i = threadIdx.x; i < N; i += blockDim.x) s_b[i] = bias ? bias[i] : 0.f;
+  __syncthreads();
+  const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= M) return;
+  float a[KMAX];
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) a[k] = k < K ? __ldg(A + m * lda + k) : 0.f;
+  OutT* crow = C + m * ldc;
+  for (int n0 = 0; n0 < N; n0 += 8) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = s_b[n0 + j];
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      if (k < K) {
+        const float4 w0 = *reinterpret_cast<const float4*>(&s_wt[k * N + n0]);
+        const float4 w1 = *reinterpret_cast<const float4*>(&s_wt[k * N + n0 + 4]);
+        acc[0] = fmaf(a[k], w0.x, acc[0]); acc[1] = fmaf(a[k], w0.y, acc[1]);
+        acc[2] = fmaf(a[k], w0.z, acc[2]); acc[3] = fmaf(a[k], w0.w, acc[3]);
+        acc[4] = fmaf(a[k], w1.x, acc[4]); acc[5] = fmaf(a[k], w1.y, acc[5]);
+        acc[6] = fmaf(a[k], w1.z, acc[6]); acc[7] = fmaf(a[k], w1.w, acc[7]);
+      }
+    }
+    OutT o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = cvt_out<OutT>(acc[j]);
+    *reinterpret_cast<uint4*>(crow + n0) = *reinterpret_cast<const uint4*>(o);
   }
 }
 
@@ -333,6 +393,26 @@ static int linear_f32_t(const float* A, int64_t lda, const float* W, const float
 int linear_f32(const float* A, int64_t lda, const float* W, const float* bias, void* C,
                int64_t ldc, int c_dtype, int64_t M, int N, int K, int act, cudaStream_t st) {
   if (M == 0) return GN_OK;
+  if (K <= SK_MAXK && N % 8 == 0 && ldc % 8 == 0 && act == GN_ACT_NONE && c_dtype != GN_F32 &&
+      (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (size_t)(K + 1) * N * sizeof(float) <= 96 * 1024 &&
+      M * (int64_t)N >= (1 << 16)) {
+    const size_t smem = (size_t)(K + 1) * N * sizeof(float);
+    const unsigned grid = (unsigned)ceil_div(M, 128);
+#define GN_SK_CASE(T_, KM_)                                                                      \
+  {                                                                                              \
+    auto kern = linear_smallk_kernel<T_, KM_>;                                                   \
+    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    kern<<<grid, 128, smem, st>>>(A, lda, W, bias, reinterpret_cast<T_*>(C), ldc, M, N, K);      \
+  }
+    if (c_dtype == GN_F16) {
+      if (K <= 20) GN_SK_CASE(__half, 20) else GN_SK_CASE(__half, 32)
+    } else {
+      if (K <= 20) GN_SK_CASE(__nv_bfloat16, 20) else GN_SK_CASE(__nv_bfloat16, 32)
+    }
+#undef GN_SK_CASE
+    GN_LAUNCH_CHECK();
+    return GN_OK;
+  }
   if (c_dtype == GN_F32) return linear_f32_t<float>(A, lda, W, bias, C, ldc, M, N, K, act, st);
   if (c_dtype == GN_BF16)
     return linear_f32_t<__nv_bfloat16>(A, lda, W, bias, C, ldc, M, N, K, act, st);
