@@ -12,6 +12,7 @@
 // epilogue (one TMEM lane quadrant each).  A/W tiles travel as 128B-swizzled 64-column boxes
 // through a 4-stage mbarrier ring; rows/columns beyond M, N, K are zero-filled by the TMA unit.
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include "tc_common.cuh"
 
@@ -75,7 +76,7 @@ namespace tc {
 
 constexpr int LIN_BM = 128;
 constexpr int LIN_BK = 64;        // 64 bf16 = one 128-byte swizzle row
-constexpr int LIN_STAGES = 4;
+constexpr int LIN_STAGES = 8;     // capacity of the barrier arrays; the ring uses `stages` of them
 constexpr int LIN_EPI_WARPS = 8;
 constexpr int LIN_THREADS = 32 * (2 + LIN_EPI_WARPS);  // TMA + MMA + 8 epilogue warps
 constexpr int LIN_MAX_N = 2048;   // bias staged in shared memory
@@ -97,10 +98,10 @@ __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&p);
 }
 template <>
-__device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {  // saturating
-  __half2 p = __floats2half2_rn(fminf(fmaxf(a, -65504.f), 65504.f),
-                                fminf(fmaxf(b, -65504.f), 65504.f));
-  return *reinterpret_cast<uint32_t*>(&p);
+__device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {  // saturating, one CVT
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));  // hi <- b, lo <- a
+  return r;
 }
 
 // one thread stores 32 consecutive columns of its row; 16-byte vector stores for every full
@@ -108,6 +109,26 @@ __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {  // satura
 template <typename OutT>
 __device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int nvalid) {
   const bool aligned = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+  if (aligned && nvalid >= 32) {
+    // common case, branch-free body: 32 columns as 16-byte stores
+    if constexpr (sizeof(OutT) == 4) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        uint4 u;
+        u.x = pack2<OutT>(v[j], v[j + 1]);
+        u.y = pack2<OutT>(v[j + 2], v[j + 3]);
+        u.z = pack2<OutT>(v[j + 4], v[j + 5]);
+        u.w = pack2<OutT>(v[j + 6], v[j + 7]);
+        *reinterpret_cast<uint4*>(dst + j) = u;
+      }
+    }
+    return;
+  }
+  // ragged tail of a tile / unaligned rows: 16-byte stores for whole groups, scalars after
   if constexpr (sizeof(OutT) == 4) {
 #pragma unroll
     for (int j = 0; j < 32; j += 4) {
@@ -120,6 +141,7 @@ __device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int
       }
     }
   } else {
+    uint16_t* d16 = reinterpret_cast<uint16_t*>(dst);
 #pragma unroll
     for (int j = 0; j < 32; j += 8) {
       if (aligned && j + 8 <= nvalid) {
@@ -133,7 +155,6 @@ __device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int
 #pragma unroll
         for (int t = 0; t < 8; t += 2) {
           const uint32_t pr = pack2<OutT>(v[j + t], v[j + t + 1]);
-          uint16_t* d16 = reinterpret_cast<uint16_t*>(dst);
           if (j + t < nvalid) d16[j + t] = (uint16_t)(pr & 0xffffu);
           if (j + t + 1 < nvalid) d16[j + t + 1] = (uint16_t)(pr >> 16);
         }
@@ -146,14 +167,14 @@ template <typename OutT, int ACT>
 __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
-    int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc) {
+    int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   const int b_bytes = BN * LIN_BK * 2;
   const int stage_bytes = LIN_A_BYTES + b_bytes;
-  LinBarriers* bars = reinterpret_cast<LinBarriers*>(smem + LIN_STAGES * stage_bytes);
+  LinBarriers* bars = reinterpret_cast<LinBarriers*>(smem + stages * stage_bytes);
   float* s_bias = reinterpret_cast<float*>(bars + 1);  // [num_n_tiles * BN]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -192,8 +213,8 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
         const int32_t m0 = (int32_t)((t / num_n_tiles) * LIN_BM);
         const int32_t n0 = (int32_t)(t % num_n_tiles) * BN;
         for (int kb = 0; kb < nk; ++kb, ++g) {
-          const uint32_t s = g % LIN_STAGES;
-          mbar_wait(&bars->empty[s], ((g / LIN_STAGES) & 1) ^ 1);
+          const uint32_t s = g % stages;
+          mbar_wait(&bars->empty[s], ((g / stages) & 1) ^ 1);
           uint8_t* a_dst = smem + s * stage_bytes;
           uint8_t* b_dst = a_dst + LIN_A_BYTES;
           mbar_arrive_expect_tx(&bars->full[s], (uint32_t)stage_bytes);
@@ -211,8 +232,8 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + buf * 256;
       for (int kb = 0; kb < nk; ++kb, ++g) {
-        const uint32_t s = g % LIN_STAGES;
-        mbar_wait(&bars->full[s], (g / LIN_STAGES) & 1);
+        const uint32_t s = g % stages;
+        mbar_wait(&bars->full[s], (g / stages) & 1);
         tc_fence_after();
         if (elect_one()) {
           const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
@@ -276,8 +297,11 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
   const uint32_t idesc =
       ab_dtype == GN_F16 ? make_idesc_f16(LIN_BM, BN) : make_idesc_bf16(LIN_BM, BN);
   const int num_n_tiles = (int)ceil_div(N, BN);
-  const size_t smem = (size_t)LIN_STAGES * (LIN_A_BYTES + BN * LIN_BK * 2) + sizeof(LinBarriers) +
-                      (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024;
+  const size_t stage_bytes = (size_t)LIN_A_BYTES + (size_t)BN * LIN_BK * 2;
+  const size_t fixed = sizeof(LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024;
+  int stages = (int)((227 * 1024 - fixed) / stage_bytes);  // as deep as shared memory allows
+  stages = stages > LIN_STAGES ? LIN_STAGES : stages;
+  const size_t smem = (size_t)stages * stage_bytes + fixed;
   const int64_t num_tiles = ceil_div(M, LIN_BM) * num_n_tiles;
   int dev = 0, sms = 0;
   GN_CUDA(cudaGetDevice(&dev));
@@ -288,7 +312,7 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
     auto kern = tc_linear_kernel<OutT, A_>;                                                     \
     GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, LIN_THREADS, smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
-                                          K, BN, num_n_tiles, num_tiles, idesc);                       \
+                                          K, BN, num_n_tiles, num_tiles, idesc, stages);                       \
   }
   switch (act) {
     case GN_ACT_NONE: GN_TC_LIN_CASE(ACT_NONE) break;
@@ -305,8 +329,10 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
 
 int tc_pick_bn(int N) {
   // largest tile width <= 256 (multiple of 16) that minimises padding
-  int best = 256, best_waste = 1 << 30;
-  for (int bn = 256; bn >= 64; bn -= 16) {
+  static const char* env = getenv("GN_TC_BN_MAX");
+  const int bn_max = env ? atoi(env) : 256;
+  int best = bn_max, best_waste = 1 << 30;
+  for (int bn = bn_max; bn >= 64; bn -= 16) {
     int tiles = (N + bn - 1) / bn;
     int waste = tiles * bn - N;
     if (waste < best_waste) { best = bn; best_waste = waste; }
