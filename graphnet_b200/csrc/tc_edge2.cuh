@@ -59,6 +59,13 @@ struct __align__(16) Edge2Shared {
 __device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void* gsrc) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
 }
+// the same under a predicate (no branch around the copy: the gather loop stays straight-line)
+__device__ __forceinline__ void cp_async16_if(uint32_t smem_dst, const void* gsrc, uint32_t on) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t"
+      "@p cp.async.cg.shared.global [%0], [%1], 16;\n\t}" ::"r"(smem_dst), "l"(gsrc), "r"(on)
+      : "memory");
+}
 // the mbarrier receives one arrival when all cp.async issued so far by this thread have landed
 __device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar))
@@ -210,8 +217,15 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
     // when its copies have landed; one plain arrive per warp publishes the row-valid flags.
     const int so = warp - (E2_EPI_WARPS + E2_BLD_WARPS);  // the stage this warp owns
     const int ppr = rowbytes / 16;                        // 16-byte pieces per row (<= 44)
-    const bool two = lane + 32 < ppr;
+    const uint32_t on1 = lane < ppr, on2 = lane + 32 < ppr;
     const uint32_t stage = smem_u32(q_smem) + so * qstage_bytes + lane * 16;
+    // base pointers and row pitches live in registers for the whole loop (the per-row address is
+    // one 64-bit multiply-add); "+l" keeps the compiler from re-deriving them from the
+    // parameter bank in front of every copy
+    uint64_t qbase = reinterpret_cast<uint64_t>(p.qmat) + (uint64_t)lane * 16;
+    uint64_t pbase = reinterpret_cast<uint64_t>(p.pmat) + (uint64_t)lane * 16;
+    uint32_t qpitch = (uint32_t)p.ldq * 2, ppitch = (uint32_t)p.ldp * 2;
+    asm volatile("" : "+l"(qbase), "+l"(pbase), "+r"(qpitch), "+r"(ppitch));
     int32_t j_nx = -1, pn_nx = -1;
     auto fetch_ids = [&](uint32_t g2) {
       j_nx = -1;
@@ -234,30 +248,23 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
       mbar_wait_t<true>(&sh->q_empty[so], ((g2 / E2_QSTAGES) & 1) ^ 1, w0, timed);
       sh->row_valid[so][lane] = j >= 0 ? 1 : 0;
       // four rows per step (independent address chains); lanes = consecutive 16-byte pieces
-#pragma unroll 1
-      for (int r0 = 0; r0 < E2_HALF; r0 += 4) {
-        int32_t src[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) src[i] = __shfl_sync(0xffffffffu, j, r0 + i);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          if (src[i] >= 0) {
-            const __half* g = p.qmat + (int64_t)src[i] * p.ldq + lane * 8;
-            const uint32_t d = stage + (uint32_t)((r0 + i) * rowbytes);
-            if (lane < ppr) cp_async16(d, g);
-            if (two) cp_async16(d + 512, g + 256);
-          }
-        }
+#pragma unroll 8
+      for (int r = 0; r < E2_HALF; ++r) {
+        const int32_t src = __shfl_sync(0xffffffffu, j, r);
+        const uint32_t ok = src >= 0;
+        const uint8_t* g = reinterpret_cast<const uint8_t*>(qbase + (uint64_t)(uint32_t)max(src, 0) * qpitch);
+        const uint32_t d = stage + (uint32_t)(r * rowbytes);
+        cp_async16_if(d, g, ok & on1);
+        cp_async16_if(d + 512, g + 512, ok & on2);
       }
 #pragma unroll
       for (int r = 0; r < PMAX; ++r) {
         const int32_t src = __shfl_sync(0xffffffffu, pn, r);
-        if (src >= 0) {
-          const __half* g = p.pmat + (int64_t)src * p.ldp + lane * 8;
-          const uint32_t d = stage + (uint32_t)((E2_HALF + r) * rowbytes);
-          if (lane < ppr) cp_async16(d, g);
-          if (two) cp_async16(d + 512, g + 256);
-        }
+        const uint32_t ok = src >= 0;
+        const uint8_t* g = reinterpret_cast<const uint8_t*>(pbase + (uint64_t)(uint32_t)max(src, 0) * ppitch);
+        const uint32_t d = stage + (uint32_t)((E2_HALF + r) * rowbytes);
+        cp_async16_if(d, g, ok & on1);
+        cp_async16_if(d + 512, g + 512, ok & on2);
       }
       cp_async_arrive_noinc(&sh->q_full[so]);
       __syncwarp();
