@@ -76,6 +76,7 @@ struct EdgeParams {
   int ncoord;
   uint32_t coord_mask[8];
   const void* w2;           // W2p [bnp, Kp] fp16 row-major (second-generation kernel reads it directly)
+  int use_ws;               // weight-stationary MMA form (collector re-use of the h chunk)
   void* dbg;                // optional 8 x uint64 wait-time counters (GN_EDGE_DEBUG), else null
 };
 
@@ -98,10 +99,9 @@ __device__ __forceinline__ uint4 ldg16_keep(const __half* p, uint64_t pol) {
 }
 
 __device__ __forceinline__ uint32_t relu_add_f16x2(uint32_t a, uint32_t b) {
-  __half2 x = *reinterpret_cast<__half2*>(&a);
-  __half2 y = *reinterpret_cast<__half2*>(&b);
-  __half2 s = __hmax2(__hadd2(x, y), __float2half2_rn(0.f));
-  return *reinterpret_cast<uint32_t*>(&s);
+  uint32_t r;  // one HFMA2.RELU: max(a * 1 + b, 0)
+  asm("fma.rn.relu.f16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(0x3C003C00u), "r"(b));
+  return r;
 }
 
 __device__ __forceinline__ uint32_t pack2_16(float a, float b, bool f16) {
@@ -393,6 +393,7 @@ __global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
 }  // namespace tc
 }  // namespace gn
 #include "tc_edge2.cuh"
+#include "tc_edge3.cuh"
 namespace gn {
 namespace tc {
 
@@ -437,17 +438,32 @@ static int64_t edge_overflow_cap(const gn_graph* graph, int64_t N, int slots) {
   return graph->num_edges / slots + 1;
 }
 
-static __device__ unsigned long long g_edge_dbg[8];
+// 8 wait-time counters, then a timeline of CTA 0: [warp 0..31][iteration 0..31][4 stamps]
+constexpr int EDGE_DBG_WORDS = 8 + 32 * 32 * 4;
+static __device__ unsigned long long g_edge_dbg[EDGE_DBG_WORDS];
 
 // diagnostic only (not part of include/graphnet_b200.h): copy out and clear the counters
 extern "C" int gn_debug_edge_counters(unsigned long long* host8) {
   GN_CUDA(cudaDeviceSynchronize());
-  GN_CUDA(cudaMemcpyFromSymbol(host8, g_edge_dbg, sizeof(g_edge_dbg)));
+  GN_CUDA(cudaMemcpyFromSymbol(host8, g_edge_dbg, 8 * sizeof(unsigned long long)));
   unsigned long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   GN_CUDA(cudaMemcpyToSymbol(g_edge_dbg, zero, sizeof(zero)));
   return GN_OK;
 }
+// diagnostic only: the per-warp timeline of CTA 0 of the last launch (clock64 stamps)
+extern "C" int gn_debug_edge_trace(unsigned long long* host, int words) {
+  GN_CUDA(cudaDeviceSynchronize());
+  if (words > EDGE_DBG_WORDS - 8) words = EDGE_DBG_WORDS - 8;
+  GN_CUDA(cudaMemcpyFromSymbol(host, g_edge_dbg, words * sizeof(unsigned long long),
+                               8 * sizeof(unsigned long long)));
+  return GN_OK;
+}
 
+static bool edge_use_v2() {
+  // the third-generation kernel (tc_edge3.cuh) is opt-in until it beats the second
+  static const bool v3 = getenv("GN_EDGE_V3") != nullptr;
+  return !v3;
+}
 static bool edge_use_v1() {
   static const bool v = getenv("GN_EDGE_V1") != nullptr;  // first-generation kernel (A/B runs)
   return v;
@@ -536,6 +552,8 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
   // into g_edge_dbg, read back with the undeclared diagnostic export gn_debug_edge_counters()
   static const bool dbg_on = getenv("GN_EDGE_DEBUG") != nullptr;
   p.dbg = nullptr;
+  static const bool ws_off = getenv("GN_EDGE_NO_WS") != nullptr;
+  p.use_ws = ws_off ? 0 : 1;
   if (dbg_on) GN_CUDA(cudaGetSymbolAddress(&p.dbg, g_edge_dbg));
   p.pmat = reinterpret_cast<const __half*>(P);
   p.ldp = ldp;
@@ -559,7 +577,8 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
   GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const size_t smem1 = (size_t)p.nch * bnp * 64 + tc::EK_STAGES * tc::EK_STAGE_BYTES +
                        sizeof(tc::EdgeBarriers) + 1024;
-  const size_t smem2 = tc::edge2_smem_bytes(Kp, slots);
+  const bool use_v2 = edge_use_v2();
+  const size_t smem2 = use_v2 ? tc::edge2_smem_bytes(Kp, slots) : tc::edge3_smem_bytes(Kp);
   for (int pass = 0; pass < 2; ++pass) {
     int64_t max_tiles;
     if (pass == 0) {
@@ -585,9 +604,10 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
   }
 #define GN_EDGE_LAUNCH2(KP_, ACC_, F16_)                                                         \
   {                                                                                              \
-    auto kern = tc::edge_mlp_aggregate_v2_kernel<KP_, ACC_, F16_>;                               \
+    auto kern = use_v2 ? tc::edge_mlp_aggregate_v2_kernel<KP_, ACC_, F16_>                       \
+                       : tc::edge_mlp_aggregate_v3_kernel<KP_, ACC_, F16_>;                      \
     GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2)); \
-    kern<<<grid, tc::E2_THREADS, smem2, st>>>(p);                                                \
+    kern<<<grid, use_v2 ? tc::E2_THREADS : tc::E3_THREADS, smem2, st>>>(p);                      \
   }
 #define GN_EDGE_CASE2(KP_)                                                                       \
   {                                                                                              \

@@ -113,6 +113,38 @@ __device__ __forceinline__ void mma_f16_ts_c(uint32_t tmem_d, uint32_t tmem_a, u
   }
 }
 
+// Weight-stationary form: the B operand (the h chunk) is latched in collector buffer b<BUF> by
+// the FILL instruction and re-used by the LASTUSE one, so the two channel blocks of a K step read
+// the chunk from shared memory once instead of twice.
+template <int BUF, bool FILL, bool ACC>
+__device__ __forceinline__ void mma_f16_ts_ws(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc,
+                                              uint32_t idesc) {
+#define GN_WS_MMA(BUFS, OP)                                                                      \
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %4, 0;\n\t"                               \
+               "tcgen05.mma.ws.cta_group::1.kind::f16.collector::" BUFS "::" OP                  \
+               " [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),                                     \
+               "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"((uint32_t)ACC)                           \
+               : "memory")
+  if (BUF == 0) { if (FILL) GN_WS_MMA("b0", "fill"); else GN_WS_MMA("b0", "lastuse"); }
+  else { if (FILL) GN_WS_MMA("b1", "fill"); else GN_WS_MMA("b1", "lastuse"); }
+#undef GN_WS_MMA
+}
+
+// the same with a run-time accumulate flag (first K step of a tile)
+template <int BUF, bool FILL>
+__device__ __forceinline__ void mma_f16_ts_ws_p(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc,
+                                                uint32_t idesc, uint32_t acc) {
+#define GN_WS_MMA(BUFS, OP)                                                                      \
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %4, 0;\n\t"                               \
+               "tcgen05.mma.ws.cta_group::1.kind::f16.collector::" BUFS "::" OP                  \
+               " [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),                                     \
+               "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(acc)                                     \
+               : "memory")
+  if (BUF == 0) { if (FILL) GN_WS_MMA("b0", "fill"); else GN_WS_MMA("b0", "lastuse"); }
+  else { if (FILL) GN_WS_MMA("b1", "fill"); else GN_WS_MMA("b1", "lastuse"); }
+#undef GN_WS_MMA
+}
+
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 r;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
@@ -277,6 +309,36 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
     for (int64_t it = 0; it < my_tiles; ++it) {
       const uint32_t hb = (uint32_t)(it % E2_HBUFS);
       mbar_wait_t(&sh->h_full[hb], (uint32_t)((it / E2_HBUFS) & 1), w0, timed);
+      if (p.use_ws && nblk == 2) {
+        // both channel blocks advance together, K step by K step: the second block takes the h
+        // chunk from the collector buffer the first one filled (one shared-memory read, not two)
+        mbar_wait_t(&sh->d_empty[0], (uint32_t)(it & 1) ^ 1, w1, timed);
+        mbar_wait_t(&sh->d_empty[1], (uint32_t)(it & 1) ^ 1, w1, timed);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t d0 = tmem_base + E2_TMEM_D0, d1 = tmem_base + E2_TMEM_D1;
+          uint64_t bdesc = make_kmajor_desc<64>(h_addr + hb * htile_bytes);
+          uint32_t a = tmem_base;
+          mma_f16_ts_ws<0, true, false>(d0, a, bdesc, idesc);
+          mma_f16_ts_ws<0, false, false>(d1, a + E2_TMEM_A1, bdesc, idesc);
+          mma_f16_ts_ws<1, true, true>(d0, a + 8, bdesc + 2, idesc);
+          mma_f16_ts_ws<1, false, true>(d1, a + E2_TMEM_A1 + 8, bdesc + 2, idesc);
+#pragma unroll 1
+          for (int kc = 1; kc < nch; ++kc) {
+            bdesc += (E2_ROWS * 64) >> 4;
+            a += 16;
+            mma_f16_ts_ws<0, true, true>(d0, a, bdesc, idesc);
+            mma_f16_ts_ws<0, false, true>(d1, a + E2_TMEM_A1, bdesc, idesc);
+            mma_f16_ts_ws<1, true, true>(d0, a + 8, bdesc + 2, idesc);
+            mma_f16_ts_ws<1, false, true>(d1, a + E2_TMEM_A1 + 8, bdesc + 2, idesc);
+          }
+          mma_commit(&sh->d_full[0]);
+          mma_commit(&sh->d_full[1]);
+          mma_commit(&sh->h_empty[hb]);
+        }
+        __syncwarp();
+        continue;
+      }
       for (int blk = 0; blk < nblk; ++blk) {
         mbar_wait_t(&sh->d_empty[blk], (uint32_t)(it & 1) ^ 1, w1, timed);
         tc_fence_after();
