@@ -332,6 +332,22 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def ncu_traffic_bytes(kernel_name):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the
+    committed `ncu --set full` capture of this workload (profiles/r01_edge_kernel_ncu.json);
+    None when the capture is of another kernel."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
+                        "r01_edge_kernel_ncu.json")
+    try:
+        with open(path) as f:
+            cap = json.load(f)
+    except (OSError, ValueError):
+        return None
+    if cap.get("kernel_prefix") and cap["kernel_prefix"] in kernel_name:
+        return cap.get("dram_bytes_per_launch")
+    return None
+
+
 def dominant_kernel_roofline(backbone, data, precision, N, E, dev, flush_buf):
     """Time the fused EdgeConv of layer 2 alone, CUDA events on the launch stream."""
     import graphnet_b200.ops as ops
@@ -366,7 +382,7 @@ def dominant_kernel_roofline(backbone, data, precision, N, E, dev, flush_buf):
         peak = pk["bf16_tflops"]
         ach = algorithmic / (ms * 1e-3) / 1e12
         return {"bound": "tensor", "kernel": name, "achieved": ach, "peak": peak,
-                "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+                "unit": "TFLOP/s", "frac": ach / peak, "traffic": ncu_traffic_bytes(name),
                 "peak_source": f"{pk['source']} cuBLAS bf16 burst (kernel timed alone)",
                 "ms_per_launch": ms, "algorithmic_gflop_per_launch": algorithmic / 1e9,
                 "executed_gflop_per_launch": executed_flops / 1e9,
