@@ -1,0 +1,419 @@
+// Backward-pass kernels of the 16-bit DynEdge training path (BASELINE config 3).
+//
+// The reference has no backward code of its own: gradients come from torch autograd through
+// PyG's EdgeConv (components/layers.py:62-76), torch_scatter's pooling (gnn/dynedge.py:252-265)
+// and nn.Linear/ReLU (dynedge.py:193-232).  The edge MLP's backward is run UNFUSED here: the
+// per-slot hidden activations are re-materialised (bf16) so that all three contractions
+//     Z  = H  W2^T          (recomputed pre-activations, for the ReLU mask)
+//     dH = G2 W2            (G2 = dOut[target] * [Z > 0])
+//     dW2 = G2^T H          (K = all edge slots: split-K, fp32 reductions)
+// are plain calls of the tcgen05 GEMM (tc_linear.cu).  The kernels in this file are the byte
+// movers between them; all are HBM bound and written for coalesced 16-byte accesses.
+#include "common.cuh"
+
+#include <cuda_fp16.h>
+
+namespace gn {
+
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) {
+  return __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+}
+
+// ------------------------------------------------------------------ transpose (16-bit elements)
+// dst[c, r] = src[r, c]; 64 x 64 tiles through shared memory, both sides coalesced.
+__global__ void __launch_bounds__(256) transpose16_kernel(const uint16_t* __restrict__ src,
+                                                          int64_t lds_, int64_t rows, int cols,
+                                                          uint16_t* __restrict__ dst,
+                                                          int64_t ldd) {
+  __shared__ uint16_t tile[64][66];
+  const int64_t r0 = (int64_t)blockIdx.x * 64;
+  const int c0 = blockIdx.y * 64;
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;  // 64 x 4
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int r = ty + 4 * i;
+    tile[r][tx] = (r0 + r < rows && c0 + tx < cols) ? src[(r0 + r) * lds_ + c0 + tx] : (uint16_t)0;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int c = ty + 4 * i;
+    if (c0 + c < cols && r0 + tx < rows) dst[(int64_t)(c0 + c) * ldd + r0 + tx] = tile[tx][c];
+  }
+}
+
+// ------------------------------------------------------------------ column sums (bias gradients)
+// out[n] (+)= sum_m X[m, n]; one thread per column, 512 rows per CTA, one atomic per CTA and column
+template <typename T>
+__global__ void __launch_bounds__(128) colsum_kernel(const T* __restrict__ X, int64_t ldx,
+                                                     int64_t M, int N, float* __restrict__ out) {
+  const int n = blockIdx.y * 128 + threadIdx.x;
+  const int64_t m0 = (int64_t)blockIdx.x * 512;
+  if (n >= N) return;
+  const int64_t m1 = m0 + 512 < M ? m0 + 512 : M;
+  float acc = 0.f;
+  for (int64_t m = m0; m < m1; ++m) acc += to_f32<T>(X[m * ldx + n]);
+  atomicAdd(out + n, acc);
+}
+
+// ------------------------------------------------------------------ dZ = dY * [Y > 0], converted
+// Y == nullptr: plain conversion.  Four elements per thread.
+template <typename TG, typename TY, typename TO>
+__global__ void __launch_bounds__(256) mask_convert_kernel(const TG* __restrict__ dY, int64_t ldg,
+                                                           const TY* __restrict__ Y, int64_t ldy,
+                                                           TO* __restrict__ out, int64_t ldo,
+                                                           int64_t M, int N) {
+  const int nq = (N + 3) / 4;
+  const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= M * nq) return;
+  const int64_t m = idx / nq;
+  const int n0 = (int)(idx % nq) * 4;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int n = n0 + j;
+    if (n < N) {
+      float g = to_f32<TG>(dY[m * ldg + n]);
+      if (Y != nullptr && !(to_f32<TY>(Y[m * ldy + n]) > 0.f)) g = 0.f;
+      out[m * ldo + n] = from_f32<TO>(g);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ edge slots: H and H^T
+// Row e = i * KP + t of the slot table (ELL, stride KP): H[e, :] = ReLU(P_i + Q_j) for a filled
+// slot (j = nbr[e] >= 0), 0 for an empty one; bf16.  A CTA takes 32 slot rows: the row-major copy
+// is written directly, the transposed copy HT[k, e] through a shared-memory tile.
+constexpr int EB_ROWS = 32;
+__global__ void __launch_bounds__(256) edge_build_h_kernel(
+    const __half* __restrict__ P, int64_t ldp, const __half* __restrict__ Q, int64_t ldq, int Kp,
+    const int32_t* __restrict__ nbr, int KP, int64_t E, __nv_bfloat16* __restrict__ H,
+    int64_t ldh, __nv_bfloat16* __restrict__ HT, int64_t ldht) {
+  extern __shared__ __nv_bfloat16 tile[];  // [EB_ROWS][Kp + 2]
+  const int pitch = Kp + 2;
+  const int64_t e0 = (int64_t)blockIdx.x * EB_ROWS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int r = warp; r < EB_ROWS; r += 8) {
+    const int64_t e = e0 + r;
+    int32_t j = -1;
+    int64_t i = 0;
+    if (e < E) {
+      j = nbr[e];
+      i = e / KP;
+    }
+    for (int k = lane * 2; k < Kp; k += 64) {
+      float2 h = make_float2(0.f, 0.f);
+      if (j >= 0) {
+        const float2 p = __half22float2(*reinterpret_cast<const __half2*>(P + i * ldp + k));
+        const float2 q = __half22float2(*reinterpret_cast<const __half2*>(Q + (int64_t)j * ldq + k));
+        h.x = fmaxf(p.x + q.x, 0.f);
+        h.y = fmaxf(p.y + q.y, 0.f);
+      }
+      const __nv_bfloat162 hb = __floats2bfloat162_rn(h.x, h.y);
+      *reinterpret_cast<__nv_bfloat162*>(tile + r * pitch + k) = hb;
+      if (e < E) *reinterpret_cast<__nv_bfloat162*>(H + e * ldh + k) = hb;
+    }
+  }
+  if (HT == nullptr) return;
+  __syncthreads();
+  // transposed copy: thread = (k, row-quad): 32 consecutive e of one k are 64 contiguous bytes
+  const int rvalid = (int)(E - e0 < EB_ROWS ? E - e0 : EB_ROWS);
+  for (int idx = threadIdx.x; idx < Kp * 4; idx += 256) {
+    const int k = idx >> 2, r8 = (idx & 3) * 8;
+    __nv_bfloat16 v[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) v[t] = tile[(r8 + t) * pitch + k];
+    __nv_bfloat16* dst = HT + (int64_t)k * ldht + e0 + r8;
+    if (r8 + 8 <= rvalid && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<uint4*>(v);
+    } else {
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        if (r8 + t < rvalid) dst[t] = v[t];
+    }
+  }
+}
+
+// ------------------------------------------------------------------ G2 = dOut[target] * [Z > 0]
+// Z [E, b] recomputed pre-activations (bf16), dOut [N, b] fp32.  Writes G2 [E, ldg] and
+// G2T [b, E] (bf16).  Empty slots give zero rows.
+__global__ void __launch_bounds__(256) edge_grad_z_kernel(
+    const __nv_bfloat16* __restrict__ Z, int64_t ldz, const float* __restrict__ dOut, int64_t ldd,
+    int b, const int32_t* __restrict__ nbr, int KP, int64_t E, __nv_bfloat16* __restrict__ G2,
+    int64_t ldg, __nv_bfloat16* __restrict__ G2T, int64_t ldgt) {
+  extern __shared__ __nv_bfloat16 tile[];  // [EB_ROWS][b + 2]
+  const int pitch = b + 2;
+  const int64_t e0 = (int64_t)blockIdx.x * EB_ROWS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int r = warp; r < EB_ROWS; r += 8) {
+    const int64_t e = e0 + r;
+    const bool filled = e < E && nbr[e] >= 0;
+    const int64_t i = e < E ? e / KP : 0;
+    for (int c = lane * 2; c < b; c += 64) {
+      float2 g = make_float2(0.f, 0.f);
+      if (filled) {
+        const float2 z = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(Z + e * ldz + c));
+        const float2 d = *reinterpret_cast<const float2*>(dOut + i * ldd + c);
+        g.x = z.x > 0.f ? d.x : 0.f;
+        g.y = z.y > 0.f ? d.y : 0.f;
+      }
+      const __nv_bfloat162 gb = __floats2bfloat162_rn(g.x, g.y);
+      *reinterpret_cast<__nv_bfloat162*>(tile + r * pitch + c) = gb;
+      if (e < E) *reinterpret_cast<__nv_bfloat162*>(G2 + e * ldg + c) = gb;
+    }
+  }
+  __syncthreads();
+  const int rvalid = (int)(E - e0 < EB_ROWS ? E - e0 : EB_ROWS);
+  for (int idx = threadIdx.x; idx < b * 4; idx += 256) {
+    const int c = idx >> 2, r8 = (idx & 3) * 8;
+    __nv_bfloat16 v[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) v[t] = tile[(r8 + t) * pitch + c];
+    __nv_bfloat16* dst = G2T + (int64_t)c * ldgt + e0 + r8;
+    if (r8 + 8 <= rvalid && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<uint4*>(v);
+    } else {
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        if (r8 + t < rvalid) dst[t] = v[t];
+    }
+  }
+}
+
+// ------------------------------------------------------------------ dP, dQ from dH
+// m = dH * [H > 0]; dP_i = sum over the node's slots (one write), dQ_j += m (fp32 red.add).
+// One warp per node, lanes stride the hidden columns in pairs.
+__global__ void __launch_bounds__(256) edge_grad_pq_kernel(
+    const __nv_bfloat16* __restrict__ dH, int64_t lddh, const __nv_bfloat16* __restrict__ H,
+    int64_t ldh, int Kp, const int32_t* __restrict__ nbr, int KP, int64_t N,
+    __nv_bfloat16* __restrict__ dP, int64_t ldp, float* __restrict__ dQ, int64_t ldq) {
+  const int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= N) return;
+  for (int k = lane * 2; k < Kp; k += 64) {
+    float2 acc = make_float2(0.f, 0.f);
+    for (int t = 0; t < KP; ++t) {
+      const int64_t e = i * KP + t;
+      const int32_t j = nbr[e];
+      if (j < 0) continue;
+      const float2 h = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(H + e * ldh + k));
+      float2 g = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(dH + e * lddh + k));
+      g.x = h.x > 0.f ? g.x : 0.f;
+      g.y = h.y > 0.f ? g.y : 0.f;
+      acc.x += g.x;
+      acc.y += g.y;
+      if (g.x != 0.f) atomicAdd(dQ + (int64_t)j * ldq + k, g.x);
+      if (g.y != 0.f) atomicAdd(dQ + (int64_t)j * ldq + k + 1, g.y);
+    }
+    *reinterpret_cast<__nv_bfloat162*>(dP + i * ldp + k) = __floats2bfloat162_rn(acc.x, acc.y);
+  }
+}
+
+// ------------------------------------------------------------------ pooling backward
+// dX[n, c] = sum over schemes of the gradient that reaches row n: sum -> g, mean -> g / count,
+// min / max -> g at the FIRST row of the event that attains the pooled value (torch_scatter's
+// CPU arg convention), 0 elsewhere.  One CTA per (event, 128 columns), one thread per column.
+struct PoolSchemesB { int n; int s[8]; };
+template <typename T>
+__global__ void __launch_bounds__(128) segment_pool_backward_kernel(
+    const T* __restrict__ x, int64_t ldx, int C, const int32_t* __restrict__ ptr,
+    PoolSchemesB sch, const float* __restrict__ pooled, int64_t ldpool,
+    const float* __restrict__ dpooled, int64_t lddp, float* __restrict__ dX, int64_t lddx) {
+  const int64_t ev = blockIdx.x;
+  const int c = blockIdx.y * 128 + threadIdx.x;
+  if (c >= C) return;
+  const int32_t n0 = ptr[ev], n1 = ptr[ev + 1];
+  if (n1 <= n0) return;
+  float g_all = 0.f;                      // same for every row: sum and mean
+  float vmin = 0.f, vmax = 0.f, gmin = 0.f, gmax = 0.f;
+  bool has_min = false, has_max = false;
+  for (int k = 0; k < sch.n; ++k) {
+    const float g = dpooled[ev * lddp + (int64_t)k * C + c];
+    const float v = pooled[ev * ldpool + (int64_t)k * C + c];
+    if (sch.s[k] == GN_POOL_SUM) g_all += g;
+    else if (sch.s[k] == GN_POOL_MEAN) g_all += g / (float)(n1 - n0);
+    else if (sch.s[k] == GN_POOL_MIN) { has_min = true; vmin = v; gmin += g; }
+    else { has_max = true; vmax = v; gmax += g; }
+  }
+  bool min_done = !has_min, max_done = !has_max;
+  for (int32_t n = n0; n < n1; ++n) {
+    const float v = to_f32<T>(x[(int64_t)n * ldx + c]);
+    float g = g_all;
+    if (!min_done && v == vmin) { g += gmin; min_done = true; }
+    if (!max_done && v == vmax) { g += gmax; max_done = true; }
+    dX[(int64_t)n * lddx + c] = g;
+  }
+}
+
+}  // namespace gn
+
+using namespace gn;
+
+extern "C" int gn_transpose_16(const void* src, int64_t ld_src, int64_t rows, int cols, void* dst,
+                               int64_t ld_dst, void* stream) {
+  GN_CHECK_ARG(rows >= 0 && cols >= 1 && ld_src >= cols && ld_dst >= rows,
+               "gn_transpose_16: bad sizes");
+  if (rows == 0) return GN_OK;
+  GN_CHECK_ARG(src && dst, "gn_transpose_16: null pointer");
+  dim3 grid((unsigned)ceil_div(rows, 64), (unsigned)ceil_div(cols, 64));
+  transpose16_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+      reinterpret_cast<const uint16_t*>(src), ld_src, rows, cols, reinterpret_cast<uint16_t*>(dst),
+      ld_dst);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_colsum_accumulate(const void* X, int x_dtype, int64_t ldx, int64_t M, int N,
+                                    float* out, void* stream) {
+  GN_CHECK_ARG(M >= 0 && N >= 1 && ldx >= N, "gn_colsum_accumulate: bad sizes");
+  if (M == 0) return GN_OK;
+  GN_CHECK_ARG(X && out, "gn_colsum_accumulate: null pointer");
+  dim3 grid((unsigned)ceil_div(M, 512), (unsigned)ceil_div(N, 128));
+  cudaStream_t st = as_stream(stream);
+  if (x_dtype == GN_F32)
+    colsum_kernel<float><<<grid, 128, 0, st>>>(reinterpret_cast<const float*>(X), ldx, M, N, out);
+  else if (x_dtype == GN_BF16)
+    colsum_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(X),
+                                                       ldx, M, N, out);
+  else
+    GN_CHECK_ARG(false, "gn_colsum_accumulate: bad x_dtype %d", x_dtype);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_relu_backward(const void* dY, int dy_dtype, int64_t ld_dy, const void* Y,
+                                int y_dtype, int64_t ld_y, void* out, int64_t ld_out, int64_t M,
+                                int N, void* stream) {
+  GN_CHECK_ARG(M >= 0 && N >= 1 && ld_dy >= N && ld_out >= N && (Y == nullptr || ld_y >= N),
+               "gn_relu_backward: bad sizes");
+  if (M == 0) return GN_OK;
+  GN_CHECK_ARG(dY && out, "gn_relu_backward: null pointer");
+  GN_CHECK_ARG(dy_dtype == GN_F32 || dy_dtype == GN_BF16, "gn_relu_backward: bad dy_dtype");
+  GN_CHECK_ARG(Y == nullptr || y_dtype == GN_F32 || y_dtype == GN_BF16,
+               "gn_relu_backward: bad y_dtype");
+  const int64_t work = M * ((N + 3) / 4);
+  const unsigned grid = (unsigned)ceil_div(work, 256);
+  cudaStream_t st = as_stream(stream);
+  __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+#define GN_MC(TG, TY)                                                                        \
+  mask_convert_kernel<TG, TY, __nv_bfloat16><<<grid, 256, 0, st>>>(                          \
+      reinterpret_cast<const TG*>(dY), ld_dy, reinterpret_cast<const TY*>(Y), ld_y, o, ld_out, M, N)
+  const bool yf = (Y == nullptr) || y_dtype == GN_F32;
+  if (dy_dtype == GN_F32) {
+    if (yf) GN_MC(float, float); else GN_MC(float, __nv_bfloat16);
+  } else {
+    if (yf) GN_MC(__nv_bfloat16, float); else GN_MC(__nv_bfloat16, __nv_bfloat16);
+  }
+#undef GN_MC
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+static int check_ell(const gn_graph* graph, const char* who) {
+  if (!graph || !graph->col || graph->ell_stride <= 0) {
+    set_error("%s: the graph must be in ELL layout (slot table)", who);
+    return GN_ERR_INVALID_ARGUMENT;
+  }
+  return GN_OK;
+}
+
+extern "C" int gn_edge_build_h(const void* P, int64_t ldp, const void* Q, int64_t ldq, int Kp,
+                               const gn_graph* graph, int64_t N, void* H, int64_t ldh, void* HT,
+                               int64_t ldht, void* stream) {
+  int rc = check_ell(graph, "gn_edge_build_h");
+  if (rc != GN_OK) return rc;
+  const int KP = graph->ell_stride;
+  const int64_t E = N * KP;
+  GN_CHECK_ARG(Kp >= 2 && Kp % 2 == 0 && ldp >= Kp && ldq >= Kp && ldh >= Kp &&
+                   (HT == nullptr || ldht >= E),
+               "gn_edge_build_h: bad sizes");
+  if (N == 0) return GN_OK;
+  GN_CHECK_ARG(P && Q && H, "gn_edge_build_h: null pointer");
+  const size_t smem = (size_t)EB_ROWS * (Kp + 2) * 2;
+  edge_build_h_kernel<<<(unsigned)ceil_div(E, EB_ROWS), 256, smem, as_stream(stream)>>>(
+      reinterpret_cast<const __half*>(P), ldp, reinterpret_cast<const __half*>(Q), ldq, Kp,
+      graph->col, KP, E, reinterpret_cast<__nv_bfloat16*>(H), ldh,
+      reinterpret_cast<__nv_bfloat16*>(HT), ldht);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_edge_grad_z(const void* Z, int64_t ldz, const float* dOut, int64_t ldd, int b,
+                              const gn_graph* graph, int64_t N, void* G2, int64_t ldg, void* G2T,
+                              int64_t ldgt, void* stream) {
+  int rc = check_ell(graph, "gn_edge_grad_z");
+  if (rc != GN_OK) return rc;
+  const int KP = graph->ell_stride;
+  const int64_t E = N * KP;
+  GN_CHECK_ARG(b >= 2 && b % 2 == 0 && ldz >= b && ldd >= b && ldg >= b && ldgt >= E &&
+                   ldd % 2 == 0,
+               "gn_edge_grad_z: bad sizes");
+  if (N == 0) return GN_OK;
+  GN_CHECK_ARG(Z && dOut && G2 && G2T, "gn_edge_grad_z: null pointer");
+  GN_CHECK_ARG((reinterpret_cast<uintptr_t>(dOut) & 7) == 0, "gn_edge_grad_z: dOut alignment");
+  const size_t smem = (size_t)EB_ROWS * (b + 2) * 2;
+  edge_grad_z_kernel<<<(unsigned)ceil_div(E, EB_ROWS), 256, smem, as_stream(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(Z), ldz, dOut, ldd, b, graph->col, KP, E,
+      reinterpret_cast<__nv_bfloat16*>(G2), ldg, reinterpret_cast<__nv_bfloat16*>(G2T), ldgt);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_edge_grad_pq(const void* dH, int64_t lddh, const void* H, int64_t ldh, int Kp,
+                               const gn_graph* graph, int64_t N, void* dP, int64_t ldp, float* dQ,
+                               int64_t ldq, void* stream) {
+  int rc = check_ell(graph, "gn_edge_grad_pq");
+  if (rc != GN_OK) return rc;
+  GN_CHECK_ARG(Kp >= 2 && Kp % 2 == 0 && lddh >= Kp && ldh >= Kp && ldp >= Kp && ldq >= Kp,
+               "gn_edge_grad_pq: bad sizes");
+  if (N == 0) return GN_OK;
+  GN_CHECK_ARG(dH && H && dP && dQ, "gn_edge_grad_pq: null pointer");
+  edge_grad_pq_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, as_stream(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(dH), lddh, reinterpret_cast<const __nv_bfloat16*>(H),
+      ldh, Kp, graph->col, graph->ell_stride, N, reinterpret_cast<__nv_bfloat16*>(dP), ldp, dQ,
+      ldq);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_segment_pool_backward(const void* x, int x_dtype, int64_t ldx, int C,
+                                        const int32_t* ptr, int64_t B, const int32_t* schemes,
+                                        int n_schemes, const float* pooled, int64_t ld_pooled,
+                                        const float* d_pooled, int64_t ld_dpooled, float* dX,
+                                        int64_t ld_dx, void* stream) {
+  GN_CHECK_ARG(C >= 1 && n_schemes >= 1 && n_schemes <= 8, "gn_segment_pool_backward: bad sizes");
+  GN_CHECK_ARG(ld_pooled >= (int64_t)C * n_schemes && ld_dpooled >= (int64_t)C * n_schemes &&
+                   ld_dx >= C && ldx >= C,
+               "gn_segment_pool_backward: leading dimension too small");
+  if (B == 0) return GN_OK;
+  GN_CHECK_ARG(x && ptr && schemes && pooled && d_pooled && dX,
+               "gn_segment_pool_backward: null pointer");
+  PoolSchemesB sch;
+  sch.n = n_schemes;
+  for (int k = 0; k < n_schemes; ++k) {
+    GN_CHECK_ARG(schemes[k] >= GN_POOL_MIN && schemes[k] <= GN_POOL_MEAN,
+                 "gn_segment_pool_backward: unknown scheme %d", schemes[k]);
+    sch.s[k] = schemes[k];
+  }
+  dim3 grid((unsigned)B, (unsigned)ceil_div(C, 128));
+  cudaStream_t st = as_stream(stream);
+  if (x_dtype == GN_F32)
+    segment_pool_backward_kernel<float><<<grid, 128, 0, st>>>(
+        reinterpret_cast<const float*>(x), ldx, C, ptr, sch, pooled, ld_pooled, d_pooled,
+        ld_dpooled, dX, ld_dx);
+  else if (x_dtype == GN_BF16)
+    segment_pool_backward_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), ldx, C, ptr, sch, pooled, ld_pooled, d_pooled,
+        ld_dpooled, dX, ld_dx);
+  else
+    GN_CHECK_ARG(false, "gn_segment_pool_backward: bad x_dtype %d", x_dtype);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}

@@ -167,7 +167,8 @@ template <typename OutT, int ACT>
 __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
-    int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages) {
+    int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages, int splits,
+    int accumulate) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -203,16 +204,22 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
 
-  // Persistent: this CTA walks tiles blockIdx.x, +gridDim.x, ...; consecutive tile ids share the
-  // A row block (n fastest), so concurrently running CTAs hit the same A tile in L2.
+  // Persistent: this CTA walks work items blockIdx.x, +gridDim.x, ...; item = (tile, K split),
+  // split fastest; consecutive tile ids share the A row block (n fastest), so concurrently
+  // running CTAs hit the same A tile in L2.  splits > 1 (weight gradients: few tiles, K = rows of
+  // the batch) gives every item the K blocks [kb0, kb1) and the epilogue adds with red.add.
+  const int64_t num_items = num_tiles * splits;
   if (warp == 0) {
     // ---------------------------------------------------------- TMA producer
     if (elect_one()) {
       uint32_t g = 0;
-      for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int64_t w = blockIdx.x; w < num_items; w += gridDim.x) {
+        const int64_t t = w / splits;
+        const int sp = (int)(w % splits);
+        const int kb0 = (int)((int64_t)sp * nk / splits), kb1 = (int)((int64_t)(sp + 1) * nk / splits);
         const int32_t m0 = (int32_t)((t / num_n_tiles) * LIN_BM);
         const int32_t n0 = (int32_t)(t % num_n_tiles) * BN;
-        for (int kb = 0; kb < nk; ++kb, ++g) {
+        for (int kb = kb0; kb < kb1; ++kb, ++g) {
           const uint32_t s = g % stages;
           mbar_wait(&bars->empty[s], ((g / stages) & 1) ^ 1);
           uint8_t* a_dst = smem + s * stage_bytes;
@@ -226,12 +233,14 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
     uint32_t g = 0, it = 0;
-    for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+    for (int64_t w = blockIdx.x; w < num_items; w += gridDim.x, ++it) {
+      const int sp = (int)(w % splits);
+      const int kb0 = (int)((int64_t)sp * nk / splits), kb1 = (int)((int64_t)(sp + 1) * nk / splits);
       const uint32_t buf = it & 1;
       mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + buf * 256;
-      for (int kb = 0; kb < nk; ++kb, ++g) {
+      for (int kb = kb0; kb < kb1; ++kb, ++g) {
         const uint32_t s = g % stages;
         mbar_wait(&bars->full[s], (g / stages) & 1);
         tc_fence_after();
@@ -244,10 +253,10 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
           for (int k4 = 0; k4 < LIN_BK / 16; ++k4) {
             // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4) units
             mma_bf16_ss(tmem_d, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc,
-                        (kb | k4) != 0);
+                        ((kb - kb0) | k4) != 0);
           }
           mma_commit(&bars->empty[s]);
-          if (kb == nk - 1) mma_commit(&bars->tmem_full[buf]);
+          if (kb == kb1 - 1) mma_commit(&bars->tmem_full[buf]);
         }
         __syncwarp();
       }
@@ -257,7 +266,8 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
     const int par = (warp - 2) >> 2;  // the two warps of a quadrant take alternate 32-col chunks
     uint32_t it = 0;
-    for (int64_t t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+    for (int64_t w = blockIdx.x; w < num_items; w += gridDim.x, ++it) {
+      const int64_t t = w / splits;
       const uint32_t buf = it & 1;
       const int64_t m0 = (t / num_n_tiles) * LIN_BM;
       const int n0 = (int)(t % num_n_tiles) * BN;
@@ -278,7 +288,19 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
           v[j + 2] = activate<ACT>(v[j + 2] + b.z);
           v[j + 3] = activate<ACT>(v[j + 3] + b.w);
         }
-        if (row < M) store_row32<OutT>(C + row * ldc + n, v, min(N - n, BN - c));
+        if (row < M) {
+          if constexpr (sizeof(OutT) == 4) {
+            if (accumulate) {  // C += : fp32 reductions in L2 (split K, or adding onto a gradient)
+              const int nv = min(N - n, BN - c);
+              float* dst = reinterpret_cast<float*>(C) + row * ldc + n;
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j < nv) atomicAdd(dst + j, v[j]);
+              continue;
+            }
+          }
+          store_row32<OutT>(C + row * ldc + n, v, min(N - n, BN - c));
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -293,7 +315,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
 template <typename OutT>
 static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, const float* bias,
                             void* C, int64_t ldc, int64_t M, int N, int K, int BN, int act,
-                            int ab_dtype, cudaStream_t st) {
+                            int ab_dtype, cudaStream_t st, int splits = 1, int accumulate = 0) {
   const uint32_t idesc =
       ab_dtype == GN_F16 ? make_idesc_f16(LIN_BM, BN) : make_idesc_bf16(LIN_BM, BN);
   const int num_n_tiles = (int)ceil_div(N, BN);
@@ -306,13 +328,22 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
   int dev = 0, sms = 0;
   GN_CUDA(cudaGetDevice(&dev));
   GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const unsigned grid = (unsigned)(num_tiles < sms ? num_tiles : sms);
+  const int nkb = (int)ceil_div(K, LIN_BK);
+  if (splits == 0) {  // automatic: enough items to fill the machine, at least 4 K blocks each
+    splits = (int)(sms / (num_tiles < sms ? num_tiles : sms));
+    if (splits > nkb / 4) splits = nkb / 4;
+  }
+  if (splits > nkb) splits = nkb;
+  if (splits < 1) splits = 1;
+  const int64_t num_items = num_tiles * splits;
+  const unsigned grid = (unsigned)(num_items < sms ? num_items : sms);
 #define GN_TC_LIN_CASE(A_)                                                                      \
   {                                                                                             \
     auto kern = tc_linear_kernel<OutT, A_>;                                                     \
     GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, LIN_THREADS, smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
-                                          K, BN, num_n_tiles, num_tiles, idesc, stages);                       \
+                                          K, BN, num_n_tiles, num_tiles, idesc, stages, splits,  \
+                                          accumulate);                                          \
   }
   switch (act) {
     case GN_ACT_NONE: GN_TC_LIN_CASE(ACT_NONE) break;
@@ -369,4 +400,24 @@ extern "C" int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
     return tc::launch_tc_linear<__half>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype, st);
   return tc::launch_tc_linear<__nv_bfloat16>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype,
                                              st);
+}
+
+extern "C" int gn_tc_linear_accumulate(const void* A, int64_t lda, const void* W, int64_t ldw,
+                                       int ab_dtype, float* C, int64_t ldc, int64_t M, int N,
+                                       int K, int splits, void* stream) {
+  GN_CHECK_ARG(M >= 0 && N >= 1 && K >= 1 && lda >= K && ldw >= K && ldc >= N && splits >= 0,
+               "gn_tc_linear_accumulate: bad sizes");
+  if (M == 0) return GN_OK;
+  GN_CHECK_ARG(A && W && C, "gn_tc_linear_accumulate: null pointer");
+  GN_CHECK_ARG(ab_dtype == GN_BF16 || ab_dtype == GN_F16, "gn_tc_linear_accumulate: bad ab_dtype");
+  GN_CHECK_ARG(N <= tc::LIN_MAX_N, "gn_tc_linear_accumulate: N=%d exceeds %d", N, tc::LIN_MAX_N);
+  const int BN = tc_pick_bn(N);
+  CUtensorMap tmA, tmW;
+  auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
+  int rc = mk(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, tc::LIN_BM, tc::LIN_BK, 128);
+  if (rc != GN_OK) return rc;
+  rc = mk(&tmW, W, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)BN, tc::LIN_BK, 128);
+  if (rc != GN_OK) return rc;
+  return tc::launch_tc_linear<float>(tmA, tmW, nullptr, C, ldc, M, N, K, BN, GN_ACT_NONE, ab_dtype,
+                                     as_stream(stream), splits, 1);
 }

@@ -349,3 +349,122 @@ def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: in
             _host_i32(coord_cols) if ncoord else None,
             ncoord, _ptr(scratch), nbytes, _stream(dev)), "gn_tc_edge_mlp_aggregate")
     return out
+
+
+# ------------------------------------------------- backward pass (16-bit training path)
+def _dt_of(t: Tensor) -> int:
+    return {torch.bfloat16: DTYPE_BF16, torch.float16: DTYPE_F16, torch.float32: DTYPE_F32}[t.dtype]
+
+
+def tc_linear_accumulate(A: Tensor, W: Tensor, out: Tensor, K: int, splits: int = 0) -> Tensor:
+    """out[:, :N] += A[:, :K] W[:, :K]^T (fp32 red.add; split K when few output tiles)."""
+    dev = _require_cuda(A, W, out)
+    assert A.dtype == W.dtype and A.dtype in (torch.bfloat16, torch.float16)
+    assert out.dtype == torch.float32
+    assert A.stride(1) == 1 and W.stride(1) == 1 and out.stride(1) == 1
+    M, Nout = A.shape[0], W.shape[0]
+    assert out.shape[0] == M and out.shape[1] >= Nout
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_tc_linear_accumulate(_ptr(A), A.stride(0), _ptr(W), W.stride(0),
+                                                  _DT[A.dtype], _ptr(out), out.stride(0), M, Nout,
+                                                  K, splits, _stream(dev)),
+              "gn_tc_linear_accumulate")
+    return out
+
+
+def transpose_16(src: Tensor, out: Optional[Tensor] = None) -> Tensor:
+    """[rows, cols] 16-bit -> [cols, rows padded to a multiple of 8] (row stride of the result)."""
+    dev = _require_cuda(src, out)
+    assert src.dtype in (torch.bfloat16, torch.float16) and src.stride(1) == 1
+    rows, cols = src.shape
+    if out is None:
+        ld = (rows + 7) // 8 * 8
+        out = torch.empty((cols, ld), dtype=src.dtype, device=dev)
+    assert out.stride(1) == 1 and out.shape[0] >= cols and out.shape[1] >= rows
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_transpose_16(_ptr(src), src.stride(0), rows, cols, _ptr(out),
+                                          out.stride(0), _stream(dev)), "gn_transpose_16")
+    return out
+
+
+def colsum_accumulate(X: Tensor, out: Tensor) -> Tensor:
+    """out[n] += sum_m X[m, n] (fp32)."""
+    dev = _require_cuda(X, out)
+    assert X.stride(1) == 1 and out.dtype == torch.float32 and out.is_contiguous()
+    M, N = X.shape
+    assert out.numel() >= N
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_colsum_accumulate(_ptr(X), _dt_of(X), X.stride(0), M, N, _ptr(out),
+                                               _stream(dev)), "gn_colsum_accumulate")
+    return out
+
+
+def relu_backward(dY: Tensor, Y: Optional[Tensor], out: Optional[Tensor] = None) -> Tensor:
+    """bf16(dY * [Y > 0]) (Y None: plain conversion)."""
+    dev = _require_cuda(dY, Y, out)
+    M, N = dY.shape
+    if out is None:
+        out = torch.empty((M, (N + 7) // 8 * 8), dtype=torch.bfloat16, device=dev)[:, :N]
+    assert out.dtype == torch.bfloat16 and dY.stride(1) == 1 and out.stride(1) == 1
+    assert Y is None or (Y.stride(1) == 1 and Y.shape[0] == M and Y.shape[1] >= N)
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_relu_backward(_ptr(dY), _dt_of(dY), dY.stride(0), _ptr(Y),
+                                           0 if Y is None else _dt_of(Y),
+                                           0 if Y is None else Y.stride(0), _ptr(out),
+                                           out.stride(0), M, N, _stream(dev)), "gn_relu_backward")
+    return out
+
+
+def edge_build_h(P: Tensor, Q: Tensor, Kp: int, graph: Graph, H: Tensor,
+                 HT: Optional[Tensor]) -> None:
+    dev = _require_cuda(P, Q, H, HT)
+    assert P.dtype == torch.float16 and Q.dtype == torch.float16 and H.dtype == torch.bfloat16
+    N = P.shape[0]
+    gs = graph.c_struct()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_edge_build_h(_ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp,
+                                          C.byref(gs), N, _ptr(H), H.stride(0), _ptr(HT),
+                                          0 if HT is None else HT.stride(0), _stream(dev)),
+              "gn_edge_build_h")
+
+
+def edge_grad_z(Z: Tensor, dOut: Tensor, b: int, graph: Graph, G2: Tensor, G2T: Tensor) -> None:
+    dev = _require_cuda(Z, dOut, G2, G2T)
+    assert Z.dtype == torch.bfloat16 and dOut.dtype == torch.float32
+    assert G2.dtype == torch.bfloat16 and G2T.dtype == torch.bfloat16
+    N = dOut.shape[0]
+    gs = graph.c_struct()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_edge_grad_z(_ptr(Z), Z.stride(0), _ptr(dOut), dOut.stride(0), b,
+                                         C.byref(gs), N, _ptr(G2), G2.stride(0), _ptr(G2T),
+                                         G2T.stride(0), _stream(dev)), "gn_edge_grad_z")
+
+
+def edge_grad_pq(dH: Tensor, H: Tensor, Kp: int, graph: Graph, dP: Tensor, dQ: Tensor) -> None:
+    dev = _require_cuda(dH, H, dP, dQ)
+    assert dH.dtype == torch.bfloat16 and H.dtype == torch.bfloat16
+    assert dP.dtype == torch.bfloat16 and dQ.dtype == torch.float32
+    N = dP.shape[0]
+    gs = graph.c_struct()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_edge_grad_pq(_ptr(dH), dH.stride(0), _ptr(H), H.stride(0), Kp,
+                                          C.byref(gs), N, _ptr(dP), dP.stride(0), _ptr(dQ),
+                                          dQ.stride(0), _stream(dev)), "gn_edge_grad_pq")
+
+
+def segment_pool_backward(x: Tensor, ptr: Tensor, schemes: Sequence[str], pooled: Tensor,
+                          d_pooled: Tensor) -> Tensor:
+    """Gradient of `segment_pool` with respect to x -> [N, C] fp32."""
+    dev = _require_cuda(x, ptr, pooled, d_pooled)
+    assert x.stride(1) == 1 and pooled.dtype == torch.float32 and d_pooled.dtype == torch.float32
+    assert pooled.stride(1) == 1 and d_pooled.stride(1) == 1
+    N, C_ = x.shape
+    B = ptr.shape[0] - 1
+    dX = torch.zeros((N, C_), dtype=torch.float32, device=dev)
+    dt = DTYPE_BF16 if x.dtype == torch.bfloat16 else DTYPE_F32
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_segment_pool_backward(
+            _ptr(x), dt, x.stride(0), C_, _ptr(ptr), B, _host_i32([POOL[s] for s in schemes]),
+            len(schemes), _ptr(pooled), pooled.stride(0), _ptr(d_pooled), d_pooled.stride(0),
+            _ptr(dX), dX.stride(0), _stream(dev)), "gn_segment_pool_backward")
+    return dX

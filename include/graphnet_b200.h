@@ -229,6 +229,62 @@ int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t 
 int gn_task_head(const float* y, int64_t M, int p, int kind, float* out,
                  void* stream);
 
+/* ---- backward pass of the 16-bit training path (BASELINE config 3) ------------- */
+/* The reference holds no backward code: gradients come from torch autograd through the modules
+ * cited at each entry.  All matrices row-major; 16-bit operands 16-byte aligned with row strides
+ * that are multiples of 8 elements wherever they feed gn_tc_linear*. */
+
+/* C += A W^T with fp32 reductions (red.add): weight gradients dW = dY^T X of nn.Linear
+ * (gnn/dynedge.py:193-232), as A = dY^T [N_out, rows], W = X^T [K_in, rows]; also input gradients
+ * added onto an existing gradient (dX += dY W).  A [M,K], W [N,K] of ab_dtype; C [M,N] fp32 must
+ * hold the value to add onto (zeros for a fresh gradient).  `splits` > 1 cuts K into that many
+ * ranges handled by different CTAs (0 = choose so that all SMs are busy). */
+int gn_tc_linear_accumulate(const void* A, int64_t lda, const void* W, int64_t ldw, int ab_dtype,
+                            float* C, int64_t ldc, int64_t M, int N, int K, int splits,
+                            void* stream);
+
+/* dst[c, r] = src[r, c] for 16-bit elements (operand layout for the weight-gradient GEMMs). */
+int gn_transpose_16(const void* src, int64_t ld_src, int64_t rows, int cols, void* dst,
+                    int64_t ld_dst, void* stream);
+
+/* out[n] += sum_m X[m, n]: bias gradients of nn.Linear.  X of x_dtype (GN_F32 / GN_BF16). */
+int gn_colsum_accumulate(const void* X, int x_dtype, int64_t ldx, int64_t M, int N, float* out,
+                         void* stream);
+
+/* out = dY * [Y > 0] converted to bf16: backward of the ReLU after every Linear
+ * (dynedge.py:199-204, :224-232).  Y == NULL: plain conversion to bf16.  dY GN_F32 / GN_BF16. */
+int gn_relu_backward(const void* dY, int dy_dtype, int64_t ld_dy, const void* Y, int y_dtype,
+                     int64_t ld_y, void* out, int64_t ld_out, int64_t M, int N, void* stream);
+
+/* Re-materialise the hidden activations of the EdgeConv message MLP (PyG EdgeConv.message,
+ * components/layers.py:67) for every slot of an ELL graph (stride = slots per node, -1 = empty):
+ * H[i*stride + t, :] = ReLU(P_i + Q_j), zero rows for empty slots; bf16.  HT (optional) receives
+ * the transpose [Kp, N*stride] (row stride ldht). */
+int gn_edge_build_h(const void* P, int64_t ldp, const void* Q, int64_t ldq, int Kp,
+                    const gn_graph* graph, int64_t N, void* H, int64_t ldh, void* HT,
+                    int64_t ldht, void* stream);
+
+/* G2[e, :] = dOut[target(e), :] * [Z[e, :] > 0] (backward of the ReLU after the second Linear and
+ * of the aggr="add" sum, dynedge.py:206-211); Z [N*stride, b] bf16 recomputed pre-activations,
+ * dOut [N, b] fp32; writes G2 [N*stride, b] and its transpose G2T [b, N*stride], bf16. */
+int gn_edge_grad_z(const void* Z, int64_t ldz, const float* dOut, int64_t ldd, int b,
+                   const gn_graph* graph, int64_t N, void* G2, int64_t ldg, void* G2T,
+                   int64_t ldgt, void* stream);
+
+/* Backward of h = ReLU(P_i + Q_j): m = dH * [H > 0]; dP[i] = sum over the slots of node i (bf16,
+ * overwritten), dQ[j] += m (fp32, must be zeroed by the caller). */
+int gn_edge_grad_pq(const void* dH, int64_t lddh, const void* H, int64_t ldh, int Kp,
+                    const gn_graph* graph, int64_t N, void* dP, int64_t ldp, float* dQ,
+                    int64_t ldq, void* stream);
+
+/* Backward of gn_segment_pool (torch_scatter.scatter_{min,max,sum,mean}, dynedge.py:252-265):
+ * dX [N, C] fp32 (overwritten) from d_pooled [B, C*n_schemes]; min / max send their gradient to
+ * the first row of the event that attains the pooled value. */
+int gn_segment_pool_backward(const void* x, int x_dtype, int64_t ldx, int C, const int32_t* ptr,
+                             int64_t B, const int32_t* schemes, int n_schemes,
+                             const float* pooled, int64_t ld_pooled, const float* d_pooled,
+                             int64_t ld_dpooled, float* dX, int64_t ld_dx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
