@@ -14,6 +14,7 @@ from .graphs import KNNEdges, KNNGraph  # noqa: F401
 from .losses import LogCoshLoss, VonMisesFisher3DLoss  # noqa: F401
 from .ops import knn_graph  # noqa: F401
 from .standard_model import StandardModel  # noqa: F401
+from . import training  # noqa: F401
 from .tasks import (  # noqa: F401
     AzimuthReconstructionWithKappa,
     DirectionReconstructionWithKappa,

@@ -65,11 +65,13 @@ SIGNATURES = {
     "gn_tc_linear": (_int, [_p, _i64, _p, _i64, _int, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),
     "gn_tc_linear_accumulate": (_int, [_p, _i64, _p, _i64, _int, _p, _i64, _i64, _int, _int, _int, _p]),
     "gn_transpose_16": (_int, [_p, _i64, _i64, _int, _p, _i64, _p]),
+    "gn_csr_to_ell": (_int, [_p, _p, _i64, _int, _p, _p, _p, _p]),
     "gn_colsum_accumulate": (_int, [_p, _int, _i64, _i64, _int, _p, _p]),
     "gn_relu_backward": (_int, [_p, _int, _i64, _p, _int, _i64, _p, _i64, _i64, _int, _p]),
     "gn_edge_build_h": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _p, _i64, _p, _i64, _p]),
     "gn_edge_grad_z": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _p, _i64, _p, _i64, _p]),
-    "gn_edge_grad_pq": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _p, _i64, _p, _i64, _p]),
+    "gn_edge_grad_pq": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _p, _i64, _p, _i64, _p, _i64, _p]),
+    "gn_outer_accumulate_f32": (_int, [_p, _i64, _int, _p, _i64, _int, _i64, _p, _i64, _p]),
     "gn_segment_pool_backward": (_int, [_p, _int, _i64, _int, _p, _i64, _p, _int, _p, _i64, _p, _i64, _p, _i64, _p]),
     "gn_tc_edge_scratch_bytes": (_sz, [_gp, _i64, _int]),
     "gn_tc_edge_mlp_aggregate": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _int, _p, _int, _p, _i64, _int,

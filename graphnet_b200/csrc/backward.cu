@@ -193,7 +193,8 @@ __global__ void __launch_bounds__(256) edge_grad_z_kernel(
 __global__ void __launch_bounds__(256) edge_grad_pq_kernel(
     const __nv_bfloat16* __restrict__ dH, int64_t lddh, const __nv_bfloat16* __restrict__ H,
     int64_t ldh, int Kp, const int32_t* __restrict__ nbr, int KP, int64_t N,
-    __nv_bfloat16* __restrict__ dP, int64_t ldp, float* __restrict__ dQ, int64_t ldq) {
+    __nv_bfloat16* __restrict__ dP, int64_t ldp, float* __restrict__ dQ, int64_t ldq,
+    float* __restrict__ dP32, int64_t ldp32) {
   const int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (i >= N) return;
@@ -213,6 +214,42 @@ __global__ void __launch_bounds__(256) edge_grad_pq_kernel(
       if (g.y != 0.f) atomicAdd(dQ + (int64_t)j * ldq + k + 1, g.y);
     }
     *reinterpret_cast<__nv_bfloat162*>(dP + i * ldp + k) = __floats2bfloat162_rn(acc.x, acc.y);
+    if (dP32 != nullptr) *reinterpret_cast<float2*>(dP32 + i * ldp32 + k) = acc;
+  }
+}
+
+// ------------------------------------------------------------------ out += G^T X, X narrow, fp32
+// Weight gradient of the FIRST EdgeConv Linear (K = 2F+5 <= 32 raw input features): out[c, k] +=
+// sum_n G[n, c] X[n, k], all fp32 - the two halves of that gradient are subtracted from each
+// other (W1 acts on x_j - x_i), which amplifies any rounding of G or X.  A CTA takes 128 rows;
+// a thread owns output rows c, c+256, ... with KMAX accumulators each; X rows come from smem.
+template <int KMAX>
+__global__ void __launch_bounds__(256) outer_accumulate_kernel(const float* __restrict__ G,
+                                                               int64_t ldg, int cols,
+                                                               const float* __restrict__ X,
+                                                               int64_t ldx, int K, int64_t N,
+                                                               float* __restrict__ out,
+                                                               int64_t ldo) {
+  __shared__ float xs[128][KMAX];
+  const int64_t n0 = (int64_t)blockIdx.x * 128;
+  const int rows = (int)(N - n0 < 128 ? N - n0 : 128);
+  for (int idx = threadIdx.x; idx < 128 * KMAX; idx += 256) {
+    const int r = idx / KMAX, k = idx % KMAX;
+    xs[r][k] = (r < rows && k < K) ? X[(n0 + r) * ldx + k] : 0.f;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < cols; c += 256) {
+    float acc[KMAX];
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) acc[k] = 0.f;
+    for (int r = 0; r < rows; ++r) {
+      const float g = G[(n0 + r) * ldg + c];
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) acc[k] = fmaf(g, xs[r][k], acc[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k)
+      if (k < K) atomicAdd(out + (int64_t)c * ldo + k, acc[k]);
   }
 }
 
@@ -249,6 +286,27 @@ __global__ void __launch_bounds__(128) segment_pool_backward_kernel(
     if (!min_done && v == vmin) { g += gmin; min_done = true; }
     if (!max_done && v == vmax) { g += gmax; max_done = true; }
     dX[(int64_t)n * lddx + c] = g;
+  }
+}
+
+// ------------------------------------------------------------------ CSR -> slot table
+// nbr[i*stride + t] = t-th in-edge of node i (order kept), -1 beyond its degree; flags |=
+// GN_FLAG_DEGREE_OVERFLOW if a node has more than `stride` in-edges (those are dropped).
+__global__ void __launch_bounds__(256) csr_to_ell_kernel(const int32_t* __restrict__ rowptr,
+                                                         const int32_t* __restrict__ col,
+                                                         int64_t N, int stride,
+                                                         int32_t* __restrict__ nbr,
+                                                         int32_t* __restrict__ deg,
+                                                         int32_t* __restrict__ flags) {
+  const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= N * stride) return;
+  const int64_t i = idx / stride;
+  const int t = (int)(idx % stride);
+  const int32_t a = rowptr[i], b = rowptr[i + 1];
+  nbr[idx] = t < b - a ? col[a + t] : -1;
+  if (t == 0) {
+    deg[i] = b - a < stride ? b - a : stride;
+    if (b - a > stride && flags) atomicOr(flags, GN_FLAG_DEGREE_OVERFLOW);
   }
 }
 
@@ -368,17 +426,20 @@ extern "C" int gn_edge_grad_z(const void* Z, int64_t ldz, const float* dOut, int
 
 extern "C" int gn_edge_grad_pq(const void* dH, int64_t lddh, const void* H, int64_t ldh, int Kp,
                                const gn_graph* graph, int64_t N, void* dP, int64_t ldp, float* dQ,
-                               int64_t ldq, void* stream) {
+                               int64_t ldq, float* dP32, int64_t ldp32, void* stream) {
   int rc = check_ell(graph, "gn_edge_grad_pq");
   if (rc != GN_OK) return rc;
   GN_CHECK_ARG(Kp >= 2 && Kp % 2 == 0 && lddh >= Kp && ldh >= Kp && ldp >= Kp && ldq >= Kp,
                "gn_edge_grad_pq: bad sizes");
   if (N == 0) return GN_OK;
   GN_CHECK_ARG(dH && H && dP && dQ, "gn_edge_grad_pq: null pointer");
+  GN_CHECK_ARG(dP32 == nullptr || (ldp32 >= Kp && ldp32 % 2 == 0 &&
+                                   (reinterpret_cast<uintptr_t>(dP32) & 7) == 0),
+               "gn_edge_grad_pq: bad dP32");
   edge_grad_pq_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, as_stream(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(dH), lddh, reinterpret_cast<const __nv_bfloat16*>(H),
       ldh, Kp, graph->col, graph->ell_stride, N, reinterpret_cast<__nv_bfloat16*>(dP), ldp, dQ,
-      ldq);
+      ldq, dP32, ldp32);
   GN_LAUNCH_CHECK();
   return GN_OK;
 }
@@ -414,6 +475,33 @@ extern "C" int gn_segment_pool_backward(const void* x, int x_dtype, int64_t ldx,
         ld_dpooled, dX, ld_dx);
   else
     GN_CHECK_ARG(false, "gn_segment_pool_backward: bad x_dtype %d", x_dtype);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_csr_to_ell(const int32_t* rowptr, const int32_t* col, int64_t N, int stride,
+                             int32_t* nbr, int32_t* deg, int32_t* flags, void* stream) {
+  GN_CHECK_ARG(N >= 0 && stride >= 1, "gn_csr_to_ell: bad sizes");
+  if (N == 0) return GN_OK;
+  GN_CHECK_ARG(rowptr && col && nbr && deg, "gn_csr_to_ell: null pointer");
+  csr_to_ell_kernel<<<(unsigned)ceil_div(N * stride, 256), 256, 0, as_stream(stream)>>>(
+      rowptr, col, N, stride, nbr, deg, flags);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_outer_accumulate_f32(const float* G, int64_t ldg, int cols, const float* X,
+                                       int64_t ldx, int K, int64_t N, float* out, int64_t ldo,
+                                       void* stream) {
+  GN_CHECK_ARG(N >= 0 && cols >= 1 && K >= 1 && K <= 32 && ldg >= cols && ldx >= K && ldo >= K,
+               "gn_outer_accumulate_f32: bad sizes (K must be <= 32)");
+  if (N == 0) return GN_OK;
+  GN_CHECK_ARG(G && X && out, "gn_outer_accumulate_f32: null pointer");
+  const unsigned grid = (unsigned)ceil_div(N, 128);
+  cudaStream_t st = as_stream(stream);
+  if (K <= 8) outer_accumulate_kernel<8><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
+  else if (K <= 20) outer_accumulate_kernel<20><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
+  else outer_accumulate_kernel<32><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
   GN_LAUNCH_CHECK();
   return GN_OK;
 }

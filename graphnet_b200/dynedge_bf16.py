@@ -144,7 +144,8 @@ def _post_pack(model, total: int, D0: int, widths: List[int], offs: List[int],
 
 
 def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
-                 return_intermediates: bool = False):
+                 return_intermediates: bool = False, save: Optional[Dict[str, Any]] = None):
+    """`save` (training): receives the tensors the backward pass needs (training.py)."""
     x, n_pulses, ptr, graph, N, B = model._graph_inputs(data, edge_index)
     model._last_flags = graph.flags
     dev = x.device
@@ -180,6 +181,9 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
         else:
             ops.tc_linear_bf16(skip[:, off_in:], pk.Wp, pk.bias_p, P, K=d_in, act="none")
             ops.tc_linear_bf16(skip[:, off_in:], pk.Wq, None, Q, K=d_in, act="none")
+        if save is not None:
+            save["layers"].append({"P": P, "Q": Q, "graph": graph, "pack": pk, "off_in": off_in,
+                                   "d_in": d_in, "off_out": offs[li]})
         last = li + 1 == len(convs)
         need_graph = (not last) or return_intermediates
         cols = sorted(ops._columns(conv.features_subset, pk.b))
@@ -202,6 +206,8 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
                           dtype=torch.float32 if lastp else io, device=dev)
         ops.tc_linear_bf16(h, Wp, bias, out, K=K, act="relu")
         h = out
+        if save is not None:
+            save["post"].append(out)
     inter["post"] = h
 
     if not model._skip_readout:
@@ -217,7 +223,14 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
             h = pooled
         ro, ract = _parse_mlp(model._readout)
         for lin in ro:
+            hin = h
             h = ops.linear_f32(h, lin.weight, lin.bias, act=ract)
+            if save is not None:
+                save["readout"].append((lin, hin, h, ract))
+    if save is not None:
+        save.update({"x0": x0, "skip": skip, "offs": offs, "widths": widths, "D0": D0, "total": total,
+                     "ptr": ptr, "N": N, "B": B, "post_packs": packs,
+                     "pooled": inter.get("pooled")})
     if return_intermediates:
         inter["skip"] = skip
         inter["skip_offsets"] = offs

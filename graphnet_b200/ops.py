@@ -440,8 +440,9 @@ def edge_grad_z(Z: Tensor, dOut: Tensor, b: int, graph: Graph, G2: Tensor, G2T: 
                                          G2T.stride(0), _stream(dev)), "gn_edge_grad_z")
 
 
-def edge_grad_pq(dH: Tensor, H: Tensor, Kp: int, graph: Graph, dP: Tensor, dQ: Tensor) -> None:
-    dev = _require_cuda(dH, H, dP, dQ)
+def edge_grad_pq(dH: Tensor, H: Tensor, Kp: int, graph: Graph, dP: Tensor, dQ: Tensor,
+                 dP32: Optional[Tensor] = None) -> None:
+    dev = _require_cuda(dH, H, dP, dQ, dP32)
     assert dH.dtype == torch.bfloat16 and H.dtype == torch.bfloat16
     assert dP.dtype == torch.bfloat16 and dQ.dtype == torch.float32
     N = dP.shape[0]
@@ -449,7 +450,24 @@ def edge_grad_pq(dH: Tensor, H: Tensor, Kp: int, graph: Graph, dP: Tensor, dQ: T
     with torch.cuda.device(dev):
         check(_lib.load().gn_edge_grad_pq(_ptr(dH), dH.stride(0), _ptr(H), H.stride(0), Kp,
                                           C.byref(gs), N, _ptr(dP), dP.stride(0), _ptr(dQ),
-                                          dQ.stride(0), _stream(dev)), "gn_edge_grad_pq")
+                                          dQ.stride(0), _ptr(dP32),
+                                          0 if dP32 is None else dP32.stride(0), _stream(dev)),
+              "gn_edge_grad_pq")
+
+
+def outer_accumulate_f32(G: Tensor, X: Tensor, out: Tensor) -> Tensor:
+    """out[c, k] += sum_n G[n, c] X[n, k] (fp32, X at most 32 columns wide)."""
+    dev = _require_cuda(G, X, out)
+    assert G.dtype == X.dtype == out.dtype == torch.float32
+    assert G.stride(1) == 1 and X.stride(1) == 1 and out.stride(1) == 1
+    N, cols = G.shape
+    K = X.shape[1]
+    assert X.shape[0] == N and out.shape[0] >= cols and out.shape[1] >= K
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_outer_accumulate_f32(_ptr(G), G.stride(0), cols, _ptr(X), X.stride(0),
+                                                  K, N, _ptr(out), out.stride(0), _stream(dev)),
+              "gn_outer_accumulate_f32")
+    return out
 
 
 def segment_pool_backward(x: Tensor, ptr: Tensor, schemes: Sequence[str], pooled: Tensor,
@@ -468,3 +486,19 @@ def segment_pool_backward(x: Tensor, ptr: Tensor, schemes: Sequence[str], pooled
             len(schemes), _ptr(pooled), pooled.stride(0), _ptr(d_pooled), d_pooled.stride(0),
             _ptr(dX), dX.stride(0), _stream(dev)), "gn_segment_pool_backward")
     return dX
+
+
+def csr_to_ell(graph: Graph, stride: int) -> Graph:
+    """Slot-table (ELL) form of a CSR graph; `stride` must be >= its maximum in-degree."""
+    if graph.ell_stride > 0:
+        return graph
+    dev = _require_cuda(graph.col, graph.rowptr)
+    N = graph.num_nodes
+    nbr = torch.empty((N, stride), dtype=torch.int32, device=dev)
+    deg = torch.empty(N, dtype=torch.int32, device=dev)
+    flags = graph.flags if graph.flags is not None else torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_csr_to_ell(_ptr(graph.rowptr), _ptr(graph.col), N, stride, _ptr(nbr),
+                                        _ptr(deg), _ptr(flags), _stream(dev)), "gn_csr_to_ell")
+    return Graph(col=nbr, deg=deg, rowptr=None, ell_stride=stride, num_nodes=N, flags=flags,
+                 max_degree=graph.max_degree)

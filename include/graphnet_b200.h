@@ -63,6 +63,7 @@ extern "C" {
 #define GN_FLAG_UNSORTED_BATCH 1
 #define GN_FLAG_UNSORTED_TARGETS 2
 #define GN_FLAG_INDEX_OUT_OF_RANGE 4
+#define GN_FLAG_DEGREE_OVERFLOW 8
 
 /*
  * In-edges grouped by target node.  Two layouts:
@@ -272,10 +273,17 @@ int gn_edge_grad_z(const void* Z, int64_t ldz, const float* dOut, int64_t ldd, i
                    int64_t ldgt, void* stream);
 
 /* Backward of h = ReLU(P_i + Q_j): m = dH * [H > 0]; dP[i] = sum over the slots of node i (bf16,
- * overwritten), dQ[j] += m (fp32, must be zeroed by the caller). */
+ * overwritten; dP32, if not NULL, receives the same sums unrounded), dQ[j] += m (fp32, must be
+ * zeroed by the caller). */
 int gn_edge_grad_pq(const void* dH, int64_t lddh, const void* H, int64_t ldh, int Kp,
                     const gn_graph* graph, int64_t N, void* dP, int64_t ldp, float* dQ,
-                    int64_t ldq, void* stream);
+                    int64_t ldq, float* dP32, int64_t ldp32, void* stream);
+
+/* out[c, k] += sum_n G[n, c] X[n, k], all fp32, K <= 32: weight gradient of the first EdgeConv
+ * Linear (dynedge.py:193-199) with respect to the raw input features - its two halves are
+ * subtracted (the Linear acts on [x_i, x_j - x_i]), so it is kept out of 16-bit arithmetic. */
+int gn_outer_accumulate_f32(const float* G, int64_t ldg, int cols, const float* X, int64_t ldx,
+                            int K, int64_t N, float* out, int64_t ldo, void* stream);
 
 /* Backward of gn_segment_pool (torch_scatter.scatter_{min,max,sum,mean}, dynedge.py:252-265):
  * dX [N, C] fp32 (overwritten) from d_pooled [B, C*n_schemes]; min / max send their gradient to
@@ -284,6 +292,14 @@ int gn_segment_pool_backward(const void* x, int x_dtype, int64_t ldx, int C, con
                              int64_t B, const int32_t* schemes, int n_schemes,
                              const float* pooled, int64_t ld_pooled, const float* d_pooled,
                              int64_t ld_dpooled, float* dX, int64_t ld_dx, void* stream);
+
+/* CSR -> slot table (ELL) for the backward kernels, which address edges as (node, slot):
+ * nbr[i*stride + t] = t-th in-edge of node i in CSR order, -1 beyond its degree; deg[i] =
+ * min(degree, stride).  A node with more than `stride` in-edges sets GN_FLAG_DEGREE_OVERFLOW in
+ * *flags (may be NULL) and loses the excess: the caller picks stride >= the maximum degree
+ * reported by gn_coo_to_csr.  Layout plumbing for the user edge_index (PyG Batch) of layer 1. */
+int gn_csr_to_ell(const int32_t* rowptr, const int32_t* col, int64_t N, int stride, int32_t* nbr,
+                  int32_t* deg, int32_t* flags, void* stream);
 
 #ifdef __cplusplus
 }

@@ -96,9 +96,15 @@ def test_edge_backward_blocks(dev):
     dH = torch.randn((E, Kp), generator=g, device=dev).to(torch.bfloat16)
     dP = torch.empty((N, Kp), dtype=torch.bfloat16, device=dev)
     dQ = torch.zeros((N, Kp), dtype=torch.float32, device=dev)
-    ops.edge_grad_pq(dH, H, Kp, ell, dP, dQ)
+    dP32 = torch.empty((N, Kp), dtype=torch.float32, device=dev)
+    ops.edge_grad_pq(dH, H, Kp, ell, dP, dQ, dP32)
     m = dH.float() * (H.float() > 0) * filled[:, None]
     dPref = m.reshape(N, KP, Kp).sum(1)
+    assert _rel(dP32, dPref) < 1e-5
+    X = torch.randn((N, 19), generator=g, device=dev)
+    acc = torch.ones((Kp, 19), device=dev)
+    ops.outer_accumulate_f32(dP32, X, acc)
+    assert _rel(acc, 1.0 + dP32.double().t() @ X.double()) < 1e-5
     dQref = torch.zeros((N, Kp), device=dev).index_add_(0, nbr.clamp_min(0), m)
     assert _rel(dP.float(), dPref) < 5e-3
     assert _rel(dQ, dQref) < 1e-5
