@@ -143,6 +143,21 @@ class DynEdgeConv(torch.nn.Module):
 from . import _lib as _lib_flags  # noqa: E402  (flag constants)
 
 
+class _DataView:
+    """`data` with another edge_index (the sorted copy), same attributes otherwise."""
+
+    def __init__(self, data: Any, edge_index: Tensor):
+        self._data = data
+        self.edge_index = edge_index
+
+    def __getattr__(self, name: str) -> Any:
+        return getattr(self._data, name)
+
+
+def _with_edge_index(data: Any, edge_index: Tensor) -> Any:
+    return _DataView(data, edge_index)
+
+
 class DynEdge(torch.nn.Module):
     """DynEdge (dynamical edge convolutional) model (dynedge.py:22-350).
 
@@ -294,7 +309,6 @@ class DynEdge(torch.nn.Module):
         self._readout = torch.nn.Sequential(*readout_layers)
 
     # ------------------------------------------------------------------ forward
-    @torch.no_grad()
     def forward(self, data: Any) -> Tensor:
         """Apply the forward pass (dynedge.py:296-350) to a collated batch.
 
@@ -304,6 +318,14 @@ class DynEdge(torch.nn.Module):
         """
         if self._add_norm_layer:
             raise NotImplementedError("add_norm_layer=True is not built yet")
+        training = (self.training and self.precision == "bf16" and torch.is_grad_enabled()
+                    and any(p.requires_grad for p in self.parameters()))
+        if not training:   # inference kernels allocate nothing for autograd
+            with torch.no_grad():
+                return self._forward_checked(data)
+        return self._forward_checked(data)
+
+    def _forward_checked(self, data: Any) -> Tensor:
         out = self._dispatch(data, None)
         if self.validate_inputs and self._last_flags is not None:
             # one 4-byte device->host read per forward; set validate_inputs=False to
@@ -323,6 +345,15 @@ class DynEdge(torch.nn.Module):
     _last_flags: Optional[Tensor] = None
 
     def _dispatch(self, data: Any, edge_index: Optional[Tensor]) -> Tensor:
+        if (self.training and self.precision == "bf16" and torch.is_grad_enabled()
+                and any(p.requires_grad for p in self.parameters())):
+            # train mode with autograd recording: the forward that keeps what the hand-written
+            # backward needs (the fp32 / fp16 paths have no backward: their outputs carry no
+            # grad_fn, so `.backward()` on them fails loudly)
+            from .training import dynedge_train_forward
+            if edge_index is not None:
+                data = _with_edge_index(data, edge_index)
+            return dynedge_train_forward(self, data)
         if self.precision in ("bf16", "fp16"):
             from .dynedge_bf16 import forward_bf16
             return forward_bf16(self, data, edge_index)

@@ -90,6 +90,24 @@ class StandardModel(torch.nn.Module):
         preds = self(batch)
         return self.compute_loss(preds, batch)
 
+    def training_step(self, train_batch: Any, batch_idx: int = 0) -> Tensor:
+        """easy_model.py:223-239 without the Lightning logging: the loss of one batch, with
+        autograd recording (call `.backward()` on it; the backbone's backward is hand-written,
+        training.py)."""
+        if isinstance(train_batch, (list, tuple)) and len(train_batch) == 1:
+            train_batch = train_batch[0]
+        return self.shared_step(train_batch, batch_idx)
+
+    def configure_optimizers(self) -> Any:
+        """easy_model.py:77-96: optimizer (+ optional scheduler dict) from the ctor arguments."""
+        optimizer = self._optimizer_class(self.parameters(), **self._optimizer_kwargs)
+        if self._scheduler_class is None:
+            return {"optimizer": optimizer}
+        scheduler = self._scheduler_class(optimizer, **self._scheduler_kwargs)
+        config = {"optimizer": optimizer, "lr_scheduler": {"scheduler": scheduler}}
+        config["lr_scheduler"].update(self._scheduler_config)
+        return config
+
     def inference(self) -> None:
         """easy_model.py:276-279."""
         for task in self._tasks:

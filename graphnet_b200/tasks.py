@@ -17,6 +17,29 @@ from torch import Tensor
 from . import ops
 
 
+def _head_autograd(x: Tensor, kind: str) -> Tensor:
+    """The `_forward` transforms of task/reconstruction.py:11-112 as differentiable torch ops
+    (same arithmetic as csrc/heads.cu; used only while autograd is recording)."""
+    eps = torch.finfo(x.dtype).eps
+    if kind == "IdentityTask":
+        return x
+    if kind == "EnergyReconstruction":
+        return torch.nn.functional.softplus(x, beta=0.05) + eps
+    if kind == "DirectionReconstructionWithKappa":
+        kappa = torch.linalg.vector_norm(x, dim=1) + eps
+        return torch.cat([x[:, :3] / kappa[:, None], kappa[:, None]], dim=1)
+    if kind == "ZenithReconstruction":
+        return torch.sigmoid(x[:, :1]) * np.pi
+    if kind == "ZenithReconstructionWithKappa":
+        return torch.stack([torch.sigmoid(x[:, 0]) * np.pi, x[:, 1].abs() + eps], dim=1)
+    if kind == "AzimuthReconstructionWithKappa":
+        kappa = torch.linalg.vector_norm(x, dim=1) + eps
+        angle = torch.atan2(x[:, 1], x[:, 0])
+        angle = torch.where(angle < 0, angle + 2 * np.pi, angle)
+        return torch.stack([angle, kappa], dim=1)
+    raise NotImplementedError(f"training through the {kind} head")
+
+
 class StandardLearnedTask(torch.nn.Module):
     """affine -> `_forward` head transform -> prediction transform (task.py:284-295)."""
 
@@ -114,13 +137,19 @@ class StandardLearnedTask(torch.nn.Module):
             return self._transform_prediction_inference(prediction)
         return self._transform_prediction_training(prediction)
 
-    @torch.no_grad()
     def forward(self, x: Tensor) -> Tensor:
         self._regularisation_loss = 0
-        if isinstance(self._affine, torch.nn.Linear):
-            x = ops.linear_f32(x.float().contiguous(), self._affine.weight, self._affine.bias)
-        x = ops.task_head(x, self._head_kind)
-        return self._transform_prediction(x)
+        if torch.is_grad_enabled() and (x.requires_grad or any(
+                p.requires_grad for p in self._affine.parameters())):
+            # training: [B, hidden] -> [B, <=4]; autograd records these few element-wise torch
+            # ops (the backbone's backward is the hand-written one, training.py)
+            x = self._affine(x.float())
+            return self._transform_prediction(_head_autograd(x, self._head_kind))
+        with torch.no_grad():
+            if isinstance(self._affine, torch.nn.Linear):
+                x = ops.linear_f32(x.float().contiguous(), self._affine.weight, self._affine.bias)
+            x = ops.task_head(x, self._head_kind)
+            return self._transform_prediction(x)
 
     def compute_loss(self, pred: Tensor, data: Any) -> Tensor:
         """task.py:330-348."""

@@ -135,3 +135,38 @@ def test_optimizer_step_reduces_loss(dev):
         opt.step()
         losses.append(float(loss))
     assert losses[-1] < losses[0], losses
+
+
+def test_standard_model_training_step(dev):
+    """StandardModel.training_step -> backward -> Adam, through the public API."""
+    import graphnet_b200 as g
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(48, 25.0, seed=31)
+    x = pb.x.to(dev)
+    batch = pb.batch.to(dev)
+    ei = g.knn_graph(x[:, :3].contiguous(), 8, batch, num_events=48)
+    data = g.Data(x=x, edge_index=ei, batch=batch, n_pulses=pb.n_pulses.to(dev),
+                  energy=torch.rand(48, device=dev) * 3 + 0.5)
+    torch.manual_seed(1)
+    backbone = g.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision="bf16")
+    task = g.EnergyReconstruction(hidden_size=backbone.nb_outputs, target_labels="energy",
+                                  loss_function=g.LogCoshLoss())
+    model = g.StandardModel(tasks=[task], graph_definition=object(), gnn=backbone,
+                            optimizer_kwargs={"lr": 1e-3, "eps": 1e-3}).to(dev)
+    model.train()
+    opt = model.configure_optimizers()["optimizer"]
+    losses = []
+    for _ in range(10):
+        opt.zero_grad(set_to_none=True)
+        loss = model.training_step(data, 0)
+        loss.backward()
+        assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters())
+        opt.step()
+        losses.append(float(loss))
+    assert losses[-1] < losses[0], losses
+    # inference afterwards still runs the kernel heads and carries no graph
+    model.train(False)
+    model.inference()
+    with torch.no_grad():
+        pred = model(data)[0]
+    assert pred.shape == (48, 1) and not pred.requires_grad
