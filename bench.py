@@ -32,6 +32,7 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 METRIC = "DynEdge inference events/sec"
+TRAIN_METRIC = "DynEdge training events/sec"
 UNIT = "events/s"
 POOLS = ["min", "max", "mean", "sum"]
 
@@ -48,10 +49,17 @@ def parse_args():
     ap.add_argument("--cpu-events", type=int, default=128,
                     help="events per CPU-baseline step (reference distribute step is O(N*B))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="infer", choices=["infer", "train"],
+                    help="infer: BASELINE configs[1] (default); train: configs[2] (bf16 training "
+                         "step: forward, backward, gradient all-reduce, Adam)")
     return ap.parse_args()
 
 
 def workload_name(args):
+    if getattr(args, "mode", "infer") == "train":
+        return (f"C3: DynEdge training step (forward, backward, gradient all-reduce, Adam), bf16, "
+                f"synthetic IceCube-86 events, ~{args.pulses:g} pulses/event, k=8, batch "
+                f"{args.events}/GPU, LogCosh on log10-energy targets ~U(0,4)")
     return (f"C2: DynEdge inference, synthetic IceCube-86 pulse maps, ~{args.pulses:g} pulses/event, "
             f"k=8, batch {args.events}/GPU, pools min/max/mean/sum, EnergyReconstruction head")
 
@@ -109,6 +117,50 @@ def cpu_reference_events_per_s(num_events, pulses, steps, warmup, seed=1234):
     return num_events * steps / total, cores, total / steps
 
 
+def cpu_reference_train_events_per_s(num_events, pulses, steps, warmup, seed=1234):
+    """Oracle port of the reference's CPU training step (torch autograd + Adam)."""
+    import oracle
+    from oracle.ops import knn_graph_padded
+    from oracle import tasks as otasks
+    from graphnet_b200.synthetic import make_pulse_batch
+    import oracle.ops as oops
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    pb = make_pulse_batch(num_events, pulses, seed=seed)
+    ei = knn_graph_padded(pb.x[:, :3], 8, pb.batch)
+    spec = oracle.DynEdgeSpec(nb_inputs=7, global_pooling_schemes=POOLS)
+    sd = {k: v.clone().requires_grad_(True) for k, v in
+          oracle.init_dynedge_state_dict(spec, seed=0).items()}
+    torch.manual_seed(1)
+    head = torch.nn.Linear(128, 1)
+    target = torch.rand(num_events, 1, generator=torch.Generator().manual_seed(7)) * 4
+    opt = torch.optim.Adam(list(sd.values()) + list(head.parameters()), lr=1e-3, eps=1e-3)
+    loop_knn = oops.knn_graph
+    oops.knn_graph = lambda x, k, batch=None, loop=False: knn_graph_padded(x, k, batch)
+    try:
+        def step():
+            opt.zero_grad(set_to_none=True)
+            y = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses,
+                                       dense_distribute=True)
+            pred = otasks.task_forward("EnergyReconstruction", head.weight, head.bias, y)
+            d = pred - target
+            loss = (d + torch.nn.functional.softplus(-2.0 * d) - 0.6931471805599453).mean()
+            loss.backward()
+            opt.step()
+        for _ in range(warmup):
+            step()
+        times = []
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            step()
+            times.append(time.perf_counter() - t0)
+    finally:
+        oops.knn_graph = loop_knn
+    total = sum(times)
+    return num_events * steps / total, cores, total / steps
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -117,12 +169,16 @@ def run_reference(args):
     # bound the run: ~0.3 s per 128-event step on 8 cores
     steps = min(steps, 40)
     warmup = min(warmup, 3)
-    v, cores, sec = cpu_reference_events_per_s(args.cpu_events, args.pulses, steps, warmup)
+    train = args.mode == "train"
+    fn = cpu_reference_train_events_per_s if train else cpu_reference_events_per_s
+    if train:
+        steps = min(steps, 15)
+    v, cores, sec = fn(args.cpu_events, args.pulses, steps, warmup)
     sample = (f"{args.cpu_events}-event batch of the same workload per step (reference distribute "
               f"step allocates N*B*G floats), {steps} steps, oracle port of the reference's CPU path "
               f"incl. its dense one-hot distribute")
     line = {
-        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+        "impl": "reference", "metric": TRAIN_METRIC if train else METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args), "cpu_events_per_step": args.cpu_events},
@@ -332,6 +388,136 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_ours_train(args):
+    """BASELINE configs[2]: one step = forward + backward + gradient all-reduce + Adam on one
+    collated batch per GPU (data parallel, weak scaling; the all-reduce is the one exchange)."""
+    import torch.distributed as dist
+    import graphnet_b200 as g
+    from graphnet_b200 import _lib
+    from graphnet_b200.sharding import allreduce_gradients
+    from graphnet_b200.synthetic import make_pulse_batch
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+
+    pb = make_pulse_batch(args.events, args.pulses, seed=1234 + rank)
+    x_dev, batch_dev, npulse_dev = pb.x.to(dev), pb.batch.to(dev), pb.n_pulses.to(dev)
+    ei_dev = g.knn_graph(x_dev[:, :3].contiguous(), 8, batch_dev, num_events=args.events)
+    target = torch.rand(args.events, generator=torch.Generator().manual_seed(7 + rank)) * 4
+    host = {"x": pb.x.pin_memory(), "edge_index": ei_dev.cpu().pin_memory(),
+            "batch": pb.batch.pin_memory(), "n_pulses": pb.n_pulses.pin_memory(),
+            "energy": target.pin_memory()}
+    N, E = x_dev.shape[0], ei_dev.shape[1]
+
+    torch.manual_seed(0)   # same initial weights on every rank (DDP broadcasts them; same seed here)
+    backbone = g.DynEdge(7, global_pooling_schemes=POOLS, precision="bf16")
+    task = g.EnergyReconstruction(hidden_size=backbone.nb_outputs, target_labels="energy",
+                                  loss_function=g.LogCoshLoss())
+    model = g.StandardModel(tasks=[task], graph_definition=object(), gnn=backbone,
+                            optimizer_kwargs={"lr": 1e-3, "eps": 1e-3}).to(dev)
+    model.train()
+    backbone.validate_inputs = False
+    params = [p for p in model.parameters() if p.requires_grad]
+    opt = model.configure_optimizers()["optimizer"]
+    data_dev = g.Data(x=x_dev, edge_index=ei_dev, batch=batch_dev, n_pulses=npulse_dev,
+                      energy=target.to(dev))
+    backbone.check_inputs(data_dev)
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    grad_bytes = [0]
+
+    def train_step(d):
+        opt.zero_grad(set_to_none=True)
+        loss = model.training_step(d, 0)
+        loss.backward()
+        grad_bytes[0] = allreduce_gradients(params)
+        opt.step()
+        return loss
+
+    def step_resident():
+        return train_step(data_dev)
+
+    def step_e2e():
+        d = g.Data(**{k: v.to(dev, non_blocking=True) for k, v in host.items()})
+        return float(train_step(d).item())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        ends = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+        launches0 = lib.gn_launch_count()
+        for i in range(steps):
+            flush_buf.fill_(i & 0xFF)
+            starts[i].record()
+            fn()
+            ends[i].record()
+        barrier()
+        launches = lib.gn_launch_count() - launches0
+        ms = sum(a.elapsed_time(b) for a, b in zip(starts, ends))
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, launches
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_res, launches = timed(step_resident, args.steps, max(3, args.warmup))
+    ms_e2e, _ = timed(step_e2e, args.steps, max(3, args.warmup))
+    clocks = sampler.stop() if rank == 0 else None
+    peak_mem = torch.cuda.max_memory_allocated(dev)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    events_total = args.events * world
+    h2d = sum(t.numel() * t.element_size() for t in host.values())
+    # executed tensor work per step (factored forward; backward = 3 slot GEMMs per EdgeConv +
+    # two GEMMs per Linear), for orientation only
+    line = {
+        "metric": TRAIN_METRIC, "value": events_total * args.steps / (ms_res * 1e-3), "unit": UNIT,
+        "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "ms_per_step": ms_res / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": workload_name(args), "nodes_per_batch": N, "edges_per_batch": E,
+                   "l2": "256 MiB buffer written between timed steps (L2 flush)",
+                   "parallelism": f"data parallel, {world} rank(s), one flat NCCL all-reduce of "
+                                  f"{grad_bytes[0]} gradient bytes per step",
+                   "optimizer": "torch.optim.Adam(lr=1e-3, eps=1e-3) on fp32 master weights",
+                   "peak_device_memory_mb": peak_mem / 1e6},
+        "e2e": {"value": events_total * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": None,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        v, cores, sec = cpu_reference_train_events_per_s(args.cpu_events, args.pulses, steps=5,
+                                                         warmup=1)
+        line["cpu_baseline"] = {
+            "value": v, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"5 training steps of a {args.cpu_events}-event batch of the same workload "
+                      f"({sec * 1e3:.0f} ms/step), oracle port (torch autograd + Adam on CPU)"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def ncu_traffic_bytes(kernel_name):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the
     committed `ncu --set full` capture of this workload (profiles/r01_edge_kernel_ncu.json);
@@ -396,5 +582,7 @@ if __name__ == "__main__":
     a = parse_args()
     if a.impl == "reference":
         run_reference(a)
+    elif a.mode == "train":
+        run_ours_train(a)
     else:
         run_ours(a)

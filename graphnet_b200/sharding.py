@@ -81,3 +81,33 @@ def predict_sharded(model: Callable[[Any], Tensor], data: Any, device: torch.dev
     if isinstance(out, (list, tuple)):
         out = out[0]
     return gather_event_outputs(out, [h - l for l, h in ranges])
+
+
+def allreduce_gradients(params: Sequence[torch.nn.Parameter], average: bool = True) -> int:
+    """Data-parallel training: one all-reduce over every gradient of the replica.
+
+    The reference trains under Lightning's DDP strategy (easy_model.py:101-124), i.e. an NCCL
+    all-reduce of the gradients per step; DynEdge has 1.38 M parameters (5.5 MB fp32), so the
+    whole set goes out as ONE flat buffer after the backward pass - launch latency, not
+    bandwidth, is what this exchange costs on NVLink.  Parameters without a gradient count as
+    zeros (every rank must contribute the same layout).  Returns the bytes reduced.
+    """
+    params = [p for p in params if p.requires_grad]
+    if not params or not (dist.is_available() and dist.is_initialized()) or \
+            dist.get_world_size() == 1:
+        return 0
+    flat = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1).float()
+                      for p in params])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+    if average:
+        flat /= dist.get_world_size()
+    off = 0
+    for p in params:
+        n = p.numel()
+        g = flat[off:off + n].view_as(p).to(p.dtype)
+        if p.grad is None:
+            p.grad = g.clone()
+        else:
+            p.grad.copy_(g)
+        off += n
+    return flat.numel() * 4

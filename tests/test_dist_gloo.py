@@ -10,7 +10,8 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from graphnet_b200.sharding import predict_sharded, shard_ranges, take_events
+from graphnet_b200.sharding import (allreduce_gradients, predict_sharded, shard_ranges,
+                                    take_events)
 from graphnet_b200.synthetic import make_pulse_batch
 from graphnet_b200.data import Data
 import oracle
@@ -77,3 +78,44 @@ def test_predict_sharded_world2_gloo():
         assert p.exitcode == 0
     want = _fake_model(_make())
     assert torch.allclose(outs[0], want) and torch.allclose(outs[1], want)
+
+
+def _grad_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.ReLU(), torch.nn.Linear(7, 2))
+    frozen = torch.nn.Parameter(torch.ones(3), requires_grad=False)
+    x = torch.randn(16, 5, generator=torch.Generator().manual_seed(100 + rank))
+    net(x).square().mean().backward()
+    if rank == 1:
+        net[2].bias.grad = None          # a rank that produced no gradient for a tensor
+    local = [None if p.grad is None else p.grad.clone() for p in net.parameters()]
+    nbytes = allreduce_gradients(list(net.parameters()) + [frozen])
+    q.put((rank, nbytes, [None if t is None else t.tolist() for t in local],
+           [p.grad.tolist() for p in net.parameters()]))   # plain lists: no shared-memory handles
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_allreduce_gradients_world2():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 200) + 211
+    procs = [ctx.Process(target=_grad_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, nb0, loc0, red0), (_, nb1, loc1, red1) = res
+    red0 = [torch.tensor(t) for t in red0]
+    red1 = [torch.tensor(t) for t in red1]
+    nparam = sum(t.numel() for t in red0)
+    assert nb0 == nb1 == 4 * nparam
+    for a, b, r0, r1 in zip(loc0, loc1, red0, red1):
+        a = torch.tensor(a)
+        b = torch.zeros_like(a) if b is None else torch.tensor(b)
+        assert torch.allclose(r0, (a + b) / 2, atol=1e-7) and torch.equal(r0, r1)
