@@ -1,0 +1,88 @@
+"""BASELINE.json configs 4 and 5 as parity cases (sizes the CPU oracle finishes in seconds).
+
+C4: IceCube-Upgrade geometry, F = 14, ~500 pulses/event, k = 16, pools min/max/mean (QUESO).
+C5: direction + energy heads on one backbone, pulses/event swept from 16 to 2048 (fixed n).
+"""
+import pytest
+import torch
+
+import oracle
+from oracle import tasks as otasks
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda:0")
+
+
+def rel_l2(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm().clamp(min=1e-30))
+
+
+def _run(pb, ei, nb_inputs, k, pools, precision, seed=0):
+    import graphnet_b200 as gb
+    spec = oracle.DynEdgeSpec(nb_inputs=nb_inputs, nb_neighbours=k, global_pooling_schemes=pools)
+    sd = oracle.init_dynedge_state_dict(spec, seed=seed)
+    want = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
+    m = gb.DynEdge(nb_inputs, nb_neighbours=k, global_pooling_schemes=pools, precision=precision)
+    m.load_state_dict(sd)
+    m = m.to(DEV)
+    data = gb.Data(x=pb.x.to(DEV), edge_index=ei.to(DEV), batch=pb.batch.to(DEV),
+                   n_pulses=pb.n_pulses.to(DEV))
+    with torch.no_grad():
+        got = m(data).cpu()
+    return got, want, m, data
+
+
+def test_c4_upgrade_k16_graph_is_bit_exact():
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(6, 500.0, detector="upgrade", seed=41)
+    assert pb.x.shape[1] == 14
+    want = oracle.knn_graph(pb.x[:, :3], 16, pb.batch)
+    got = gb.knn_graph(pb.x[:, :3].contiguous().to(DEV), 16, pb.batch.to(DEV), num_events=6)
+    assert torch.equal(got.cpu(), want)
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("bf16", 2e-2), ("fp16", 2e-2)])
+def test_c4_upgrade_forward(precision, tol):
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(6, 500.0, detector="upgrade", seed=41)
+    ei = oracle.knn_graph(pb.x[:, :3], 16, pb.batch)
+    got, want, _, _ = _run(pb, ei, 14, 16, ["min", "max", "mean"], precision)
+    per_event = (got - want).norm(dim=1) / want.norm(dim=1)
+    # the layer 2-4 graphs are rebuilt from latents: a near-tie resolved the other way changes
+    # one event's output at the 1e-3 level in fp32, so the fp32 bar is on
+    # the median event and a looser one on the worst
+    assert float(per_event.median()) < tol, per_event
+    assert float(per_event.max()) < (5e-3 if precision == "fp32" else 2 * tol), per_event
+
+
+@pytest.mark.parametrize("n", [16, 256, 2048])
+def test_c5_sweep_two_tasks(n):
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    events = 3 if n >= 1024 else 8
+    pb = make_pulse_batch(events, fixed_pulses=n, seed=50 + n)
+    ei = oracle.knn_graph(pb.x[:, :3], 8, pb.batch)
+    pools = ["min", "max", "mean", "sum"]
+    for precision, tol in (("fp32", 1e-4), ("bf16", 2e-2)):
+        got, want, m, data = _run(pb, ei, 7, 8, pools, precision)
+        per_event = (got - want).norm(dim=1) / want.norm(dim=1)
+        assert float(per_event.median()) < tol, (precision, per_event)
+        assert float(per_event.max()) < (5e-3 if precision == "fp32" else 2 * tol), (precision, per_event)
+    # the two task heads of config 5 on the fp32 backbone output
+    torch.manual_seed(9)
+    tasks = [gb.DirectionReconstructionWithKappa(hidden_size=128, loss_function=gb.VonMisesFisher3DLoss()),
+             gb.EnergyReconstruction(hidden_size=128, loss_function=gb.LogCoshLoss())]
+    m32 = gb.DynEdge(7, global_pooling_schemes=pools)
+    m32.load_state_dict({k: v for k, v in m.state_dict().items()})
+    model = gb.StandardModel(tasks=tasks, graph_definition=object(), gnn=m32).to(DEV)
+    model.train(False)
+    with torch.no_grad():
+        preds = model(data)
+    y = want
+    w0 = otasks.task_forward("DirectionReconstructionWithKappa", tasks[0]._affine.weight.detach().cpu(),
+                             tasks[0]._affine.bias.detach().cpu(), y)
+    w1 = otasks.task_forward("EnergyReconstruction", tasks[1]._affine.weight.detach().cpu(),
+                             tasks[1]._affine.bias.detach().cpu(), y)
+    assert preds[0].shape == (events, 4) and preds[1].shape == (events, 1)
+    assert rel_l2(preds[0].cpu(), w0) < 5e-3 and rel_l2(preds[1].cpu(), w1) < 5e-3
