@@ -81,6 +81,10 @@ constexpr int LIN_EPI_WARPS = 8;
 constexpr int LIN_THREADS = 32 * (2 + LIN_EPI_WARPS);  // TMA + MMA + 8 epilogue warps
 constexpr int LIN_MAX_N = 2048;   // bias staged in shared memory
 constexpr int LIN_A_BYTES = LIN_BM * LIN_BK * 2;  // 16 KB
+// per epilogue warp: a 32-row x 32-column chunk on its way from "lane = row" (tcgen05.ld) to
+// "lanes = consecutive 16-byte pieces of a row" (coalesced global stores); rows padded by 16 B
+constexpr int LIN_SCR_PITCH = 32 * 4 + 16;
+constexpr int LIN_SCR_BYTES = 32 * LIN_SCR_PITCH;  // 4608
 
 struct __align__(16) LinBarriers {
   uint64_t full[LIN_STAGES];
@@ -168,7 +172,8 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
     int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages, int splits,
-    int accumulate) {
+    int accumulate, int coalesce_in) {
+  const bool coalesce = coalesce_in != 0 && accumulate == 0;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -177,6 +182,8 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
   const int stage_bytes = LIN_A_BYTES + b_bytes;
   LinBarriers* bars = reinterpret_cast<LinBarriers*>(smem + stages * stage_bytes);
   float* s_bias = reinterpret_cast<float*>(bars + 1);  // [num_n_tiles * BN]
+  uint8_t* s_scr = reinterpret_cast<uint8_t*>(s_bias + num_n_tiles * BN);  // 8 x LIN_SCR_BYTES
+  s_scr = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_scr) + 15) & ~uintptr_t(15));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = (K + LIN_BK - 1) / LIN_BK;
@@ -299,7 +306,52 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
               continue;
             }
           }
-          store_row32<OutT>(C + row * ldc + n, v, min(N - n, BN - c));
+          if (!coalesce) store_row32<OutT>(C + row * ldc + n, v, min(N - n, BN - c));
+        }
+        if (coalesce) {
+          // registers (lane = row) -> this warp's scratch -> 16-byte pieces, lanes along the row:
+          // one store instruction covers 32/P rows x (P x 16) contiguous bytes instead of 32 rows
+          // x 16 bytes
+          constexpr int P = (32 * (int)sizeof(OutT)) / 16;   // pieces per 32-column row: 4 or 8
+          constexpr int EPP = 16 / (int)sizeof(OutT);        // elements per piece
+          uint8_t* scr = s_scr + (warp - 2) * LIN_SCR_BYTES;
+          uint8_t* mine = scr + lane * LIN_SCR_PITCH;
+          if constexpr (sizeof(OutT) == 4) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<float4*>(mine + j * 4) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 u;
+              u.x = pack2<OutT>(v[j], v[j + 1]);
+              u.y = pack2<OutT>(v[j + 2], v[j + 3]);
+              u.z = pack2<OutT>(v[j + 4], v[j + 5]);
+              u.w = pack2<OutT>(v[j + 6], v[j + 7]);
+              *reinterpret_cast<uint4*>(mine + j * 2) = u;
+            }
+          }
+          __syncwarp();
+          const int nv = min(N - n, BN - c);                 // valid columns of this chunk
+          const int piece = lane % P, rsub = lane / P;
+#pragma unroll
+          for (int i = 0; i < P; ++i) {
+            const int r = i * (32 / P) + rsub;
+            const int64_t grow = m0 + q * 32 + r;
+            if (grow < M && piece * EPP < nv) {
+              const uint4 u = *reinterpret_cast<const uint4*>(scr + r * LIN_SCR_PITCH + piece * 16);
+              OutT* dst = C + grow * ldc + n + piece * EPP;
+              if ((piece + 1) * EPP <= nv) {
+                *reinterpret_cast<uint4*>(dst) = u;
+              } else {
+                const OutT* e = reinterpret_cast<const OutT*>(&u);
+#pragma unroll
+                for (int t = 0; t < EPP; ++t)
+                  if (piece * EPP + t < nv) dst[t] = e[t];
+              }
+            }
+          }
+          __syncwarp();
         }
       }
       tc_fence_before();
@@ -320,7 +372,13 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
       ab_dtype == GN_F16 ? make_idesc_f16(LIN_BM, BN) : make_idesc_bf16(LIN_BM, BN);
   const int num_n_tiles = (int)ceil_div(N, BN);
   const size_t stage_bytes = (size_t)LIN_A_BYTES + (size_t)BN * LIN_BK * 2;
-  const size_t fixed = sizeof(LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024;
+  const size_t fixed = sizeof(LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024 +
+                       (size_t)LIN_EPI_WARPS * LIN_SCR_BYTES + 16;
+  // 16-byte stores need C rows and the tile's first column on 16-byte boundaries
+  static const bool no_coalesce = getenv("GN_TC_NO_COALESCE") != nullptr;
+  const int coalesce = !no_coalesce && (reinterpret_cast<uintptr_t>(C) % 16 == 0) &&
+                       ((ldc * (int64_t)sizeof(OutT)) % 16 == 0) &&
+                       ((BN * (int)sizeof(OutT)) % 16 == 0);
   int stages = (int)((227 * 1024 - fixed) / stage_bytes);  // as deep as shared memory allows
   stages = stages > LIN_STAGES ? LIN_STAGES : stages;
   const size_t smem = (size_t)stages * stage_bytes + fixed;
@@ -343,7 +401,7 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
     GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, LIN_THREADS, smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
                                           K, BN, num_n_tiles, num_tiles, idesc, stages, splits,  \
-                                          accumulate);                                          \
+                                          accumulate, coalesce);                                \
   }
   switch (act) {
     case GN_ACT_NONE: GN_TC_LIN_CASE(ACT_NONE) break;
