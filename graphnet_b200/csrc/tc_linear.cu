@@ -91,6 +91,7 @@ struct __align__(16) LinBarriers {
   uint64_t empty[LIN_STAGES];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
+  uint64_t w_full;
   uint32_t tmem_base;
 };
 
@@ -167,20 +168,35 @@ __device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int
   }
 }
 
+// profiling runs (GN_TC_DEBUG=1): clock64 stamps of CTA 0, [warp 0..9][item 0..15][4]
+__device__ unsigned long long g_lin_trace[10 * 16 * 4];
+
 template <typename OutT, int ACT>
 __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
     int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages, int splits,
-    int accumulate, int coalesce_in) {
+    int accumulate, int coalesce_in, int wres) {
   const bool coalesce = coalesce_in != 0 && accumulate == 0;
+  const bool traced = (coalesce_in & 4) && blockIdx.x == 0 && (threadIdx.x & 31) == 0;
+  auto stamp = [&](uint32_t i, int k) {
+    if (traced && i < 16) g_lin_trace[((threadIdx.x >> 5) * 16 + i) * 4 + k] = clock64();
+  };
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   const int b_bytes = BN * LIN_BK * 2;
-  const int stage_bytes = LIN_A_BYTES + b_bytes;
-  LinBarriers* bars = reinterpret_cast<LinBarriers*>(smem + stages * stage_bytes);
+  const int nk_all = (K + LIN_BK - 1) / LIN_BK;
+  // wres ("weights resident"): this CTA works on ONE column tile of W for its whole life and
+  // keeps that tile (all K blocks) in shared memory; only A streams through the ring.  Without
+  // it every 128-row tile re-reads its W tile from L2, which is more bytes than A itself
+  // (ncu, node GEMM of C2: 157 MB of TMA loads for 63 MB of A) and the kernel sits at the
+  // L2->SM limit with the tensor pipe 27 % busy.
+  uint8_t* w_res = smem;                                   // [nk_all][BN x 128 B] when wres
+  uint8_t* ring = smem + (wres ? nk_all * b_bytes : 0);
+  const int stage_bytes = LIN_A_BYTES + (wres ? 0 : b_bytes);
+  LinBarriers* bars = reinterpret_cast<LinBarriers*>(ring + stages * stage_bytes);
   float* s_bias = reinterpret_cast<float*>(bars + 1);  // [num_n_tiles * BN]
   uint8_t* s_scr = reinterpret_cast<uint8_t*>(s_bias + num_n_tiles * BN);  // 8 x LIN_SCR_BYTES
   s_scr = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_scr) + 15) & ~uintptr_t(15));
@@ -203,6 +219,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
       mbar_init(&bars->tmem_full[b], 1);
       mbar_init(&bars->tmem_empty[b], LIN_EPI_WARPS);
     }
+    mbar_init(&bars->w_full, 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc<512>(&bars->tmem_base);
@@ -216,48 +233,83 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
   // running CTAs hit the same A tile in L2.  splits > 1 (weight gradients: few tiles, K = rows of
   // the batch) gives every item the K blocks [kb0, kb1) and the epilogue adds with red.add.
   const int64_t num_items = num_tiles * splits;
+  // i-th work item of this CTA -> (tile t, K split sp); false when the CTA is done
+  const int cta_n = blockIdx.x % num_n_tiles, cta_m0 = blockIdx.x / num_n_tiles;
+  const int cta_mstep = gridDim.x / num_n_tiles;           // wres: grid is a multiple of n tiles
+  const int64_t num_m_tiles = num_tiles / num_n_tiles;
+  auto work_item = [&](uint32_t i, int64_t& t, int& sp) -> bool {
+    if (wres) {
+      const int64_t mt = cta_m0 + (int64_t)i * cta_mstep;
+      if (mt >= num_m_tiles) return false;
+      t = mt * num_n_tiles + cta_n;
+      sp = 0;
+      return true;
+    }
+    const int64_t w = blockIdx.x + (int64_t)i * gridDim.x;
+    if (w >= num_items) return false;
+    t = w / splits;
+    sp = (int)(w % splits);
+    return true;
+  };
   if (warp == 0) {
     // ---------------------------------------------------------- TMA producer
     if (elect_one()) {
       uint32_t g = 0;
-      for (int64_t w = blockIdx.x; w < num_items; w += gridDim.x) {
-        const int64_t t = w / splits;
-        const int sp = (int)(w % splits);
+      if (wres) {  // the CTA's W tile, once
+        mbar_arrive_expect_tx(&bars->w_full, (uint32_t)(nk_all * b_bytes));
+        for (int kb = 0; kb < nk_all; ++kb)
+          tma_load_2d(w_res + kb * b_bytes, &tmW, &bars->w_full, kb * LIN_BK, cta_n * BN);
+      }
+      int64_t t;
+      int sp;
+      for (uint32_t i = 0; work_item(i, t, sp); ++i) {
         const int kb0 = (int)((int64_t)sp * nk / splits), kb1 = (int)((int64_t)(sp + 1) * nk / splits);
         const int32_t m0 = (int32_t)((t / num_n_tiles) * LIN_BM);
         const int32_t n0 = (int32_t)(t % num_n_tiles) * BN;
+        stamp(i, 0);
         for (int kb = kb0; kb < kb1; ++kb, ++g) {
           const uint32_t s = g % stages;
           mbar_wait(&bars->empty[s], ((g / stages) & 1) ^ 1);
-          uint8_t* a_dst = smem + s * stage_bytes;
-          uint8_t* b_dst = a_dst + LIN_A_BYTES;
+          if (kb == kb0) stamp(i, 1);
+          if (kb == kb1 - 1) stamp(i, 2);
+          uint8_t* a_dst = ring + s * stage_bytes;
           mbar_arrive_expect_tx(&bars->full[s], (uint32_t)stage_bytes);
           tma_load_2d(a_dst, &tmA, &bars->full[s], kb * LIN_BK, m0);
-          tma_load_2d(b_dst, &tmW, &bars->full[s], kb * LIN_BK, n0);
+          if (!wres) tma_load_2d(a_dst + LIN_A_BYTES, &tmW, &bars->full[s], kb * LIN_BK, n0);
         }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    uint32_t g = 0, it = 0;
-    for (int64_t w = blockIdx.x; w < num_items; w += gridDim.x, ++it) {
-      const int sp = (int)(w % splits);
+    uint32_t g = 0;
+    if (wres) {
+      mbar_wait(&bars->w_full, 0);
+      tc_fence_after();
+    }
+    int64_t t;
+    int sp;
+    for (uint32_t it = 0; work_item(it, t, sp); ++it) {
       const int kb0 = (int)((int64_t)sp * nk / splits), kb1 = (int)((int64_t)(sp + 1) * nk / splits);
       const uint32_t buf = it & 1;
+      stamp(it, 0);
       mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+      stamp(it, 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + buf * 256;
       for (int kb = kb0; kb < kb1; ++kb, ++g) {
         const uint32_t s = g % stages;
         mbar_wait(&bars->full[s], (g / stages) & 1);
+        if (kb == kb0) stamp(it, 2);
+        if (kb == kb1 - 1) stamp(it, 3);
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
-          const uint32_t b_addr = a_addr + LIN_A_BYTES;
+          const uint32_t a_addr = smem_u32(ring + s * stage_bytes);
+          const uint32_t b_addr = wres ? smem_u32(w_res + kb * b_bytes) : a_addr + LIN_A_BYTES;
           const uint64_t adesc = make_kmajor_desc<128>(a_addr);
           const uint64_t bdesc = make_kmajor_desc<128>(b_addr);
 #pragma unroll
           for (int k4 = 0; k4 < LIN_BK / 16; ++k4) {
+            if (coalesce_in & 8) break;   // profiling: no tensor work, data path only
             // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4) units
             mma_bf16_ss(tmem_d, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc,
                         ((kb - kb0) | k4) != 0);
@@ -272,20 +324,28 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
     // -------------------------------------------------------------- epilogue
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
     const int par = (warp - 2) >> 2;  // the two warps of a quadrant take alternate 32-col chunks
-    uint32_t it = 0;
-    for (int64_t w = blockIdx.x; w < num_items; w += gridDim.x, ++it) {
-      const int64_t t = w / splits;
+    int64_t t;
+    int sp;
+    for (uint32_t it = 0; work_item(it, t, sp); ++it) {
       const uint32_t buf = it & 1;
       const int64_t m0 = (t / num_n_tiles) * LIN_BM;
       const int n0 = (int)(t % num_n_tiles) * BN;
+      stamp(it, 0);
       mbar_wait(&bars->tmem_full[buf], (it >> 1) & 1);
+      stamp(it, 1);
       tc_fence_after();
       const int64_t row = m0 + q * 32 + lane;
-      for (int c = par * 32; c < BN; c += 64) {
+      // The warp's chunks are c = par*32, +64, ...; the tcgen05.ld of chunk i+1 is issued before
+      // chunk i is processed (two register sets), so TMEM latency overlaps the arithmetic,
+      // the transpose and the stores.
+      const uint32_t t_addr = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
+      auto chunk_ok = [&](int c) { return c < BN && n0 + c < N; };
+      uint32_t ra[32], rb[32];
+      auto process = [&](uint32_t (&raw)[32], const int c) {
         const int n = n0 + c;
-        if (n >= N) break;
         float v[32];
-        tmem_ld_32x32(tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
         const float4* b4 = reinterpret_cast<const float4*>(s_bias + n);
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
@@ -303,7 +363,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
 #pragma unroll
               for (int j = 0; j < 32; ++j)
                 if (j < nv) atomicAdd(dst + j, v[j]);
-              continue;
+              return;
             }
           }
           if (!coalesce) store_row32<OutT>(C + row * ldc + n, v, min(N - n, BN - c));
@@ -338,7 +398,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
           for (int i = 0; i < P; ++i) {
             const int r = i * (32 / P) + rsub;
             const int64_t grow = m0 + q * 32 + r;
-            if (grow < M && piece * EPP < nv) {
+            if (grow < M && piece * EPP < nv && !(coalesce_in & 2)) {
               const uint4 u = *reinterpret_cast<const uint4*>(scr + r * LIN_SCR_PITCH + piece * 16);
               OutT* dst = C + grow * ldc + n + piece * EPP;
               if ((piece + 1) * EPP <= nv) {
@@ -353,10 +413,30 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
           }
           __syncwarp();
         }
+      };
+      {
+        int c = par * 32;
+        if (chunk_ok(c) && !(coalesce_in & 16)) {   // (16: profiling without the epilogue body)
+          tmem_ld_32x32_issue(t_addr + (uint32_t)c, ra);
+          for (;;) {
+            tmem_ld_wait(ra);
+            const bool more1 = chunk_ok(c + 64);
+            if (more1) tmem_ld_32x32_issue(t_addr + (uint32_t)(c + 64), rb);
+            process(ra, c);
+            if (!more1) break;
+            tmem_ld_wait(rb);
+            const bool more2 = chunk_ok(c + 128);
+            if (more2) tmem_ld_32x32_issue(t_addr + (uint32_t)(c + 128), ra);
+            process(rb, c + 64);
+            if (!more2) break;
+            c += 128;
+          }
+        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
+      stamp(it, 2);
     }
   }
   tc_fence_before();
@@ -376,12 +456,30 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
                        (size_t)LIN_EPI_WARPS * LIN_SCR_BYTES + 16;
   // 16-byte stores need C rows and the tile's first column on 16-byte boundaries
   static const bool no_coalesce = getenv("GN_TC_NO_COALESCE") != nullptr;
-  const int coalesce = !no_coalesce && (reinterpret_cast<uintptr_t>(C) % 16 == 0) &&
+  static const bool hack_nostore = getenv("GN_TC_HACK_NOSTORE") != nullptr;
+  static const bool dbg_trace = getenv("GN_TC_DEBUG") != nullptr;
+  static const int hack_bits = getenv("GN_TC_HACK") ? atoi(getenv("GN_TC_HACK")) : 0;
+  const int coalesce = ((hack_nostore ? 3 : 1) | (dbg_trace ? 4 : 0) | (hack_bits & 24)) * (int)(!no_coalesce && (reinterpret_cast<uintptr_t>(C) % 16 == 0) &&
                        ((ldc * (int64_t)sizeof(OutT)) % 16 == 0) &&
-                       ((BN * (int)sizeof(OutT)) % 16 == 0);
+                       ((BN * (int)sizeof(OutT)) % 16 == 0));
   int stages = (int)((227 * 1024 - fixed) / stage_bytes);  // as deep as shared memory allows
   stages = stages > LIN_STAGES ? LIN_STAGES : stages;
-  const size_t smem = (size_t)stages * stage_bytes + fixed;
+  size_t smem = (size_t)stages * stage_bytes + fixed;
+  // weights-resident variant: one K-complete W tile per CTA + a ring of A-only stages (>= 4)
+  int dev0 = 0, sms0 = 0;
+  GN_CUDA(cudaGetDevice(&dev0));
+  GN_CUDA(cudaDeviceGetAttribute(&sms0, cudaDevAttrMultiProcessorCount, dev0));
+  static const bool no_wres = getenv("GN_TC_NO_WRES") != nullptr;
+  const size_t w_bytes = (size_t)ceil_div(K, LIN_BK) * BN * LIN_BK * 2;
+  int wres = 0;
+  if (!no_wres && splits == 1 && !accumulate && num_n_tiles <= sms0 &&
+      w_bytes + 4 * (size_t)LIN_A_BYTES + fixed <= 227 * 1024 &&
+      ceil_div(M, LIN_BM) >= 2 * (sms0 / num_n_tiles)) {
+    wres = 1;
+    stages = (int)((227 * 1024 - fixed - w_bytes) / LIN_A_BYTES);
+    stages = stages > LIN_STAGES ? LIN_STAGES : stages;
+    smem = w_bytes + (size_t)stages * LIN_A_BYTES + fixed;
+  }
   const int64_t num_tiles = ceil_div(M, LIN_BM) * num_n_tiles;
   int dev = 0, sms = 0;
   GN_CUDA(cudaGetDevice(&dev));
@@ -394,14 +492,15 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
   if (splits > nkb) splits = nkb;
   if (splits < 1) splits = 1;
   const int64_t num_items = num_tiles * splits;
-  const unsigned grid = (unsigned)(num_items < sms ? num_items : sms);
+  unsigned grid = (unsigned)(num_items < sms ? num_items : sms);
+  if (wres) grid = (unsigned)((sms / num_n_tiles) * num_n_tiles);
 #define GN_TC_LIN_CASE(A_)                                                                      \
   {                                                                                             \
     auto kern = tc_linear_kernel<OutT, A_>;                                                     \
     GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     kern<<<grid, LIN_THREADS, smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
                                           K, BN, num_n_tiles, num_tiles, idesc, stages, splits,  \
-                                          accumulate, coalesce);                                \
+                                          accumulate, coalesce, wres);                          \
   }
   switch (act) {
     case GN_ACT_NONE: GN_TC_LIN_CASE(ACT_NONE) break;
@@ -416,10 +515,21 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
 
 }  // namespace tc
 
-int tc_pick_bn(int N) {
+static size_t tc_fixed_smem(int N, int BN) {
+  const int num_n_tiles = (N + BN - 1) / BN;
+  return sizeof(tc::LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024 +
+         (size_t)tc::LIN_EPI_WARPS * tc::LIN_SCR_BYTES + 16;
+}
+// does a K-complete W tile of width BN fit next to a ring of at least four A stages?
+static bool tc_wres_fits(int N, int K, int BN) {
+  const size_t w_bytes = (size_t)ceil_div(K, tc::LIN_BK) * BN * tc::LIN_BK * 2;
+  return w_bytes + 4 * (size_t)tc::LIN_A_BYTES + tc_fixed_smem(N, BN) <= 227 * 1024;
+}
+
+int tc_pick_bn(int N, int bn_max_arg = 256) {
   // largest tile width <= 256 (multiple of 16) that minimises padding
   static const char* env = getenv("GN_TC_BN_MAX");
-  const int bn_max = env ? atoi(env) : 256;
+  const int bn_max = env ? atoi(env) : bn_max_arg;
   int best = bn_max, best_waste = 1 << 30;
   for (int bn = bn_max; bn >= 64; bn -= 16) {
     int tiles = (N + bn - 1) / bn;
@@ -444,7 +554,12 @@ extern "C" int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
   GN_CHECK_ARG(N <= tc::LIN_MAX_N, "gn_tc_linear: N=%d exceeds %d", N, tc::LIN_MAX_N);
   GN_CHECK_ARG(c_dtype == GN_F32 || c_dtype == GN_BF16 || c_dtype == GN_F16,
                "gn_tc_linear: bad c_dtype");
-  const int BN = tc_pick_bn(N);
+  int BN = tc_pick_bn(N);
+  // a narrower tile whose K-complete W fits in shared memory beats a wide one that streams W
+  if (!tc_wres_fits(N, K, BN) && M >= 4096) {
+    const int bn2 = tc_pick_bn(N, 128);
+    if (tc_wres_fits(N, K, bn2)) BN = bn2;
+  }
   CUtensorMap tmA, tmW;
   auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
   int rc = mk(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, tc::LIN_BM, tc::LIN_BK, 128);
@@ -478,4 +593,12 @@ extern "C" int gn_tc_linear_accumulate(const void* A, int64_t lda, const void* W
   if (rc != GN_OK) return rc;
   return tc::launch_tc_linear<float>(tmA, tmW, nullptr, C, ldc, M, N, K, BN, GN_ACT_NONE, ab_dtype,
                                      as_stream(stream), splits, 1);
+}
+
+// diagnostic only (not part of include/graphnet_b200.h): timeline of CTA 0 of the last tc_linear
+extern "C" int gn_debug_linear_trace(unsigned long long* host, int words) {
+  GN_CUDA(cudaDeviceSynchronize());
+  if (words > 10 * 16 * 4) words = 10 * 16 * 4;
+  GN_CUDA(cudaMemcpyFromSymbol(host, tc::g_lin_trace, words * sizeof(unsigned long long)));
+  return GN_OK;
 }
