@@ -51,17 +51,37 @@ __global__ void __launch_bounds__(256) transpose16_kernel(const uint16_t* __rest
 }
 
 // ------------------------------------------------------------------ column sums (bias gradients)
-// out[n] (+)= sum_m X[m, n]; one thread per column, 512 rows per CTA, one atomic per CTA and column
+// out[n] += sum_m X[m, n].  A CTA takes 256 rows x 64 columns: 8 row groups x 32 column pairs,
+// coalesced 128-byte (bf16: 4-byte per lane) row segments, a shared-memory reduction over the
+// row groups and one atomic per column and CTA.
 template <typename T>
-__global__ void __launch_bounds__(128) colsum_kernel(const T* __restrict__ X, int64_t ldx,
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ X, int64_t ldx,
                                                      int64_t M, int N, float* __restrict__ out) {
-  const int n = blockIdx.y * 128 + threadIdx.x;
-  const int64_t m0 = (int64_t)blockIdx.x * 512;
-  if (n >= N) return;
-  const int64_t m1 = m0 + 512 < M ? m0 + 512 : M;
-  float acc = 0.f;
-  for (int64_t m = m0; m < m1; ++m) acc += to_f32<T>(X[m * ldx + n]);
-  atomicAdd(out + n, acc);
+  __shared__ float part[8][64];
+  const int cp = threadIdx.x & 31, rg = threadIdx.x >> 5;
+  const int n = blockIdx.y * 64 + cp * 2;
+  const int64_t m0 = (int64_t)blockIdx.x * 256;
+  const int64_t m1 = m0 + 256 < M ? m0 + 256 : M;
+  float a0 = 0.f, a1 = 0.f;
+  if (n < N) {
+    const bool two = n + 1 < N;
+    for (int64_t m = m0 + rg; m < m1; m += 8) {
+      a0 += to_f32<T>(X[m * ldx + n]);
+      if (two) a1 += to_f32<T>(X[m * ldx + n + 1]);
+    }
+  }
+  part[rg][cp * 2] = a0;
+  part[rg][cp * 2 + 1] = a1;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    const int c = blockIdx.y * 64 + threadIdx.x;
+    if (c < N) {
+      float acc = 0.f;
+#pragma unroll
+      for (int g = 0; g < 8; ++g) acc += part[g][threadIdx.x];
+      atomicAdd(out + c, acc);
+    }
+  }
 }
 
 // ------------------------------------------------------------------ dZ = dY * [Y > 0], converted
@@ -333,12 +353,12 @@ extern "C" int gn_colsum_accumulate(const void* X, int x_dtype, int64_t ldx, int
   GN_CHECK_ARG(M >= 0 && N >= 1 && ldx >= N, "gn_colsum_accumulate: bad sizes");
   if (M == 0) return GN_OK;
   GN_CHECK_ARG(X && out, "gn_colsum_accumulate: null pointer");
-  dim3 grid((unsigned)ceil_div(M, 512), (unsigned)ceil_div(N, 128));
+  dim3 grid((unsigned)ceil_div(M, 256), (unsigned)ceil_div(N, 64));
   cudaStream_t st = as_stream(stream);
   if (x_dtype == GN_F32)
-    colsum_kernel<float><<<grid, 128, 0, st>>>(reinterpret_cast<const float*>(X), ldx, M, N, out);
+    colsum_kernel<float><<<grid, 256, 0, st>>>(reinterpret_cast<const float*>(X), ldx, M, N, out);
   else if (x_dtype == GN_BF16)
-    colsum_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(X),
+    colsum_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(X),
                                                        ldx, M, N, out);
   else
     GN_CHECK_ARG(false, "gn_colsum_accumulate: bad x_dtype %d", x_dtype);
