@@ -73,3 +73,50 @@ class Batch(Data):
         out.ptr = torch.tensor(offsets, dtype=torch.long)
         out.num_graphs = len(sizes)
         return out
+
+
+class DevicePrefetcher:
+    """Iterate over host batches, yielding device batches whose host->device copy overlapped the
+    work on the previous batch.
+
+    The reference feeds its models from a `torch.utils.data.DataLoader(pin_memory=...)` whose
+    batches Lightning moves to the device synchronously before each step.  Here the copy of batch
+    i+1 is issued on a side stream as soon as batch i has been handed out, so it runs under
+    batch i's kernels; the consumer's stream waits on the copy's event (no host sync).  Tensors
+    should be pinned; the 10 MB of a 1024-event IceCube batch (8 MB of it the int64 `edge_index`
+    PyG batches carry) then cost no step time.
+    """
+
+    def __init__(self, batches: Iterable[Any], device: Any):
+        self._it = iter(batches)
+        self._device = torch.device(device)
+        self._stream = torch.cuda.Stream(device=self._device)
+        self._next = None
+        self._preload()
+
+    def _preload(self) -> None:
+        try:
+            host = next(self._it)
+        except StopIteration:
+            self._next = None
+            return
+        with torch.cuda.stream(self._stream):
+            dev = host.to(self._device, non_blocking=True)
+            event = torch.cuda.Event()
+            event.record(self._stream)
+        self._next = (dev, event, host)
+
+    def __iter__(self) -> "DevicePrefetcher":
+        return self
+
+    def __next__(self) -> Any:
+        if self._next is None:
+            raise StopIteration
+        dev, event, _host = self._next
+        cur = torch.cuda.current_stream(self._device)
+        cur.wait_event(event)
+        for v in dev.__dict__.values():      # the caching allocator must not recycle these
+            if isinstance(v, Tensor):        # buffers for the side stream while `cur` uses them
+                v.record_stream(cur)
+        self._preload()
+        return dev

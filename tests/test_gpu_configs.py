@@ -86,3 +86,27 @@ def test_c5_sweep_two_tasks(n):
                              tasks[1]._affine.bias.detach().cpu(), y)
     assert preds[0].shape == (events, 4) and preds[1].shape == (events, 1)
     assert rel_l2(preds[0].cpu(), w0) < 5e-3 and rel_l2(preds[1].cpu(), w1) < 5e-3
+
+
+def test_device_prefetcher_yields_every_batch_in_order():
+    import graphnet_b200 as gb
+    from graphnet_b200.data import DevicePrefetcher
+    from graphnet_b200.synthetic import make_pulse_batch
+    host = []
+    for s in range(5):
+        pb = make_pulse_batch(4 + s, 20.0, seed=60 + s)
+        ei = oracle.knn_graph(pb.x[:, :3], 8, pb.batch)
+        host.append(gb.Data(x=pb.x.pin_memory(), edge_index=ei.pin_memory(),
+                            batch=pb.batch.pin_memory(), n_pulses=pb.n_pulses.pin_memory()))
+    m = gb.DynEdge(7, global_pooling_schemes=["max"]).to(DEV)
+    m.train(False)
+    got = []
+    for d in DevicePrefetcher(host, DEV):
+        assert d.x.is_cuda and d.edge_index.is_cuda
+        with torch.no_grad():
+            got.append(m(d).cpu())
+    assert len(got) == 5
+    for h, y in zip(host, got):
+        with torch.no_grad():
+            want = m(h.to(DEV)).cpu()
+        assert torch.equal(y, want)
