@@ -57,6 +57,48 @@ def _parse_mlp(seq: torch.nn.Module) -> Tuple[List[torch.nn.Linear], str]:
     return linears, act
 
 
+def _apply_act_rows(h: Tensor, act: str) -> Tensor:
+    if act == "none":
+        return h
+    # activation alone (first EdgeConv Linear without a norm layer after it): LayerNorm kernel
+    # is not involved; a Linear-free activation only occurs on this unfused path
+    return torch.relu_(h) if act == "relu" else torch.nn.functional.gelu(h)
+
+
+def _parse_mlp_norm(seq: torch.nn.Module):
+    """Sequential(Linear[, LayerNorm], act, ...) -> [(Linear, LayerNorm | None)], activation."""
+    mods = list(seq) if isinstance(seq, torch.nn.Sequential) else [seq]
+    steps, act, i = [], None, 0
+    while i < len(mods):
+        if not isinstance(mods[i], torch.nn.Linear):
+            raise NotImplementedError(f"unsupported layer {type(mods[i]).__name__} in MLP")
+        lin, ln = mods[i], None
+        i += 1
+        if i < len(mods) and isinstance(mods[i], torch.nn.LayerNorm):
+            ln = mods[i]
+            i += 1
+        if i >= len(mods):
+            raise NotImplementedError("every Linear must be followed by an activation")
+        a = _act_name(mods[i])
+        if act is not None and a != act:
+            raise NotImplementedError("mixed activations inside one MLP")
+        act = a
+        i += 1
+        steps.append((lin, ln))
+    return steps, act
+
+
+def _mlp_rows_norm(h: Tensor, steps, act: str) -> Tensor:
+    """Row-wise MLP with LayerNorm between Linear and activation (fp32 kernels)."""
+    for lin, ln in steps:
+        if ln is None:
+            h = ops.linear_f32(h, lin.weight, lin.bias, act=act)
+        else:
+            h = ops.linear_f32(h, lin.weight, lin.bias, act="none")
+            ops.layernorm_act_(h, ln.weight, ln.bias, ln.eps, act=act)
+    return h
+
+
 class _WeightCache:
     """Repacked weights, rebuilt when a parameter is modified in place or replaced."""
 
@@ -107,11 +149,43 @@ class DynEdgeConv(torch.nn.Module):
                 "DynEdgeConv MLPs with more than two Linear layers are not built yet")
         return linears, act
 
+    def _has_norm(self) -> bool:
+        return any(isinstance(m, torch.nn.LayerNorm) for m in self.nn)
+
     @property
     def out_features(self) -> int:
-        return self._mlp()[0][-1].out_features
+        return [m for m in self.nn if isinstance(m, torch.nn.Linear)][-1].out_features
+
+    def _conv_f32_norm(self, x: Tensor, graph: Graph, out: Optional[Tensor] = None) -> Tensor:
+        """EdgeConv with LayerNorm inside the message MLP (add_norm_layer=True,
+        gnn/dynedge.py:202-203): the normalisation needs every edge's full feature row, so the
+        per-slot rows are materialised - the reference's own route - around the dense kernels."""
+        if self.aggr not in ("add", "sum"):
+            raise NotImplementedError("add_norm_layer=True supports aggr='add'")
+        steps, act = _parse_mlp_norm(self.nn)
+        (l1, n1), rest = steps[0], steps[1:]
+        N = x.shape[0]
+        if graph.ell_stride <= 0:   # user edge_index: CSR -> slot table (one host read)
+            graph = ops.csr_to_ell(graph, max(int(graph.max_degree.item()), 1))
+        Wpq, _ = self._cache_f32.get([l1.weight], lambda: ops.edgeconv_prepare_f32(l1.weight, None))
+        a = l1.out_features
+        bias = torch.zeros(2 * a, dtype=torch.float32, device=x.device)
+        if l1.bias is not None:
+            bias[:a] = l1.bias.detach().float()
+        pq = ops.linear_f32(x, Wpq, bias, act="none")                # [N, 2a] = [P | Q]
+        h = ops.edge_preact_f32(pq, a, graph)                        # [N*S, a]
+        if n1 is not None:
+            ops.layernorm_act_(h, n1.weight, n1.bias, n1.eps, act=act)
+        else:
+            h = _apply_act_rows(h, act)
+        h = _mlp_rows_norm(h, rest, act)
+        if out is None:
+            out = torch.empty((N, h.shape[1]), dtype=torch.float32, device=x.device)
+        return ops.slot_sum_f32(h, graph, out)
 
     def _conv_f32(self, x: Tensor, graph: Graph, out: Optional[Tensor] = None) -> Tensor:
+        if self._has_norm():
+            return self._conv_f32_norm(x, graph, out)
         linears, act = self._mlp()
         l1 = linears[0]
         l2 = linears[1] if len(linears) == 2 else None
@@ -316,8 +390,8 @@ class DynEdge(torch.nn.Module):
         int64 sorted, `n_pulses` [B] (any object with those attributes, e.g. a
         torch_geometric `Batch`).
         """
-        if self._add_norm_layer:
-            raise NotImplementedError("add_norm_layer=True is not built yet")
+        if self._add_norm_layer and self.precision != "fp32":
+            raise NotImplementedError("add_norm_layer=True runs on precision='fp32'")
         training = (self.training and self.precision == "bf16" and torch.is_grad_enabled()
                     and any(p.requires_grad for p in self.parameters()))
         if not training:   # inference kernels allocate nothing for autograd
@@ -419,10 +493,8 @@ class DynEdge(torch.nn.Module):
             off_in, d_in = off_out, conv_out[li]
             off_out += conv_out[li]
 
-        h = skip
-        post, pact = _parse_mlp(self._post_processing)
-        for lin in post:
-            h = ops.linear_f32(h, lin.weight, lin.bias, act=pact)
+        post, pact = _parse_mlp_norm(self._post_processing)
+        h = _mlp_rows_norm(skip, post, pact)
         inter["post"] = h
 
         if not self._skip_readout:

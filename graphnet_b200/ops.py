@@ -502,3 +502,45 @@ def csr_to_ell(graph: Graph, stride: int) -> Graph:
                                         _ptr(deg), _ptr(flags), _stream(dev)), "gn_csr_to_ell")
     return Graph(col=nbr, deg=deg, rowptr=None, ell_stride=stride, num_nodes=N, flags=flags,
                  max_degree=graph.max_degree)
+
+
+# ------------------------------------------------- add_norm_layer=True (fp32, unfused)
+def layernorm_act_(X: Tensor, gamma: Optional[Tensor], beta: Optional[Tensor], eps: float,
+                   act: str = "none") -> Tensor:
+    """In place: X <- act(LayerNorm(X) * gamma + beta), row-wise (torch.nn.LayerNorm semantics)."""
+    dev = _require_cuda(X, gamma, beta)
+    assert X.dtype == torch.float32 and X.stride(1) == 1
+    M, N = X.shape
+    g = None if gamma is None else gamma.detach().float().contiguous()
+    b = None if beta is None else beta.detach().float().contiguous()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_layernorm_act_f32(_ptr(X), X.stride(0), M, N, _ptr(g), _ptr(b),
+                                               float(eps), ACT[act], _stream(dev)),
+              "gn_layernorm_act_f32")
+    return X
+
+
+def edge_preact_f32(pq: Tensor, a: int, graph: Graph) -> Tensor:
+    """[N*stride, a] rows P_i + Q_j of every slot of an ELL graph (zero rows for empty slots)."""
+    dev = _require_cuda(pq)
+    assert pq.dtype == torch.float32 and pq.is_contiguous() and pq.shape[1] == 2 * a
+    N = pq.shape[0]
+    out = torch.empty((N * graph.ell_stride, a), dtype=torch.float32, device=dev)
+    gs = graph.c_struct()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_edge_preact_f32(_ptr(pq), a, C.byref(gs), N, _ptr(out), out.stride(0),
+                                             _stream(dev)), "gn_edge_preact_f32")
+    return out
+
+
+def slot_sum_f32(Z: Tensor, graph: Graph, out: Tensor) -> Tensor:
+    """out[i] = sum of Z[i*stride + t] over the filled slots of node i."""
+    dev = _require_cuda(Z, out)
+    assert Z.dtype == torch.float32 and out.dtype == torch.float32
+    assert Z.stride(1) == 1 and out.stride(1) == 1
+    N, b = out.shape[0], Z.shape[1]
+    gs = graph.c_struct()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_slot_sum_f32(_ptr(Z), Z.stride(0), b, C.byref(gs), N, _ptr(out),
+                                          out.stride(0), _stream(dev)), "gn_slot_sum_f32")
+    return out

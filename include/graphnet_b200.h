@@ -230,6 +230,24 @@ int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t 
 int gn_task_head(const float* y, int64_t M, int p, int kind, float* out,
                  void* stream);
 
+/* ---- add_norm_layer=True (gnn/dynedge.py:202-203, :224-226) ---------------------- */
+
+/* X[m, :] <- act(LayerNorm(X[m, :]) * gamma + beta) in place (torch.nn.LayerNorm: biased
+ * variance, eps under the root; gamma / beta may be NULL), N <= 512. */
+int gn_layernorm_act_f32(float* X, int64_t ldx, int64_t M, int N, const float* gamma,
+                         const float* beta, float eps, int act, void* stream);
+
+/* Pre-activations of the first EdgeConv Linear for every slot of an ELL graph:
+ * out[i*stride + t, :] = P_i + Q_j with pq = [P | Q] [N, 2a] as written by gn_linear_f32 with the
+ * factored weights of gn_edgeconv_prepare_f32 (zero rows for empty slots). */
+int gn_edge_preact_f32(const float* pq, int a, const gn_graph* graph, int64_t N, float* out,
+                       int64_t ldo, void* stream);
+
+/* aggr="add" over materialised per-slot messages: out[i, :] = sum of Z[i*stride + t, :] over the
+ * filled slots of node i. */
+int gn_slot_sum_f32(const float* Z, int64_t ldz, int b, const gn_graph* graph, int64_t N,
+                    float* out, int64_t ldo, void* stream);
+
 /* ---- backward pass of the 16-bit training path (BASELINE config 3) ------------- */
 /* The reference holds no backward code: gradients come from torch autograd through the modules
  * cited at each entry.  All matrices row-major; 16-bit operands 16-byte aligned with row strides

@@ -110,3 +110,34 @@ def test_device_prefetcher_yields_every_batch_in_order():
         with torch.no_grad():
             want = m(h.to(DEV)).cpu()
         assert torch.equal(y, want)
+
+
+@pytest.mark.parametrize("activation", ["relu", "gelu"])
+def test_add_norm_layer_matches_oracle(activation):
+    """add_norm_layer=True (gnn/dynedge.py:202-203, :224-226): LayerNorm between every Linear and
+    its activation in the EdgeConv and post-processing MLPs (fp32, unfused path)."""
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(20, 35.0, seed=71)
+    ei = oracle.knn_graph(pb.x[:, :3], 8, pb.batch)
+    pools = ["min", "max", "mean", "sum"]
+    spec = oracle.DynEdgeSpec(nb_inputs=7, global_pooling_schemes=pools, add_norm_layer=True,
+                              activation_layer=activation)
+    sd = oracle.init_dynedge_state_dict(spec, seed=3)
+    # non-trivial affine parameters of the norm layers
+    g = torch.Generator().manual_seed(8)
+    for k in sd:
+        if sd[k].dim() == 1 and k.split(".")[-2] in ("1",):
+            sd[k] = sd[k] + 0.2 * torch.randn(sd[k].shape, generator=g)
+    want = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
+    m = gb.DynEdge(7, global_pooling_schemes=pools, add_norm_layer=True, activation_layer=activation)
+    m.load_state_dict(sd)
+    m = m.to(DEV)
+    m.train(False)
+    data = gb.Data(x=pb.x.to(DEV), edge_index=ei.to(DEV), batch=pb.batch.to(DEV),
+                   n_pulses=pb.n_pulses.to(DEV))
+    with torch.no_grad():
+        got = m(data).cpu()
+    per_event = (got - want).norm(dim=1) / want.norm(dim=1)
+    assert float(per_event.median()) < 1e-4, per_event
+    assert float(per_event.max()) < 5e-3, per_event
