@@ -184,7 +184,8 @@ class DynEdgeConv(torch.nn.Module):
         return ops.slot_sum_f32(h, graph, out)
 
     def _conv_f32(self, x: Tensor, graph: Graph, out: Optional[Tensor] = None) -> Tensor:
-        if self._has_norm():
+        n_lin = sum(isinstance(m, torch.nn.Linear) for m in self.nn)
+        if self._has_norm() or n_lin > 2:   # the fused kernel covers one or two Linear layers
             return self._conv_f32_norm(x, graph, out)
         linears, act = self._mlp()
         l1 = linears[0]

@@ -141,3 +141,26 @@ def test_add_norm_layer_matches_oracle(activation):
     per_event = (got - want).norm(dim=1) / want.norm(dim=1)
     assert float(per_event.median()) < 1e-4, per_event
     assert float(per_event.max()) < 5e-3, per_event
+
+
+def test_deeper_edgeconv_mlps_fp32():
+    """dynedge_layer_sizes with one and three Linear layers per EdgeConv (dynedge.py:193-204)."""
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(12, 30.0, seed=72)
+    ei = oracle.knn_graph(pb.x[:, :3], 8, pb.batch)
+    sizes = [(48, 64, 96), (80,), (64, 64)]
+    spec = oracle.DynEdgeSpec(nb_inputs=7, global_pooling_schemes=["max", "mean"],
+                              dynedge_layer_sizes=sizes)
+    sd = oracle.init_dynedge_state_dict(spec, seed=4)
+    want = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
+    m = gb.DynEdge(7, global_pooling_schemes=["max", "mean"], dynedge_layer_sizes=sizes)
+    m.load_state_dict(sd)
+    m = m.to(DEV)
+    m.train(False)
+    data = gb.Data(x=pb.x.to(DEV), edge_index=ei.to(DEV), batch=pb.batch.to(DEV),
+                   n_pulses=pb.n_pulses.to(DEV))
+    with torch.no_grad():
+        got = m(data).cpu()
+    per_event = (got - want).norm(dim=1) / want.norm(dim=1)
+    assert float(per_event.median()) < 1e-4 and float(per_event.max()) < 5e-3, per_event
