@@ -15,6 +15,7 @@ from .losses import LogCoshLoss, VonMisesFisher3DLoss  # noqa: F401
 from .ops import knn_graph  # noqa: F401
 from .standard_model import StandardModel  # noqa: F401
 from . import training  # noqa: F401
+from .graphed import GraphedInference  # noqa: F401
 from .tasks import (  # noqa: F401
     AzimuthReconstructionWithKappa,
     DirectionReconstructionWithKappa,

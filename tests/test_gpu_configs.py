@@ -164,3 +164,39 @@ def test_deeper_edgeconv_mlps_fp32():
         got = m(data).cpu()
     per_event = (got - want).norm(dim=1) / want.norm(dim=1)
     assert float(per_event.median()) < 1e-4 and float(per_event.max()) < 5e-3, per_event
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_graphed_inference_replays_bit_exact(precision):
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    def batch(seed):
+        pb = make_pulse_batch(32, fixed_pulses=24, seed=seed)     # fixed shape: N, B constant
+        x = pb.x.to(DEV)
+        ei = gb.knn_graph(x[:, :3].contiguous(), 8, pb.batch.to(DEV), num_events=32)
+        return gb.Data(x=x, edge_index=ei, batch=pb.batch.to(DEV), n_pulses=pb.n_pulses.to(DEV))
+    a, b = batch(80), batch(81)
+    if a.edge_index.shape != b.edge_index.shape:
+        pytest.skip("the two synthetic batches differ in edge count")
+    torch.manual_seed(4)
+    backbone = gb.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision=precision)
+    task = gb.EnergyReconstruction(hidden_size=128, target_labels="energy", loss_function=gb.LogCoshLoss())
+    model = gb.StandardModel(tasks=[task], graph_definition=object(), gnn=backbone).to(DEV)
+    model.train(False)
+    model.inference()
+    with torch.no_grad():
+        want_a, want_b = model(a)[0].clone(), model(b)[0].clone()
+    runner = gb.GraphedInference(model, a)
+    assert torch.equal(runner(a)[0], want_a)
+    assert torch.equal(runner(b)[0], want_b)
+    assert torch.equal(runner(a)[0], want_a)
+    with pytest.raises(ValueError):
+        runner(batch_other_shape(gb))
+
+
+def batch_other_shape(gb):
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(8, fixed_pulses=10, seed=3)
+    x = pb.x.to(DEV)
+    ei = gb.knn_graph(x[:, :3].contiguous(), 8, pb.batch.to(DEV), num_events=8)
+    return gb.Data(x=x, edge_index=ei, batch=pb.batch.to(DEV), n_pulses=pb.n_pulses.to(DEV))
