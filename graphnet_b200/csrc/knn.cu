@@ -37,7 +37,7 @@ __global__ void batch_to_ptr_kernel(const int64_t* __restrict__ batch, int64_t N
 // ------------------------------------------------------------------------ kNN
 constexpr int KNN_MAX_DIMS = 16;
 constexpr int KNN_THREADS = 128;
-constexpr int KNN_SMEM_FLOATS = 8192;  // 32 KB of staged coordinates per CTA
+constexpr int KNN_SMEM_FLOATS = 3072;  // 12 KB of staged coordinates per CTA: 1024 events fit ONE wave (10 CTAs/SM by registers; 32 KB gave 6 and a 15 % second wave)
 
 struct KnnParams {
   const float* x;
