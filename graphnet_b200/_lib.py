@@ -63,6 +63,7 @@ SIGNATURES = {
     "gn_edgeconv_prepare_f32": (_int, [_p, _p, _int, _int, _int, _p, _p, _p]),
     "gn_edgeconv_f32": (_int, [_p, _i64, _int, _gp, _i64, _p, _p, _int, _p, _p, _int, _int, _int, _p, _p, _i64, _p]),
     "gn_tc_linear": (_int, [_p, _i64, _p, _i64, _int, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),
+    "gn_convert_scale_16": (_int, [_p, _i64, _p, _int, _i64, _i64, _int, C.c_float, _p]),
     "gn_layernorm_act_f32": (_int, [_p, _i64, _i64, _int, _p, _p, C.c_float, _int, _p]),
     "gn_edge_preact_f32": (_int, [_p, _int, _gp, _i64, _p, _i64, _p]),
     "gn_slot_sum_f32": (_int, [_p, _i64, _int, _gp, _i64, _p, _i64, _p]),

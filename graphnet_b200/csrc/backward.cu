@@ -107,6 +107,21 @@ __global__ void __launch_bounds__(256) mask_convert_kernel(const TG* __restrict_
   }
 }
 
+// ------------------------------------------------------------------ fp32 -> 16-bit with a scale
+template <typename TO>
+__global__ void __launch_bounds__(256) convert_scale_kernel(const float* __restrict__ X, int64_t ldx,
+                                                            TO* __restrict__ out, int64_t ldo,
+                                                            int64_t M, int N, float scale) {
+  const int nq = (N + 3) / 4;
+  const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= M * nq) return;
+  const int64_t m = idx / nq;
+  const int n0 = (int)(idx % nq) * 4;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (n0 + j < N) out[m * ldo + n0 + j] = from_f32<TO>(X[m * ldx + n0 + j] * scale);
+}
+
 // ------------------------------------------------------------------ edge slots: H and H^T
 // Row e = i * KP + t of the slot table (ELL, stride KP): H[e, :] = ReLU(P_i + Q_j) for a filled
 // slot (j = nbr[e] >= 0), 0 for an empty one; bf16.  A CTA takes 32 slot rows: the row-major copy
@@ -522,6 +537,25 @@ extern "C" int gn_outer_accumulate_f32(const float* G, int64_t ldg, int cols, co
   if (K <= 8) outer_accumulate_kernel<8><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
   else if (K <= 20) outer_accumulate_kernel<20><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
   else outer_accumulate_kernel<32><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_convert_scale_16(const float* X, int64_t ldx, void* out, int out_dtype,
+                                   int64_t ldo, int64_t M, int N, float scale, void* stream) {
+  GN_CHECK_ARG(M >= 0 && N >= 1 && ldx >= N && ldo >= N, "gn_convert_scale_16: bad sizes");
+  if (M == 0) return GN_OK;
+  GN_CHECK_ARG(X && out, "gn_convert_scale_16: null pointer");
+  const unsigned grid = (unsigned)ceil_div(M * ((N + 3) / 4), 256);
+  cudaStream_t st = as_stream(stream);
+  if (out_dtype == GN_F16)
+    convert_scale_kernel<__half><<<grid, 256, 0, st>>>(X, ldx, reinterpret_cast<__half*>(out), ldo,
+                                                       M, N, scale);
+  else if (out_dtype == GN_BF16)
+    convert_scale_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(
+        X, ldx, reinterpret_cast<__nv_bfloat16*>(out), ldo, M, N, scale);
+  else
+    GN_CHECK_ARG(false, "gn_convert_scale_16: bad out_dtype %d", out_dtype);
   GN_LAUNCH_CHECK();
   return GN_OK;
 }

@@ -544,3 +544,16 @@ def slot_sum_f32(Z: Tensor, graph: Graph, out: Tensor) -> Tensor:
         check(_lib.load().gn_slot_sum_f32(_ptr(Z), Z.stride(0), b, C.byref(gs), N, _ptr(out),
                                           out.stride(0), _stream(dev)), "gn_slot_sum_f32")
     return out
+
+
+def convert_scale_16(X: Tensor, dtype: torch.dtype, scale: float = 1.0) -> Tensor:
+    """16-bit copy of an fp32 matrix, multiplied by `scale` (a power of two keeps it exact)."""
+    dev = _require_cuda(X)
+    assert X.dtype == torch.float32 and X.stride(1) == 1
+    M, N = X.shape
+    out = torch.empty((M, (N + 7) // 8 * 8), dtype=dtype, device=dev)[:, :N]
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_convert_scale_16(_ptr(X), X.stride(0), _ptr(out), _DT[dtype],
+                                              out.stride(0), M, N, float(scale), _stream(dev)),
+              "gn_convert_scale_16")
+    return out

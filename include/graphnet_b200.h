@@ -230,6 +230,12 @@ int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t 
 int gn_task_head(const float* y, int64_t M, int p, int kind, float* out,
                  void* stream);
 
+/* out = 16-bit(X * scale): operand conversion in front of gn_tc_linear (the readout Linear,
+ * gnn/dynedge.py:347-348, runs with fp16 operands scaled by a power of two so that pooled sums
+ * stay in range; fp16 conversions saturate at +-65504). */
+int gn_convert_scale_16(const float* X, int64_t ldx, void* out, int out_dtype, int64_t ldo,
+                        int64_t M, int N, float scale, void* stream);
+
 /* ---- add_norm_layer=True (gnn/dynedge.py:202-203, :224-226) ---------------------- */
 
 /* X[m, :] <- act(LayerNorm(X[m, :]) * gamma + beta) in place (torch.nn.LayerNorm: biased
