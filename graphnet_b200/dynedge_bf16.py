@@ -75,6 +75,8 @@ class _ConvPack:
         self.first = first
         Wpq = Wpq.contiguous() if first else Wpq.to(io_dtype).contiguous()
         self.Wp, self.Wq = Wpq[:Kp], Wpq[Kp:]   # P = x Wp^T + bias_p ; Q = x Wq^T
+        self.Wpq = Wpq                           # both in one GEMM: [P | Q] = x Wpq^T + bias_pq
+        self.bias_pq = bias.contiguous()         # (zeros in the Q half)
         self.bias_p = bias[:Kp].contiguous()
         self.W2p = W2p.contiguous()
 
@@ -172,15 +174,14 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
     for li, conv in enumerate(convs):
         pk = _conv_pack(conv, io, first=(li == 0))
         assert pk.d == d_in
-        # P and Q live in separate dense arrays: Q is the gathered operand and stays L2 resident
-        P = torch.empty((N, pk.Kp), dtype=torch.float16, device=dev)
-        Q = torch.empty((N, pk.Kp), dtype=torch.float16, device=dev)
+        # one node GEMM writes [P | Q] (the layer input is read once); the edge kernel takes the
+        # two halves as strided matrices
+        PQ = torch.empty((N, 2 * pk.Kp), dtype=torch.float16, device=dev)
+        P, Q = PQ[:, :pk.Kp], PQ[:, pk.Kp:]
         if li == 0:
-            ops.linear_f32(x0, pk.Wp, pk.bias_p, act="none", out=P)
-            ops.linear_f32(x0, pk.Wq, None, act="none", out=Q)
+            ops.linear_f32(x0, pk.Wpq, pk.bias_pq, act="none", out=PQ)
         else:
-            ops.tc_linear_bf16(skip[:, off_in:], pk.Wp, pk.bias_p, P, K=d_in, act="none")
-            ops.tc_linear_bf16(skip[:, off_in:], pk.Wq, None, Q, K=d_in, act="none")
+            ops.tc_linear_bf16(skip[:, off_in:], pk.Wpq, pk.bias_pq, PQ, K=d_in, act="none")
         if save is not None:
             save["layers"].append({"P": P, "Q": Q, "graph": graph, "pack": pk, "off_in": off_in,
                                    "d_in": d_in, "off_out": offs[li]})
