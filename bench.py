@@ -49,13 +49,26 @@ def parse_args():
     ap.add_argument("--cpu-events", type=int, default=128,
                     help="events per CPU-baseline step (reference distribute step is O(N*B))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c4"],
+                    help="c2: BASELINE configs[1] (default); c4: configs[3] shapes (IceCube-Upgrade "
+                         "geometry, F=14, k=16, pools min/max/mean; use --events 256 --pulses 500)")
     ap.add_argument("--mode", default="infer", choices=["infer", "train"],
                     help="infer: BASELINE configs[1] (default); train: configs[2] (bf16 training "
                          "step: forward, backward, gradient all-reduce, Adam)")
     return ap.parse_args()
 
 
+def workload_cfg(args):
+    """(detector, k, pools) of the selected workload."""
+    if getattr(args, "workload", "c2") == "c4":
+        return "upgrade", 16, ["min", "max", "mean"]
+    return "icecube86", 8, POOLS
+
+
 def workload_name(args):
+    if getattr(args, "workload", "c2") == "c4":
+        return (f"C4: DynEdge inference, synthetic IceCube-Upgrade pulse maps, ~{args.pulses:g} "
+                f"pulses/event, F=14, k=16, batch {args.events}/GPU, pools min/max/mean")
     if getattr(args, "mode", "infer") == "train":
         return (f"C3: DynEdge training step (forward, backward, gradient all-reduce, Adam), bf16, "
                 f"synthetic IceCube-86 events, ~{args.pulses:g} pulses/event, k=8, batch "
@@ -279,19 +292,21 @@ def run_ours(args):
     lib = _lib.load()
 
     # ---- inputs: one synthetic batch per rank, host (pinned) and device copies
-    pb = make_pulse_batch(args.events, args.pulses, seed=1234 + rank)
+    det, knn_k, pools = workload_cfg(args)
+    pb = make_pulse_batch(args.events, args.pulses, detector=det, seed=1234 + rank)
     x_dev = pb.x.to(dev)
     batch_dev = pb.batch.to(dev)
     npulse_dev = pb.n_pulses.to(dev)
     # the initial graph is built by the dataset in the reference (KNNGraph in the
     # dataloader workers), not by the model: build it once here, on the device
-    ei_dev = g.knn_graph(x_dev[:, :3].contiguous(), 8, batch_dev, num_events=args.events)
+    ei_dev = g.knn_graph(x_dev[:, :3].contiguous(), knn_k, batch_dev, num_events=args.events)
     N, E = x_dev.shape[0], ei_dev.shape[1]
     host = {"x": pb.x.pin_memory(), "edge_index": ei_dev.cpu().pin_memory(),
             "batch": pb.batch.pin_memory(), "n_pulses": pb.n_pulses.pin_memory()}
 
     torch.manual_seed(0)
-    backbone = g.DynEdge(7, global_pooling_schemes=POOLS, precision=precision)
+    backbone = g.DynEdge(x_dev.shape[1], nb_neighbours=knn_k, global_pooling_schemes=pools,
+                         precision=precision)
     task = g.EnergyReconstruction(hidden_size=backbone.nb_outputs, target_labels="energy",
                                   loss_function=g.LogCoshLoss())
     model = g.StandardModel(tasks=[task], graph_definition=object(), gnn=backbone).to(dev)
@@ -365,6 +380,8 @@ def run_ours(args):
     # `--mode train` prints it as the main line) rides along; it can never cost the line above
     train = None
     try:
+        if args.workload != "c2":
+            raise RuntimeError("training summary only rides along the C2 workload")
         del model, backbone, feeder
         torch.cuda.synchronize(dev)
         torch.cuda.empty_cache()   # same allocator state as a stand-alone `--mode train` run
@@ -385,7 +402,7 @@ def run_ours(args):
     e2e_value = events_total * args.steps / (ms_e2e * 1e-3)
     h2d = sum(t.numel() * t.element_size() for t in host.values())
     d2h = args.events * 4
-    flops = algorithmic_flops_per_event_batch(N, E)
+    flops = algorithmic_flops_per_event_batch(N, E, F=int(x_dev.shape[1]))
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": ms_res / args.steps,
@@ -406,12 +423,12 @@ def run_ours(args):
         line["graph_replay"] = {"value": events_total * args.steps / (ms_graph * 1e-3), "unit": UNIT,
                                 "ms_per_step": ms_graph / args.steps,
                                 "note": "same step, inputs resident, replayed from one CUDA graph"}
-    if rank == 0 and train is not None:
+    if rank == 0 and train is not None and args.workload == "c2":
         line["train"] = ({k: train[k] for k in ("metric", "value", "unit", "ms_per_step", "dtype",
                                                 "steps", "gpu_launches")}
                          | {"e2e": train["e2e"], "workload": train["config"]["workload"]}
                          if "error" not in train else train)
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and args.workload == "c2":
         v, cores, sec = cpu_reference_events_per_s(args.cpu_events, args.pulses, steps=10, warmup=2)
         line["cpu_baseline"] = {
             "value": v, "unit": UNIT, "cores": cores, "kind": "port",
