@@ -60,6 +60,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 
 // Same, for roles with slack: back off between polls so that the waiting warp does not compete
 // for issue slots with the warps on the critical path.
+template <int SLEEP_NS = 200>
 __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
   for (uint32_t it = 0; it < (1u << 22); ++it) {
@@ -72,7 +73,7 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
         : "r"(addr), "r"(parity)
         : "memory");
     if (done) return;
-    __nanosleep(200);
+    __nanosleep(SLEEP_NS);
   }
   __trap();
 }

@@ -19,8 +19,8 @@
 //     - and KP need not be a power of two: with KP = k+1 = 9 slots per node a kNN graph needs
 //     no overflow pass at all;
 // Tile = 64 ELL rows = floor(64/KP) nodes.  Warp roles (17 warps): 0-7 epilogue (warp>>2 =
-// channel block of 128, warp&3 = TMEM lane quadrant), 8-11 h builders (16 rows each), 12-15
-// gather warps (one per ring stage), 16 tcgen05.mma issuer.  TMEM columns: [0,Kp/2) W2 block 0, [176,176+Kp/2) W2 block 1,
+// channel block of 128, warp&3 = TMEM lane quadrant), 8-15 h builders (8 rows each), 16-19
+// gather warps (one per ring stage), 20 tcgen05.mma issuer.  TMEM columns: [0,Kp/2) W2 block 0, [176,176+Kp/2) W2 block 1,
 // [352,416) D block 0, [416,480) D block 1 - the epilogue of one channel block overlaps the
 // MMAs of the other.
 #pragma once
@@ -33,8 +33,9 @@ constexpr int E2_HALF = 32;          // rows per gather stage
 constexpr int E2_QSTAGES = 4;        // gather ring depth (half tiles): 2 tiles of lookahead
 constexpr int E2_HBUFS = 2;          // h tiles (B operand) in shared memory
 constexpr int E2_EPI_WARPS = 8;      // (channel block, TMEM lane quadrant)
-constexpr int E2_BLD_WARPS = 4;      // h builders: 16 tile rows per warp
-constexpr int E2_GAT_WARPS = E2_QSTAGES;  // one gather warp owns each ring stage
+constexpr int E2_BLD_WARPS = 8;      // h builders: 8 tile rows per warp (one row per lane quad)
+constexpr int E2_GAT_SPLIT = 1;     // gather warps per ring stage (2: even / odd rows - tried, the 72-register cap of 25 warps costs the epilogue more than the gather gains)
+constexpr int E2_GAT_WARPS = E2_QSTAGES * E2_GAT_SPLIT;
 constexpr int E2_MMA_WARP = E2_EPI_WARPS + E2_BLD_WARPS + E2_GAT_WARPS;  // warp 16
 constexpr int E2_THREADS = 32 * (E2_MMA_WARP + 1);                       // 544
 constexpr int E2_TMEM_A1 = 176;      // column offset of W2 block 1
@@ -158,7 +159,7 @@ template <bool RELAXED = false>
 __device__ __forceinline__ void mbar_wait_t(uint64_t* bar, uint32_t parity, long long& acc,
                                             bool timed) {
   const long long t0 = timed ? clock64() : 0;
-  if (RELAXED) mbar_wait_relaxed(bar, parity);
+  if (RELAXED) mbar_wait_relaxed<40>(bar, parity);
   else mbar_wait(bar, parity);
   if (timed) acc += clock64() - t0;
 }
@@ -189,7 +190,7 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
   if (threadIdx.x == 0) {
 #pragma unroll
     for (int s = 0; s < E2_QSTAGES; ++s) {
-      mbar_init(&sh->q_full[s], 32 + 1);              // the stage's gather warp
+      mbar_init(&sh->q_full[s], E2_GAT_SPLIT * (32 + 1));  // the stage's gather warps
       mbar_init(&sh->q_empty[s], E2_BLD_WARPS / 2);
     }
 #pragma unroll
@@ -247,7 +248,9 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
     // touches, Kp fp16 each, filled with 16-byte cp.async pieces (one row per warp iteration,
     // lanes = consecutive pieces).  Every thread makes the stage's mbarrier count one arrival
     // when its copies have landed; one plain arrive per warp publishes the row-valid flags.
-    const int so = warp - (E2_EPI_WARPS + E2_BLD_WARPS);  // the stage this warp owns
+    const int gw = warp - (E2_EPI_WARPS + E2_BLD_WARPS);
+    const int so = gw / E2_GAT_SPLIT;                     // the stage this warp helps to fill
+    const int sub = gw % E2_GAT_SPLIT;                    // ... rows r = sub (mod E2_GAT_SPLIT)
     const int ppr = rowbytes / 16;                        // 16-byte pieces per row (<= 44)
     const uint32_t on1 = lane < ppr, on2 = lane + 32 < ppr;
     const uint32_t stage = smem_u32(q_smem) + so * qstage_bytes + lane * 16;
@@ -278,10 +281,10 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
       const int32_t j = j_nx, pn = pn_nx;
       fetch_ids(g2 + E2_QSTAGES);  // ids of this pair's next half-stage, in flight meanwhile
       mbar_wait_t<true>(&sh->q_empty[so], ((g2 / E2_QSTAGES) & 1) ^ 1, w0, timed);
-      sh->row_valid[so][lane] = j >= 0 ? 1 : 0;
+      if (sub == 0) sh->row_valid[so][lane] = j >= 0 ? 1 : 0;
       // four rows per step (independent address chains); lanes = consecutive 16-byte pieces
 #pragma unroll 8
-      for (int r = 0; r < E2_HALF; ++r) {
+      for (int r = sub; r < E2_HALF; r += E2_GAT_SPLIT) {
         const int32_t src = __shfl_sync(0xffffffffu, j, r);
         const uint32_t ok = src >= 0;
         const uint8_t* g = reinterpret_cast<const uint8_t*>(qbase + (uint64_t)(uint32_t)max(src, 0) * qpitch);
@@ -292,7 +295,7 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
 #pragma unroll
       for (int r = 0; r < PMAX; ++r) {
         const int32_t src = __shfl_sync(0xffffffffu, pn, r);
-        const uint32_t ok = src >= 0;
+        const uint32_t ok = src >= 0 && (r % E2_GAT_SPLIT) == sub;
         const uint8_t* g = reinterpret_cast<const uint8_t*>(pbase + (uint64_t)(uint32_t)max(src, 0) * ppitch);
         const uint32_t d = stage + (uint32_t)((E2_HALF + r) * rowbytes);
         cp_async16_if(d, g, ok & on1);
@@ -370,18 +373,20 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
     // warp bw owns rows 16 bw .. 16 bw + 15 of the tile; lane = (row rr = lane >> 2, 16-byte
     // piece c4 = lane & 3 of the 64-byte K chunk), two rows per lane (rr and rr + 8).
     // Quarter-warps touch 2 rows x 64 B: conflict free.
-    const int bw = warp - E2_EPI_WARPS;  // 0..3
-    const int hs = bw >> 1;              // which gather stage of the tile
+    constexpr int RW = E2_ROWS / E2_BLD_WARPS;   // tile rows per builder warp
+    constexpr int U = RW / 8;                    // rows per lane
+    const int bw = warp - E2_EPI_WARPS;
+    const int hs = (bw * RW) / E2_HALF;          // which gather stage of the tile
     const int rr = lane >> 2, c4 = lane & 3;
     const uint32_t q_addr = smem_u32(q_smem);
     const uint32_t h_addr = smem_u32(h_smem);
     const int nfirst = (hs * E2_HALF) / KP;
-    int srow[2];
-    uint32_t dst_off[2], q_off[2], p_off[2];
+    int srow[U];
+    uint32_t dst_off[U], q_off[U], p_off[U];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      const int row = bw * 16 + rr + 8 * u;           // row in tile
-      srow[u] = (bw & 1) * 16 + rr + 8 * u;           // row in stage
+    for (int u = 0; u < U; ++u) {
+      const int row = bw * RW + rr + 8 * u;           // row in tile
+      srow[u] = row - hs * E2_HALF;                   // row in stage
       dst_off[u] = (uint32_t)(row * 64 + ((c4 ^ ((row >> 1) & 3)) << 4));
       q_off[u] = (uint32_t)(srow[u] * rowbytes + c4 * 16);
       const int pslot = row < USED ? row / KP - nfirst : 0;
@@ -392,20 +397,21 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
       const uint32_t s = g2 % E2_QSTAGES;
       const uint32_t hb = (uint32_t)(it % E2_HBUFS);
       mbar_wait_t(&sh->q_full[s], (g2 / E2_QSTAGES) & 1, w0, timed);
-      const bool valid0 = sh->row_valid[s][srow[0]] != 0;
-      const bool valid1 = sh->row_valid[s][srow[1]] != 0;
+      bool valid[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) valid[u] = sh->row_valid[s][srow[u]] != 0;
       mbar_wait_t(&sh->h_empty[hb], (uint32_t)((it / E2_HBUFS) & 1) ^ 1, w1, timed);
       const uint32_t sbase = q_addr + s * qstage_bytes;
       const uint32_t dbase = h_addr + hb * htile_bytes;
       // four K chunks per step: all eight loads are issued before the first use
 #pragma unroll 1
       for (int kc0 = 0; kc0 < nch; kc0 += 4) {
-        uint4 Q[4][2], P[4][2];
+        uint4 Q[4][U], P[4][U];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
 #pragma unroll
-          for (int u = 0; u < 2; ++u) {
-            const bool ld = (u == 0 ? valid0 : valid1) && kc0 + i < nch;
+          for (int u = 0; u < U; ++u) {
+            const bool ld = valid[u] && kc0 + i < nch;
             Q[i][u] = ld ? lds128(sbase + q_off[u] + (kc0 + i) * 64) : make_uint4(0, 0, 0, 0);
             P[i][u] = ld ? lds128(sbase + p_off[u] + (kc0 + i) * 64) : make_uint4(0, 0, 0, 0);
           }
@@ -414,7 +420,7 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
         for (int i = 0; i < 4; ++i) {
           if (kc0 + i < nch) {
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
+            for (int u = 0; u < U; ++u) {
               // empty slots: P = Q = 0 -> h = 0 (the "ones" columns included)
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(
                                dbase + dst_off[u] + (kc0 + i) * (E2_ROWS * 64)),
@@ -457,25 +463,22 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
         const int nvalid = (int)min((int64_t)NPT, num_groups - grp0);  // groups of this tile
         mbar_wait_t<true>(&sh->d_full[blk], (uint32_t)(it & 1), w0, timed);
         tc_fence_after();
-        float v0[32], v1[32];
-        tmem_ld_32x32(d_addr, v0);
-        tmem_ld_32x32(d_addr + 32, v1);
+        float sums[NPT];
+#pragma unroll
+        for (int n = 0; n < NPT; ++n) sums[n] = 0.f;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {   // 32 columns at a time: half the registers
+          float v[32];
+          tmem_ld_32x32(d_addr + 32 * half, v);
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const int col = 32 * half + c;
+            if (col < USED) sums[col / KP] += fmaxf(v[c], 0.f);
+          }
+        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&sh->d_empty[blk]);  // values are in registers now
-        float sums[NPT];
-#pragma unroll
-        for (int n = 0; n < NPT; ++n) {
-          // two interleaved partial sums shorten the dependent FADD chain
-          float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-          for (int t = 0; t < KP; ++t) {
-            const int col = n * KP + t;
-            const float r = fmaxf(col < 32 ? v0[col & 31] : v1[col & 31], 0.f);
-            if (t & 1) s1 += r; else s0 += r;
-          }
-          sums[n] = s0 + s1;
-        }
         if (ch_ok) {
           if (!ACC) {
             // pass 1: group g is node g -> consecutive rows of `out`
