@@ -12,6 +12,8 @@ if ROOT not in sys.path:
 
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 GOLDEN_CASES = ["oscnext5", "upgrade5", "prometheus50", "adversarial", "adversarial_k16_after"]
+# options off the default path (LayerNorm, GELU, 1- and 3-Linear EdgeConv MLPs): fp32 only
+GOLDEN_EXTRA = ["oscnext5_norm_gelu"]
 
 
 def pytest_configure(config):
@@ -40,7 +42,7 @@ def load_golden(name):
     return out
 
 
-@pytest.fixture(params=GOLDEN_CASES)
+@pytest.fixture(params=GOLDEN_CASES + GOLDEN_EXTRA)
 def golden(request):
     return load_golden(request.param)
 

@@ -18,6 +18,8 @@ upgrade5    data/tests/sqlite/upgrade_genie_step4... (5 events, 85-167 pulses,
             DynEdge(14, pools=[min,max,mean]) (QUESO shape), k=8.
 prometheus  data/examples/sqlite/prometheus (50 events, 3-99 pulses, F=4),
             DynEdge(4) ctor defaults except pools=[min,max,mean,sum]; direction head.
+oscnext5_norm_gelu  the oscNext events through DynEdge(add_norm_layer=True,
+            activation_layer="gelu") with 3-, 1- and 2-Linear EdgeConv MLPs.
 adversarial synthetic: events with n<k+1, all points identical, 2-pulse events,
             ties straddling the k+1 cut; DynEdge(7) node-level (no pooling).
 """
@@ -157,6 +159,20 @@ def adversarial_inputs():
     return x.contiguous(), batch, counts.to(torch.int32)
 
 
+def run_extra_cases(ref):
+    """Options off the default path: LayerNorm + GELU (dynedge.py:161-165, :202-203, :224-226)
+    and EdgeConv MLPs with one / three Linear layers, on the oscNext events."""
+    x, b, n = load_db(
+        f"{REF_DATA}/tests/sqlite/oscNext_genie_level7_v02/oscNext_genie_level7_v02_first_5_frames.db",
+        "SRTInIcePulses", FEATURES_ICECUBE86, IceCube86())
+    run_case("oscnext5_norm_gelu", ref, x, b, n, 8,
+             dict(global_pooling_schemes=["min", "max", "mean", "sum"], add_norm_layer=True,
+                  activation_layer="gelu",
+                  dynedge_layer_sizes=[(48, 64, 96), (80,), (64, 64)],
+                  post_processing_layer_sizes=[72, 48], readout_layer_sizes=[40]),
+             None, seed=5)
+
+
 def main():
     ref = refstub.load_reference()
     pools4 = ["min", "max", "mean", "sum"]
@@ -176,6 +192,7 @@ def main():
     assert bool(keep.all())
     run_case("prometheus50", ref, x, b, n, 8, dict(global_pooling_schemes=pools4),
              "direction", seed=2)
+    run_extra_cases(ref)
     x, b, n = adversarial_inputs()
     run_case("adversarial", ref, x, b, n, 8, dict(), None, seed=3)
     run_case("adversarial_k16_after", ref, x, b, n, 8,
@@ -187,4 +204,7 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "--extra-only" in sys.argv:
+        run_extra_cases(refstub.load_reference())
+    else:
+        main()

@@ -200,3 +200,22 @@ def batch_other_shape(gb):
     x = pb.x.to(DEV)
     ei = gb.knn_graph(x[:, :3].contiguous(), 8, pb.batch.to(DEV), num_events=8)
     return gb.Data(x=x, edge_index=ei, batch=pb.batch.to(DEV), n_pulses=pb.n_pulses.to(DEV))
+
+
+def test_norm_gelu_deep_mlps_match_reference_golden():
+    """The golden recorded from the reference's own DynEdge code (refstub) with add_norm_layer,
+    GELU and 3/1/2-Linear EdgeConv MLPs."""
+    import graphnet_b200 as gb
+    from conftest import load_golden
+    g = load_golden("oscnext5_norm_gelu")
+    spec = oracle.DynEdgeSpec(nb_inputs=g["x"].shape[1], **g["dyn_kwargs"])
+    sd = oracle.init_dynedge_state_dict(spec, seed=int(g["seed"]))
+    m = gb.DynEdge(g["x"].shape[1], **g["dyn_kwargs"])
+    m.load_state_dict(sd)
+    m = m.to(DEV)
+    m.train(False)
+    data = gb.Data(x=g["x"].to(DEV), edge_index=g["edge_index"].to(DEV), batch=g["batch"].to(DEV),
+                   n_pulses=g["n_pulses"].to(DEV))
+    with torch.no_grad():
+        got = m(data).cpu()
+    assert rel_l2(got, g["out"]) < 1e-4
