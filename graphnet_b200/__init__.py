@@ -10,6 +10,7 @@ does, and fails loudly when it is missing (no CPU fallback).
 from .data import Batch, Data  # noqa: F401
 from .detector import IceCube86, IceCubeUpgrade, Prometheus, ORCA150SuperDense  # noqa: F401
 from .dynedge import DynEdge, DynEdgeConv  # noqa: F401
+from .dynedge_jinst import DynEdgeJINST  # noqa: F401
 from .graphs import KNNEdges, KNNGraph  # noqa: F401
 from .losses import LogCoshLoss, VonMisesFisher3DLoss  # noqa: F401
 from .ops import knn_graph  # noqa: F401

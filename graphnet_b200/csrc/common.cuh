@@ -86,11 +86,15 @@ inline int make_graph_view(const gn_graph* g, GraphView* v) {
   return GN_OK;
 }
 
-enum Act : int { ACT_NONE = GN_ACT_NONE, ACT_RELU = GN_ACT_RELU, ACT_GELU = GN_ACT_GELU };
+enum Act : int {
+  ACT_NONE = GN_ACT_NONE, ACT_RELU = GN_ACT_RELU, ACT_GELU = GN_ACT_GELU,
+  ACT_LEAKY_RELU = GN_ACT_LEAKY_RELU
+};
 
 template <int ACT>
 __device__ __forceinline__ float activate(float v) {
   if (ACT == ACT_RELU) return fmaxf(v, 0.0f);
+  if (ACT == ACT_LEAKY_RELU) return v > 0.0f ? v : 0.01f * v;
   if (ACT == ACT_GELU) return 0.5f * v * (1.0f + erff(v * 0.70710678118654752440f));
   return v;
 }

@@ -384,6 +384,9 @@ static int linear_f32_t(const float* A, int64_t lda, const float* W, const float
     case GN_ACT_NONE: launch_linear<ACT_NONE, OutT>(A, lda, W, bias, C, ldc, M, N, K, st); break;
     case GN_ACT_RELU: launch_linear<ACT_RELU, OutT>(A, lda, W, bias, C, ldc, M, N, K, st); break;
     case GN_ACT_GELU: launch_linear<ACT_GELU, OutT>(A, lda, W, bias, C, ldc, M, N, K, st); break;
+    case GN_ACT_LEAKY_RELU:
+      launch_linear<ACT_LEAKY_RELU, OutT>(A, lda, W, bias, C, ldc, M, N, K, st);
+      break;
     default: set_error("unknown activation %d", act); return GN_ERR_INVALID_ARGUMENT;
   }
   GN_LAUNCH_CHECK();
@@ -508,6 +511,8 @@ extern "C" int gn_edgeconv_f32(const float* x, int64_t ldx, int d, const gn_grap
     case GN_ACT_NONE: return dispatch_aggr<ACT_NONE>(aggr, pq, a, g, N, W2T, b2, b, out, ldo, st);
     case GN_ACT_RELU: return dispatch_aggr<ACT_RELU>(aggr, pq, a, g, N, W2T, b2, b, out, ldo, st);
     case GN_ACT_GELU: return dispatch_aggr<ACT_GELU>(aggr, pq, a, g, N, W2T, b2, b, out, ldo, st);
+    case GN_ACT_LEAKY_RELU:
+      return dispatch_aggr<ACT_LEAKY_RELU>(aggr, pq, a, g, N, W2T, b2, b, out, ldo, st);
   }
   set_error("unknown activation %d", act);
   return GN_ERR_INVALID_ARGUMENT;

@@ -100,6 +100,7 @@ extern "C" int gn_layernorm_act_f32(float* X, int64_t ldx, int64_t M, int N, con
     case GN_ACT_NONE: layernorm_act_kernel<ACT_NONE><<<grid, 256, 0, st>>>(X, ldx, M, N, gamma, beta, eps); break;
     case GN_ACT_RELU: layernorm_act_kernel<ACT_RELU><<<grid, 256, 0, st>>>(X, ldx, M, N, gamma, beta, eps); break;
     case GN_ACT_GELU: layernorm_act_kernel<ACT_GELU><<<grid, 256, 0, st>>>(X, ldx, M, N, gamma, beta, eps); break;
+    case GN_ACT_LEAKY_RELU: layernorm_act_kernel<ACT_LEAKY_RELU><<<grid, 256, 0, st>>>(X, ldx, M, N, gamma, beta, eps); break;
     default: set_error("unknown activation %d", act); return GN_ERR_INVALID_ARGUMENT;
   }
   GN_LAUNCH_CHECK();

@@ -31,6 +31,10 @@ def _act_name(module: torch.nn.Module) -> str:
         if getattr(module, "approximate", "none") != "none":
             raise NotImplementedError("GELU(approximate=...) is not supported")
         return "gelu"
+    if isinstance(module, torch.nn.LeakyReLU):
+        if abs(module.negative_slope - 0.01) > 1e-12:
+            raise NotImplementedError("LeakyReLU with a slope other than 0.01 is not supported")
+        return "leaky_relu"
     raise NotImplementedError(f"activation {type(module).__name__} is not supported")
 
 
@@ -62,7 +66,11 @@ def _apply_act_rows(h: Tensor, act: str) -> Tensor:
         return h
     # activation alone (first EdgeConv Linear without a norm layer after it): LayerNorm kernel
     # is not involved; a Linear-free activation only occurs on this unfused path
-    return torch.relu_(h) if act == "relu" else torch.nn.functional.gelu(h)
+    if act == "relu":
+        return torch.relu_(h)
+    if act == "leaky_relu":
+        return torch.nn.functional.leaky_relu_(h, 0.01)
+    return torch.nn.functional.gelu(h)
 
 
 def _parse_mlp_norm(seq: torch.nn.Module):

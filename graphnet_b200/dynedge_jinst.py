@@ -1,0 +1,87 @@
+"""`DynEdgeJINST` on the CUDA kernels (fp32).
+
+Mirrors /root/reference/src/graphnet/models/gnn/dynedge_jinst.py:19-160 - constructor arguments,
+parameter names (`conv_add{1..4}.nn.{0,2}.*`, `nn1`, `nn2`, `nn3`) and output - so checkpoints of
+the reference load.  It is DynEdge's older sibling: four DynEdgeConv layers with LeakyReLU MLPs
+and "add" aggregation, the input and all four layer outputs concatenated, a two-layer node MLP,
+max/min/sum/mean pooling with the xyzt homophily of the input graph and the raw pulse count
+appended, and one output layer.  Every step runs on the same kernels as `DynEdge`'s fp32 path.
+"""
+
+from __future__ import annotations
+
+from typing import Any
+
+import torch
+from torch import Tensor
+
+from . import ops
+from .dynedge import DynEdgeConv
+
+
+class DynEdgeJINST(torch.nn.Module):
+    def __init__(self, nb_inputs: int, layer_size_scale: int = 4):
+        super().__init__()
+        c = layer_size_scale
+        l1, l2, l3, l4, l5, l6 = nb_inputs, c * 16 * 2, c * 32 * 2, c * 42 * 2, c * 32 * 2, c * 16 * 2
+        self._nb_inputs, self._nb_outputs = nb_inputs, l6
+        self._dims = (l1, l3, l5)
+
+        def conv(i: int, o: int, m: int) -> DynEdgeConv:
+            return DynEdgeConv(
+                torch.nn.Sequential(torch.nn.Linear(i * 2, m), torch.nn.LeakyReLU(),
+                                    torch.nn.Linear(m, o), torch.nn.LeakyReLU()),
+                aggr="add", nb_neighbors=8, features_subset=slice(0, 3))
+
+        self.conv_add1 = conv(l1, l3, l2)
+        self.conv_add2 = conv(l3, l3, l4)
+        self.conv_add3 = conv(l3, l3, l4)
+        self.conv_add4 = conv(l3, l3, l4)
+        self.nn1 = torch.nn.Linear(l3 * 4 + l1, l4)
+        self.nn2 = torch.nn.Linear(l4, l5)
+        self.nn3 = torch.nn.Linear(4 * l5 + 5, l6)
+        self.lrelu = torch.nn.LeakyReLU()
+
+    @property
+    def nb_inputs(self) -> int:
+        return self._nb_inputs
+
+    @property
+    def nb_outputs(self) -> int:
+        return self._nb_outputs
+
+    @torch.no_grad()
+    def forward(self, data: Any) -> Tensor:
+        x = data.x
+        if not x.is_cuda:
+            raise RuntimeError("graphnet_b200.DynEdgeJINST needs CUDA tensors (no CPU fallback)")
+        x = x.float().contiguous()
+        dev = x.device
+        N, F = x.shape
+        l1, l3, l5 = self._dims
+        n_pulses = data.n_pulses.reshape(-1)
+        B = int(n_pulses.shape[0])
+        ptr, _ = ops.batch_to_ptr(data.batch, B)
+        graph = ops.coo_to_csr(data.edge_index, N)
+        # homophily of x, y, z, t over the input graph (models/utils.py:17-33): columns F..F+3
+        gv = ops.global_variables(x, graph, ptr, n_pulses)
+        skip = torch.empty((N, l1 + 4 * l3), dtype=torch.float32, device=dev)
+        skip[:, :l1] = x
+        off_in, d_in, off_out = 0, l1, l1
+        convs = [self.conv_add1, self.conv_add2, self.conv_add3, self.conv_add4]
+        for li, conv in enumerate(convs):
+            conv._conv_f32(skip[:, off_in:off_in + d_in], graph, out=skip[:, off_out:off_out + l3])
+            if li + 1 < len(convs):      # the graph built after the last layer is never used
+                graph = ops.knn_graph_ell(skip, conv.nb_neighbors, ptr,
+                                          [off_out, off_out + 1, off_out + 2])
+            off_in, d_in = off_out, l3
+            off_out += l3
+        h = ops.linear_f32(skip, self.nn1.weight, self.nn1.bias, act="leaky_relu")
+        h = ops.linear_f32(h, self.nn2.weight, self.nn2.bias, act="none")
+        pooled = torch.empty((B, 4 * l5 + 5), dtype=torch.float32, device=dev)
+        ops.segment_pool(h, ptr, ["max", "min", "sum", "mean"], out=pooled)
+        pooled[:, 4 * l5] = gv[:, F + 3]          # h_t
+        pooled[:, 4 * l5 + 1:4 * l5 + 4] = gv[:, F:F + 3]   # h_x, h_y, h_z
+        pooled[:, 4 * l5 + 4] = n_pulses.to(torch.float32)
+        torch.nn.functional.leaky_relu_(pooled, 0.01)
+        return ops.linear_f32(pooled, self.nn3.weight, self.nn3.bias, act="leaky_relu")

@@ -33,6 +33,7 @@ extern "C" {
 #define GN_ACT_NONE 0
 #define GN_ACT_RELU 1
 #define GN_ACT_GELU 2
+#define GN_ACT_LEAKY_RELU 3 /* torch.nn.LeakyReLU(), slope 0.01 (DynEdgeJINST; FFMA kernels only) */
 
 /* aggregation of EdgeConv messages (components/layers.py:33; dynedge.py:208 uses ADD) */
 #define GN_AGGR_ADD 0

@@ -183,6 +183,7 @@ def load_reference() -> types.SimpleNamespace:
     _stub("graphnet.utilities.imports", has_jammy_flows_package=lambda: False)
 
     dynedge = importlib.import_module("graphnet.models.gnn.dynedge")
+    jinst = importlib.import_module("graphnet.models.gnn.dynedge_jinst")
     layers = importlib.import_module("graphnet.models.components.layers")
     task = importlib.import_module("graphnet.models.task.task")
     # `from graphnet.models.task import StandardLearnedTask` in reconstruction.py
@@ -191,6 +192,7 @@ def load_reference() -> types.SimpleNamespace:
     loss = importlib.import_module("graphnet.training.loss_functions")
     return types.SimpleNamespace(
         DynEdge=dynedge.DynEdge,
+        DynEdgeJINST=jinst.DynEdgeJINST,
         DynEdgeConv=layers.DynEdgeConv,
         Data=_Data,
         task=task,

@@ -173,6 +173,29 @@ def run_extra_cases(ref):
              None, seed=5)
 
 
+def run_jinst_case(ref):
+    """DynEdgeJINST (gnn/dynedge_jinst.py) on the oscNext events, from the reference's own file."""
+    from oracle.dynedge_jinst import init_jinst_state_dict, jinst_forward
+    x, b, n = load_db(
+        f"{REF_DATA}/tests/sqlite/oscNext_genie_level7_v02/oscNext_genie_level7_v02_first_5_frames.db",
+        "SRTInIcePulses", FEATURES_ICECUBE86, IceCube86())
+    ei = initial_graph(x, b, 8)
+    torch.manual_seed(6)
+    model = ref.DynEdgeJINST(x.shape[1])
+    sd = {k_: v.detach().clone() for k_, v in model.state_dict().items()}
+    sd2 = init_jinst_state_dict(x.shape[1], 4, seed=6)
+    assert set(sd) == set(sd2) and all(torch.equal(sd[k_], sd2[k_]) for k_ in sd)
+    with torch.no_grad():
+        y = model(ref.Data(x=x, edge_index=ei, batch=b, n_pulses=n))
+        y2, inter = jinst_forward(sd, x, ei, b, n, return_intermediates=True)
+    assert torch.equal(y, y2), "oracle restatement differs from the reference code"
+    path = os.path.join(OUT, "oscnext5_jinst.npz")
+    np.savez_compressed(path, x=x.numpy(), batch=b.numpy(), n_pulses=n.numpy(),
+                        edge_index=ei.numpy(), seed=np.int64(6), out=y.numpy(),
+                        conv0=inter["convs"][0].numpy(), pooled=inter["pooled"].numpy())
+    print(f"oscnext5_jinst: N={x.shape[0]} -> {os.path.getsize(path) / 1e3:.0f} kB")
+
+
 def main():
     ref = refstub.load_reference()
     pools4 = ["min", "max", "mean", "sum"]
@@ -193,6 +216,7 @@ def main():
     run_case("prometheus50", ref, x, b, n, 8, dict(global_pooling_schemes=pools4),
              "direction", seed=2)
     run_extra_cases(ref)
+    run_jinst_case(ref)
     x, b, n = adversarial_inputs()
     run_case("adversarial", ref, x, b, n, 8, dict(), None, seed=3)
     run_case("adversarial_k16_after", ref, x, b, n, 8,
@@ -205,6 +229,8 @@ def main():
 
 if __name__ == "__main__":
     if "--extra-only" in sys.argv:
-        run_extra_cases(refstub.load_reference())
+        _ref = refstub.load_reference()
+        run_extra_cases(_ref)
+        run_jinst_case(_ref)
     else:
         main()

@@ -110,3 +110,14 @@ def test_vmf_m3_closed_form_is_the_reference_test_formula():
     bessel = 0.5 * torch.log(k) - torch.log(torch.from_numpy(scipy.special.iv(0.5, k.numpy()))) \
         - 1.5 * np.log(2 * np.pi)
     assert torch.allclose(otasks.log_cmk_m3_exact(k), bessel, rtol=1e-9, atol=1e-9)
+
+
+def test_jinst_oracle_reproduces_reference_golden():
+    """oracle/dynedge_jinst.py against the output of the reference's own dynedge_jinst.py."""
+    import numpy as np, os
+    from oracle.dynedge_jinst import init_jinst_state_dict, jinst_forward
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "oscnext5_jinst.npz"))
+    x, b, n, ei = (torch.from_numpy(z[k]) for k in ("x", "batch", "n_pulses", "edge_index"))
+    sd = init_jinst_state_dict(x.shape[1], 4, seed=int(z["seed"]))
+    y = jinst_forward(sd, x, ei, b, n)
+    assert torch.equal(y, torch.from_numpy(z["out"]))
