@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(GV_THREADS) global_variables_kernel(
 }
 
 // ------------------------------------------------------------------ pooling
-constexpr int POOL_COLS = 64;   // column-threads per CTA (x4 columns each when vectorised)
+constexpr int POOL_COLS = 32;   // column-threads per CTA (x4 columns each when vectorised)
 constexpr int POOL_ROWG = 4;    // row groups per CTA
 
 struct PoolSchemes {
@@ -170,17 +170,32 @@ __global__ void __launch_bounds__(POOL_COLS * POOL_ROWG) segment_pool_kernel(
   if (col_ok) {
     const T* base = x + (int64_t)lo * ldx + c;
     int r = rg;
-    for (; r + 3 * POOL_ROWG < n; r += 4 * POOL_ROWG) {
-      float a0[VEC], a1[VEC], a2[VEC], a3[VEC];
+    // eight rows of this row group in flight per pass: an event of ~60 pulses is read in two
+    // dependent round trips to HBM instead of four
+    constexpr int UNR = 8;
+    for (; r + (UNR - 1) * POOL_ROWG < n; r += UNR * POOL_ROWG) {
+      float a[UNR][VEC];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) load_vec<T, VEC>(base + (int64_t)(r + u * POOL_ROWG) * ldx, a[u]);
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+          mn[v] = fminf(mn[v], a[u][v]);
+          mx[v] = fmaxf(mx[v], a[u][v]);
+          sm[v] += a[u][v];
+        }
+      }
+    }
+    for (; r + 1 * POOL_ROWG < n; r += 2 * POOL_ROWG) {
+      float a0[VEC], a1[VEC];
       load_vec<T, VEC>(base + (int64_t)r * ldx, a0);
       load_vec<T, VEC>(base + (int64_t)(r + POOL_ROWG) * ldx, a1);
-      load_vec<T, VEC>(base + (int64_t)(r + 2 * POOL_ROWG) * ldx, a2);
-      load_vec<T, VEC>(base + (int64_t)(r + 3 * POOL_ROWG) * ldx, a3);
 #pragma unroll
       for (int v = 0; v < VEC; ++v) {
-        mn[v] = fminf(fminf(mn[v], a0[v]), fminf(a1[v], fminf(a2[v], a3[v])));
-        mx[v] = fmaxf(fmaxf(mx[v], a0[v]), fmaxf(a1[v], fmaxf(a2[v], a3[v])));
-        sm[v] += a0[v]; sm[v] += a1[v]; sm[v] += a2[v]; sm[v] += a3[v];
+        mn[v] = fminf(mn[v], fminf(a0[v], a1[v]));
+        mx[v] = fmaxf(mx[v], fmaxf(a0[v], a1[v]));
+        sm[v] += a0[v]; sm[v] += a1[v];
       }
     }
     for (; r < n; r += POOL_ROWG) {
