@@ -528,15 +528,17 @@ extern "C" int gn_csr_to_ell(const int32_t* rowptr, const int32_t* col, int64_t 
 extern "C" int gn_outer_accumulate_f32(const float* G, int64_t ldg, int cols, const float* X,
                                        int64_t ldx, int K, int64_t N, float* out, int64_t ldo,
                                        void* stream) {
-  GN_CHECK_ARG(N >= 0 && cols >= 1 && K >= 1 && K <= 32 && ldg >= cols && ldx >= K && ldo >= K,
-               "gn_outer_accumulate_f32: bad sizes (K must be <= 32)");
+  GN_CHECK_ARG(N >= 0 && cols >= 1 && K >= 1 && K <= 64 && ldg >= cols && ldx >= K && ldo >= K,
+               "gn_outer_accumulate_f32: bad sizes (K must be <= 64)");
   if (N == 0) return GN_OK;
   GN_CHECK_ARG(G && X && out, "gn_outer_accumulate_f32: null pointer");
   const unsigned grid = (unsigned)ceil_div(N, 128);
   cudaStream_t st = as_stream(stream);
   if (K <= 8) outer_accumulate_kernel<8><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
   else if (K <= 20) outer_accumulate_kernel<20><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
-  else outer_accumulate_kernel<32><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
+  else if (K <= 32) outer_accumulate_kernel<32><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
+  else if (K <= 40) outer_accumulate_kernel<40><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
+  else outer_accumulate_kernel<64><<<grid, 256, 0, st>>>(G, ldg, cols, X, ldx, K, N, out, ldo);
   GN_LAUNCH_CHECK();
   return GN_OK;
 }

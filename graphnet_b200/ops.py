@@ -456,7 +456,7 @@ def edge_grad_pq(dH: Tensor, H: Tensor, Kp: int, graph: Graph, dP: Tensor, dQ: T
 
 
 def outer_accumulate_f32(G: Tensor, X: Tensor, out: Tensor) -> Tensor:
-    """out[c, k] += sum_n G[n, c] X[n, k] (fp32, X at most 32 columns wide)."""
+    """out[c, k] += sum_n G[n, c] X[n, k] (fp32, X at most 64 columns wide)."""
     dev = _require_cuda(G, X, out)
     assert G.dtype == X.dtype == out.dtype == torch.float32
     assert G.stride(1) == 1 and X.stride(1) == 1 and out.stride(1) == 1

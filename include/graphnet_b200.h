@@ -304,7 +304,7 @@ int gn_edge_grad_pq(const void* dH, int64_t lddh, const void* H, int64_t ldh, in
                     const gn_graph* graph, int64_t N, void* dP, int64_t ldp, float* dQ,
                     int64_t ldq, float* dP32, int64_t ldp32, void* stream);
 
-/* out[c, k] += sum_n G[n, c] X[n, k], all fp32, K <= 32: weight gradient of the first EdgeConv
+/* out[c, k] += sum_n G[n, c] X[n, k], all fp32, K <= 64: weight gradient of the first EdgeConv
  * Linear (dynedge.py:193-199) with respect to the raw input features - its two halves are
  * subtracted (the Linear acts on [x_i, x_j - x_i]), so it is kept out of 16-bit arithmetic. */
 int gn_outer_accumulate_f32(const float* G, int64_t ldg, int cols, const float* X, int64_t ldx,

@@ -170,3 +170,31 @@ def test_standard_model_training_step(dev):
     with torch.no_grad():
         pred = model(data)[0]
     assert pred.shape == (48, 1) and not pred.requires_grad
+
+
+def test_training_step_c4_shapes(dev):
+    """Upgrade geometry, F = 14, k = 16 (17 slots per node), pools min/max/mean: the backward path
+    on the shapes of BASELINE config 4."""
+    import graphnet_b200 as g
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(6, 120.0, detector="upgrade", seed=33)
+    x = pb.x.to(dev)
+    batch = pb.batch.to(dev)
+    ei = g.knn_graph(x[:, :3].contiguous(), 16, batch, num_events=6)
+    data = g.Data(x=x, edge_index=ei, batch=batch, n_pulses=pb.n_pulses.to(dev))
+    torch.manual_seed(2)
+    model = g.DynEdge(14, nb_neighbours=16, global_pooling_schemes=["min", "max", "mean"],
+                      precision="bf16").to(dev)
+    head = torch.nn.Linear(128, 1).to(dev)
+    target = torch.rand(6, 1, device=dev) * 4
+    opt = torch.optim.Adam(list(model.parameters()) + list(head.parameters()), lr=1e-3, eps=1e-3)
+    losses = []
+    for _ in range(8):
+        opt.zero_grad(set_to_none=True)
+        d = head(model(data)) - target
+        loss = (d + torch.nn.functional.softplus(-2.0 * d) - 0.6931471805599453).mean()
+        loss.backward()
+        assert all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in model.parameters())
+        opt.step()
+        losses.append(float(loss.detach()))
+    assert losses[-1] < losses[0], losses
