@@ -198,3 +198,38 @@ def test_training_step_c4_shapes(dev):
         opt.step()
         losses.append(float(loss.detach()))
     assert losses[-1] < losses[0], losses
+
+
+@pytest.mark.parametrize("kwargs,F", [
+    (dict(global_pooling_schemes=["max"], readout_layer_sizes=[64, 32]), 4),
+    (dict(global_pooling_schemes=None), 7),
+    (dict(global_pooling_schemes=["mean", "sum"], dynedge_layer_sizes=[(64, 96), (80, 64)],
+          post_processing_layer_sizes=[72, 48], readout_layer_sizes=[40, 24]), 7),
+])
+def test_training_other_architectures(dev, kwargs, F):
+    """Architectures off the default: one pooling scheme, node-level output, other layer sizes."""
+    import graphnet_b200 as g
+    pb_x = torch.randn(300, F, generator=torch.Generator().manual_seed(1))
+    counts = torch.tensor([40, 25, 60, 35, 50, 90])
+    batch = torch.repeat_interleave(torch.arange(6), counts)
+    x = pb_x.to(dev)
+    b = batch.to(dev)
+    ei = g.knn_graph(x[:, :3].contiguous(), 8, b, num_events=6)
+    data = g.Data(x=x, edge_index=ei, batch=b, n_pulses=counts.to(torch.int32).to(dev))
+    torch.manual_seed(3)
+    model = g.DynEdge(F, precision="bf16", **kwargs).to(dev)
+    out = model(data)
+    rows = 300 if kwargs["global_pooling_schemes"] is None else 6
+    assert out.shape[0] == rows and out.requires_grad
+    head = torch.nn.Linear(out.shape[1], 1).to(dev)
+    target = torch.rand(rows, 1, device=dev)
+    opt = torch.optim.Adam(list(model.parameters()) + list(head.parameters()), lr=1e-3, eps=1e-3)
+    losses = []
+    for _ in range(8):
+        opt.zero_grad(set_to_none=True)
+        loss = (head(model(data)) - target).square().mean()
+        loss.backward()
+        assert all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in model.parameters())
+        opt.step()
+        losses.append(float(loss.detach()))
+    assert losses[-1] < losses[0], losses
