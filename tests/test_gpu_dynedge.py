@@ -3,38 +3,11 @@ import pytest
 import torch
 
 import oracle
-from conftest import load_golden, GOLDEN_CASES
+from conftest import load_golden, GOLDEN_CASES, rel_l2, assert_same_graph_up_to_near_ties
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 FP32_TOL = 1e-4  # BASELINE.json north_star: forward outputs within 1e-4 relative in fp32
-
-
-def rel_l2(a, b):
-    return float((a.double() - b.double()).norm() / b.double().norm().clamp(min=1e-30))
-
-
-def assert_same_graph_up_to_near_ties(ei, want, coords, what, coord_noise=2e-5, max_frac=0.02):
-    """The dynamic graphs are built from latents that carry fp32 rounding noise (a different
-    summation order than the CPU reference), so neighbours at (nearly) equal distance may swap.
-    Same targets and degrees are required; where a source differs, its squared distance to the
-    target - measured in the REFERENCE latents - must equal the reference neighbour's up to what
-    a relative coordinate noise `coord_noise` can move it: |delta d^2| <= 2 d eps + eps^2 with
-    eps = coord_noise * |c|max."""
-    assert ei.shape == want.shape, what
-    assert torch.equal(ei[1], want[1]), what
-    diff = (ei[0] != want[0]).nonzero().flatten()
-    if diff.numel() == 0:
-        return
-    assert diff.numel() <= max(2, int(max_frac * ei.shape[1])), f"{what}: {diff.numel()} edges differ"
-    c = coords.double()
-    tgt = want[1][diff]
-    d_mine = ((c[ei[0][diff]] - c[tgt]) ** 2).sum(1)
-    d_want = ((c[want[0][diff]] - c[tgt]) ** 2).sum(1)
-    eps = coord_noise * c.abs().max()
-    bound = 2 * torch.sqrt(torch.maximum(d_mine, d_want)) * eps * 3 ** 0.5 + 3 * eps ** 2
-    assert bool(((d_mine - d_want).abs() <= bound).all()), \
-        f"{what}: a differing neighbour is not a near-tie"
 
 
 def _model(g, precision="fp32"):

@@ -4,7 +4,7 @@ import torch
 import oracle
 from oracle import tasks as otasks
 from oracle.ops import knn_graph_padded
-from conftest import load_golden, random_events
+from conftest import load_golden, random_events, rel_l2, assert_same_graph_up_to_near_ties
 
 
 def _spec_and_params(g):
@@ -18,16 +18,52 @@ def _spec_and_params(g):
     return spec, sd
 
 
+def test_oracle_reproduces_golden_layers(golden):
+    """Layer by layer on the GOLDEN inputs and the GOLDEN graph of each layer (no near-tie chaos):
+    summation order inside the host's sgemm differs between CPUs, so values are compared to 1e-5
+    relative; the graph rebuilt from the golden latents is integer work and must be bit-exact."""
+    from oracle import ops as oops
+    from oracle.dynedge import _mlp, global_variables
+    g = golden
+    spec, sd = _spec_and_params(g)
+    gv = global_variables(g["x"], g["edge_index"], g["batch"], g["n_pulses"])
+    assert torch.allclose(gv, g["global_variables"], rtol=1e-6, atol=1e-7)
+    x = g["x"] if spec.add_global_variables_after_pooling else torch.cat([g["x"], gv[g["batch"]]], 1)
+    graph = g["edge_index"]
+    skip = [x]
+    for i, sizes in enumerate(spec.dynedge_layer_sizes):
+        nn_ = lambda t, i=i, n=len(sizes): _mlp(spec, sd, f"_conv_layers.{i}.nn", n, t,
+                                                spec.add_norm_layer)
+        out = oops.edge_conv(x, graph, nn_, aggr="add")
+        assert rel_l2(out, g[f"conv{i}"]) < 1e-5, f"conv{i}"
+        x = g[f"conv{i}"]
+        graph = oops.knn_graph(x[:, spec.features_subset], spec.nb_neighbours, g["batch"])
+        assert torch.equal(graph, g[f"graph{i + 1}"]), f"graph{i + 1}"
+        skip.append(x)
+    post = _mlp(spec, sd, "_post_processing", len(spec.post_processing_layer_sizes),
+                torch.cat(skip, 1), spec.add_norm_layer)
+    assert rel_l2(post, g["post"]) < 1e-5
+
+
 def test_oracle_reproduces_golden_forward(golden):
+    """Free-running forward.  The graphs of layers 2-4 are rebuilt from latents that carry this
+    host's sgemm rounding (~1e-6), so a neighbour may differ from the recorded one only where it is
+    a near-tie; outputs agree to 1e-5 when no neighbour flipped, to 2e-3 otherwise."""
     g = golden
     spec, sd = _spec_and_params(g)
     out, inter = oracle.dynedge_forward(spec, sd, g["x"], g["edge_index"], g["batch"],
                                         g["n_pulses"], return_intermediates=True)
-    assert torch.allclose(out, g["out"], rtol=1e-5, atol=1e-6)
     assert torch.allclose(inter["global_variables"], g["global_variables"], rtol=1e-6, atol=1e-7)
+    flips = 0
     for i in range(len(spec.dynedge_layer_sizes)):
-        assert torch.equal(inter["graphs"][i + 1], g[f"graph{i + 1}"])
-        assert torch.allclose(inter[f"conv{i}"], g[f"conv{i}"], rtol=1e-5, atol=1e-6)
+        tol = 1e-5 if flips == 0 else 2e-3
+        assert rel_l2(inter[f"conv{i}"], g[f"conv{i}"]) < tol, f"conv{i}"
+        if flips == 0:  # later graphs are compared in the reference latents only while those agree
+            assert_same_graph_up_to_near_ties(inter["graphs"][i + 1], g[f"graph{i + 1}"],
+                                              g[f"conv{i}"][:, :3], f"graph{i + 1}")
+        flips += int((inter["graphs"][i + 1] != g[f"graph{i + 1}"]).sum()) \
+            if inter["graphs"][i + 1].shape == g[f"graph{i + 1}"].shape else 1
+    assert rel_l2(out, g["out"]) < (1e-5 if flips == 0 else 2e-3)
 
 
 def test_oracle_initial_graph_matches_golden(golden):
@@ -93,7 +129,7 @@ def test_heads_and_losses_match_golden():
     for name in ("oscnext5", "upgrade5", "prometheus50"):
         g = load_golden(name)
         p = otasks.task_forward(g["head_kind"], g["head_weight"], g["head_bias"], g["out"])
-        assert torch.allclose(p, g["head_out"], rtol=1e-6, atol=1e-7)
+        assert torch.allclose(p, g["head_out"], rtol=1e-5, atol=1e-6)  # host sgemm order varies
         if g["head_kind"] == "EnergyReconstruction":
             loss = otasks.logcosh_loss(g["head_out"], g["target"])
         else:
@@ -120,4 +156,5 @@ def test_jinst_oracle_reproduces_reference_golden():
     x, b, n, ei = (torch.from_numpy(z[k]) for k in ("x", "batch", "n_pulses", "edge_index"))
     sd = init_jinst_state_dict(x.shape[1], 4, seed=int(z["seed"]))
     y = jinst_forward(sd, x, ei, b, n)
-    assert torch.equal(y, torch.from_numpy(z["out"]))
+    # bit-equal on the host that recorded it; another CPU's sgemm sums in a different order
+    assert rel_l2(y, torch.from_numpy(z["out"])) < 1e-5
