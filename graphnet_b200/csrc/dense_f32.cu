@@ -114,48 +114,61 @@ __global__ void __launch_bounds__(LIN_THREADS) linear_f32_kernel(
 }
 
 // Small-K variant (K <= 32, 16-bit output): the first EdgeConv's node GEMM has K = 2F+5 = 19
-// and is store bound (N*Kp*2 bytes out).  One thread owns one input row (K values in
-// registers) and walks the output columns 8 at a time; W^T (K x N) sits in shared memory and is
-// read with warp-uniform addresses (broadcast, one wavefront per load); one 16-byte store per
-// 8 outputs.
+// and is store bound (N*Kp*2 bytes out).  A thread owns two adjacent output columns - its two
+// weight rows (2K values) and biases stay in registers - and a CTA walks SK_ROWS input rows that
+// are staged in shared memory and read with warp-uniform addresses (16-byte broadcasts).  A
+// warp therefore stores 128 contiguous bytes of one output row per instruction; the previous
+// shape of this kernel (a thread per row) wrote 16 bytes per lane 2*N bytes apart.
+// The k order of the sum (bias first, k ascending) is that of the generic kernel above.
 constexpr int SK_MAXK = 32;
+constexpr int SK_ROWS = 64;
 template <typename OutT, int KMAX>
-__global__ void __launch_bounds__(128) linear_smallk_kernel(
+__global__ void __launch_bounds__(1024) linear_smallk_kernel(
     const float* __restrict__ A, int64_t lda, const float* __restrict__ W,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K) {
-  extern __shared__ __align__(16) float s_wt[];  // [K][N] then bias [N]
-  float* s_b = s_wt + (size_t)K * N;
-  for (int i = threadIdx.x; i < N * K; i += blockDim.x) {
-    const int n = i / K, k = i - n * K;
-    s_wt[k * N + n] = W[i];
+  static_assert(KMAX % 4 == 0, "rows are read as float4");
+  __shared__ __align__(16) float s_a[SK_ROWS][KMAX];
+  const int n0 = threadIdx.x * 2;
+  const bool col_ok = n0 < N;  // N is even
+  float w0[KMAX], w1[KMAX];
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) {
+    w0[k] = (col_ok && k < K) ? __ldg(W + (int64_t)n0 * K + k) : 0.f;
+    w1[k] = (col_ok && k < K) ? __ldg(W + (int64_t)(n0 + 1) * K + k) : 0.f;
   }
-  for (int i = threadIdx.x; i < N; i += blockDim.x) s_b[i] = bias ? bias[i] : 0.f;
+  const float b0 = (col_ok && bias) ? bias[n0] : 0.f;
+  const float b1 = (col_ok && bias) ? bias[n0 + 1] : 0.f;
+  const int64_t m0 = (int64_t)blockIdx.x * SK_ROWS;
+  const int rows = (int)(M - m0 < SK_ROWS ? M - m0 : SK_ROWS);
+  for (int i = threadIdx.x; i < SK_ROWS * KMAX; i += blockDim.x) {
+    const int r = i / KMAX, k = i - r * KMAX;
+    s_a[r][k] = (r < rows && k < K) ? __ldg(A + (m0 + r) * lda + k) : 0.f;
+  }
   __syncthreads();
-  const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= M) return;
-  float a[KMAX];
+  if (!col_ok) return;
+  for (int r = 0; r < rows; r += 2) {  // two rows per step: four independent FMA chains
+    float c00 = b0, c01 = b1, c10 = b0, c11 = b1;
 #pragma unroll
-  for (int k = 0; k < KMAX; ++k) a[k] = k < K ? __ldg(A + m * lda + k) : 0.f;
-  OutT* crow = C + m * ldc;
-  for (int n0 = 0; n0 < N; n0 += 8) {
-    float acc[8];
+    for (int k4 = 0; k4 < KMAX; k4 += 4) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&s_a[r][k4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&s_a[r + 1][k4]);
+      const float x0[4] = {a0.x, a0.y, a0.z, a0.w};
+      const float x1[4] = {a1.x, a1.y, a1.z, a1.w};
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = s_b[n0 + j];
-#pragma unroll
-    for (int k = 0; k < KMAX; ++k) {
-      if (k < K) {
-        const float4 w0 = *reinterpret_cast<const float4*>(&s_wt[k * N + n0]);
-        const float4 w1 = *reinterpret_cast<const float4*>(&s_wt[k * N + n0 + 4]);
-        acc[0] = fmaf(a[k], w0.x, acc[0]); acc[1] = fmaf(a[k], w0.y, acc[1]);
-        acc[2] = fmaf(a[k], w0.z, acc[2]); acc[3] = fmaf(a[k], w0.w, acc[3]);
-        acc[4] = fmaf(a[k], w1.x, acc[4]); acc[5] = fmaf(a[k], w1.y, acc[5]);
-        acc[6] = fmaf(a[k], w1.z, acc[6]); acc[7] = fmaf(a[k], w1.w, acc[7]);
+      for (int u = 0; u < 4; ++u) {
+        c00 = fmaf(x0[u], w0[k4 + u], c00);
+        c01 = fmaf(x0[u], w1[k4 + u], c01);
+        c10 = fmaf(x1[u], w0[k4 + u], c10);
+        c11 = fmaf(x1[u], w1[k4 + u], c11);
       }
     }
-    OutT o[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = cvt_out<OutT>(acc[j]);
-    *reinterpret_cast<uint4*>(crow + n0) = *reinterpret_cast<const uint4*>(o);
+    OutT o0[2] = {cvt_out<OutT>(c00), cvt_out<OutT>(c01)};
+    *reinterpret_cast<uint32_t*>(C + (m0 + r) * ldc + n0) = *reinterpret_cast<const uint32_t*>(o0);
+    if (r + 1 < rows) {
+      OutT o1[2] = {cvt_out<OutT>(c10), cvt_out<OutT>(c11)};
+      *reinterpret_cast<uint32_t*>(C + (m0 + r + 1) * ldc + n0) =
+          *reinterpret_cast<const uint32_t*>(o1);
+    }
   }
 }
 
@@ -396,16 +409,14 @@ static int linear_f32_t(const float* A, int64_t lda, const float* W, const float
 int linear_f32(const float* A, int64_t lda, const float* W, const float* bias, void* C,
                int64_t ldc, int c_dtype, int64_t M, int N, int K, int act, cudaStream_t st) {
   if (M == 0) return GN_OK;
-  if (K <= SK_MAXK && N % 8 == 0 && ldc % 8 == 0 && act == GN_ACT_NONE && c_dtype != GN_F32 &&
-      (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (size_t)(K + 1) * N * sizeof(float) <= 96 * 1024 &&
-      M * (int64_t)N >= (1 << 16)) {
-    const size_t smem = (size_t)(K + 1) * N * sizeof(float);
-    const unsigned grid = (unsigned)ceil_div(M, 128);
+  if (K <= SK_MAXK && N % 2 == 0 && N <= 2048 && ldc % 2 == 0 && act == GN_ACT_NONE &&
+      c_dtype != GN_F32 && (reinterpret_cast<uintptr_t>(C) & 3) == 0 && M * (int64_t)N >= (1 << 16)) {
+    const unsigned threads = (unsigned)((N / 2 + 31) / 32 * 32);
+    const unsigned grid = (unsigned)ceil_div(M, SK_ROWS);
 #define GN_SK_CASE(T_, KM_)                                                                      \
   {                                                                                              \
-    auto kern = linear_smallk_kernel<T_, KM_>;                                                   \
-    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    kern<<<grid, 128, smem, st>>>(A, lda, W, bias, reinterpret_cast<T_*>(C), ldc, M, N, K);      \
+    linear_smallk_kernel<T_, KM_><<<grid, threads, 0, st>>>(                                     \
+        A, lda, W, bias, reinterpret_cast<T_*>(C), ldc, M, N, K);                                \
   }
     if (c_dtype == GN_F16) {
       if (K <= 20) GN_SK_CASE(__half, 20) else GN_SK_CASE(__half, 32)

@@ -37,7 +37,11 @@ __global__ void batch_to_ptr_kernel(const int64_t* __restrict__ batch, int64_t N
 // ------------------------------------------------------------------------ kNN
 constexpr int KNN_MAX_DIMS = 16;
 constexpr int KNN_THREADS = 128;
-constexpr int KNN_SMEM_FLOATS = 3072;  // 12 KB of staged coordinates per CTA: 1024 events fit ONE wave (10 CTAs/SM by registers; 32 KB gave 6 and a 15 % second wave)
+constexpr int KNN_SMEM_FLOATS = 3072;  // 12 KB of staged coordinates per CTA
+constexpr int KNN_QDEPTH = 12;         // pending candidates per thread between flushes (queued scan)
+constexpr int KNN_QUEUED_MIN_N = 160;  // events at least this large take the queued scan
+constexpr int KNN_MAX_SPLIT = 16;      // CTAs per event (query blocks are dealt round robin)
+constexpr uint32_t KNN_EMPTY = 0xffffffffu;
 
 struct KnnParams {
   const float* x;
@@ -53,40 +57,84 @@ struct KnnParams {
   int chunk;  // candidates staged per pass (multiple of 32)
 };
 
-// Sorted list of the CAP best (distance, index) pairs seen so far.
+// Sorted list of the CAP best (distance, index) pairs seen so far.  Distances are kept as the
+// bit pattern of the (non-negative) float: unsigned order == float order, an empty slot
+// (0xffffffff) ranks after everything, a NaN distance after every real one.
 template <int CAP>
 struct TopList {
-  float d[CAP];
+  uint32_t d[CAP];
   int idx[CAP];
-  int m;
   __device__ __forceinline__ void init() {
 #pragma unroll
-    for (int s = 0; s < CAP; ++s) { d[s] = __int_as_float(0x7f800000); idx[s] = -1; }
-    m = 0;
+    for (int s = 0; s < CAP; ++s) { d[s] = KNN_EMPTY; idx[s] = -1; }
   }
-  // Candidates arrive in ascending index order; an equal distance never displaces
-  // an earlier entry, so ties rank by index.
-  __device__ __forceinline__ void push(float cd, int ci) {
-    if (m == CAP && !(cd < d[CAP - 1])) return;
-    bool ins = false;
+  __device__ __forceinline__ uint32_t worst() const { return d[CAP - 1]; }
+  // Candidates arrive in ascending index order and an equal distance never displaces an
+  // earlier entry, so ties rank by index.  Every slot is updated independently of the others
+  // (no carried value): slot s keeps its entry if that entry is <= the candidate, otherwise it
+  // takes the candidate (if its left neighbour stays) or the left neighbour's entry.  A
+  // candidate that is not better than the worst entry changes nothing.
+  __device__ __forceinline__ void push(uint32_t cd, int ci) {
+    bool keep[CAP];
 #pragma unroll
-    for (int s = 0; s < CAP; ++s) {
-      bool sw = ins | (s >= m) | (cd < d[s]);
-      float td = d[s];
-      int ti = idx[s];
-      d[s] = sw ? cd : td;
-      idx[s] = sw ? ci : ti;
-      cd = sw ? td : cd;
-      ci = sw ? ti : ci;
-      ins = sw;
+    for (int s = 0; s < CAP; ++s) keep[s] = d[s] <= cd;
+#pragma unroll
+    for (int s = CAP - 1; s > 0; --s) {
+      const uint32_t nd = keep[s - 1] ? cd : d[s - 1];
+      const int ni = keep[s - 1] ? ci : idx[s - 1];
+      d[s] = keep[s] ? d[s] : nd;
+      idx[s] = keep[s] ? idx[s] : ni;
     }
-    m = min(m + 1, CAP);
+    d[0] = keep[0] ? d[0] : cd;
+    idx[0] = keep[0] ? idx[0] : ci;
   }
 };
 
+template <int DIMS>
+__device__ __forceinline__ uint32_t knn_dist_bits(const float* qc, const float* s_coord, int chunk,
+                                                  int c, int dims) {
+  float d = 0.f;
+#pragma unroll
+  for (int t = 0; t < (DIMS > 0 ? DIMS : KNN_MAX_DIMS); ++t) {
+    if (t < dims) {
+      const float diff = __fsub_rn(qc[t], s_coord[t * chunk + c]);
+      d = __fadd_rn(d, __fmul_rn(diff, diff));
+    }
+  }
+  return __float_as_uint(d);
+}
+
+template <int CAP>
+__device__ __forceinline__ void knn_write_row(const KnnParams& p, const TopList<CAP>& top, int lo,
+                                              int q) {
+  int32_t* row = p.nbr + (int64_t)(lo + q) * p.stride;
+  int cnt = 0;
+#pragma unroll
+  for (int s = 0; s < CAP; ++s) {
+    if (s < p.kk) {
+      const int j = top.idx[s];
+      if (j >= 0 && (p.loop || j != q)) row[cnt++] = lo + j;
+    }
+  }
+  p.deg[lo + q] = cnt;
+  for (int r = cnt; r < p.stride; ++r) row[r] = -1;
+}
+
+// grid = (events, split).  Three shapes of the same scan, chosen per event (uniform per CTA):
+//  * n <= 64: two threads per query, each scans half of the candidates; the upper half's list
+//    is then pushed, in order, into the lower half's (all its indices are larger, so the
+//    (distance, index) order is the same as one scan would give);
+//  * n < KNN_QUEUED_MIN_N: one thread per query, a candidate better than the current worst is
+//    inserted at once;
+//  * larger events: a passing candidate is appended to a per-thread queue in shared memory and
+//    the warp inserts together when a queue fills - by then most lanes have work, where an
+//    immediate insertion would run the whole warp through the insertion code for the one or
+//    two lanes that need it.  The threshold is the worst entry as of the last flush, so a few
+//    candidates are queued that no longer qualify; push() ignores them.
+//    The query blocks of a large event are dealt to the `split` CTAs of its grid row.
 template <int CAP, int DIMS>  // DIMS == 0: runtime p.dims
 __global__ void __launch_bounds__(KNN_THREADS) knn_kernel(KnnParams p) {
-  extern __shared__ float s_coord[];  // [dims][chunk]
+  extern __shared__ __align__(16) float s_coord[];  // [dims][chunk], then the queues
   const int dims = DIMS > 0 ? DIMS : p.dims;
   const int e = blockIdx.x;
   const int lo = p.ptr[e];
@@ -94,55 +142,114 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_kernel(KnnParams p) {
   if (n <= 0) return;
   const int chunk = p.chunk;
   const int tid = threadIdx.x;
+  constexpr int QD = DIMS > 0 ? DIMS : KNN_MAX_DIMS;
 
-  for (int qbase = 0; qbase < n; qbase += KNN_THREADS) {
+  if (n <= KNN_THREADS / 2) {
+    if (blockIdx.y != 0) return;
+    for (int t = 0; t < dims; ++t)
+      for (int c = tid; c < n; c += KNN_THREADS)
+        s_coord[t * chunk + c] = p.x[(int64_t)(lo + c) * p.ldx + p.cols[t]];
+    __syncthreads();
+    const int q = tid >> 1, h = tid & 1;
+    const bool active = q < n;
+    float qc[QD];
+#pragma unroll
+    for (int t = 0; t < QD; ++t) qc[t] = (active && t < dims) ? s_coord[t * chunk + q] : 0.f;
+    TopList<CAP> top;
+    top.init();
+    const int mid = (n + 1) >> 1;
+    const int c0 = h ? mid : 0, c1 = active ? (h ? n : mid) : 0;
+    for (int c = c0; c < c1; ++c) {
+      const uint32_t cd = knn_dist_bits<DIMS>(qc, s_coord, chunk, c, dims);
+      if (cd < top.worst()) top.push(cd, c);
+    }
+#pragma unroll
+    for (int s = 0; s < CAP; ++s) {
+      const uint32_t od = __shfl_down_sync(0xffffffffu, top.d[s], 1);
+      const int oi = __shfl_down_sync(0xffffffffu, top.idx[s], 1);
+      if (h == 0) top.push(od, oi);
+    }
+    if (active && h == 0) knn_write_row<CAP>(p, top, lo, q);
+    return;
+  }
+
+  uint2* const queue = reinterpret_cast<uint2*>(s_coord + dims * chunk);  // [KNN_QDEPTH][threads]
+  const bool queued = n >= KNN_QUEUED_MIN_N;
+  const int qfirst = blockIdx.y * KNN_THREADS;
+  for (int qbase = qfirst; qbase < n; qbase += gridDim.y * KNN_THREADS) {
     const int q = qbase + tid;
     const bool active = q < n;
-    float qc[DIMS > 0 ? DIMS : KNN_MAX_DIMS];
+    float qc[QD];
 #pragma unroll
-    for (int t = 0; t < (DIMS > 0 ? DIMS : KNN_MAX_DIMS); ++t)
+    for (int t = 0; t < QD; ++t)
       qc[t] = (active && t < dims) ? p.x[(int64_t)(lo + q) * p.ldx + p.cols[t]] : 0.f;
     TopList<CAP> top;
     top.init();
+    int pending = 0;
+    uint32_t thr = active ? KNN_EMPTY : 0u;  // an idle lane queues nothing
 
     for (int cbase = 0; cbase < n; cbase += chunk) {
       const int cn = min(chunk, n - cbase);
-      if (n > chunk || qbase == 0) {
+      if (n > chunk || qbase == qfirst) {
         __syncthreads();
         for (int t = 0; t < dims; ++t)
           for (int c = tid; c < cn; c += KNN_THREADS)
             s_coord[t * chunk + c] = p.x[(int64_t)(lo + cbase + c) * p.ldx + p.cols[t]];
         __syncthreads();
       }
-      if (active) {
-        for (int c = 0; c < cn; ++c) {
-          float d = 0.f;
+      if (!queued) {
+        if (active) {
+          for (int c = 0; c < cn; ++c) {
+            const uint32_t cd = knn_dist_bits<DIMS>(qc, s_coord, chunk, c, dims);
+            if (cd < top.worst()) top.push(cd, cbase + c);
+          }
+        }
+        continue;
+      }
+      for (int c4 = 0; c4 < cn; c4 += 4) {
+        // four candidates per step (the staged columns are 16-byte aligned at c4)
+        float dd[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int t = 0; t < (DIMS > 0 ? DIMS : KNN_MAX_DIMS); ++t) {
-            if (t < dims) {
-              float diff = __fsub_rn(qc[t], s_coord[t * chunk + c]);
-              d = __fadd_rn(d, __fmul_rn(diff, diff));
+        for (int t = 0; t < QD; ++t) {
+          if (t < dims) {
+            const float4 cc = *reinterpret_cast<const float4*>(s_coord + t * chunk + c4);
+            const float v[4] = {cc.x, cc.y, cc.z, cc.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const float diff = __fsub_rn(qc[t], v[u]);
+              dd[u] = __fadd_rn(dd[u], __fmul_rn(diff, diff));
             }
           }
-          top.push(d, cbase + c);
         }
-      }
-    }
-
-    if (active) {
-      const int keep = min(top.m, p.kk);
-      int32_t* row = p.nbr + (int64_t)(lo + q) * p.stride;
-      int cnt = 0;
 #pragma unroll
-      for (int s = 0; s < CAP; ++s) {
-        if (s < keep) {
-          int j = top.idx[s];
-          if (p.loop || j != q) row[cnt++] = lo + j;
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t cd = __float_as_uint(dd[u]);
+          if (c4 + u < cn && cd < thr) {
+            queue[pending * KNN_THREADS + tid] = make_uint2(cd, (uint32_t)(cbase + c4 + u));
+            ++pending;
+          }
+        }
+        if (__any_sync(0xffffffffu, pending > KNN_QDEPTH - 4)) {
+          for (int r = 0; __any_sync(0xffffffffu, r < pending); ++r) {
+            if (r < pending) {
+              const uint2 v = queue[r * KNN_THREADS + tid];
+              top.push(v.x, (int)v.y);
+            }
+          }
+          pending = 0;
+          thr = active ? top.worst() : 0u;
         }
       }
-      p.deg[lo + q] = cnt;
-      for (int r = cnt; r < p.stride; ++r) row[r] = -1;
     }
+    if (queued) {
+      for (int r = 0; __any_sync(0xffffffffu, r < pending); ++r) {
+        if (r < pending) {
+          const uint2 v = queue[r * KNN_THREADS + tid];
+          top.push(v.x, (int)v.y);
+        }
+      }
+    }
+    if (active) knn_write_row<CAP>(p, top, lo, q);
   }
 }
 
@@ -206,10 +313,17 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_kernel_bigk(KnnParams p) {
   }
 }
 
+static size_t knn_smem_bytes(const KnnParams& p) {
+  return (size_t)p.dims * p.chunk * sizeof(float) + (size_t)KNN_QDEPTH * KNN_THREADS * sizeof(uint2);
+}
+
 template <int CAP>
-static int launch_knn(const KnnParams& p, int64_t B, cudaStream_t st) {
-  size_t smem = (size_t)p.dims * p.chunk * sizeof(float);
-  dim3 grid((unsigned)B), block(KNN_THREADS);
+static int launch_knn(const KnnParams& p, int64_t N, int64_t B, cudaStream_t st) {
+  const size_t smem = knn_smem_bytes(p);
+  // CTAs per event from the mean event size (the host knows N and B, not the largest event)
+  int64_t split = ceil_div(ceil_div(N, B), (int64_t)KNN_THREADS);
+  split = split < 1 ? 1 : (split > KNN_MAX_SPLIT ? KNN_MAX_SPLIT : split);
+  dim3 grid((unsigned)B, (unsigned)split), block(KNN_THREADS);
   switch (p.dims) {
     case 1: knn_kernel<CAP, 1><<<grid, block, smem, st>>>(p); break;
     case 2: knn_kernel<CAP, 2><<<grid, block, smem, st>>>(p); break;
@@ -389,9 +503,9 @@ extern "C" int gn_knn_graph(const float* x, int64_t ldx, const int32_t* cols, in
     GN_CHECK_ARG(cols[t] >= 0 && cols[t] < ldx, "gn_knn_graph: column %d out of range", cols[t]);
   p.chunk = (KNN_SMEM_FLOATS / dims) & ~31;
   cudaStream_t st = as_stream(stream);
-  if (kk <= 9) launch_knn<9>(p, B, st);
-  else if (kk <= 17) launch_knn<17>(p, B, st);
-  else if (kk <= 33) launch_knn<33>(p, B, st);
+  if (kk <= 9) launch_knn<9>(p, N, B, st);
+  else if (kk <= 17) launch_knn<17>(p, N, B, st);
+  else if (kk <= 33) launch_knn<33>(p, N, B, st);
   else {
     size_t smem = (size_t)dims * p.chunk * sizeof(float);
     knn_kernel_bigk<0><<<(unsigned)B, KNN_THREADS, smem, st>>>(p);

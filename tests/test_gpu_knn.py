@@ -75,6 +75,28 @@ def test_large_events_cross_chunk():
     assert torch.equal(gpu_knn(x, 8, batch), oracle.knn_graph(x, 8, batch))
 
 
+@pytest.mark.parametrize("k", [8, 16])
+@pytest.mark.parametrize("counts", [
+    [500, 480, 700, 130, 70, 20],          # mean > 128: several CTAs per event, queued scan
+    [65, 100, 159, 160, 161, 64, 63, 2],   # around the switch points of the three scan shapes
+    [900] + [30] * 40,                     # one large event in a batch of small ones (one CTA)
+    [2048, 1500],                          # several staging chunks and several CTAs per event
+])
+def test_scan_shapes_with_ties(counts, k):
+    """Two threads per query (n <= 64), immediate insertion, and the queued scan of large
+    events (csrc/knn.cu) must all give the (distance, index) order; lattice coordinates and
+    copied rows put many exact ties across the k-th place."""
+    g = torch.Generator().manual_seed(sum(counts) + k)
+    counts_t = torch.tensor(counts)
+    n_all = int(counts_t.sum())
+    x = torch.round(torch.randn(n_all, 3, generator=g) * 3) / 2       # coarse lattice: ties
+    x[n_all // 3: n_all // 3 + 40] = x[n_all // 3]                     # 40 coincident pulses
+    fine = torch.rand(n_all, generator=g) < 0.5
+    x[fine] += torch.randn(int(fine.sum()), 3, generator=g) * 1e-3
+    batch = torch.repeat_interleave(torch.arange(len(counts)), counts_t)
+    assert torch.equal(gpu_knn(x.contiguous(), k, batch), oracle.knn_graph(x, k, batch))
+
+
 def test_strided_latent_columns_via_ell():
     """The in-model call: columns of a wide row-major matrix, ELL output, no COO."""
     import graphnet_b200.ops as ops
