@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(LIN_THREADS) linear_f32_kernel(
 constexpr int SK_MAXK = 32;
 constexpr int SK_ROWS = 64;
 template <typename OutT, int KMAX>
-__global__ void __launch_bounds__(1024) linear_smallk_kernel(
+__global__ void __launch_bounds__(512) linear_smallk_kernel(
     const float* __restrict__ A, int64_t lda, const float* __restrict__ W,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K) {
   static_assert(KMAX % 4 == 0, "rows are read as float4");
@@ -409,7 +409,7 @@ static int linear_f32_t(const float* A, int64_t lda, const float* W, const float
 int linear_f32(const float* A, int64_t lda, const float* W, const float* bias, void* C,
                int64_t ldc, int c_dtype, int64_t M, int N, int K, int act, cudaStream_t st) {
   if (M == 0) return GN_OK;
-  if (K <= SK_MAXK && N % 2 == 0 && N <= 2048 && ldc % 2 == 0 && act == GN_ACT_NONE &&
+  if (K <= SK_MAXK && N % 2 == 0 && N <= 1024 && ldc % 2 == 0 && act == GN_ACT_NONE &&
       c_dtype != GN_F32 && (reinterpret_cast<uintptr_t>(C) & 3) == 0 && M * (int64_t)N >= (1 << 16)) {
     const unsigned threads = (unsigned)((N / 2 + 31) / 32 * 32);
     const unsigned grid = (unsigned)ceil_div(M, SK_ROWS);

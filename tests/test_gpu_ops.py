@@ -97,6 +97,27 @@ def test_linear_f32(M, N, K, act):
     assert torch.allclose(got.double(), want, rtol=1e-4, atol=1e-5)
 
 
+@pytest.mark.parametrize("M,N,K", [(300, 320, 19), (1001, 704, 19), (2049, 64, 7), (4096, 34, 32),
+                                   (999, 320, 33), (515, 1024, 20)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_linear_f32_16bit_output_small_k(M, N, K, dtype):
+    """First EdgeConv node GEMM: fp32 inputs, K = 2F+5, [P | Q] written as 16-bit rows (a
+    column slice of a wider buffer); the small-K kernel of csrc/dense_f32.cu and, where it does
+    not apply (K > 32), the generic one."""
+    import graphnet_b200.ops as ops
+    g = torch.Generator().manual_seed(M + N + K)
+    A = torch.randn(M, K + 3, generator=g)[:, :K]          # strided input rows
+    W = torch.randn(N, K, generator=g) / K ** 0.5
+    b = torch.randn(N, generator=g)
+    wide = torch.full((M, N + 16), 7.0, dtype=dtype, device=DEV)
+    out = wide[:, 8:8 + N]
+    ops.linear_f32(A.to(DEV), W.to(DEV), b.to(DEV), act="none", out=out)
+    want = torch.nn.functional.linear(A.double(), W.double(), b.double())
+    tol = 2e-3 if dtype == torch.float16 else 1.6e-2
+    assert torch.allclose(out.cpu().double(), want, rtol=tol, atol=tol)
+    assert bool((wide[:, :8] == 7).all()) and bool((wide[:, 8 + N:] == 7).all())
+
+
 def _mlp(W1, b1, W2, b2, act):
     f = {"relu": torch.relu, "gelu": torch.nn.functional.gelu}[act]
 
