@@ -13,6 +13,8 @@
 
 #include <cuda_fp16.h>
 
+#include <cstdlib>
+
 namespace gn {
 
 template <typename T> __device__ __forceinline__ float to_f32(T v);
@@ -125,14 +127,59 @@ __global__ void __launch_bounds__(256) convert_scale_kernel(const float* __restr
 // ------------------------------------------------------------------ edge slots: H and H^T
 // Row e = i * KP + t of the slot table (ELL, stride KP): H[e, :] = ReLU(P_i + Q_j) for a filled
 // slot (j = nbr[e] >= 0), 0 for an empty one; bf16.  A CTA takes 32 slot rows: the row-major copy
-// is written directly, the transposed copy HT[k, e] through a shared-memory tile.
+// is written directly, the transposed copy HT[k, e] through a shared-memory tile.  Everything
+// moves in 16-byte pieces of eight elements per lane (these kernels are bound by instruction
+// issue, not by bytes, when they touch memory 4 bytes at a time).
+//
+// Shared tile [EB_ROWS][W] of 16-bit elements, W a multiple of 32: the 16-byte piece p of row r
+// is stored at piece p ^ ((r >> 3) & 3), so that the transposing read below - four lanes on rows
+// r, r+8, r+16, r+24 of the same column - touches four different bank groups.
+// (128-row tiles, i.e. 256-byte runs per transposed row, were measured: 1.5-2x SLOWER - two
+// CTAs of 98 KB per SM do not keep enough loads in flight.)
 constexpr int EB_ROWS = 32;
+__host__ __device__ __forceinline__ int tile_width(int cols) { return (cols + 31) & ~31; }
+__device__ __forceinline__ uint4* tile_piece(uint16_t* tile, int W, int r, int p) {
+  return reinterpret_cast<uint4*>(tile + r * W) + (p ^ ((r >> 3) & 3));
+}
+__device__ __forceinline__ uint16_t tile_at(const uint16_t* tile, int W, int r, int k) {
+  return tile[r * W + ((((k >> 3) ^ ((r >> 3) & 3)) << 3) | (k & 7))];
+}
+// dstT[k, e0 + r] = tile[r, k] for k < cols, r < rvalid: a thread gathers eight rows of one
+// column and stores them as one 16-byte piece of the transposed row.
+__device__ __forceinline__ void tile_store_transposed(const uint16_t* tile, int W, int cols,
+                                                      int rvalid, uint16_t* dstT, int64_t ldt,
+                                                      int64_t e0) {
+  constexpr int G = EB_ROWS / 8;  // 16-byte pieces per transposed row and CTA
+  for (int idx = threadIdx.x; idx < cols * G; idx += blockDim.x) {
+    const int k = idx / G, r8 = (idx % G) * 8;
+    uint16_t v[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) v[t] = tile_at(tile, W, r8 + t, k);
+    uint16_t* dst = dstT + (int64_t)k * ldt + e0 + r8;
+    if (r8 + 8 <= rvalid && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
+    } else {
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        if (r8 + t < rvalid) dst[t] = v[t];
+    }
+  }
+}
+
+__device__ __forceinline__ uint4 pack8_bf16(const float (&f)[8]) {
+  __nv_bfloat162 o[4];
+#pragma unroll
+  for (int x = 0; x < 4; ++x) o[x] = __floats2bfloat162_rn(f[2 * x], f[2 * x + 1]);
+  return *reinterpret_cast<const uint4*>(o);
+}
+
 __global__ void __launch_bounds__(256) edge_build_h_kernel(
     const __half* __restrict__ P, int64_t ldp, const __half* __restrict__ Q, int64_t ldq, int Kp,
     const int32_t* __restrict__ nbr, int KP, int64_t E, __nv_bfloat16* __restrict__ H,
     int64_t ldh, __nv_bfloat16* __restrict__ HT, int64_t ldht) {
-  extern __shared__ __nv_bfloat16 tile[];  // [EB_ROWS][Kp + 2]
-  const int pitch = Kp + 2;
+  extern __shared__ __align__(16) uint16_t tile[];  // [EB_ROWS][W]
+  const int W = tile_width(Kp);
+  const int pieces = Kp >> 3;
   const int64_t e0 = (int64_t)blockIdx.x * EB_ROWS;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int r = warp; r < EB_ROWS; r += 8) {
@@ -143,83 +190,86 @@ __global__ void __launch_bounds__(256) edge_build_h_kernel(
       j = nbr[e];
       i = e / KP;
     }
-    for (int k = lane * 2; k < Kp; k += 64) {
-      float2 h = make_float2(0.f, 0.f);
+    for (int pc = lane; pc < pieces; pc += 32) {
+      float h[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       if (j >= 0) {
-        const float2 p = __half22float2(*reinterpret_cast<const __half2*>(P + i * ldp + k));
-        const float2 q = __half22float2(*reinterpret_cast<const __half2*>(Q + (int64_t)j * ldq + k));
-        h.x = fmaxf(p.x + q.x, 0.f);
-        h.y = fmaxf(p.y + q.y, 0.f);
+        const uint4 pv = __ldg(reinterpret_cast<const uint4*>(P + i * ldp) + pc);
+        const uint4 qv = __ldg(reinterpret_cast<const uint4*>(Q + (int64_t)j * ldq) + pc);
+        const __half2* p2 = reinterpret_cast<const __half2*>(&pv);
+        const __half2* q2 = reinterpret_cast<const __half2*>(&qv);
+#pragma unroll
+        for (int x = 0; x < 4; ++x) {
+          const float2 pf = __half22float2(p2[x]), qf = __half22float2(q2[x]);
+          h[2 * x] = fmaxf(pf.x + qf.x, 0.f);
+          h[2 * x + 1] = fmaxf(pf.y + qf.y, 0.f);
+        }
       }
-      const __nv_bfloat162 hb = __floats2bfloat162_rn(h.x, h.y);
-      *reinterpret_cast<__nv_bfloat162*>(tile + r * pitch + k) = hb;
-      if (e < E) *reinterpret_cast<__nv_bfloat162*>(H + e * ldh + k) = hb;
+      const uint4 hb = pack8_bf16(h);
+      *tile_piece(tile, W, r, pc) = hb;
+      if (H != nullptr && e < E) *(reinterpret_cast<uint4*>(H + e * ldh) + pc) = hb;
     }
   }
   if (HT == nullptr) return;
   __syncthreads();
-  // transposed copy: thread = (k, row-quad): 32 consecutive e of one k are 64 contiguous bytes
   const int rvalid = (int)(E - e0 < EB_ROWS ? E - e0 : EB_ROWS);
-  for (int idx = threadIdx.x; idx < Kp * 4; idx += 256) {
-    const int k = idx >> 2, r8 = (idx & 3) * 8;
-    __nv_bfloat16 v[8];
-#pragma unroll
-    for (int t = 0; t < 8; ++t) v[t] = tile[(r8 + t) * pitch + k];
-    __nv_bfloat16* dst = HT + (int64_t)k * ldht + e0 + r8;
-    if (r8 + 8 <= rvalid && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<uint4*>(v);
-    } else {
-#pragma unroll
-      for (int t = 0; t < 8; ++t)
-        if (r8 + t < rvalid) dst[t] = v[t];
-    }
-  }
+  tile_store_transposed(tile, W, Kp, rvalid, reinterpret_cast<uint16_t*>(HT), ldht, e0);
 }
 
 // ------------------------------------------------------------------ G2 = dOut[target] * [Z > 0]
-// Z [E, b] recomputed pre-activations (bf16), dOut [N, b] fp32.  Writes G2 [E, ldg] and
-// G2T [b, E] (bf16).  Empty slots give zero rows.
+// Z [E, b] recomputed pre-activations (bf16), dOut [N, b] fp32.  Writes G2 [E, ldg] (all
+// round_up(b, 8) columns; the pad columns as zeros) and G2T [b, E] (bf16).  Empty slots give
+// zero rows.  MASK: the ReLU pattern comes from the bits the training forward recorded
+// (gn_tc_edge_mlp_aggregate_mask) instead of from Z: one word per (32-channel group, tile row),
+// bit c = [z(row, 32 g + c) > 0]; slot e sits in tile e / used at row e % used (used = slots of
+// whole nodes in a 64-row tile).
+template <bool MASK>
 __global__ void __launch_bounds__(256) edge_grad_z_kernel(
-    const __nv_bfloat16* __restrict__ Z, int64_t ldz, const float* __restrict__ dOut, int64_t ldd,
-    int b, const int32_t* __restrict__ nbr, int KP, int64_t E, __nv_bfloat16* __restrict__ G2,
+    const __nv_bfloat16* __restrict__ Z, int64_t ldz, const uint32_t* __restrict__ mask,
+    int64_t mask_ld, int used, const float* __restrict__ dOut, int64_t ldd, int b,
+    const int32_t* __restrict__ nbr, int KP, int64_t E, __nv_bfloat16* __restrict__ G2,
     int64_t ldg, __nv_bfloat16* __restrict__ G2T, int64_t ldgt) {
-  extern __shared__ __nv_bfloat16 tile[];  // [EB_ROWS][b + 2]
-  const int pitch = b + 2;
+  extern __shared__ __align__(16) uint16_t tile[];  // [EB_ROWS][W]
+  const int W = tile_width(b);
+  const int pieces = (b + 7) >> 3;
   const int64_t e0 = (int64_t)blockIdx.x * EB_ROWS;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int r = warp; r < EB_ROWS; r += 8) {
     const int64_t e = e0 + r;
     const bool filled = e < E && nbr[e] >= 0;
     const int64_t i = e < E ? e / KP : 0;
-    for (int c = lane * 2; c < b; c += 64) {
-      float2 g = make_float2(0.f, 0.f);
+    const int64_t mrow = (MASK && e < E) ? (e / used) * 64 + (e % used) : 0;
+    for (int pc = lane; pc < pieces; pc += 32) {
+      const int c = pc * 8;
+      float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       if (filled) {
-        const float2 z = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(Z + e * ldz + c));
-        const float2 d = *reinterpret_cast<const float2*>(dOut + i * ldd + c);
-        g.x = z.x > 0.f ? d.x : 0.f;
-        g.y = z.y > 0.f ? d.y : 0.f;
+        uint32_t bits;
+        if (MASK) {
+          bits = (__ldg(mask + (int64_t)(c >> 5) * mask_ld + mrow) >> (c & 31)) & 0xffu;
+        } else {
+          const uint4 zv = __ldg(reinterpret_cast<const uint4*>(Z + e * ldz) + pc);
+          const __nv_bfloat162* z2 = reinterpret_cast<const __nv_bfloat162*>(&zv);
+          bits = 0;
+#pragma unroll
+          for (int x = 0; x < 4; ++x) {
+            const float2 zf = __bfloat1622float2(z2[x]);
+            bits |= (zf.x > 0.f ? 1u : 0u) << (2 * x);
+            bits |= (zf.y > 0.f ? 1u : 0u) << (2 * x + 1);
+          }
+        }
+        const float4 d0 = __ldg(reinterpret_cast<const float4*>(dOut + i * ldd + c));
+        const float4 d1 = __ldg(reinterpret_cast<const float4*>(dOut + i * ldd + c + 4));
+        const float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+        for (int x = 0; x < 8; ++x) g[x] = (c + x < b && ((bits >> x) & 1u)) ? d[x] : 0.f;
       }
-      const __nv_bfloat162 gb = __floats2bfloat162_rn(g.x, g.y);
-      *reinterpret_cast<__nv_bfloat162*>(tile + r * pitch + c) = gb;
-      if (e < E) *reinterpret_cast<__nv_bfloat162*>(G2 + e * ldg + c) = gb;
+      const uint4 gb = pack8_bf16(g);
+      *tile_piece(tile, W, r, pc) = gb;
+      if (e < E) *(reinterpret_cast<uint4*>(G2 + e * ldg) + pc) = gb;
     }
   }
   __syncthreads();
   const int rvalid = (int)(E - e0 < EB_ROWS ? E - e0 : EB_ROWS);
-  for (int idx = threadIdx.x; idx < b * 4; idx += 256) {
-    const int c = idx >> 2, r8 = (idx & 3) * 8;
-    __nv_bfloat16 v[8];
-#pragma unroll
-    for (int t = 0; t < 8; ++t) v[t] = tile[(r8 + t) * pitch + c];
-    __nv_bfloat16* dst = G2T + (int64_t)c * ldgt + e0 + r8;
-    if (r8 + 8 <= rvalid && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<uint4*>(v);
-    } else {
-#pragma unroll
-      for (int t = 0; t < 8; ++t)
-        if (r8 + t < rvalid) dst[t] = v[t];
-    }
-  }
+  tile_store_transposed(tile, W, b, rvalid, reinterpret_cast<uint16_t*>(G2T), ldgt, e0);
 }
 
 // ------------------------------------------------------------------ dP, dQ from dH
@@ -251,6 +301,217 @@ __global__ void __launch_bounds__(256) edge_grad_pq_kernel(
     *reinterpret_cast<__nv_bfloat162*>(dP + i * ldp + k) = __floats2bfloat162_rn(acc.x, acc.y);
     if (dP32 != nullptr) *reinterpret_cast<float2*>(dP32 + i * ldp32 + k) = acc;
   }
+}
+
+// ------------------------------------------------------------------ slots grouped by SOURCE node
+// For every node j of an ELL graph: the slots e = i*KP + t with nbr[e] == j, in ascending e
+// (deterministic), as rslot[rstart[j] .. rstart[j] + rcount[j]).  Edges never leave an event, so
+// the lists of event [lo, hi) live in rslot[lo*KP, hi*KP) and no global scan is needed.  One
+// warp per event walks its slots three times (count, scan, fill); the fill takes 32 slots at a
+// time and ranks equal sources inside the warp with match_any, so list order is slot order.
+// rcount must be zero on entry.
+__global__ void __launch_bounds__(128) ell_reverse_kernel(const int32_t* __restrict__ nbr, int KP,
+                                                          const int32_t* __restrict__ ptr,
+                                                          int64_t B, int32_t* __restrict__ rstart,
+                                                          int32_t* __restrict__ rcount,
+                                                          int32_t* __restrict__ rslot) {
+  const int64_t ev = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (ev >= B) return;
+  const int lo = ptr[ev], hi = ptr[ev + 1];
+  const int64_t s0 = (int64_t)lo * KP, s1 = (int64_t)hi * KP;
+  for (int64_t e = s0 + lane; e < s1; e += 32) {
+    const int32_t j = nbr[e];
+    if (j >= 0) atomicAdd(rcount + j, 1);
+  }
+  __threadfence();
+  __syncwarp();
+  int32_t carry = (int32_t)s0;
+  for (int base = lo; base < hi; base += 32) {
+    const int j = base + lane;
+    const int32_t c = j < hi ? __ldcg(rcount + j) : 0;
+    int32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (j < hi) {
+      rstart[j] = carry + incl - c;
+      rcount[j] = 0;  // re-used as the fill cursor; ends at the count again
+    }
+    carry += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  __threadfence();
+  __syncwarp();
+  for (int64_t eb = s0; eb < s1; eb += 32) {
+    const int64_t e = eb + lane;
+    const int32_t j = e < s1 ? nbr[e] : -1;
+    const uint32_t peers = __match_any_sync(0xffffffffu, j);
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    const int leader = __ffs(peers) - 1;
+    int32_t base = 0;
+    if (j >= 0 && lane == leader) base = atomicAdd(rcount + j, __popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (j >= 0) rslot[__ldcg(rstart + j) + base + rank] = (int32_t)e;
+  }
+}
+
+// ------------------------------------------------------------------ dP, dQ from dH by gathering
+// m[e] = dH[e] * [P_i + Q_j > 0] (the fp16 sum the forward kernel clamps: the same sign).
+//   dP_i = sum of m over the node's own slots (contiguous rows of dH),
+//   dQ_j = sum of m over the slots that name j as neighbour (ell_reverse_kernel's lists),
+// both as plain sums in registers: no atomics, one write per output element, a fixed order.
+// A CTA takes one event and `gch` 16-byte column pieces of every row: the event's rows are read
+// from HBM by the first loop and found in L2 by the second.
+__device__ __forceinline__ void pq_accumulate(float (&acc)[8], const uint4& g, const uint4& p,
+                                              const uint4& q) {
+  const __half2* p2 = reinterpret_cast<const __half2*>(&p);
+  const __half2* q2 = reinterpret_cast<const __half2*>(&q);
+  const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&g);
+#pragma unroll
+  for (int x = 0; x < 4; ++x) {
+    const float2 s = __half22float2(__hadd2(p2[x], q2[x]));
+    const float2 gv = __bfloat1622float2(g2[x]);
+    acc[2 * x] += s.x > 0.f ? gv.x : 0.f;
+    acc[2 * x + 1] += s.y > 0.f ? gv.y : 0.f;
+  }
+}
+
+__device__ __forceinline__ void pq_store(const float (&acc)[8], __nv_bfloat16* d16, float* d32) {
+  __nv_bfloat162 o[4];
+#pragma unroll
+  for (int x = 0; x < 4; ++x) o[x] = __floats2bfloat162_rn(acc[2 * x], acc[2 * x + 1]);
+  *reinterpret_cast<uint4*>(d16) = *reinterpret_cast<const uint4*>(o);
+  if (d32 != nullptr) {
+    *reinterpret_cast<float4*>(d32) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(d32 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  }
+}
+
+__global__ void __launch_bounds__(256) edge_grad_pq_gather_kernel(
+    const __nv_bfloat16* __restrict__ dH, int64_t lddh, const __half* __restrict__ P, int64_t ldp,
+    const __half* __restrict__ Q, int64_t ldq, int Kp, const int32_t* __restrict__ nbr, int KP,
+    const int32_t* __restrict__ ptr, const int32_t* __restrict__ rstart,
+    const int32_t* __restrict__ rcount, const int32_t* __restrict__ rslot, int gch,
+    __nv_bfloat16* __restrict__ dP, int64_t lddp, __nv_bfloat16* __restrict__ dQ, int64_t lddq,
+    float* __restrict__ dP32, int64_t ldp32, float* __restrict__ dQ32, int64_t ldq32) {
+  const int lo = ptr[blockIdx.x], n = ptr[blockIdx.x + 1] - lo;
+  const int pieces = Kp / 8;
+  const int c_first = blockIdx.y * gch;
+  const int nc = min(gch, pieces - c_first);
+  if (n <= 0 || nc <= 0) return;
+  const int items = n * nc;
+  // four slots per step: ids first, then all eight 16-byte loads, then the arithmetic - a
+  // thread's loads are dependent chains (id -> row), so they must overlap each other
+  for (int it = threadIdx.x; it < items; it += blockDim.x) {  // own slots -> dP
+    const int64_t i = lo + it / nc;
+    const int col = (c_first + it % nc) * 8;
+    const uint4 p = __ldg(reinterpret_cast<const uint4*>(P + i * ldp + col));
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int t0 = 0; t0 < KP; t0 += 4) {
+      int32_t j[4];
+      uint4 g[4], q[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) j[u] = t0 + u < KP ? __ldg(nbr + i * KP + t0 + u) : -1;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (j[u] >= 0) {
+          g[u] = *reinterpret_cast<const uint4*>(dH + (i * KP + t0 + u) * lddh + col);
+          q[u] = __ldg(reinterpret_cast<const uint4*>(Q + (int64_t)j[u] * ldq + col));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (j[u] >= 0) pq_accumulate(acc, g[u], p, q[u]);
+    }
+    pq_store(acc, dP + i * lddp + col, dP32 ? dP32 + i * ldp32 + col : nullptr);
+  }
+  for (int it = threadIdx.x; it < items; it += blockDim.x) {  // slots naming this node -> dQ
+    const int64_t j = lo + it / nc;
+    const int col = (c_first + it % nc) * 8;
+    const uint4 q = __ldg(reinterpret_cast<const uint4*>(Q + j * ldq + col));
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    const int32_t* list = rslot + rstart[j];
+    const int cnt = rcount[j];
+    for (int r0 = 0; r0 < cnt; r0 += 4) {
+      int64_t e[4];
+      uint4 g[4], p[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) e[u] = r0 + u < cnt ? (int64_t)__ldg(list + r0 + u) : -1;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (e[u] >= 0) {
+          g[u] = *reinterpret_cast<const uint4*>(dH + e[u] * lddh + col);
+          p[u] = __ldg(reinterpret_cast<const uint4*>(P + (e[u] / KP) * ldp + col));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (e[u] >= 0) pq_accumulate(acc, g[u], p[u], q);
+    }
+    pq_store(acc, dQ + j * lddq + col, dQ32 ? dQ32 + j * ldq32 + col : nullptr);
+  }
+}
+
+// ------------------------------------------------------------------ dP, dQ in one pass over dH
+// The same sums from ONE streaming read of dH: a thread takes all the slots of one node for one
+// 16-byte piece, keeps dP in registers and sends m to dQ32[j] with two red.global.add.v4.f32 per
+// slot (four fp32 additions per L2 operation; the scalar form of this kernel spent its time on
+// 97 M single-word atomics per layer, and shared-memory float atomics compile to a CAS loop).
+// dQ32 must be zero on entry; the order of the additions is not fixed.
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b),
+               "f"(c), "f"(d)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(256) edge_grad_pq_scatter_kernel(
+    const __nv_bfloat16* __restrict__ dH, int64_t lddh, const __half* __restrict__ P, int64_t ldp,
+    const __half* __restrict__ Q, int64_t ldq, int Kp, const int32_t* __restrict__ nbr, int KP,
+    int64_t N, __nv_bfloat16* __restrict__ dP, int64_t lddp, float* __restrict__ dP32,
+    int64_t ldp32, float* __restrict__ dQ32, int64_t ldq32) {
+  const int pieces = Kp / 8;
+  const int64_t it = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (it >= N * pieces) return;
+  const int64_t i = it / pieces;
+  const int col = (int)(it - i * pieces) * 8;
+  const uint4 p = __ldg(reinterpret_cast<const uint4*>(P + i * ldp + col));
+  const __half2* p2 = reinterpret_cast<const __half2*>(&p);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int t0 = 0; t0 < KP; t0 += 4) {
+    int32_t j[4];
+    uint4 g[4], q[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) j[u] = t0 + u < KP ? __ldg(nbr + i * KP + t0 + u) : -1;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (j[u] >= 0) {
+        g[u] = __ldg(reinterpret_cast<const uint4*>(dH + (i * KP + t0 + u) * lddh + col));
+        q[u] = __ldg(reinterpret_cast<const uint4*>(Q + (int64_t)j[u] * ldq + col));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (j[u] < 0) continue;
+      const __half2* q2 = reinterpret_cast<const __half2*>(&q[u]);
+      const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&g[u]);
+      float m[8];
+#pragma unroll
+      for (int x = 0; x < 4; ++x) {
+        const float2 sum = __half22float2(__hadd2(p2[x], q2[x]));
+        const float2 gv = __bfloat1622float2(g2[x]);
+        m[2 * x] = sum.x > 0.f ? gv.x : 0.f;
+        m[2 * x + 1] = sum.y > 0.f ? gv.y : 0.f;
+        acc[2 * x] += m[2 * x];
+        acc[2 * x + 1] += m[2 * x + 1];
+      }
+      float* dst = dQ32 + (int64_t)j[u] * ldq32 + col;
+      red_add_v4(dst, m[0], m[1], m[2], m[3]);
+      red_add_v4(dst + 4, m[4], m[5], m[6], m[7]);
+    }
+  }
+  pq_store(acc, dP + i * lddp + col, dP32 ? dP32 + i * ldp32 + col : nullptr);
 }
 
 // ------------------------------------------------------------------ out += G^T X, X narrow, fp32
@@ -424,12 +685,18 @@ extern "C" int gn_edge_build_h(const void* P, int64_t ldp, const void* Q, int64_
   if (rc != GN_OK) return rc;
   const int KP = graph->ell_stride;
   const int64_t E = N * KP;
-  GN_CHECK_ARG(Kp >= 2 && Kp % 2 == 0 && ldp >= Kp && ldq >= Kp && ldh >= Kp &&
-                   (HT == nullptr || ldht >= E),
-               "gn_edge_build_h: bad sizes");
+  GN_CHECK_ARG(Kp >= 8 && Kp % 8 == 0 && ldp >= Kp && ldq >= Kp && ldp % 8 == 0 && ldq % 8 == 0 &&
+                   (H == nullptr || (ldh >= Kp && ldh % 8 == 0)) && (HT == nullptr || ldht >= E),
+               "gn_edge_build_h: Kp and the row strides must be multiples of 8");
   if (N == 0) return GN_OK;
-  GN_CHECK_ARG(P && Q && H, "gn_edge_build_h: null pointer");
-  const size_t smem = (size_t)EB_ROWS * (Kp + 2) * 2;
+  GN_CHECK_ARG(P && Q && (H || HT), "gn_edge_build_h: null pointer");
+  GN_CHECK_ARG(((reinterpret_cast<uintptr_t>(P) | reinterpret_cast<uintptr_t>(Q) |
+                 reinterpret_cast<uintptr_t>(H)) & 15) == 0,
+               "gn_edge_build_h: P, Q, H must be 16-byte aligned");
+  const size_t smem = (size_t)EB_ROWS * tile_width(Kp) * 2;
+  GN_CHECK_ARG(smem <= 200 * 1024, "gn_edge_build_h: Kp=%d too wide", Kp);
+  GN_CUDA(cudaFuncSetAttribute(edge_build_h_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)smem));
   edge_build_h_kernel<<<(unsigned)ceil_div(E, EB_ROWS), 256, smem, as_stream(stream)>>>(
       reinterpret_cast<const __half*>(P), ldp, reinterpret_cast<const __half*>(Q), ldq, Kp,
       graph->col, KP, E, reinterpret_cast<__nv_bfloat16*>(H), ldh,
@@ -445,16 +712,124 @@ extern "C" int gn_edge_grad_z(const void* Z, int64_t ldz, const float* dOut, int
   if (rc != GN_OK) return rc;
   const int KP = graph->ell_stride;
   const int64_t E = N * KP;
-  GN_CHECK_ARG(b >= 2 && b % 2 == 0 && ldz >= b && ldd >= b && ldg >= b && ldgt >= E &&
-                   ldd % 2 == 0,
-               "gn_edge_grad_z: bad sizes");
+  const int bw = (b + 7) & ~7;
+  GN_CHECK_ARG(b >= 2 && b % 2 == 0 && b <= 1024 && ldz >= bw && ldd >= bw && ldg >= bw &&
+                   ldgt >= E && ldz % 8 == 0 && ldd % 4 == 0 && ldg % 8 == 0,
+               "gn_edge_grad_z: rows must hold round_up(b, 8) columns; strides multiples of 8");
   if (N == 0) return GN_OK;
   GN_CHECK_ARG(Z && dOut && G2 && G2T, "gn_edge_grad_z: null pointer");
-  GN_CHECK_ARG((reinterpret_cast<uintptr_t>(dOut) & 7) == 0, "gn_edge_grad_z: dOut alignment");
-  const size_t smem = (size_t)EB_ROWS * (b + 2) * 2;
-  edge_grad_z_kernel<<<(unsigned)ceil_div(E, EB_ROWS), 256, smem, as_stream(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(Z), ldz, dOut, ldd, b, graph->col, KP, E,
+  GN_CHECK_ARG(((reinterpret_cast<uintptr_t>(dOut) | reinterpret_cast<uintptr_t>(Z) |
+                 reinterpret_cast<uintptr_t>(G2)) & 15) == 0,
+               "gn_edge_grad_z: Z, dOut, G2 must be 16-byte aligned");
+  const size_t smem = (size_t)EB_ROWS * tile_width(b) * 2;
+  GN_CHECK_ARG(smem <= 200 * 1024, "gn_edge_grad_z: b=%d too wide", b);
+  GN_CUDA(cudaFuncSetAttribute(edge_grad_z_kernel<false>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  edge_grad_z_kernel<false><<<(unsigned)ceil_div(E, EB_ROWS), 256, smem, as_stream(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(Z), ldz, nullptr, 0, 1, dOut, ldd, b, graph->col, KP,
+      E, reinterpret_cast<__nv_bfloat16*>(G2), ldg, reinterpret_cast<__nv_bfloat16*>(G2T), ldgt);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_edge_grad_z_mask(const uint32_t* relu_mask, int64_t mask_ld, const float* dOut,
+                                   int64_t ldd, int b, const gn_graph* graph, int64_t N, void* G2,
+                                   int64_t ldg, void* G2T, int64_t ldgt, void* stream) {
+  int rc = check_ell(graph, "gn_edge_grad_z_mask");
+  if (rc != GN_OK) return rc;
+  const int KP = graph->ell_stride;
+  const int64_t E = N * KP;
+  GN_CHECK_ARG(KP <= 64, "gn_edge_grad_z_mask: %d slots per node (max 64)", KP);
+  const int used = (64 / KP) * KP;
+  const int bw = (b + 7) & ~7;
+  GN_CHECK_ARG(b >= 2 && b % 2 == 0 && b <= 256 && ldd >= bw && ldg >= bw && ldgt >= E &&
+                   ldd % 4 == 0 && ldg % 8 == 0 && mask_ld >= ceil_div(E, (int64_t)used) * 64,
+               "gn_edge_grad_z_mask: rows must hold round_up(b, 8) columns; strides multiples of 8");
+  if (N == 0) return GN_OK;
+  GN_CHECK_ARG(relu_mask && dOut && G2 && G2T, "gn_edge_grad_z_mask: null pointer");
+  GN_CHECK_ARG(((reinterpret_cast<uintptr_t>(dOut) | reinterpret_cast<uintptr_t>(G2)) & 15) == 0,
+               "gn_edge_grad_z_mask: dOut, G2 must be 16-byte aligned");
+  const size_t smem = (size_t)EB_ROWS * tile_width(b) * 2;
+  GN_CUDA(cudaFuncSetAttribute(edge_grad_z_kernel<true>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  edge_grad_z_kernel<true><<<(unsigned)ceil_div(E, EB_ROWS), 256, smem, as_stream(stream)>>>(
+      nullptr, 0, relu_mask, mask_ld, used, dOut, ldd, b, graph->col, KP, E,
       reinterpret_cast<__nv_bfloat16*>(G2), ldg, reinterpret_cast<__nv_bfloat16*>(G2T), ldgt);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_ell_reverse(const gn_graph* graph, const int32_t* ptr, int64_t N, int64_t B,
+                              int32_t* rstart, int32_t* rcount, int32_t* rslot, void* stream) {
+  int rc = check_ell(graph, "gn_ell_reverse");
+  if (rc != GN_OK) return rc;
+  GN_CHECK_ARG(N >= 0 && B >= 0 && N * (int64_t)graph->ell_stride < INT32_MAX,
+               "gn_ell_reverse: bad sizes");
+  if (N == 0 || B == 0) return GN_OK;
+  GN_CHECK_ARG(ptr && rstart && rcount && rslot, "gn_ell_reverse: null pointer");
+  cudaStream_t st = as_stream(stream);
+  GN_CUDA(cudaMemsetAsync(rcount, 0, (size_t)N * sizeof(int32_t), st));
+  ell_reverse_kernel<<<(unsigned)ceil_div(B, 4), 128, 0, st>>>(graph->col, graph->ell_stride, ptr,
+                                                               B, rstart, rcount, rslot);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_edge_grad_pq_gather(const void* dH, int64_t lddh, const void* P, int64_t ldp,
+                                      const void* Q, int64_t ldq, int Kp, const gn_graph* graph,
+                                      const int32_t* ptr, int64_t N, int64_t B,
+                                      const int32_t* rstart, const int32_t* rcount,
+                                      const int32_t* rslot, void* dP, int64_t lddp, void* dQ,
+                                      int64_t lddq, float* dP32, int64_t ldp32, float* dQ32,
+                                      int64_t ldq32, void* stream) {
+  int rc = check_ell(graph, "gn_edge_grad_pq_gather");
+  if (rc != GN_OK) return rc;
+  GN_CHECK_ARG(Kp >= 8 && Kp % 8 == 0 && lddh >= Kp && ldp >= Kp && ldq >= Kp && lddp >= Kp &&
+                   lddq >= Kp && lddh % 8 == 0 && ldp % 8 == 0 && ldq % 8 == 0 && lddp % 8 == 0 &&
+                   lddq % 8 == 0,
+               "gn_edge_grad_pq_gather: widths and row strides must be multiples of 8");
+  if (N == 0 || B == 0) return GN_OK;
+  GN_CHECK_ARG(dH && P && Q && ptr && dP && dQ, "gn_edge_grad_pq_gather: null pointer");
+  GN_CHECK_ARG(rstart == nullptr || (rcount && rslot),
+               "gn_edge_grad_pq_gather: the list form needs all three arrays of gn_ell_reverse");
+  GN_CHECK_ARG(((reinterpret_cast<uintptr_t>(dH) | reinterpret_cast<uintptr_t>(P) |
+                 reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(dP) |
+                 reinterpret_cast<uintptr_t>(dQ)) & 15) == 0,
+               "gn_edge_grad_pq_gather: 16-byte alignment");
+  GN_CHECK_ARG((dP32 == nullptr || (ldp32 >= Kp && ldp32 % 4 == 0 &&
+                                    (reinterpret_cast<uintptr_t>(dP32) & 15) == 0)) &&
+                   (dQ32 == nullptr || (ldq32 >= Kp && ldq32 % 4 == 0 &&
+                                        (reinterpret_cast<uintptr_t>(dQ32) & 15) == 0)),
+               "gn_edge_grad_pq_gather: bad fp32 outputs");
+  GN_CHECK_ARG(B <= 2147483647LL, "gn_edge_grad_pq_gather: too many events");
+  static const int gch_env = getenv("GN_PQ_CHUNKS") ? atoi(getenv("GN_PQ_CHUNKS")) : 0;
+  const bool use_lists = rstart != nullptr;
+  const int pieces = Kp / 8;
+  if (!use_lists) {
+    GN_CHECK_ARG(dQ32 != nullptr,
+                 "gn_edge_grad_pq_gather: the one-pass form accumulates in dQ32 (fp32), pass it");
+    cudaStream_t st = as_stream(stream);
+    GN_CUDA(cudaMemset2DAsync(dQ32, (size_t)ldq32 * sizeof(float), 0, (size_t)Kp * sizeof(float),
+                              (size_t)N, st));
+    const int64_t items = N * pieces;
+    edge_grad_pq_scatter_kernel<<<(unsigned)ceil_div(items, 256), 256, 0, st>>>(
+        reinterpret_cast<const __nv_bfloat16*>(dH), lddh, reinterpret_cast<const __half*>(P), ldp,
+        reinterpret_cast<const __half*>(Q), ldq, Kp, graph->col, graph->ell_stride, N,
+        reinterpret_cast<__nv_bfloat16*>(dP), lddp, dP32, ldp32, dQ32, ldq32);
+    GN_LAUNCH_CHECK();
+    const int64_t work = N * (int64_t)((Kp + 3) / 4);
+    mask_convert_kernel<float, float, __nv_bfloat16><<<(unsigned)ceil_div(work, 256), 256, 0, st>>>(
+        dQ32, ldq32, nullptr, 0, reinterpret_cast<__nv_bfloat16*>(dQ), lddq, N, Kp);
+    GN_LAUNCH_CHECK();
+    return GN_OK;
+  }
+  const int gch = gch_env > 0 ? gch_env : 4;  // 64-byte row pieces: the event's block stays in L2
+  dim3 grid((unsigned)B, (unsigned)ceil_div(pieces, gch));
+  edge_grad_pq_gather_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(dH), lddh, reinterpret_cast<const __half*>(P), ldp,
+      reinterpret_cast<const __half*>(Q), ldq, Kp, graph->col, graph->ell_stride, ptr, rstart,
+      rcount, rslot, gch, reinterpret_cast<__nv_bfloat16*>(dP), lddp,
+      reinterpret_cast<__nv_bfloat16*>(dQ), lddq, dP32, ldp32, dQ32, ldq32);
   GN_LAUNCH_CHECK();
   return GN_OK;
 }

@@ -78,6 +78,8 @@ struct EdgeParams {
   const void* w2;           // W2p [bnp, Kp] fp16 row-major (second-generation kernel reads it directly)
   int use_ws;               // weight-stationary MMA form (collector re-use of the h chunk)
   void* dbg;                // optional 8 x uint64 wait-time counters (GN_EDGE_DEBUG), else null
+  uint32_t* relu_mask;      // training: [8][mask_ld] words, bit c of word (g, row) = [z(row, 32g+c) > 0]
+  int64_t mask_ld;          // words per 32-channel group: >= tiles * 64
 };
 
 __device__ __forceinline__ uint4 ldg16(const __half* p) {
@@ -482,12 +484,18 @@ extern "C" size_t gn_tc_edge_scratch_bytes(const gn_graph* graph, int64_t N, int
   return (size_t)(n * slots + cap * slots + cap + 4) * sizeof(int32_t);
 }
 
-extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t ldq,
-                                        int Kp, const gn_graph* graph, int64_t N, int slots,
-                                        const void* W2p, int b, void* out, int64_t ldo,
-                                        int out_dtype, float* coords,
-                                        const int32_t* coord_cols, int ncoord, void* scratch,
-                                        size_t scratch_bytes, void* stream) {
+extern "C" int64_t gn_tc_edge_relu_mask_ld(int64_t N, int slots) {
+  if (N <= 0 || !tc::edge2_supported_slots(slots)) return 0;
+  return ceil_div(N, (int64_t)(tc::E2_ROWS / slots)) * tc::E2_ROWS;
+}
+
+static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q, int64_t ldq,
+                                      int Kp, const gn_graph* graph, int64_t N, int slots,
+                                      const void* W2p, int b, void* out, int64_t ldo,
+                                      int out_dtype, float* coords,
+                                      const int32_t* coord_cols, int ncoord, void* scratch,
+                                      size_t scratch_bytes, uint32_t* relu_mask, int64_t mask_ld,
+                                      void* stream) {
   GN_CHECK_ARG(out_dtype == GN_BF16 || out_dtype == GN_F16,
                "gn_tc_edge_mlp_aggregate: out_dtype must be GN_BF16 or GN_F16");
   GN_CHECK_ARG(N >= 0 && b >= 1 && b <= 256, "gn_tc_edge_mlp_aggregate: b=%d not in [1,256]", b);
@@ -528,6 +536,15 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
   }
   const bool direct = edge_direct_ell(graph);
   if (direct) slots = graph->ell_stride;
+  if (relu_mask != nullptr) {
+    if (!direct || !edge_use_v2()) {
+      set_error("gn_tc_edge_mlp_aggregate_mask: needs an ELL graph with 8, 9, 16, 17 or 32 slots "
+                "per node and the default (second-generation) kernel");
+      return GN_ERR_UNSUPPORTED;
+    }
+    GN_CHECK_ARG(mask_ld >= gn_tc_edge_relu_mask_ld(N, slots),
+                 "gn_tc_edge_mlp_aggregate_mask: mask_ld=%lld too small", (long long)mask_ld);
+  }
   const int64_t cap = direct ? 0 : edge_overflow_cap(graph, N, slots);
   int32_t* ell = reinterpret_cast<int32_t*>(scratch);
   int32_t* ovf_ell = ell + N * slots;
@@ -548,6 +565,8 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
   }
 
   p.w2 = W2p;
+  p.relu_mask = relu_mask;
+  p.mask_ld = mask_ld;
   // GN_EDGE_DEBUG=1: the second-generation kernel accumulates wait-time counters (tc_edge2.cuh)
   // into g_edge_dbg, read back with the undeclared diagnostic export gn_debug_edge_counters()
   static const bool dbg_on = getenv("GN_EDGE_DEBUG") != nullptr;
@@ -639,3 +658,28 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
   }
   return GN_OK;
 }
+
+extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t ldq,
+                                        int Kp, const gn_graph* graph, int64_t N, int slots,
+                                        const void* W2p, int b, void* out, int64_t ldo,
+                                        int out_dtype, float* coords,
+                                        const int32_t* coord_cols, int ncoord, void* scratch,
+                                        size_t scratch_bytes, void* stream) {
+  return tc_edge_mlp_aggregate_impl(P, ldp, Q, ldq, Kp, graph, N, slots, W2p, b, out, ldo,
+                                    out_dtype, coords, coord_cols, ncoord, scratch, scratch_bytes,
+                                    nullptr, 0, stream);
+}
+
+extern "C" int gn_tc_edge_mlp_aggregate_mask(const void* P, int64_t ldp, const void* Q,
+                                             int64_t ldq, int Kp, const gn_graph* graph, int64_t N,
+                                             int slots, const void* W2p, int b, void* out,
+                                             int64_t ldo, int out_dtype, float* coords,
+                                             const int32_t* coord_cols, int ncoord, void* scratch,
+                                             size_t scratch_bytes, uint32_t* relu_mask,
+                                             int64_t mask_ld, void* stream) {
+  GN_CHECK_ARG(relu_mask != nullptr, "gn_tc_edge_mlp_aggregate_mask: relu_mask is null");
+  return tc_edge_mlp_aggregate_impl(P, ldp, Q, ldq, Kp, graph, N, slots, W2p, b, out, ldo,
+                                    out_dtype, coords, coord_cols, ncoord, scratch, scratch_bytes,
+                                    relu_mask, mask_ld, stream);
+}
+

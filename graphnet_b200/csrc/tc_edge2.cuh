@@ -475,6 +475,18 @@ __global__ void __launch_bounds__(E2_THREADS, 1) edge_mlp_aggregate_v2_kernel(co
             const int col = 32 * half + c;
             if (col < USED) sums[col / KP] += fmaxf(v[c], 0.f);
           }
+          if (!ACC && p.relu_mask != nullptr) {
+            // training: the ReLU pattern of the 32 channels of this warp, one word per tile row
+            // (the backward pass masks dOut with it instead of recomputing Z = H W2^T)
+            uint32_t mword = 0;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+              const uint32_t w = __ballot_sync(0xffffffffu, v[c] > 0.f);
+              if (lane == c) mword = w;
+            }
+            p.relu_mask[(int64_t)(blk * 4 + q) * p.mask_ld + tile * E2_ROWS + 32 * half + lane] =
+                mword;
+          }
         }
         tc_fence_before();
         __syncwarp();

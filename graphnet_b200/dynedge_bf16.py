@@ -182,16 +182,25 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
             ops.linear_f32(x0, pk.Wpq, pk.bias_pq, act="none", out=PQ)
         else:
             ops.tc_linear_bf16(skip[:, off_in:], pk.Wpq, pk.bias_pq, PQ, K=d_in, act="none")
+        slots = _slots(conv.nb_neighbors)
+        relu_mask = None
         if save is not None:
+            if graph.ell_stride <= 0 and graph.max_degree is not None and \
+                    int(graph.max_degree.item()) <= slots:
+                # the data set's edge_index (layer 1) as a slot table, the layout the backward
+                # kernels address edges in
+                graph = ops.csr_to_ell(graph, slots)
+            if graph.ell_stride in (8, 9, 16, 17, 32):
+                relu_mask = ops.edge_relu_mask(N, graph.ell_stride, dev)
             save["layers"].append({"P": P, "Q": Q, "graph": graph, "pack": pk, "off_in": off_in,
-                                   "d_in": d_in, "off_out": offs[li]})
+                                   "d_in": d_in, "off_out": offs[li], "relu_mask": relu_mask})
         last = li + 1 == len(convs)
         need_graph = (not last) or return_intermediates
         cols = sorted(ops._columns(conv.features_subset, pk.b))
         coords = (torch.empty((N, len(cols)), dtype=torch.float32, device=dev)
                   if need_graph else None)
-        ops.tc_edge_mlp_aggregate(P, Q, pk.Kp, graph, _slots(conv.nb_neighbors), pk.W2p, pk.b,
-                                  skip[:, offs[li]:], coords, cols)
+        ops.tc_edge_mlp_aggregate(P, Q, pk.Kp, graph, slots, pk.W2p, pk.b,
+                                  skip[:, offs[li]:], coords, cols, relu_mask=relu_mask)
         if need_graph:
             graph = ops.knn_graph_ell(coords, conv.nb_neighbors, ptr, list(range(len(cols))))
             if return_intermediates:

@@ -330,9 +330,12 @@ def tc_linear_bf16(A: Tensor, W: Tensor, bias: Optional[Tensor], out: Tensor, K:
 
 def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: int, W2p: Tensor,
                           b: int, out: Tensor, coords: Optional[Tensor],
-                          coord_cols: Sequence[int]) -> Tensor:
-    """out[i] = sum_j ReLU(W2 ReLU(P_i + Q_j) + b2) on tcgen05 (see include/graphnet_b200.h)."""
-    dev = _require_cuda(P, Q, W2p, out, coords)
+                          coord_cols: Sequence[int], relu_mask: Optional[Tensor] = None) -> Tensor:
+    """out[i] = sum_j ReLU(W2 ReLU(P_i + Q_j) + b2) on tcgen05 (see include/graphnet_b200.h).
+
+    `relu_mask` ([8, ld] int32 from `edge_relu_mask`, training): receives the ReLU bits of the
+    second Linear for the backward pass (gn_tc_edge_mlp_aggregate_mask)."""
+    dev = _require_cuda(P, Q, W2p, out, coords, relu_mask)
     assert P.dtype == torch.float16 and Q.dtype == torch.float16 and W2p.dtype == torch.float16
     assert out.dtype in (torch.bfloat16, torch.float16)
     assert P.stride(1) == 1 and Q.stride(1) == 1 and P.shape[0] == Q.shape[0]
@@ -343,12 +346,30 @@ def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: in
     scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     ncoord = 0 if coords is None else len(coord_cols)
     with torch.cuda.device(dev):
+        if relu_mask is not None:
+            assert relu_mask.dtype == torch.int32 and relu_mask.shape[0] == 8 \
+                and relu_mask.stride(1) == 1
+            check(lib.gn_tc_edge_mlp_aggregate_mask(
+                _ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp, C.byref(gs), N, slots, _ptr(W2p),
+                b, _ptr(out), out.stride(0), _DT[out.dtype], _ptr(coords),
+                _host_i32(coord_cols) if ncoord else None, ncoord, _ptr(scratch), nbytes,
+                _ptr(relu_mask), relu_mask.stride(0), _stream(dev)),
+                "gn_tc_edge_mlp_aggregate_mask")
+            return out
         check(lib.gn_tc_edge_mlp_aggregate(
             _ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp, C.byref(gs), N, slots, _ptr(W2p), b,
             _ptr(out), out.stride(0), _DT[out.dtype], _ptr(coords),
             _host_i32(coord_cols) if ncoord else None,
             ncoord, _ptr(scratch), nbytes, _stream(dev)), "gn_tc_edge_mlp_aggregate")
     return out
+
+
+def edge_relu_mask(N: int, slots: int, device) -> Tensor:
+    """Buffer for the ReLU bits of one EdgeConv layer: [8, ld] int32 (8 groups of 32 channels)."""
+    ld = int(_lib.load().gn_tc_edge_relu_mask_ld(N, slots))
+    if ld <= 0:
+        raise ValueError(f"no ReLU-bit layout for {slots} slots per node")
+    return torch.empty((8, ld), dtype=torch.int32, device=device)
 
 
 # ------------------------------------------------- backward pass (16-bit training path)
@@ -415,15 +436,17 @@ def relu_backward(dY: Tensor, Y: Optional[Tensor], out: Optional[Tensor] = None)
     return out
 
 
-def edge_build_h(P: Tensor, Q: Tensor, Kp: int, graph: Graph, H: Tensor,
+def edge_build_h(P: Tensor, Q: Tensor, Kp: int, graph: Graph, H: Optional[Tensor],
                  HT: Optional[Tensor]) -> None:
     dev = _require_cuda(P, Q, H, HT)
-    assert P.dtype == torch.float16 and Q.dtype == torch.float16 and H.dtype == torch.bfloat16
+    assert P.dtype == torch.float16 and Q.dtype == torch.float16
+    assert (H is None or H.dtype == torch.bfloat16) and (H is not None or HT is not None)
     N = P.shape[0]
     gs = graph.c_struct()
     with torch.cuda.device(dev):
         check(_lib.load().gn_edge_build_h(_ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp,
-                                          C.byref(gs), N, _ptr(H), H.stride(0), _ptr(HT),
+                                          C.byref(gs), N, _ptr(H),
+                                          0 if H is None else H.stride(0), _ptr(HT),
                                           0 if HT is None else HT.stride(0), _stream(dev)),
               "gn_edge_build_h")
 
@@ -438,6 +461,57 @@ def edge_grad_z(Z: Tensor, dOut: Tensor, b: int, graph: Graph, G2: Tensor, G2T: 
         check(_lib.load().gn_edge_grad_z(_ptr(Z), Z.stride(0), _ptr(dOut), dOut.stride(0), b,
                                          C.byref(gs), N, _ptr(G2), G2.stride(0), _ptr(G2T),
                                          G2T.stride(0), _stream(dev)), "gn_edge_grad_z")
+
+
+def edge_grad_z_mask(relu_mask: Tensor, dOut: Tensor, b: int, graph: Graph, G2: Tensor,
+                     G2T: Tensor) -> None:
+    """G2 / G2T from the ReLU bits the training forward recorded (no Z)."""
+    dev = _require_cuda(relu_mask, dOut, G2, G2T)
+    assert relu_mask.dtype == torch.int32 and dOut.dtype == torch.float32
+    assert G2.dtype == torch.bfloat16 and G2T.dtype == torch.bfloat16
+    N = dOut.shape[0]
+    gs = graph.c_struct()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_edge_grad_z_mask(_ptr(relu_mask), relu_mask.stride(0), _ptr(dOut),
+                                              dOut.stride(0), b, C.byref(gs), N, _ptr(G2),
+                                              G2.stride(0), _ptr(G2T), G2T.stride(0),
+                                              _stream(dev)), "gn_edge_grad_z_mask")
+
+
+def ell_reverse(graph: Graph, ptr: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+    """(rstart [N], rcount [N], rslot [N*stride]): the slots of an ELL graph grouped by source."""
+    dev = _require_cuda(graph.col, ptr)
+    N, S = graph.num_nodes, graph.ell_stride
+    assert S > 0 and ptr.dtype == torch.int32
+    rstart = torch.empty(N, dtype=torch.int32, device=dev)
+    rcount = torch.empty(N, dtype=torch.int32, device=dev)
+    rslot = torch.empty(max(N * S, 1), dtype=torch.int32, device=dev)
+    gs = graph.c_struct()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_ell_reverse(C.byref(gs), _ptr(ptr), N, ptr.shape[0] - 1, _ptr(rstart),
+                                         _ptr(rcount), _ptr(rslot), _stream(dev)), "gn_ell_reverse")
+    return rstart, rcount, rslot
+
+
+def edge_grad_pq_gather(dH: Tensor, P: Tensor, Q: Tensor, Kp: int, graph: Graph, ptr: Tensor,
+                        reverse: Optional[Tuple[Tensor, Tensor, Tensor]], dP: Tensor, dQ: Tensor,
+                        dP32: Optional[Tensor] = None, dQ32: Optional[Tensor] = None) -> None:
+    """dP / dQ (bf16, fp32 copies) from dH.  `reverse` None: one pass, dQ accumulated in `dQ32`
+    (required) by vector reductions; `ell_reverse(...)`: list form, fixed summation order."""
+    dev = _require_cuda(dH, P, Q, dP, dQ, dP32, dQ32)
+    assert dH.dtype == torch.bfloat16 and P.dtype == torch.float16 and Q.dtype == torch.float16
+    assert dP.dtype == torch.bfloat16 and dQ.dtype == torch.bfloat16
+    N = dP.shape[0]
+    rstart, rcount, rslot = reverse if reverse is not None else (None, None, None)
+    gs = graph.c_struct()
+    with torch.cuda.device(dev):
+        check(_lib.load().gn_edge_grad_pq_gather(
+            _ptr(dH), dH.stride(0), _ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp, C.byref(gs),
+            _ptr(ptr), N, ptr.shape[0] - 1, _ptr(rstart), _ptr(rcount), _ptr(rslot),
+            _ptr(dP), dP.stride(0), _ptr(dQ), dQ.stride(0),
+            _ptr(dP32), 0 if dP32 is None else dP32.stride(0),
+            _ptr(dQ32), 0 if dQ32 is None else dQ32.stride(0), _stream(dev)),
+            "gn_edge_grad_pq_gather")
 
 
 def edge_grad_pq(dH: Tensor, H: Tensor, Kp: int, graph: Graph, dP: Tensor, dQ: Tensor,

@@ -16,6 +16,7 @@ pulses, and the global variables derived from it) needs none.
 
 from __future__ import annotations
 
+import os
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -148,31 +149,40 @@ def _backward(model, sv: Dict[str, Any], dout: Tensor) -> List[Optional[Tensor]]
         S = graph.ell_stride
         E = N * S
         Ep = (E + 7) // 8 * 8
-        H = torch.empty((E, Kp), dtype=torch.bfloat16, device=dev)
-        HT = torch.empty((Kp, Ep), dtype=torch.bfloat16, device=dev)
-        ops.edge_build_h(P, Q, Kp, graph, H, HT)
-        W2b = pk.W2p.to(torch.bfloat16)                                     # [b16, Kp]
-        Z = torch.empty((E, b16), dtype=torch.bfloat16, device=dev)
-        ops.tc_linear_bf16(H, W2b, None, Z, K=Kp, act="none")
-        dOut = dskip[:, L["off_out"]:L["off_out"] + b]
+        mask = L.get("relu_mask")
         if b % 2:
             raise NotImplementedError("training needs an even EdgeConv output width")
+        dOut = dskip[:, L["off_out"]:L["off_out"] + b]
         alloc = torch.zeros if b16 != b else torch.empty   # pad columns feed the GEMMs as zeros
+        HT = torch.empty((Kp, Ep), dtype=torch.bfloat16, device=dev)
+        W2b = pk.W2p.to(torch.bfloat16)                                     # [b16, Kp]
         G2 = alloc((E, b16), dtype=torch.bfloat16, device=dev)
         G2T = alloc((b16, Ep), dtype=torch.bfloat16, device=dev)
-        ops.edge_grad_z(Z, dOut, b, graph, G2, G2T)
-        del Z
+        if mask is not None:
+            # the forward recorded the ReLU bits of the second Linear: no Z, no row-major H
+            ops.edge_build_h(P, Q, Kp, graph, None, HT)
+            ops.edge_grad_z_mask(mask, dOut, b, graph, G2, G2T)
+        else:
+            H = torch.empty((E, Kp), dtype=torch.bfloat16, device=dev)
+            ops.edge_build_h(P, Q, Kp, graph, H, HT)
+            Z = torch.empty((E, b16), dtype=torch.bfloat16, device=dev)
+            ops.tc_linear_bf16(H, W2b, None, Z, K=Kp, act="none")
+            ops.edge_grad_z(Z, dOut, b, graph, G2, G2T)
+            del Z, H
         dW2p = torch.zeros((b16, Kp), dtype=torch.float32, device=dev)
         ops.tc_linear_accumulate(G2T, HT, dW2p, K=E, splits=0)
         dH = torch.empty((E, Kp), dtype=torch.bfloat16, device=dev)
         ops.tc_linear_bf16(G2, _t16(W2b), None, dH, K=b16, act="none")
         del G2, G2T, HT
+        # dP, dQ: every node sums its own slots (dP, registers) and the slots that name it (dQ:
+        # vector reductions into dQf; GN_PQ_LISTS=1: through the graph grouped by source, a
+        # fixed summation order at the price of a second read of dH)
         dPQ = torch.empty((N, 2 * Kp), dtype=torch.bfloat16, device=dev)
-        dQf = torch.zeros((N, Kp), dtype=torch.float32, device=dev)
         dP32 = torch.empty((N, Kp), dtype=torch.float32, device=dev) if pk.first else None
-        ops.edge_grad_pq(dH, H, Kp, graph, dPQ[:, :Kp], dQf, dP32)
-        ops.relu_backward(dQf, None, out=dPQ[:, Kp:])
-        del dH, H
+        dQf = torch.empty((N, Kp), dtype=torch.float32, device=dev)   # fp32 accumulator of dQ
+        rev = ops.ell_reverse(graph, ptr) if os.environ.get("GN_PQ_LISTS") else None
+        ops.edge_grad_pq_gather(dH, P, Q, Kp, graph, ptr, rev, dPQ[:, :Kp], dPQ[:, Kp:], dP32, dQf)
+        del dH
         db1 = torch.zeros(Kp, dtype=torch.float32, device=dev)
         ops.colsum_accumulate(dPQ[:, :Kp], db1)
         off_in = L["off_in"]
@@ -183,7 +193,6 @@ def _backward(model, sv: Dict[str, Any], dout: Tensor) -> List[Optional[Tensor]]
         else:
             dPQT = ops.transpose_16(dPQ)                                    # [2Kp, Np]
             ops.tc_linear_accumulate(dPQT, skipT[off_in:off_in + d_in], dWpq, K=N, splits=0)
-        del dQf
         if not pk.first:  # gradient with respect to the layer input: onto its skip slice
             Wpq = torch.cat([pk.Wp, pk.Wq], 0)                              # [2Kp, Kd] bf16
             ops.tc_linear_accumulate(dPQ, _t16(Wpq[:, :d_in]), dskip[:, off_in:], K=2 * Kp,

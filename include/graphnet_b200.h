@@ -223,6 +223,21 @@ int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t 
                              const int32_t* coord_cols, int ncoord, void* scratch,
                              size_t scratch_bytes, void* stream);
 
+/* Training forward of the same op: additionally records the ReLU pattern of the second Linear
+ * (what torch autograd keeps as the saved output of the ReLU in PyG's EdgeConv.message,
+ * components/layers.py:67) as bits, so that the backward pass need not recompute Z = H W2^T.
+ * relu_mask [8, mask_ld] uint32: bit c of word (g, r) = [z(r, 32 g + c) > 0], where slot
+ * e = i*slots + t of the ELL graph is row r = (e / used)*64 + e % used, used = (64/slots)*slots.
+ * mask_ld >= gn_tc_edge_relu_mask_ld(N, slots).  Needs an ELL graph whose stride is a supported
+ * slot count (every kNN graph of this library); otherwise GN_ERR_UNSUPPORTED. */
+int64_t gn_tc_edge_relu_mask_ld(int64_t N, int slots);
+int gn_tc_edge_mlp_aggregate_mask(const void* P, int64_t ldp, const void* Q, int64_t ldq, int Kp,
+                                  const gn_graph* graph, int64_t N, int slots, const void* W2p,
+                                  int b, void* out, int64_t ldo, int out_dtype, float* coords,
+                                  const int32_t* coord_cols, int ncoord, void* scratch,
+                                  size_t scratch_bytes, uint32_t* relu_mask, int64_t mask_ld,
+                                  void* stream);
+
 /* ---- task heads ----------------------------------------------------------- */
 
 /* The `_forward` of a reconstruction head (models/task/reconstruction.py) applied
@@ -285,7 +300,7 @@ int gn_relu_backward(const void* dY, int dy_dtype, int64_t ld_dy, const void* Y,
 /* Re-materialise the hidden activations of the EdgeConv message MLP (PyG EdgeConv.message,
  * components/layers.py:67) for every slot of an ELL graph (stride = slots per node, -1 = empty):
  * H[i*stride + t, :] = ReLU(P_i + Q_j), zero rows for empty slots; bf16.  HT (optional) receives
- * the transpose [Kp, N*stride] (row stride ldht). */
+ * the transpose [Kp, N*stride] (row stride ldht); H may be NULL when only HT is wanted. */
 int gn_edge_build_h(const void* P, int64_t ldp, const void* Q, int64_t ldq, int Kp,
                     const gn_graph* graph, int64_t N, void* H, int64_t ldh, void* HT,
                     int64_t ldht, void* stream);
@@ -296,6 +311,34 @@ int gn_edge_build_h(const void* P, int64_t ldp, const void* Q, int64_t ldq, int 
 int gn_edge_grad_z(const void* Z, int64_t ldz, const float* dOut, int64_t ldd, int b,
                    const gn_graph* graph, int64_t N, void* G2, int64_t ldg, void* G2T,
                    int64_t ldgt, void* stream);
+
+/* The same from the bits recorded by gn_tc_edge_mlp_aggregate_mask (no Z): G2[e, :] =
+ * dOut[target(e), :] where the forward's z(e, :) was positive, else 0. */
+int gn_edge_grad_z_mask(const uint32_t* relu_mask, int64_t mask_ld, const float* dOut, int64_t ldd,
+                        int b, const gn_graph* graph, int64_t N, void* G2, int64_t ldg, void* G2T,
+                        int64_t ldgt, void* stream);
+
+/* Slots of an ELL graph grouped by SOURCE node (the transposed adjacency autograd's scatter-add
+ * of x_j's gradient walks implicitly, components/layers.py:67): for node j the slots e with
+ * nbr[e] == j, ascending, are rslot[rstart[j] .. rstart[j] + rcount[j]).  ptr [B+1] event offsets
+ * (edges never leave an event); rstart, rcount [N], rslot [N*stride] int32. */
+int gn_ell_reverse(const gn_graph* graph, const int32_t* ptr, int64_t N, int64_t B,
+                   int32_t* rstart, int32_t* rcount, int32_t* rslot, void* stream);
+
+/* Backward of h = ReLU(P_i + Q_j) without global atomics: m[e] = dH[e] * [P_i + Q_j > 0] (fp16
+ * sum, as the forward kernel forms it); dP[i] = sum of m over the slots of node i, dQ[j] = sum of
+ * m over the slots that name j as neighbour; bf16 outputs (overwritten), optional fp32 copies
+ * dP32 / dQ32.  dH bf16 [N*stride, lddh]; P, Q fp16; Kp a multiple of 8; 16-byte aligned rows.
+ * rstart == NULL (default): one streaming pass over dH; dQ is accumulated in dQ32 (required,
+ * zeroed by the call) with 16-byte vector reductions and then rounded to dQ (the order of those
+ * additions is not fixed: results agree to fp32 rounding between runs).  rstart, rcount, rslot
+ * from gn_ell_reverse: the list form - every dQ row is a plain sum in slot order
+ * (bit-reproducible), at the price of reading dH twice. */
+int gn_edge_grad_pq_gather(const void* dH, int64_t lddh, const void* P, int64_t ldp, const void* Q,
+                           int64_t ldq, int Kp, const gn_graph* graph, const int32_t* ptr,
+                           int64_t N, int64_t B, const int32_t* rstart, const int32_t* rcount,
+                           const int32_t* rslot, void* dP, int64_t lddp, void* dQ, int64_t lddq,
+                           float* dP32, int64_t ldp32, float* dQ32, int64_t ldq32, void* stream);
 
 /* Backward of h = ReLU(P_i + Q_j): m = dH * [H > 0]; dP[i] = sum over the slots of node i (bf16,
  * overwritten; dP32, if not NULL, receives the same sums unrounded), dQ[j] += m (fp32, must be

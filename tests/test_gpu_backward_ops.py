@@ -54,13 +54,13 @@ def test_transpose_colsum_relu_backward(dev):
                 assert torch.equal(out, ref.to(torch.bfloat16))
 
 
-def _random_ell(dev, g, B=37, k=8):
+def _random_ell(dev, g, B=37, k=8, stride=None):
     import graphnet_b200.ops as ops
     from graphnet_b200.synthetic import make_pulse_batch
     pb = make_pulse_batch(B, 20.0, seed=5)
     x = pb.x.to(dev)
     ptr, _ = ops.batch_to_ptr(pb.batch.to(dev), B)
-    ell = ops.knn_graph_ell(x, k, ptr, [0, 1, 2])
+    ell = ops.knn_graph_ell(x, k, ptr, [0, 1, 2], stride=stride)
     return x.shape[0], ptr, ell
 
 
@@ -108,6 +108,118 @@ def test_edge_backward_blocks(dev):
     dQref = torch.zeros((N, Kp), device=dev).index_add_(0, nbr.clamp_min(0), m)
     assert _rel(dP.float(), dPref) < 5e-3
     assert _rel(dQ, dQref) < 1e-5
+
+
+def test_edge_grad_pq_gather_matches_scatter(dev):
+    """dP / dQ by gathering through the graph grouped by source (gn_ell_reverse +
+    gn_edge_grad_pq_gather) against torch's index_add_; HT-only gn_edge_build_h."""
+    import graphnet_b200.ops as ops
+    g = torch.Generator(device=dev).manual_seed(11)
+    for B, k in ((12, 8), (3, 16), (40, 4)):
+        N, ptr, ell = _random_ell(dev, g, B=B, k=k)
+        KP = ell.ell_stride
+        E = N * KP
+        Ep = (E + 7) // 8 * 8
+        Kp = 96
+        P = (torch.randn((N, Kp), generator=g, device=dev) * 0.5).half()
+        Q = (torch.randn((N, Kp), generator=g, device=dev) * 0.5).half()
+        nbr = ell.col.reshape(-1).long()
+        filled = nbr >= 0
+        tgt = torch.arange(N, device=dev).repeat_interleave(KP)
+        # reverse lists: every filled slot exactly once, grouped by source, ascending
+        rstart, rcount, rslot = ops.ell_reverse(ell, ptr)
+        assert int(rcount.sum()) == int(filled.sum())
+        assert torch.equal(rcount.long(), torch.bincount(nbr[filled], minlength=N))
+        rs, rc, sl = rstart.tolist(), rcount.tolist(), rslot.tolist()
+        nb = nbr.tolist()
+        for j in range(N):
+            lst = sl[rs[j]:rs[j] + rc[j]]
+            assert lst == sorted(lst) and all(nb[e] == j for e in lst)
+        HT = torch.zeros((Kp, Ep), dtype=torch.bfloat16, device=dev)
+        ops.edge_build_h(P, Q, Kp, ell, None, HT)
+        pre = (P[tgt] + Q[nbr.clamp_min(0)])                     # fp16 sum, as the forward forms it
+        Href = torch.relu(P.float()[tgt] + Q.float()[nbr.clamp_min(0)]) * filled[:, None]
+        assert torch.equal(HT[:, :E], Href.to(torch.bfloat16).t())
+        dH = torch.randn((E, Kp), generator=g, device=dev).to(torch.bfloat16)
+        dPQ = torch.full((N, 2 * Kp), 9.0, dtype=torch.bfloat16, device=dev)
+        dP32 = torch.empty((N, Kp), dtype=torch.float32, device=dev)
+        dQ32 = torch.empty((N, Kp), dtype=torch.float32, device=dev)
+        ops.edge_grad_pq_gather(dH, P, Q, Kp, ell, ptr, (rstart, rcount, rslot), dPQ[:, :Kp],
+                                dPQ[:, Kp:], dP32, dQ32)
+        m = dH.float() * (pre.float() > 0) * filled[:, None]
+        dPref = m.reshape(N, KP, Kp).sum(1)
+        dQref = torch.zeros((N, Kp), device=dev).index_add_(0, nbr.clamp_min(0), m)
+        assert _rel(dP32, dPref) < 1e-6 and _rel(dQ32, dQref) < 1e-6
+        assert torch.equal(dPQ[:, :Kp], dP32.to(torch.bfloat16))
+        assert torch.equal(dPQ[:, Kp:], dQ32.to(torch.bfloat16))
+        # without the fp32 copies, and twice: same bits (fixed summation order)
+        again = torch.empty_like(dPQ)
+        ops.edge_grad_pq_gather(dH, P, Q, Kp, ell, ptr, ops.ell_reverse(ell, ptr), again[:, :Kp],
+                                again[:, Kp:])
+        assert torch.equal(again, dPQ)
+        # default form: one pass, dQ accumulated by vector reductions (order of additions not fixed)
+        one = torch.full((N, 2 * Kp), 9.0, dtype=torch.bfloat16, device=dev)
+        p32 = torch.empty((N, Kp), dtype=torch.float32, device=dev)
+        q32 = torch.empty((N, Kp), dtype=torch.float32, device=dev)
+        ops.edge_grad_pq_gather(dH, P, Q, Kp, ell, ptr, None, one[:, :Kp], one[:, Kp:], p32, q32)
+        assert torch.equal(p32, dP32) and _rel(q32, dQref) < 1e-6
+        assert torch.equal(one[:, :Kp], dPQ[:, :Kp])
+        assert torch.equal(one[:, Kp:], q32.to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("k,a,b", [(8, 336, 256), (16, 128, 256), (4, 40, 48), (8, 62, 130)])
+def test_edge_relu_bits_and_grad_z_mask(dev, k, a, b):
+    """The training forward records [z > 0] of the second EdgeConv Linear as bits; the backward
+    builds G2 from them.  Bits against z recomputed in fp64 from the same fp16 operands (they
+    may differ only where z is within rounding of 0); G2 / G2T exactly dOut under those bits;
+    the forward output is unchanged by recording."""
+    import graphnet_b200.ops as ops
+    from graphnet_b200.dynedge_bf16 import _slots, _round_up
+    g = torch.Generator(device=dev).manual_seed(k + a)
+    N, ptr, ell = _random_ell(dev, g, B=30, k=k, stride=_slots(k))
+    KP = ell.ell_stride
+    E = N * KP
+    Ep = (E + 7) // 8 * 8
+    Kp, b16 = _round_up(a + 2, 32), _round_up(b, 16)
+    P = torch.zeros((N, Kp), device=dev)
+    Q = torch.zeros((N, Kp), device=dev)
+    P[:, :a] = torch.randn((N, a), generator=g, device=dev)
+    P[:, a:a + 2] = 1.0
+    Q[:, :a] = torch.randn((N, a), generator=g, device=dev)
+    P, Q = P.half(), Q.half()
+    W2p = torch.zeros((b16, Kp), device=dev)
+    W2p[:b, :a + 2] = torch.randn((b, a + 2), generator=g, device=dev) / a ** 0.5
+    W2p = W2p.half()
+    out0 = torch.empty((N, b16), dtype=torch.bfloat16, device=dev)
+    out1 = torch.empty((N, b16), dtype=torch.bfloat16, device=dev)
+    ops.tc_edge_mlp_aggregate(P, Q, Kp, ell, KP, W2p, b, out0, None, [])
+    mask = ops.edge_relu_mask(N, KP, dev)
+    mask.fill_(-1)
+    ops.tc_edge_mlp_aggregate(P, Q, Kp, ell, KP, W2p, b, out1, None, [], relu_mask=mask)
+    assert torch.equal(out0[:, :b], out1[:, :b])
+    # decode: slot e -> row (e // used) * 64 + e % used; channel c -> word c // 32, bit c % 32
+    used = (64 // KP) * KP
+    e = torch.arange(E, device=dev)
+    rows = (e // used) * 64 + e % used
+    c = torch.arange(b, device=dev)
+    words = mask[(c // 32)[None, :], rows[:, None]]
+    bits = ((words >> (c % 32)[None, :]) & 1).bool()
+    nbr = ell.col.reshape(-1).long()
+    filled = nbr >= 0
+    tgt = torch.arange(N, device=dev).repeat_interleave(KP)
+    h = torch.relu((P[tgt] + Q[nbr.clamp_min(0)]).double()) * filled[:, None]
+    z = h @ W2p[:b].double().t()
+    assert not bool(bits[~filled].any())
+    wrong = bits != (z > 0)
+    assert float(z[wrong].abs().max() if bool(wrong.any()) else 0.0) < 1e-3
+    assert float(wrong.float().mean()) < 1e-3
+    dOut = torch.randn((N, b16), generator=g, device=dev)[:, :b]   # a slice, as dskip's is
+    G2 = torch.empty((E, b16), dtype=torch.bfloat16, device=dev)
+    G2T = torch.zeros((b16, Ep), dtype=torch.bfloat16, device=dev)
+    ops.edge_grad_z_mask(mask, dOut, b, ell, G2, G2T)
+    G2ref = (dOut[tgt] * bits).to(torch.bfloat16)
+    assert torch.equal(G2[:, :b], G2ref)
+    assert torch.equal(G2T[:b, :E], G2ref.t())
 
 
 def test_segment_pool_backward(dev):
