@@ -87,6 +87,8 @@ SIGNATURES = {
     "gn_ell_reverse": (_int, [_gp, _p, _i64, _i64, _p, _p, _p, _p]),
     "gn_edge_grad_pq_gather": (_int, [_p, _i64, _p, _i64, _p, _i64, _int, _gp, _p, _i64, _i64, _p, _p, _p,
                                       _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p]),
+    "gn_edgeconv_pack_tc": (_int, [_p, _p, _p, _p, _int, _int, _int, _int, _int, _p, _int, _p, _p, _p, _p, _p,
+                                   _p]),
     "gn_task_head": (_int, [_p, _i64, _int, _int, _p, _p]),
 }
 

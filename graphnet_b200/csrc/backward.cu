@@ -514,6 +514,78 @@ __global__ void __launch_bounds__(256) edge_grad_pq_scatter_kernel(
   pq_store(acc, dP + i * lddp + col, dP32 ? dP32 + i * ldp32 + col : nullptr);
 }
 
+// ------------------------------------------------------------------ EdgeConv weight repacking
+// One launch per layer and parameter version (in training: per step) instead of two dozen
+// small tensor ops on the host.  From nn.Linear's W1 [a, 2d], b1 [a], W2 [b, a], b2 [b]
+// (reference gnn/dynedge.py:193-204) to the layouts the tensor-core kernels read:
+//   Wpq  [2Kp, Kd]  rows 0..a-1 = W1[:, :d] - W1[:, d:] (acts on x_i), rows Kp..Kp+a-1 = W1[:, d:]
+//                   (acts on x_j); fp32 (first layer) or 16-bit
+//   bias [2Kp]      b1, then 1, 1 (the "ones" columns that carry b2), zeros
+//   W2p  [b16, Kp]  fp16: W2, column a = hi(b2), a+1 = lo(b2)
+// and, for the backward pass (pointers may be null): W2b = bf16(W2p), W2bT [Kp, b16] its
+// transpose, WpqT [Kd, 2Kp] the transpose of the 16-bit Wpq.
+struct PackParams {
+  const float *W1, *b1, *W2, *b2;
+  int d, a, b, Kp, Kd, b16;
+  void* Wpq;
+  int wpq_dtype;  // GN_F32 / GN_BF16 / GN_F16
+  float* bias;
+  __half* W2p;
+  __nv_bfloat16 *W2b, *W2bT;
+  void* WpqT;  // same dtype as Wpq (16-bit only)
+};
+
+__device__ __forceinline__ void store_as(void* base, int64_t idx, int dtype, float v) {
+  if (dtype == GN_F32) reinterpret_cast<float*>(base)[idx] = v;
+  else if (dtype == GN_BF16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16_rn(v);
+  else reinterpret_cast<__half*>(base)[idx] = __float2half_rn(v);
+}
+
+__global__ void __launch_bounds__(256) edgeconv_pack_tc_kernel(PackParams p) {
+  const int64_t n_pq = (int64_t)2 * p.Kp * p.Kd;
+  const int64_t n_w2 = (int64_t)p.b16 * p.Kp;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n_pq + n_w2 + 2 * p.Kp;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    if (idx < n_pq) {
+      const int r = (int)(idx / p.Kd), c = (int)(idx % p.Kd);
+      const int row = r < p.Kp ? r : r - p.Kp;
+      float v = 0.f;
+      if (row < p.a && c < p.d) {
+        const float wa = p.W1[(int64_t)row * 2 * p.d + c];
+        const float wb = p.W1[(int64_t)row * 2 * p.d + p.d + c];
+        v = r < p.Kp ? wa - wb : wb;
+      }
+      store_as(p.Wpq, idx, p.wpq_dtype, v);
+      if (p.WpqT != nullptr) store_as(p.WpqT, (int64_t)c * 2 * p.Kp + r, p.wpq_dtype, v);
+    } else if (idx < n_pq + n_w2) {
+      const int64_t t = idx - n_pq;
+      const int r = (int)(t / p.Kp), c = (int)(t % p.Kp);
+      __half h = __float2half_rn(0.f);
+      if (r < p.b) {
+        if (c < p.a) {
+          h = __float2half_rn(p.W2[(int64_t)r * p.a + c]);
+        } else if (p.b2 != nullptr && c < p.a + 2) {
+          const float bv = p.b2[r];
+          const __half hi = __float2half_rn(bv);
+          h = c == p.a ? hi : __float2half_rn(bv - __half2float(hi));
+        }
+      }
+      p.W2p[t] = h;
+      if (p.W2b != nullptr) {
+        const __nv_bfloat16 hb = __float2bfloat16_rn(__half2float(h));
+        p.W2b[t] = hb;
+        p.W2bT[(int64_t)c * p.b16 + r] = hb;
+      }
+    } else {
+      const int c = (int)(idx - n_pq - n_w2);
+      float v = 0.f;
+      if (c < p.a) v = p.b1 != nullptr ? p.b1[c] : 0.f;
+      else if (c < p.a + 2) v = 1.f;
+      p.bias[c] = v;
+    }
+  }
+}
+
 // ------------------------------------------------------------------ out += G^T X, X narrow, fp32
 // Weight gradient of the FIRST EdgeConv Linear (K = 2F+5 <= 32 raw input features): out[c, k] +=
 // sum_n G[n, c] X[n, k], all fp32 - the two halves of that gradient are subtracted from each
@@ -675,6 +747,30 @@ static int check_ell(const gn_graph* graph, const char* who) {
     set_error("%s: the graph must be in ELL layout (slot table)", who);
     return GN_ERR_INVALID_ARGUMENT;
   }
+  return GN_OK;
+}
+
+extern "C" int gn_edgeconv_pack_tc(const float* W1, const float* b1, const float* W2,
+                                   const float* b2, int d, int a, int b, int Kp, int Kd,
+                                   void* Wpq, int wpq_dtype, float* bias_pq, void* W2p, void* W2b,
+                                   void* W2bT, void* WpqT, void* stream) {
+  GN_CHECK_ARG(d >= 1 && a >= 1 && b >= 1 && Kp >= a + 2 && Kd >= d, "gn_edgeconv_pack_tc: bad sizes");
+  GN_CHECK_ARG(W1 && W2 && Wpq && bias_pq && W2p, "gn_edgeconv_pack_tc: null pointer");
+  GN_CHECK_ARG(wpq_dtype == GN_F32 || wpq_dtype == GN_BF16 || wpq_dtype == GN_F16,
+               "gn_edgeconv_pack_tc: unknown dtype");
+  GN_CHECK_ARG((W2b == nullptr) == (W2bT == nullptr), "gn_edgeconv_pack_tc: W2b and W2bT go together");
+  GN_CHECK_ARG(WpqT == nullptr || wpq_dtype != GN_F32, "gn_edgeconv_pack_tc: WpqT is 16-bit only");
+  PackParams p;
+  p.W1 = W1; p.b1 = b1; p.W2 = W2; p.b2 = b2;
+  p.d = d; p.a = a; p.b = b; p.Kp = Kp; p.Kd = Kd; p.b16 = (b + 15) & ~15;
+  p.Wpq = Wpq; p.wpq_dtype = wpq_dtype; p.bias = bias_pq;
+  p.W2p = reinterpret_cast<__half*>(W2p);
+  p.W2b = reinterpret_cast<__nv_bfloat16*>(W2b);
+  p.W2bT = reinterpret_cast<__nv_bfloat16*>(W2bT);
+  p.WpqT = WpqT;
+  const int64_t total = (int64_t)2 * Kp * Kd + (int64_t)p.b16 * Kp + 2 * Kp;
+  edgeconv_pack_tc_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, as_stream(stream)>>>(p);
+  GN_LAUNCH_CHECK();
   return GN_OK;
 }
 

@@ -41,8 +41,7 @@ class _ConvPack:
     """Repacked weights of one DynEdgeConv MLP for the tensor-core kernels."""
 
     def __init__(self, l1: torch.nn.Linear, l2: torch.nn.Linear, io_dtype: torch.dtype,
-                 first: bool):
-        dev = l1.weight.device
+                 first: bool, train: bool = False):
         a, d2 = l1.weight.shape
         d = d2 // 2
         b = l2.weight.shape[0]
@@ -52,52 +51,37 @@ class _ConvPack:
                 f"bf16 EdgeConv kernel supports hidden <= 350 and output <= 256 (got {a}, {b}); "
                 "use precision='fp32' for this architecture")
         Kd = d if first else _round_up(d, 8)
-        b16 = _round_up(b, 16)
-        W1 = l1.weight.detach().float()
-        Wpq = torch.zeros((2 * Kp, Kd), dtype=torch.float32, device=dev)
-        Wpq[:a, :d] = W1[:, :d] - W1[:, d:]
-        Wpq[Kp:Kp + a, :d] = W1[:, d:]
-        bias = torch.zeros(2 * Kp, dtype=torch.float32, device=dev)
-        bias[:a] = l1.bias.detach().float() if l1.bias is not None else 0.0
-        bias[a] = 1.0      # the two "ones" columns that carry b2 through the second GEMM
-        bias[a + 1] = 1.0
-        W2p = torch.zeros((b16, Kp), dtype=torch.float32, device=dev)
-        W2p[:b, :a] = l2.weight.detach().float()
-        W2p = W2p.to(torch.float16)  # the hidden layer runs in fp16 (see csrc/tc_edge.cu)
-        if l2.bias is not None:
-            b2 = l2.bias.detach().float()
-            hi = b2.to(torch.float16)
-            lo = (b2 - hi.float()).to(torch.float16)
-            W2p[:b, a] = hi
-            W2p[:b, a + 1] = lo
-        self.d, self.a, self.b, self.Kp, self.Kd, self.b16 = d, a, b, Kp, Kd, b16
+        self.d, self.a, self.b, self.Kp, self.Kd, self.b16 = d, a, b, Kp, Kd, _round_up(b, 16)
         # first layer: fp32 FFMA node GEMM on the fp32 input features; later layers: tcgen05
         self.first = first
-        Wpq = Wpq.contiguous() if first else Wpq.to(io_dtype).contiguous()
-        self.Wp, self.Wq = Wpq[:Kp], Wpq[Kp:]   # P = x Wp^T + bias_p ; Q = x Wq^T
-        self.Wpq = Wpq                           # both in one GEMM: [P | Q] = x Wpq^T + bias_pq
-        self.bias_pq = bias.contiguous()         # (zeros in the Q half)
-        self.bias_p = bias[:Kp].contiguous()
-        self.W2p = W2p.contiguous()
+        # one kernel writes every layout (csrc/backward.cu: edgeconv_pack_tc_kernel): Wpq = [P | Q]
+        # weights (P = x Wp^T + bias_p, Q = x Wq^T), the two "ones" columns that carry b2 through
+        # the second GEMM, W2p in fp16 (the hidden layer runs in fp16, see csrc/tc_edge.cu) and,
+        # in training, the bf16 / transposed copies the backward GEMMs read
+        packed = ops.edgeconv_pack_tc(l1.weight, l1.bias, l2.weight, l2.bias, Kp, Kd,
+                                      torch.float32 if first else io_dtype, train)
+        self.Wpq, self.bias_pq, self.W2p, self.W2b, self.W2bT, self.WpqT = packed
+        self.Wp, self.Wq = self.Wpq[:Kp], self.Wpq[Kp:]
+        self.bias_p = self.bias_pq[:Kp]
 
 
 def _io_dtype(model) -> torch.dtype:
     return torch.float16 if model.precision == "fp16" else torch.bfloat16
 
 
-def _conv_pack(conv, io_dtype: torch.dtype, first: bool) -> _ConvPack:
+def _conv_pack(conv, io_dtype: torch.dtype, first: bool, train: bool = False) -> _ConvPack:
     linears, act = conv._mlp()
     if act != "relu" or len(linears) != 2:
         raise NotImplementedError(
             "precision='bf16' supports Linear-ReLU-Linear-ReLU EdgeConv MLPs; use precision='fp32'")
     if conv.aggr not in ("add", "sum"):
         raise NotImplementedError("precision='bf16' supports aggr='add'; use precision='fp32'")
-    key = f"_cache_tc_{io_dtype}_{first}"
+    key = f"_cache_tc_{io_dtype}_{first}_{train}"
     if not hasattr(conv, key):
         setattr(conv, key, _WeightCache())
     l1, l2 = linears
     params = [p for p in (l1.weight, l1.bias, l2.weight, l2.bias) if p is not None]
-    return getattr(conv, key).get(params, lambda: _ConvPack(l1, l2, io_dtype, first))
+    return getattr(conv, key).get(params, lambda: _ConvPack(l1, l2, io_dtype, first, train))
 
 
 def _skip_layout(model) -> Tuple[int, List[int], List[int], int]:
@@ -172,7 +156,7 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
     off_in, d_in = 0, D0
     convs = list(model._conv_layers)
     for li, conv in enumerate(convs):
-        pk = _conv_pack(conv, io, first=(li == 0))
+        pk = _conv_pack(conv, io, first=(li == 0), train=save is not None)
         assert pk.d == d_in
         # one node GEMM writes [P | Q] (the layer input is read once); the edge kernel takes the
         # two halves as strided matrices

@@ -37,7 +37,27 @@ def _require_cuda(*tensors: Optional[Tensor]) -> torch.device:
 
 
 def _stream(dev: torch.device) -> C.c_void_p:
-    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    # the raw handle of torch's current stream (no Stream object per call)
+    return C.c_void_p(torch._C._cuda_getCurrentRawStream(dev.index if dev.index is not None
+                                                         else torch.cuda.current_device()))
+
+
+class _NoSwitch:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NO_SWITCH = _NoSwitch()
+
+
+def _on(dev: torch.device):
+    """Context that makes `dev` the current CUDA device - free when it already is."""
+    if dev.index is None or dev.index == torch.cuda.current_device():
+        return _NO_SWITCH
+    return torch.cuda.device(dev)
 
 
 def _ptr(t: Optional[Tensor]) -> C.c_void_p:
@@ -79,7 +99,7 @@ def batch_to_ptr(batch: Tensor, num_events: int) -> Tuple[Tensor, Tensor]:
         batch = batch.long()
     ptr = torch.empty(num_events + 1, dtype=torch.int32, device=dev)
     flags = torch.zeros(1, dtype=torch.int32, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_batch_to_ptr(_ptr(batch), batch.shape[0], num_events, _ptr(ptr),
                                           _ptr(flags), _stream(dev)), "gn_batch_to_ptr")
     return ptr, flags
@@ -104,7 +124,7 @@ def knn_graph_ell(x: Tensor, k: int, ptr: Tensor, columns: Sequence[int], loop: 
     stride = kk if stride is None else stride
     nbr = torch.empty((N, stride), dtype=torch.int32, device=dev)
     deg = torch.empty(N, dtype=torch.int32, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_knn_graph(_ptr(x), x.stride(0), _host_i32(columns), len(columns),
                                        _ptr(ptr), N, B, k, int(loop), _ptr(nbr), stride,
                                        _ptr(deg), _stream(dev)), "gn_knn_graph")
@@ -120,7 +140,7 @@ def ell_to_coo(g: Graph) -> Tensor:
     rowptr = torch.empty(N + 1, dtype=torch.int64, device=dev)
     nbytes = lib.gn_scan_scratch_bytes(N)
     scratch = torch.empty(max(nbytes, 8), dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(lib.gn_ell_row_offsets(_ptr(g.deg), N, _ptr(rowptr), _ptr(scratch), nbytes,
                                      _stream(dev)), "gn_ell_row_offsets")
         E = int(rowptr[N].item())
@@ -167,7 +187,7 @@ def coo_to_csr(edge_index: Tensor, num_nodes: int) -> Graph:
     col = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
     flags = torch.zeros(1, dtype=torch.int32, device=dev)
     maxdeg = torch.empty(1, dtype=torch.int32, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_coo_to_csr(_ptr(ei), E, num_nodes, _ptr(rowptr), _ptr(col),
                                         _ptr(flags), _ptr(maxdeg), _stream(dev)), "gn_coo_to_csr")
     return Graph(col=col, deg=None, rowptr=rowptr, ell_stride=0, num_nodes=num_nodes,
@@ -197,7 +217,7 @@ def global_variables(x: Tensor, graph: Graph, ptr: Tensor, n_pulses: Tensor,
             outs.append((_DT[t.dtype], t.stride(0)))
         else:
             outs.append((DTYPE_F32, 0))
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_global_variables(
             _ptr(x), x.stride(0), F, C.byref(gs), _ptr(ptr), _ptr(n_pulses), N, B, _ptr(gv),
             _ptr(x0), outs[0][1], x0_cols, outs[0][0], _ptr(x0b), outs[1][1], x0b_cols,
@@ -217,7 +237,7 @@ def segment_pool(x: Tensor, ptr: Tensor, schemes: Sequence[str],
         out = torch.empty((B, C_ * P), dtype=torch.float32, device=dev)
     assert out.dtype == torch.float32 and out.stride(1) == 1
     dt = DTYPE_BF16 if x.dtype == torch.bfloat16 else DTYPE_F32
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_segment_pool(_ptr(x), dt, x.stride(0), C_, _ptr(ptr), B,
                                           _host_i32([POOL[s] for s in schemes]), P, _ptr(out),
                                           out.stride(0), _stream(dev)), "gn_segment_pool")
@@ -239,7 +259,7 @@ def linear_f32(A: Tensor, W: Tensor, bias: Optional[Tensor], act: str = "none",
     assert out.stride(1) == 1 and out.shape[0] == M and out.shape[1] >= Nout
     b = None if bias is None else bias.detach().contiguous()
     dt = {torch.bfloat16: DTYPE_BF16, torch.float16: DTYPE_F16, torch.float32: DTYPE_F32}[out.dtype]
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_linear_f32(_ptr(A), A.stride(0), _ptr(W), _ptr(b), _ptr(out),
                                         out.stride(0), dt, M, Nout, K, ACT[act], _stream(dev)),
               "gn_linear_f32")
@@ -261,7 +281,7 @@ def edgeconv_prepare_f32(W1: Tensor, W2: Optional[Tensor]) -> Tuple[Tensor, Opti
         W2T = torch.empty((a, b), dtype=torch.float32, device=dev)
     else:
         b, W2T = a, None
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_edgeconv_prepare_f32(_ptr(W1), _ptr(W2), d, a, b, _ptr(Wpq),
                                                   _ptr(W2T), _stream(dev)),
               "gn_edgeconv_prepare_f32")
@@ -288,7 +308,7 @@ def edgeconv_f32(x: Tensor, graph: Graph, Wpq: Tensor, b1: Optional[Tensor],
     if b2 is None and W2T is not None:
         b2 = torch.zeros(b, dtype=torch.float32, device=dev)
     gs = graph.c_struct()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_edgeconv_f32(
             _ptr(x), x.stride(0), d, C.byref(gs), N, _ptr(Wpq), _ptr(b1.detach().contiguous()), a,
             _ptr(W2T), _ptr(None if b2 is None else b2.detach().contiguous()), b, ACT[act],
@@ -304,7 +324,7 @@ def task_head(y: Tensor, kind: str) -> Tensor:
     code = HEAD[kind]
     p_out = 4 if code == 2 else (2 if code in (4, 5) else (1 if code == 3 else p))
     out = torch.empty((M, p_out), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_task_head(_ptr(y), M, p, code, _ptr(out), _stream(dev)),
               "gn_task_head")
     return out
@@ -321,7 +341,7 @@ def tc_linear_bf16(A: Tensor, W: Tensor, bias: Optional[Tensor], out: Tensor, K:
     Nout = W.shape[0]
     assert out.shape[0] == M and out.shape[1] >= Nout and A.shape[1] >= K and W.shape[1] >= K
     dt = {torch.bfloat16: DTYPE_BF16, torch.float16: DTYPE_F16, torch.float32: DTYPE_F32}[out.dtype]
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_tc_linear(_ptr(A), A.stride(0), _ptr(W), W.stride(0), _DT[A.dtype],
                                        _ptr(bias), _ptr(out), out.stride(0), dt, M, Nout, K,
                                        ACT[act], _stream(dev)), "gn_tc_linear")
@@ -345,7 +365,7 @@ def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: in
     nbytes = lib.gn_tc_edge_scratch_bytes(C.byref(gs), N, slots)
     scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     ncoord = 0 if coords is None else len(coord_cols)
-    with torch.cuda.device(dev):
+    with _on(dev):
         if relu_mask is not None:
             assert relu_mask.dtype == torch.int32 and relu_mask.shape[0] == 8 \
                 and relu_mask.stride(1) == 1
@@ -362,6 +382,35 @@ def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: in
             _host_i32(coord_cols) if ncoord else None,
             ncoord, _ptr(scratch), nbytes, _stream(dev)), "gn_tc_edge_mlp_aggregate")
     return out
+
+
+def edgeconv_pack_tc(W1: Tensor, b1: Optional[Tensor], W2: Tensor, b2: Optional[Tensor], Kp: int,
+                     Kd: int, wpq_dtype: torch.dtype, train: bool):
+    """(Wpq, bias_pq, W2p, W2b, W2bT, WpqT) for the tensor-core EdgeConv kernels from the
+    nn.Linear parameters, in one launch; the last three only when `train` (else None)."""
+    dev = _require_cuda(W1, b1, W2, b2)
+    W1, W2 = W1.detach().contiguous(), W2.detach().contiguous()
+    b1 = None if b1 is None else b1.detach().contiguous()
+    b2 = None if b2 is None else b2.detach().contiguous()
+    assert W1.dtype == torch.float32 and W2.dtype == torch.float32
+    a, d2 = W1.shape
+    d, b = d2 // 2, W2.shape[0]
+    b16 = (b + 15) // 16 * 16
+    Wpq = torch.empty((2 * Kp, Kd), dtype=wpq_dtype, device=dev)
+    bias = torch.empty(2 * Kp, dtype=torch.float32, device=dev)
+    W2p = torch.empty((b16, Kp), dtype=torch.float16, device=dev)
+    W2b = W2bT = WpqT = None
+    if train:
+        W2b = torch.empty((b16, Kp), dtype=torch.bfloat16, device=dev)
+        W2bT = torch.empty((Kp, b16), dtype=torch.bfloat16, device=dev)
+        if wpq_dtype != torch.float32:
+            WpqT = torch.empty((Kd, 2 * Kp), dtype=wpq_dtype, device=dev)
+    with _on(dev):
+        check(_lib.load().gn_edgeconv_pack_tc(_ptr(W1), _ptr(b1), _ptr(W2), _ptr(b2), d, a, b, Kp,
+                                              Kd, _ptr(Wpq), _DT[wpq_dtype], _ptr(bias), _ptr(W2p),
+                                              _ptr(W2b), _ptr(W2bT), _ptr(WpqT), _stream(dev)),
+              "gn_edgeconv_pack_tc")
+    return Wpq, bias, W2p, W2b, W2bT, WpqT
 
 
 def edge_relu_mask(N: int, slots: int, device) -> Tensor:
@@ -385,7 +434,7 @@ def tc_linear_accumulate(A: Tensor, W: Tensor, out: Tensor, K: int, splits: int 
     assert A.stride(1) == 1 and W.stride(1) == 1 and out.stride(1) == 1
     M, Nout = A.shape[0], W.shape[0]
     assert out.shape[0] == M and out.shape[1] >= Nout
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_tc_linear_accumulate(_ptr(A), A.stride(0), _ptr(W), W.stride(0),
                                                   _DT[A.dtype], _ptr(out), out.stride(0), M, Nout,
                                                   K, splits, _stream(dev)),
@@ -402,7 +451,7 @@ def transpose_16(src: Tensor, out: Optional[Tensor] = None) -> Tensor:
         ld = (rows + 7) // 8 * 8
         out = torch.empty((cols, ld), dtype=src.dtype, device=dev)
     assert out.stride(1) == 1 and out.shape[0] >= cols and out.shape[1] >= rows
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_transpose_16(_ptr(src), src.stride(0), rows, cols, _ptr(out),
                                           out.stride(0), _stream(dev)), "gn_transpose_16")
     return out
@@ -414,7 +463,7 @@ def colsum_accumulate(X: Tensor, out: Tensor) -> Tensor:
     assert X.stride(1) == 1 and out.dtype == torch.float32 and out.is_contiguous()
     M, N = X.shape
     assert out.numel() >= N
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_colsum_accumulate(_ptr(X), _dt_of(X), X.stride(0), M, N, _ptr(out),
                                                _stream(dev)), "gn_colsum_accumulate")
     return out
@@ -428,7 +477,7 @@ def relu_backward(dY: Tensor, Y: Optional[Tensor], out: Optional[Tensor] = None)
         out = torch.empty((M, (N + 7) // 8 * 8), dtype=torch.bfloat16, device=dev)[:, :N]
     assert out.dtype == torch.bfloat16 and dY.stride(1) == 1 and out.stride(1) == 1
     assert Y is None or (Y.stride(1) == 1 and Y.shape[0] == M and Y.shape[1] >= N)
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_relu_backward(_ptr(dY), _dt_of(dY), dY.stride(0), _ptr(Y),
                                            0 if Y is None else _dt_of(Y),
                                            0 if Y is None else Y.stride(0), _ptr(out),
@@ -443,7 +492,7 @@ def edge_build_h(P: Tensor, Q: Tensor, Kp: int, graph: Graph, H: Optional[Tensor
     assert (H is None or H.dtype == torch.bfloat16) and (H is not None or HT is not None)
     N = P.shape[0]
     gs = graph.c_struct()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_edge_build_h(_ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp,
                                           C.byref(gs), N, _ptr(H),
                                           0 if H is None else H.stride(0), _ptr(HT),
@@ -457,7 +506,7 @@ def edge_grad_z(Z: Tensor, dOut: Tensor, b: int, graph: Graph, G2: Tensor, G2T: 
     assert G2.dtype == torch.bfloat16 and G2T.dtype == torch.bfloat16
     N = dOut.shape[0]
     gs = graph.c_struct()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_edge_grad_z(_ptr(Z), Z.stride(0), _ptr(dOut), dOut.stride(0), b,
                                          C.byref(gs), N, _ptr(G2), G2.stride(0), _ptr(G2T),
                                          G2T.stride(0), _stream(dev)), "gn_edge_grad_z")
@@ -471,7 +520,7 @@ def edge_grad_z_mask(relu_mask: Tensor, dOut: Tensor, b: int, graph: Graph, G2: 
     assert G2.dtype == torch.bfloat16 and G2T.dtype == torch.bfloat16
     N = dOut.shape[0]
     gs = graph.c_struct()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_edge_grad_z_mask(_ptr(relu_mask), relu_mask.stride(0), _ptr(dOut),
                                               dOut.stride(0), b, C.byref(gs), N, _ptr(G2),
                                               G2.stride(0), _ptr(G2T), G2T.stride(0),
@@ -487,7 +536,7 @@ def ell_reverse(graph: Graph, ptr: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
     rcount = torch.empty(N, dtype=torch.int32, device=dev)
     rslot = torch.empty(max(N * S, 1), dtype=torch.int32, device=dev)
     gs = graph.c_struct()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_ell_reverse(C.byref(gs), _ptr(ptr), N, ptr.shape[0] - 1, _ptr(rstart),
                                          _ptr(rcount), _ptr(rslot), _stream(dev)), "gn_ell_reverse")
     return rstart, rcount, rslot
@@ -504,7 +553,7 @@ def edge_grad_pq_gather(dH: Tensor, P: Tensor, Q: Tensor, Kp: int, graph: Graph,
     N = dP.shape[0]
     rstart, rcount, rslot = reverse if reverse is not None else (None, None, None)
     gs = graph.c_struct()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_edge_grad_pq_gather(
             _ptr(dH), dH.stride(0), _ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp, C.byref(gs),
             _ptr(ptr), N, ptr.shape[0] - 1, _ptr(rstart), _ptr(rcount), _ptr(rslot),
@@ -521,7 +570,7 @@ def edge_grad_pq(dH: Tensor, H: Tensor, Kp: int, graph: Graph, dP: Tensor, dQ: T
     assert dP.dtype == torch.bfloat16 and dQ.dtype == torch.float32
     N = dP.shape[0]
     gs = graph.c_struct()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_edge_grad_pq(_ptr(dH), dH.stride(0), _ptr(H), H.stride(0), Kp,
                                           C.byref(gs), N, _ptr(dP), dP.stride(0), _ptr(dQ),
                                           dQ.stride(0), _ptr(dP32),
@@ -537,7 +586,7 @@ def outer_accumulate_f32(G: Tensor, X: Tensor, out: Tensor) -> Tensor:
     N, cols = G.shape
     K = X.shape[1]
     assert X.shape[0] == N and out.shape[0] >= cols and out.shape[1] >= K
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_outer_accumulate_f32(_ptr(G), G.stride(0), cols, _ptr(X), X.stride(0),
                                                   K, N, _ptr(out), out.stride(0), _stream(dev)),
               "gn_outer_accumulate_f32")
@@ -554,7 +603,7 @@ def segment_pool_backward(x: Tensor, ptr: Tensor, schemes: Sequence[str], pooled
     B = ptr.shape[0] - 1
     dX = torch.zeros((N, C_), dtype=torch.float32, device=dev)
     dt = DTYPE_BF16 if x.dtype == torch.bfloat16 else DTYPE_F32
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_segment_pool_backward(
             _ptr(x), dt, x.stride(0), C_, _ptr(ptr), B, _host_i32([POOL[s] for s in schemes]),
             len(schemes), _ptr(pooled), pooled.stride(0), _ptr(d_pooled), d_pooled.stride(0),
@@ -571,7 +620,7 @@ def csr_to_ell(graph: Graph, stride: int) -> Graph:
     nbr = torch.empty((N, stride), dtype=torch.int32, device=dev)
     deg = torch.empty(N, dtype=torch.int32, device=dev)
     flags = graph.flags if graph.flags is not None else torch.zeros(1, dtype=torch.int32, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_csr_to_ell(_ptr(graph.rowptr), _ptr(graph.col), N, stride, _ptr(nbr),
                                         _ptr(deg), _ptr(flags), _stream(dev)), "gn_csr_to_ell")
     return Graph(col=nbr, deg=deg, rowptr=None, ell_stride=stride, num_nodes=N, flags=flags,
@@ -587,7 +636,7 @@ def layernorm_act_(X: Tensor, gamma: Optional[Tensor], beta: Optional[Tensor], e
     M, N = X.shape
     g = None if gamma is None else gamma.detach().float().contiguous()
     b = None if beta is None else beta.detach().float().contiguous()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_layernorm_act_f32(_ptr(X), X.stride(0), M, N, _ptr(g), _ptr(b),
                                                float(eps), ACT[act], _stream(dev)),
               "gn_layernorm_act_f32")
@@ -601,7 +650,7 @@ def edge_preact_f32(pq: Tensor, a: int, graph: Graph) -> Tensor:
     N = pq.shape[0]
     out = torch.empty((N * graph.ell_stride, a), dtype=torch.float32, device=dev)
     gs = graph.c_struct()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_edge_preact_f32(_ptr(pq), a, C.byref(gs), N, _ptr(out), out.stride(0),
                                              _stream(dev)), "gn_edge_preact_f32")
     return out
@@ -614,7 +663,7 @@ def slot_sum_f32(Z: Tensor, graph: Graph, out: Tensor) -> Tensor:
     assert Z.stride(1) == 1 and out.stride(1) == 1
     N, b = out.shape[0], Z.shape[1]
     gs = graph.c_struct()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_slot_sum_f32(_ptr(Z), Z.stride(0), b, C.byref(gs), N, _ptr(out),
                                           out.stride(0), _stream(dev)), "gn_slot_sum_f32")
     return out
@@ -626,7 +675,7 @@ def convert_scale_16(X: Tensor, dtype: torch.dtype, scale: float = 1.0) -> Tenso
     assert X.dtype == torch.float32 and X.stride(1) == 1
     M, N = X.shape
     out = torch.empty((M, (N + 7) // 8 * 8), dtype=dtype, device=dev)[:, :N]
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(_lib.load().gn_convert_scale_16(_ptr(X), X.stride(0), _ptr(out), _DT[dtype],
                                               out.stride(0), M, N, float(scale), _stream(dev)),
               "gn_convert_scale_16")

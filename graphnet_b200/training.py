@@ -155,7 +155,7 @@ def _backward(model, sv: Dict[str, Any], dout: Tensor) -> List[Optional[Tensor]]
         dOut = dskip[:, L["off_out"]:L["off_out"] + b]
         alloc = torch.zeros if b16 != b else torch.empty   # pad columns feed the GEMMs as zeros
         HT = torch.empty((Kp, Ep), dtype=torch.bfloat16, device=dev)
-        W2b = pk.W2p.to(torch.bfloat16)                                     # [b16, Kp]
+        W2b = pk.W2b                                                        # [b16, Kp] bf16
         G2 = alloc((E, b16), dtype=torch.bfloat16, device=dev)
         G2T = alloc((b16, Ep), dtype=torch.bfloat16, device=dev)
         if mask is not None:
@@ -172,7 +172,7 @@ def _backward(model, sv: Dict[str, Any], dout: Tensor) -> List[Optional[Tensor]]
         dW2p = torch.zeros((b16, Kp), dtype=torch.float32, device=dev)
         ops.tc_linear_accumulate(G2T, HT, dW2p, K=E, splits=0)
         dH = torch.empty((E, Kp), dtype=torch.bfloat16, device=dev)
-        ops.tc_linear_bf16(G2, _t16(W2b), None, dH, K=b16, act="none")
+        ops.tc_linear_bf16(G2, pk.W2bT, None, dH, K=b16, act="none")
         del G2, G2T, HT
         # dP, dQ: every node sums its own slots (dP, registers) and the slots that name it (dQ:
         # vector reductions into dQf; GN_PQ_LISTS=1: through the graph grouped by source, a
@@ -194,9 +194,7 @@ def _backward(model, sv: Dict[str, Any], dout: Tensor) -> List[Optional[Tensor]]
             dPQT = ops.transpose_16(dPQ)                                    # [2Kp, Np]
             ops.tc_linear_accumulate(dPQT, skipT[off_in:off_in + d_in], dWpq, K=N, splits=0)
         if not pk.first:  # gradient with respect to the layer input: onto its skip slice
-            Wpq = torch.cat([pk.Wp, pk.Wq], 0)                              # [2Kp, Kd] bf16
-            ops.tc_linear_accumulate(dPQ, _t16(Wpq[:, :d_in]), dskip[:, off_in:], K=2 * Kp,
-                                     splits=1)
+            ops.tc_linear_accumulate(dPQ, pk.WpqT[:d_in], dskip[:, off_in:], K=2 * Kp, splits=1)
         dWp, dWq = dWpq[:a], dWpq[Kp:Kp + a]
         dW1 = torch.cat([dWp, dWq - dWp], 1)                                # [a, 2d]
         linears, _ = model._conv_layers[li]._mlp()

@@ -297,6 +297,16 @@ int gn_colsum_accumulate(const void* X, int x_dtype, int64_t ldx, int64_t M, int
 int gn_relu_backward(const void* dY, int dy_dtype, int64_t ld_dy, const void* Y, int y_dtype,
                      int64_t ld_y, void* out, int64_t ld_out, int64_t M, int N, void* stream);
 
+/* Repack the weights of one EdgeConv MLP (nn.Linear W1 [a, 2d], b1, W2 [b, a], b2; reference
+ * gnn/dynedge.py:193-204) for the tensor-core kernels, in one launch: Wpq [2Kp, Kd] (rows 0..a-1 =
+ * W1[:, :d] - W1[:, d:], rows Kp.. = W1[:, d:]; wpq_dtype GN_F32 for the first layer, else 16-bit),
+ * bias_pq [2Kp] fp32 (b1, then the two "ones" columns), W2p [b16, Kp] fp16 (W2; columns a, a+1 =
+ * b2 split in fp16 hi/lo).  Optional, for the backward pass: W2b = bf16(W2p), W2bT [Kp, b16] its
+ * transpose, WpqT [Kd, 2Kp] the transpose of a 16-bit Wpq.  b1, b2 may be NULL (no bias). */
+int gn_edgeconv_pack_tc(const float* W1, const float* b1, const float* W2, const float* b2, int d,
+                        int a, int b, int Kp, int Kd, void* Wpq, int wpq_dtype, float* bias_pq,
+                        void* W2p, void* W2b, void* W2bT, void* WpqT, void* stream);
+
 /* Re-materialise the hidden activations of the EdgeConv message MLP (PyG EdgeConv.message,
  * components/layers.py:67) for every slot of an ELL graph (stride = slots per node, -1 = empty):
  * H[i*stride + t, :] = ReLU(P_i + Q_j), zero rows for empty slots; bf16.  HT (optional) receives

@@ -41,6 +41,51 @@ def test_tc_linear(M, N, K, act, out_dtype):
     assert torch.allclose(got[:, :N], want, rtol=tol, atol=tol)
 
 
+@pytest.mark.parametrize("d,a,b,first", [(19, 128, 256, True), (256, 336, 256, False),
+                                         (33, 62, 130, True), (130, 40, 48, False)])
+@pytest.mark.parametrize("bias", [True, False])
+def test_edgeconv_pack_tc(d, a, b, first, bias):
+    """The one-launch weight repack against the same layouts built with plain tensor ops."""
+    import graphnet_b200.ops as ops
+    from graphnet_b200.dynedge_bf16 import _round_up
+    g = torch.Generator().manual_seed(d + a + b)
+    W1 = torch.randn(a, 2 * d, generator=g)
+    b1 = torch.randn(a, generator=g) if bias else None
+    W2 = torch.randn(b, a, generator=g)
+    b2 = torch.randn(b, generator=g) if bias else None
+    Kp, b16 = _round_up(a + 2, 32), _round_up(b, 16)
+    Kd = d if first else _round_up(d, 8)
+    io = torch.float32 if first else torch.bfloat16
+    dev = lambda t: None if t is None else t.to(DEV)
+    Wpq, bias_pq, W2p, W2b, W2bT, WpqT = ops.edgeconv_pack_tc(dev(W1), dev(b1), dev(W2), dev(b2),
+                                                              Kp, Kd, io, True)
+    want = torch.zeros(2 * Kp, Kd)
+    want[:a, :d] = W1[:, :d] - W1[:, d:]
+    want[Kp:Kp + a, :d] = W1[:, d:]
+    assert torch.equal(Wpq.cpu(), want.to(io))
+    wb = torch.zeros(2 * Kp)
+    if bias:
+        wb[:a] = b1
+    wb[a:a + 2] = 1.0
+    assert torch.equal(bias_pq.cpu(), wb)
+    w2 = torch.zeros(b16, Kp)
+    w2[:b, :a] = W2
+    w2 = w2.to(torch.float16)
+    if bias:
+        hi = b2.to(torch.float16)
+        w2[:b, a] = hi
+        w2[:b, a + 1] = (b2 - hi.float()).to(torch.float16)
+    assert torch.equal(W2p.cpu(), w2)
+    assert torch.equal(W2b.cpu(), w2.to(torch.bfloat16))
+    assert torch.equal(W2bT.cpu(), w2.to(torch.bfloat16).t())
+    if first:
+        assert WpqT is None
+    else:
+        assert torch.equal(WpqT.cpu(), want.to(io).t())
+    inf = ops.edgeconv_pack_tc(dev(W1), dev(b1), dev(W2), dev(b2), Kp, Kd, io, False)
+    assert torch.equal(inf[0], Wpq) and torch.equal(inf[2], W2p) and inf[3] is None
+
+
 def _edge_reference(pq, Kp, ei, W2p, b, N):
     P, Q = pq[:, :Kp].float(), pq[:, Kp:2 * Kp].float()
     src, dst = ei[0], ei[1]
