@@ -113,14 +113,14 @@ __global__ void __launch_bounds__(LIN_THREADS) linear_f32_kernel(
   }
 }
 
-// Small-K variant (K <= 32, 16-bit output): the first EdgeConv's node GEMM has K = 2F+5 = 19
+// Small-K variant (K <= 36, 16-bit output): the first EdgeConv's node GEMM has K = 2F+5 = 19
 // and is store bound (N*Kp*2 bytes out).  A thread owns two adjacent output columns - its two
 // weight rows (2K values) and biases stay in registers - and a CTA walks SK_ROWS input rows that
 // are staged in shared memory and read with warp-uniform addresses (16-byte broadcasts).  A
 // warp therefore stores 128 contiguous bytes of one output row per instruction; the previous
 // shape of this kernel (a thread per row) wrote 16 bytes per lane 2*N bytes apart.
 // The k order of the sum (bias first, k ascending) is that of the generic kernel above.
-constexpr int SK_MAXK = 32;
+constexpr int SK_MAXK = 36;  // 2F+5 = 33 for the 14 IceCube-Upgrade features
 constexpr int SK_ROWS = 64;
 template <typename OutT, int KMAX>
 __global__ void __launch_bounds__(512) linear_smallk_kernel(
@@ -419,9 +419,11 @@ int linear_f32(const float* A, int64_t lda, const float* W, const float* bias, v
         A, lda, W, bias, reinterpret_cast<T_*>(C), ldc, M, N, K);                                \
   }
     if (c_dtype == GN_F16) {
-      if (K <= 20) GN_SK_CASE(__half, 20) else GN_SK_CASE(__half, 32)
+      if (K <= 20) GN_SK_CASE(__half, 20) else if (K <= 32) GN_SK_CASE(__half, 32) else GN_SK_CASE(__half, 36)
     } else {
-      if (K <= 20) GN_SK_CASE(__nv_bfloat16, 20) else GN_SK_CASE(__nv_bfloat16, 32)
+      if (K <= 20) GN_SK_CASE(__nv_bfloat16, 20)
+      else if (K <= 32) GN_SK_CASE(__nv_bfloat16, 32)
+      else GN_SK_CASE(__nv_bfloat16, 36)
     }
 #undef GN_SK_CASE
     GN_LAUNCH_CHECK();

@@ -17,6 +17,7 @@ namespace gn {
 
 // --------------------------------------------------------- global variables
 constexpr int GV_THREADS = 128;
+constexpr int GV_MAX_THREADS = 512;
 constexpr int GV_MAX_F = 64;
 
 struct X0Out {
@@ -35,10 +36,11 @@ __device__ __forceinline__ void store_x0(const X0Out& o, int64_t row, int c, flo
         __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
 }
 
-__global__ void __launch_bounds__(GV_THREADS) global_variables_kernel(
+__global__ void __launch_bounds__(GV_MAX_THREADS) global_variables_kernel(
     const float* __restrict__ x, int64_t ldx, int F, GraphView g, const int32_t* __restrict__ ptr,
     const int32_t* __restrict__ n_pulses, float* __restrict__ gv, X0Out o0, X0Out o1) {
-  __shared__ float s_part[GV_THREADS];
+  __shared__ float s_part[GV_MAX_THREADS];
+  const int T = blockDim.x;  // 128, or 512 for large events (chosen by the host from N / B)
   __shared__ float s_gv[GV_MAX_F + 5];
   __shared__ int s_cnt[5];
   const int e = blockIdx.x;
@@ -49,7 +51,7 @@ __global__ void __launch_bounds__(GV_THREADS) global_variables_kernel(
   if (tid < 5) s_cnt[tid] = 0;
 
   // column sums: thread (r, c) walks rows r, r + rpp, ...
-  const int rpp = GV_THREADS / F;
+  const int rpp = T / F;
   const int r0 = tid / F, c0 = tid % F;
   float s = 0.f;
   if (r0 < rpp)
@@ -66,7 +68,7 @@ __global__ void __launch_bounds__(GV_THREADS) global_variables_kernel(
   // homophily of columns 0..3 over the in-edges of this event's nodes
   int eq[4] = {0, 0, 0, 0};
   int ne = 0;
-  for (int r = tid; r < n; r += GV_THREADS) {
+  for (int r = tid; r < n; r += T) {
     const int64_t i = lo + r;
     int64_t start;
     int cnt;
@@ -100,19 +102,23 @@ __global__ void __launch_bounds__(GV_THREADS) global_variables_kernel(
   }
   if (tid == 4) s_gv[F + 4] = log10f((float)n_pulses[e]);
   __syncthreads();
-  for (int c = tid; c < G; c += GV_THREADS) gv[(int64_t)e * G + c] = s_gv[c];
+  for (int c = tid; c < G; c += T) gv[(int64_t)e * G + c] = s_gv[c];
 
 #pragma unroll
   for (int w = 0; w < 2; ++w) {
     const X0Out& o = w == 0 ? o0 : o1;
     if (o.ptr == nullptr) continue;
-    const int64_t total = (int64_t)n * o.cols;
-    for (int64_t idx = tid; idx < total; idx += GV_THREADS) {
-      const int r = (int)(idx / o.cols), c = (int)(idx % o.cols);
+    // (row, column) advance incrementally: no division per element
+    int r = tid / o.cols, c = tid % o.cols;
+    const int dr = T / o.cols, dc = T % o.cols;
+    while (r < n) {
       float v = 0.f;
       if (c < F) v = x[(int64_t)(lo + r) * ldx + c];
       else if (c < F + G) v = s_gv[c - F];
       store_x0(o, lo + r, c, v);
+      r += dr;
+      c += dc;
+      if (c >= o.cols) { c -= o.cols; ++r; }
     }
   }
 }
@@ -266,7 +272,8 @@ extern "C" int gn_global_variables(const float* x, int64_t ldx, int F, const gn_
     GN_CHECK_ARG(o->dtype == GN_F32 || o->dtype == GN_BF16 || o->dtype == GN_F16,
                  "gn_global_variables: bad x0 dtype");
   }
-  global_variables_kernel<<<(unsigned)B, GV_THREADS, 0, as_stream(stream)>>>(
+  const int threads = (N / (B > 0 ? B : 1)) > 128 ? GV_MAX_THREADS : GV_THREADS;
+  global_variables_kernel<<<(unsigned)B, threads, 0, as_stream(stream)>>>(
       x, ldx, F, g, ptr, n_pulses, gv, o0, o1);
   GN_LAUNCH_CHECK();
   return GN_OK;

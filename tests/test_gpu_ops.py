@@ -98,7 +98,7 @@ def test_linear_f32(M, N, K, act):
 
 
 @pytest.mark.parametrize("M,N,K", [(300, 320, 19), (1001, 704, 19), (2049, 64, 7), (4096, 34, 32),
-                                   (999, 320, 33), (515, 1024, 20)])
+                                   (999, 320, 33), (515, 1024, 20), (700, 320, 36), (600, 128, 37)])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 def test_linear_f32_16bit_output_small_k(M, N, K, dtype):
     """First EdgeConv node GEMM: fp32 inputs, K = 2F+5, [P | Q] written as 16-bit rows (a
