@@ -37,6 +37,25 @@ UNIT = "events/s"
 POOLS = ["min", "max", "mean", "sum"]
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """Keep stdout for the ONE JSON line: whatever else writes to file descriptor 1 (NCCL's
+    version banner, library chatter) goes to stderr from here on."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT if _REAL_STDOUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -198,7 +217,7 @@ def run_reference(args):
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------- #
@@ -434,7 +453,7 @@ def run_ours(args):
             "value": v, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"10 steps of a {args.cpu_events}-event batch of the same workload "
                       f"({sec * 1e3:.0f} ms/step), oracle port incl. the reference's dense distribute"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -461,7 +480,7 @@ def run_ours_train(args):
                 "sample": f"5 training steps of a {args.cpu_events}-event batch of the same "
                           f"workload ({sec * 1e3:.0f} ms/step), oracle port (torch autograd + "
                           f"Adam on CPU)"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -646,6 +665,7 @@ def dominant_kernel_roofline(backbone, data, precision, N, E, dev, flush_buf):
 
 if __name__ == "__main__":
     a = parse_args()
+    claim_stdout()
     if a.impl == "reference":
         run_reference(a)
     elif a.mode == "train":
