@@ -68,9 +68,11 @@ def parse_args():
     ap.add_argument("--cpu-events", type=int, default=128,
                     help="events per CPU-baseline step (reference distribute step is O(N*B))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c4"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c4", "c5"],
                     help="c2: BASELINE configs[1] (default); c4: configs[3] shapes (IceCube-Upgrade "
-                         "geometry, F=14, k=16, pools min/max/mean; use --events 256 --pulses 500)")
+                         "geometry, F=14, k=16, pools min/max/mean; use --events 256 --pulses 500); "
+                         "c5: one point of configs[4] (direction + energy heads, exactly --pulses "
+                         "pulses in every event; tools/sweep_c5.sh walks 16..2048)")
     ap.add_argument("--mode", default="infer", choices=["infer", "train"],
                     help="infer: BASELINE configs[1] (default); train: configs[2] (bf16 training "
                          "step: forward, backward, gradient all-reduce, Adam)")
@@ -88,6 +90,10 @@ def workload_name(args):
     if getattr(args, "workload", "c2") == "c4":
         return (f"C4: DynEdge inference, synthetic IceCube-Upgrade pulse maps, ~{args.pulses:g} "
                 f"pulses/event, F=14, k=16, batch {args.events}/GPU, pools min/max/mean")
+    if getattr(args, "workload", "c2") == "c5":
+        return (f"C5: DynEdge direction + energy multi-task inference, synthetic IceCube-86 pulse "
+                f"maps, exactly {int(args.pulses)} pulses/event, k=8, batch {args.events}/GPU, pools "
+                f"min/max/mean/sum")
     if getattr(args, "mode", "infer") == "train":
         return (f"C3: DynEdge training step (forward, backward, gradient all-reduce, Adam), bf16, "
                 f"synthetic IceCube-86 events, ~{args.pulses:g} pulses/event, k=8, batch "
@@ -312,7 +318,8 @@ def run_ours(args):
 
     # ---- inputs: one synthetic batch per rank, host (pinned) and device copies
     det, knn_k, pools = workload_cfg(args)
-    pb = make_pulse_batch(args.events, args.pulses, detector=det, seed=1234 + rank)
+    pb = make_pulse_batch(args.events, args.pulses, detector=det, seed=1234 + rank,
+                          fixed_pulses=int(args.pulses) if args.workload == "c5" else None)
     x_dev = pb.x.to(dev)
     batch_dev = pb.batch.to(dev)
     npulse_dev = pb.n_pulses.to(dev)
@@ -328,7 +335,12 @@ def run_ours(args):
                          precision=precision)
     task = g.EnergyReconstruction(hidden_size=backbone.nb_outputs, target_labels="energy",
                                   loss_function=g.LogCoshLoss())
-    model = g.StandardModel(tasks=[task], graph_definition=object(), gnn=backbone).to(dev)
+    tasks = [task]
+    if args.workload == "c5":   # BASELINE configs[4]: two heads on one backbone pass
+        tasks = [g.DirectionReconstructionWithKappa(hidden_size=backbone.nb_outputs,
+                                                    target_labels="direction",
+                                                    loss_function=g.VonMisesFisher3DLoss()), task]
+    model = g.StandardModel(tasks=tasks, graph_definition=object(), gnn=backbone).to(dev)
     model.inference()
     model.train(False)
     backbone.validate_inputs = False  # inputs are validated once below; keeps steps async
@@ -348,7 +360,7 @@ def run_ours(args):
     feeder = DevicePrefetcher(itertools.repeat(g.Data(**host)), dev)
 
     def step_e2e():
-        return model(next(feeder))[0].to("cpu", non_blocking=False)
+        return [p.to("cpu", non_blocking=False) for p in model(next(feeder))]
 
     def barrier():
         if world > 1:
@@ -420,7 +432,7 @@ def run_ours(args):
     value = events_total * args.steps / (ms_res * 1e-3)
     e2e_value = events_total * args.steps / (ms_e2e * 1e-3)
     h2d = sum(t.numel() * t.element_size() for t in host.values())
-    d2h = args.events * 4
+    d2h = args.events * 4 * (5 if args.workload == "c5" else 1)   # [B,1] energy (+ [B,4] direction)
     flops = algorithmic_flops_per_event_batch(N, E, F=int(x_dev.shape[1]))
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
