@@ -11,6 +11,7 @@ from .data import Batch, Data  # noqa: F401
 from .detector import IceCube86, IceCubeUpgrade, Prometheus, ORCA150SuperDense  # noqa: F401
 from .dynedge import DynEdge, DynEdgeConv  # noqa: F401
 from .dynedge_jinst import DynEdgeJINST  # noqa: F401
+from .particlenet import ParticleNeT  # noqa: F401
 from .graphs import KNNEdges, KNNGraph  # noqa: F401
 from .losses import LogCoshLoss, VonMisesFisher3DLoss  # noqa: F401
 from .ops import knn_graph  # noqa: F401

@@ -67,6 +67,7 @@ SIGNATURES = {
     "gn_layernorm_act_f32": (_int, [_p, _i64, _i64, _int, _p, _p, C.c_float, _int, _p]),
     "gn_edge_preact_f32": (_int, [_p, _int, _gp, _i64, _p, _i64, _p]),
     "gn_slot_sum_f32": (_int, [_p, _i64, _int, _gp, _i64, _p, _i64, _p]),
+    "gn_slot_aggregate_f32": (_int, [_p, _i64, _int, _gp, _i64, _int, _p, _i64, _p]),
     "gn_tc_linear_accumulate": (_int, [_p, _i64, _p, _i64, _int, _p, _i64, _i64, _int, _int, _int, _p]),
     "gn_transpose_16": (_int, [_p, _i64, _i64, _int, _p, _i64, _p]),
     "gn_csr_to_ell": (_int, [_p, _p, _i64, _int, _p, _p, _p, _p]),

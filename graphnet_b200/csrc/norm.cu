@@ -83,6 +83,34 @@ __global__ void __launch_bounds__(256) slot_sum_kernel(const float* __restrict__
   }
 }
 
+// out[i, :] = aggr over the FILLED slots of node i of Z[i*S + t, :]; aggr as GN_AGGR_* (PyG's
+// MessagePassing aggregation, components/layers.py:27-76: add / mean / max / min); a node
+// without in-edges gives 0.
+__global__ void __launch_bounds__(256) slot_aggregate_kernel(const float* __restrict__ Z,
+                                                             int64_t ldz, int b,
+                                                             const int32_t* __restrict__ nbr, int S,
+                                                             int64_t N, int aggr,
+                                                             float* __restrict__ out, int64_t ldo) {
+  const int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= N) return;
+  int cnt = 0;
+  for (int t = 0; t < S; ++t) cnt += nbr[i * S + t] >= 0;
+  for (int c = lane; c < b; c += 32) {
+    float acc = aggr == GN_AGGR_MAX ? -INFINITY : (aggr == GN_AGGR_MIN ? INFINITY : 0.f);
+    for (int t = 0; t < S; ++t) {
+      if (nbr[i * S + t] < 0) continue;
+      const float v = Z[(i * S + t) * ldz + c];
+      if (aggr == GN_AGGR_MAX) acc = fmaxf(acc, v);
+      else if (aggr == GN_AGGR_MIN) acc = fminf(acc, v);
+      else acc += v;
+    }
+    if (cnt == 0) acc = 0.f;
+    else if (aggr == GN_AGGR_MEAN) acc /= (float)cnt;
+    out[i * ldo + c] = acc;
+  }
+}
+
 }  // namespace gn
 
 using namespace gn;
@@ -130,6 +158,22 @@ extern "C" int gn_slot_sum_f32(const float* Z, int64_t ldz, int b, const gn_grap
   GN_CHECK_ARG(Z && out, "gn_slot_sum_f32: null pointer");
   slot_sum_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, as_stream(stream)>>>(
       Z, ldz, b, graph->col, graph->ell_stride, N, out, ldo);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
+extern "C" int gn_slot_aggregate_f32(const float* Z, int64_t ldz, int b, const gn_graph* graph,
+                                     int64_t N, int aggr, float* out, int64_t ldo, void* stream) {
+  GN_CHECK_ARG(graph && graph->col && graph->ell_stride > 0,
+               "gn_slot_aggregate_f32: the graph must be in ELL layout");
+  GN_CHECK_ARG(b >= 1 && ldz >= b && ldo >= b, "gn_slot_aggregate_f32: bad sizes");
+  GN_CHECK_ARG(aggr == GN_AGGR_ADD || aggr == GN_AGGR_MEAN || aggr == GN_AGGR_MAX ||
+                   aggr == GN_AGGR_MIN,
+               "gn_slot_aggregate_f32: unknown aggregation %d", aggr);
+  if (N == 0) return GN_OK;
+  GN_CHECK_ARG(Z && out, "gn_slot_aggregate_f32: null pointer");
+  slot_aggregate_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, as_stream(stream)>>>(
+      Z, ldz, b, graph->col, graph->ell_stride, N, aggr, out, ldo);
   GN_LAUNCH_CHECK();
   return GN_OK;
 }

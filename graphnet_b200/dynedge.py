@@ -168,8 +168,6 @@ class DynEdgeConv(torch.nn.Module):
         """EdgeConv with LayerNorm inside the message MLP (add_norm_layer=True,
         gnn/dynedge.py:202-203): the normalisation needs every edge's full feature row, so the
         per-slot rows are materialised - the reference's own route - around the dense kernels."""
-        if self.aggr not in ("add", "sum"):
-            raise NotImplementedError("add_norm_layer=True supports aggr='add'")
         steps, act = _parse_mlp_norm(self.nn)
         (l1, n1), rest = steps[0], steps[1:]
         N = x.shape[0]
@@ -189,7 +187,9 @@ class DynEdgeConv(torch.nn.Module):
         h = _mlp_rows_norm(h, rest, act)
         if out is None:
             out = torch.empty((N, h.shape[1]), dtype=torch.float32, device=x.device)
-        return ops.slot_sum_f32(h, graph, out)
+        if self.aggr in ("add", "sum"):
+            return ops.slot_sum_f32(h, graph, out)
+        return ops.slot_aggregate_f32(h, graph, out, self.aggr)
 
     def _conv_f32(self, x: Tensor, graph: Graph, out: Optional[Tensor] = None) -> Tensor:
         n_lin = sum(isinstance(m, torch.nn.Linear) for m in self.nn)

@@ -669,6 +669,20 @@ def slot_sum_f32(Z: Tensor, graph: Graph, out: Tensor) -> Tensor:
     return out
 
 
+def slot_aggregate_f32(Z: Tensor, graph: Graph, out: Tensor, aggr: str) -> Tensor:
+    """out[i] = add / mean / max / min of Z[i*stride + t] over the filled slots of node i."""
+    dev = _require_cuda(Z, out)
+    assert Z.dtype == torch.float32 and out.dtype == torch.float32
+    assert Z.stride(1) == 1 and out.stride(1) == 1
+    N, b = out.shape[0], Z.shape[1]
+    gs = graph.c_struct()
+    with _on(dev):
+        check(_lib.load().gn_slot_aggregate_f32(_ptr(Z), Z.stride(0), b, C.byref(gs), N, AGGR[aggr],
+                                                _ptr(out), out.stride(0), _stream(dev)),
+              "gn_slot_aggregate_f32")
+    return out
+
+
 def convert_scale_16(X: Tensor, dtype: torch.dtype, scale: float = 1.0) -> Tensor:
     """16-bit copy of an fp32 matrix, multiplied by `scale` (a power of two keeps it exact)."""
     dev = _require_cuda(X)

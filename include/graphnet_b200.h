@@ -270,6 +270,12 @@ int gn_edge_preact_f32(const float* pq, int a, const gn_graph* graph, int64_t N,
 int gn_slot_sum_f32(const float* Z, int64_t ldz, int b, const gn_graph* graph, int64_t N,
                     float* out, int64_t ldo, void* stream);
 
+/* The same with PyG's other aggregations (aggr = GN_AGGR_ADD / MEAN / MAX / MIN): ParticleNeT builds
+ * its DynEdgeConv layers with aggr="mean" (gnn/particlenet.py:193-198).  A node without in-edges
+ * gives 0. */
+int gn_slot_aggregate_f32(const float* Z, int64_t ldz, int b, const gn_graph* graph, int64_t N,
+                          int aggr, float* out, int64_t ldo, void* stream);
+
 /* ---- backward pass of the 16-bit training path (BASELINE config 3) ------------- */
 /* The reference holds no backward code: gradients come from torch autograd through the modules
  * cited at each entry.  All matrices row-major; 16-bit operands 16-byte aligned with row strides

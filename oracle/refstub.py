@@ -184,6 +184,7 @@ def load_reference() -> types.SimpleNamespace:
 
     dynedge = importlib.import_module("graphnet.models.gnn.dynedge")
     jinst = importlib.import_module("graphnet.models.gnn.dynedge_jinst")
+    particlenet = importlib.import_module("graphnet.models.gnn.particlenet")
     layers = importlib.import_module("graphnet.models.components.layers")
     task = importlib.import_module("graphnet.models.task.task")
     # `from graphnet.models.task import StandardLearnedTask` in reconstruction.py
@@ -193,6 +194,7 @@ def load_reference() -> types.SimpleNamespace:
     return types.SimpleNamespace(
         DynEdge=dynedge.DynEdge,
         DynEdgeJINST=jinst.DynEdgeJINST,
+        ParticleNeT=particlenet.ParticleNeT,
         DynEdgeConv=layers.DynEdgeConv,
         Data=_Data,
         task=task,

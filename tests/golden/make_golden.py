@@ -196,6 +196,49 @@ def run_jinst_case(ref):
     print(f"oscnext5_jinst: N={x.shape[0]} -> {os.path.getsize(path) / 1e3:.0f} kB")
 
 
+def run_particlenet_case(ref):
+    """ParticleNeT (gnn/particlenet.py) in eval mode on the oscNext events, from the reference's own
+    file: default architecture (3-Linear MLPs with BatchNorm1d, aggr="mean", k=16, dynamic graphs)
+    and a static-graph, two-pooling, GELU variant without BatchNorm."""
+    from oracle.particlenet import init_particlenet_state_dict, particlenet_forward
+    x, b, n = load_db(
+        f"{REF_DATA}/tests/sqlite/oscNext_genie_level7_v02/oscNext_genie_level7_v02_first_5_frames.db",
+        "SRTInIcePulses", FEATURES_ICECUBE86, IceCube86())
+    ei = initial_graph(x, b, 16)
+    out = {}
+    variants = {
+        "a": dict(),
+        "b": dict(dynamic=False, dynedge_layer_sizes=[(48, 40), (72,)], readout_layer_sizes=[64, 32],
+                  global_pooling_schemes=["max", "sum"], activation_layer="gelu",
+                  add_batchnorm_layer=False, nb_neighbours=8),
+    }
+    for tag, kw in variants.items():
+        torch.manual_seed(7)
+        model = ref.ParticleNeT(x.shape[1], **kw)
+        sizes = kw.get("dynedge_layer_sizes", [(64, 64, 64), (128, 128, 128), (256, 256, 256)])
+        ro = kw.get("readout_layer_sizes", [256])
+        pools = kw.get("global_pooling_schemes", ["mean"])
+        bn = kw.get("add_batchnorm_layer", True)
+        sd = init_particlenet_state_dict(x.shape[1], sizes, ro, pools, bn, seed=7)
+        assert set(sd) == set(model.state_dict())
+        model.load_state_dict(sd)
+        model.eval()
+        with torch.no_grad():
+            y = model(ref.Data(x=x, edge_index=ei, batch=b, n_pulses=n))
+            y2, inter = particlenet_forward(
+                sd, x, ei, b, sizes, ro, pools, kw.get("nb_neighbours", 16), slice(0, 3),
+                kw.get("dynamic", True), bn, kw.get("activation_layer", "relu"),
+                return_intermediates=True)
+        assert torch.equal(y, y2), "oracle restatement differs from the reference code"
+        out[f"out_{tag}"] = y.numpy()
+        out[f"conv0_{tag}"] = inter["convs"][0].numpy()
+        out[f"graph1_{tag}"] = inter["graphs"][1].numpy()
+    path = os.path.join(OUT, "oscnext5_particlenet.npz")
+    np.savez_compressed(path, x=x.numpy(), batch=b.numpy(), n_pulses=n.numpy(),
+                        edge_index=ei.numpy(), seed=np.int64(7), **out)
+    print(f"oscnext5_particlenet: N={x.shape[0]} -> {os.path.getsize(path) / 1e3:.0f} kB")
+
+
 def main():
     ref = refstub.load_reference()
     pools4 = ["min", "max", "mean", "sum"]
@@ -217,6 +260,7 @@ def main():
              "direction", seed=2)
     run_extra_cases(ref)
     run_jinst_case(ref)
+    run_particlenet_case(ref)
     x, b, n = adversarial_inputs()
     run_case("adversarial", ref, x, b, n, 8, dict(), None, seed=3)
     run_case("adversarial_k16_after", ref, x, b, n, 8,
@@ -232,5 +276,7 @@ if __name__ == "__main__":
         _ref = refstub.load_reference()
         run_extra_cases(_ref)
         run_jinst_case(_ref)
+    elif "--particlenet-only" in sys.argv:
+        run_particlenet_case(refstub.load_reference())
     else:
         main()

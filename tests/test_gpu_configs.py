@@ -244,3 +244,48 @@ def test_dynedge_jinst_matches_reference_golden_and_oracle():
                      n_pulses=pb.n_pulses.to(DEV))).cpu()
     per_event = (got2 - want).norm(dim=1) / want.norm(dim=1)
     assert float(per_event.median()) < 1e-4 and float(per_event.max()) < 5e-3, per_event
+
+
+def test_particlenet_matches_reference_golden_and_oracle():
+    """ParticleNeT (gnn/particlenet.py) in eval mode - BatchNorm folded into the
+    Linear layers, aggr="mean", 3-Linear EdgeConv MLPs, dynamic or static graphs - on the fp32
+    kernels; parameter names as in the reference (its state_dict loads)."""
+    import os
+    import numpy as np
+    import graphnet_b200 as gb
+    from oracle.particlenet import init_particlenet_state_dict, particlenet_forward
+    from graphnet_b200.synthetic import make_pulse_batch
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "oscnext5_particlenet.npz"))
+    x, b, n, ei = (torch.from_numpy(z[k]) for k in ("x", "batch", "n_pulses", "edge_index"))
+    data = gb.Data(x=x.to(DEV), edge_index=ei.to(DEV), batch=b.to(DEV), n_pulses=n.to(DEV))
+    sd = init_particlenet_state_dict(x.shape[1], seed=int(z["seed"]))
+    m = gb.ParticleNeT(x.shape[1])
+    m.load_state_dict(sd)
+    m = m.to(DEV)
+    with pytest.raises(NotImplementedError):
+        m(data)                        # train mode (batch statistics) is not built
+    m.eval()
+    assert rel_l2(m(data).cpu(), torch.from_numpy(z["out_a"])) < 1e-4
+    kw = dict(dynamic=False, dynedge_layer_sizes=[(48, 40), (72,)], readout_layer_sizes=[64, 32],
+              global_pooling_schemes=["max", "sum"], activation_layer="gelu",
+              add_batchnorm_layer=False, nb_neighbours=8)
+    sd_b = init_particlenet_state_dict(x.shape[1], kw["dynedge_layer_sizes"], [64, 32],
+                                       ["max", "sum"], False, seed=int(z["seed"]))
+    mb = gb.ParticleNeT(x.shape[1], **kw)
+    mb.load_state_dict(sd_b)
+    mb = mb.to(DEV).eval()
+    assert rel_l2(mb(data).cpu(), torch.from_numpy(z["out_b"])) < 1e-4
+    # a larger synthetic batch against the oracle (k = 16 graphs are not complete there)
+    pb = make_pulse_batch(24, 40.0, seed=91)
+    ei2 = oracle.knn_graph(pb.x[:, :3], 16, pb.batch)
+    want = particlenet_forward(sd, pb.x, ei2, pb.batch)
+    got = m(gb.Data(x=pb.x.to(DEV), edge_index=ei2.to(DEV), batch=pb.batch.to(DEV),
+                    n_pulses=pb.n_pulses.to(DEV))).cpu()
+    per_event = (got - want).norm(dim=1) / want.norm(dim=1)
+    assert float(per_event.median()) < 1e-4 and float(per_event.max()) < 5e-3, per_event
+    # node-level output (skip_readout) and the state_dict keys of the reference
+    ms = gb.ParticleNeT(x.shape[1], skip_readout=True)
+    ms.load_state_dict(sd)
+    ms = ms.to(DEV).eval()
+    want_nodes = particlenet_forward(sd, x, ei, b, skip_readout=True)
+    assert ms(data).shape == want_nodes.shape and rel_l2(ms(data).cpu(), want_nodes) < 1e-4

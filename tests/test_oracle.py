@@ -158,3 +158,20 @@ def test_jinst_oracle_reproduces_reference_golden():
     y = jinst_forward(sd, x, ei, b, n)
     # bit-equal on the host that recorded it; another CPU's sgemm sums in a different order
     assert rel_l2(y, torch.from_numpy(z["out"])) < 1e-5
+
+
+def test_particlenet_oracle_reproduces_reference_golden():
+    """oracle/particlenet.py against the output of the reference's own particlenet.py (eval mode):
+    the default architecture and a static-graph / GELU / no-BatchNorm variant."""
+    import numpy as np, os
+    from oracle.particlenet import init_particlenet_state_dict, particlenet_forward
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "oscnext5_particlenet.npz"))
+    x, b, ei = (torch.from_numpy(z[k]) for k in ("x", "batch", "edge_index"))
+    sd = init_particlenet_state_dict(x.shape[1], seed=int(z["seed"]))
+    y, inter = particlenet_forward(sd, x, ei, b, return_intermediates=True)
+    assert rel_l2(inter["convs"][0], torch.from_numpy(z["conv0_a"])) < 1e-5
+    assert rel_l2(y, torch.from_numpy(z["out_a"])) < 1e-4   # dynamic graphs: near-ties may flip
+    sizes, ro, pools = [(48, 40), (72,)], [64, 32], ["max", "sum"]
+    sd = init_particlenet_state_dict(x.shape[1], sizes, ro, pools, False, seed=int(z["seed"]))
+    y = particlenet_forward(sd, x, ei, b, sizes, ro, pools, 8, slice(0, 3), False, False, "gelu")
+    assert rel_l2(y, torch.from_numpy(z["out_b"])) < 1e-5
