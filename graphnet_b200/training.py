@@ -213,7 +213,5 @@ def dynedge_train_forward(model, data: Any) -> Tensor:
     """DynEdge forward that records what its hand-written backward needs (autograd enabled)."""
     if model.precision not in ("bf16",):
         raise NotImplementedError("training runs on the 16-bit path: DynEdge(precision='bf16')")
-    if model._add_global_variables_after_pooling:
-        raise NotImplementedError("training with add_global_variables_after_pooling")
     params = _param_list(model)
     return _DynEdgeTrain.apply(model, data, *params)

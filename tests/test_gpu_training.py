@@ -36,7 +36,7 @@ def _first_arg_pool(x, ptr, kind):
     return torch.stack(outs)
 
 
-def _reference_forward(model, x0, layers, ptr, schemes):
+def _reference_forward(model, x0, layers, ptr, schemes, gv_after=None):
     """fp32 torch restatement of dynedge.py:296-350 on fixed graphs (autograd enabled)."""
     N = x0.shape[0]
     feats = [x0]
@@ -57,11 +57,14 @@ def _reference_forward(model, x0, layers, ptr, schemes):
         else:
             tot = torch.zeros((len(p) - 1, h.shape[1]), device=h.device).index_add_(0, seg, h)
             pooled.append(tot / cnt if s == "mean" else tot)
+    if gv_after is not None:      # add_global_variables_after_pooling (dynedge.py:339-345)
+        pooled.append(gv_after)
     return model._readout(torch.cat(pooled, 1))
 
 
-@pytest.mark.parametrize("events,pulses", [(24, 18.0), (64, 40.0)])
-def test_gradients_match_autograd(dev, events, pulses):
+@pytest.mark.parametrize("events,pulses,after", [(24, 18.0, False), (64, 40.0, False),
+                                                 (24, 18.0, True)])
+def test_gradients_match_autograd(dev, events, pulses, after):
     import graphnet_b200 as g
     from graphnet_b200.synthetic import make_pulse_batch
     from graphnet_b200.training import _DynEdgeTrain, _param_list
@@ -73,7 +76,8 @@ def test_gradients_match_autograd(dev, events, pulses):
     ei = g.knn_graph(x[:, :3].contiguous(), 8, batch, num_events=events)
     data = g.Data(x=x, edge_index=ei, batch=batch, n_pulses=pb.n_pulses.to(dev))
     torch.manual_seed(3)
-    model = g.DynEdge(7, global_pooling_schemes=schemes, precision="bf16").to(dev)
+    model = g.DynEdge(7, global_pooling_schemes=schemes, precision="bf16",
+                      add_global_variables_after_pooling=after).to(dev)
     params = _param_list(model)
 
     out = g.training.dynedge_train_forward(model, data)
@@ -87,8 +91,10 @@ def test_gradients_match_autograd(dev, events, pulses):
     # reference: fp32 autograd on the graphs the forward actually used
     for p in params:
         p.grad = None
-    x0 = torch.cat([x, saved_gv(model, data)[batch]], 1)
-    ref_out = _reference_forward(model, x0, saved["layers"], saved["ptr"], schemes)
+    gv = saved_gv(model, data)
+    x0 = x if after else torch.cat([x, gv[batch]], 1)
+    ref_out = _reference_forward(model, x0, saved["layers"], saved["ptr"], schemes,
+                                 gv_after=gv if after else None)
     ((ref_out * w).sum() / events).backward()
     ref = [p.grad.detach().clone() for p in params]
 
