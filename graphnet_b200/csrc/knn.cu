@@ -55,6 +55,8 @@ struct KnnParams {
   int32_t stride;
   int32_t* deg;
   int chunk;  // candidates staged per pass (multiple of 32)
+  int group;  // events per CTA (small events), 1: one event per grid row
+  int64_t B;
 };
 
 // Sorted list of the CAP best (distance, index) pairs seen so far.  Distances are kept as the
@@ -133,10 +135,9 @@ __device__ __forceinline__ void knn_write_row(const KnnParams& p, const TopList<
 //    candidates are queued that no longer qualify; push() ignores them.
 //    The query blocks of a large event are dealt to the `split` CTAs of its grid row.
 template <int CAP, int DIMS>  // DIMS == 0: runtime p.dims
-__global__ void __launch_bounds__(KNN_THREADS) knn_kernel(KnnParams p) {
-  extern __shared__ __align__(16) float s_coord[];  // [dims][chunk], then the queues
+__device__ __forceinline__ void knn_one_event(const KnnParams& p, int e, int yb, int ny,
+                                              float* s_coord) {
   const int dims = DIMS > 0 ? DIMS : p.dims;
-  const int e = blockIdx.x;
   const int lo = p.ptr[e];
   const int n = p.ptr[e + 1] - lo;
   if (n <= 0) return;
@@ -145,7 +146,8 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_kernel(KnnParams p) {
   constexpr int QD = DIMS > 0 ? DIMS : KNN_MAX_DIMS;
 
   if (n <= KNN_THREADS / 2) {
-    if (blockIdx.y != 0) return;
+    if (yb != 0) return;
+    __syncthreads();  // a previous event of this CTA may still be read from the staging buffer
     for (int t = 0; t < dims; ++t)
       for (int c = tid; c < n; c += KNN_THREADS)
         s_coord[t * chunk + c] = p.x[(int64_t)(lo + c) * p.ldx + p.cols[t]];
@@ -175,8 +177,8 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_kernel(KnnParams p) {
 
   uint2* const queue = reinterpret_cast<uint2*>(s_coord + dims * chunk);  // [KNN_QDEPTH][threads]
   const bool queued = n >= KNN_QUEUED_MIN_N;
-  const int qfirst = blockIdx.y * KNN_THREADS;
-  for (int qbase = qfirst; qbase < n; qbase += gridDim.y * KNN_THREADS) {
+  const int qfirst = yb * KNN_THREADS;
+  for (int qbase = qfirst; qbase < n; qbase += ny * KNN_THREADS) {
     const int q = qbase + tid;
     const bool active = q < n;
     float qc[QD];
@@ -253,6 +255,66 @@ __global__ void __launch_bounds__(KNN_THREADS) knn_kernel(KnnParams p) {
   }
 }
 
+// grid = (event groups, split).  p.group events per CTA: with small events (mean below 32 pulses)
+// one event cannot occupy a CTA, so several consecutive events - their rows are contiguous in x -
+// are staged together and every pair of threads takes one query of the group, scanning only its
+// own event's candidates.  A group that does not fit that shape (an event above 64 pulses, or
+// more rows than the staging buffer) is walked event by event.
+template <int CAP, int DIMS>
+__global__ void __launch_bounds__(KNN_THREADS) knn_kernel(KnnParams p) {
+  extern __shared__ __align__(16) float s_coord[];  // [dims][chunk], then the queues
+  if (p.group <= 1) {
+    knn_one_event<CAP, DIMS>(p, blockIdx.x, blockIdx.y, gridDim.y, s_coord);
+    return;
+  }
+  const int dims = DIMS > 0 ? DIMS : p.dims;
+  constexpr int QD = DIMS > 0 ? DIMS : KNN_MAX_DIMS;
+  const int chunk = p.chunk;
+  const int tid = threadIdx.x;
+  const int e0 = blockIdx.x * p.group;
+  const int e1 = min(e0 + p.group, (int)p.B);
+  const int lo0 = p.ptr[e0];
+  const int total = p.ptr[e1] - lo0;
+  bool packed = total <= chunk;
+  for (int e = e0; e < e1; ++e) packed = packed && (p.ptr[e + 1] - p.ptr[e] <= KNN_THREADS / 2);
+  if (!packed) {
+    for (int e = e0; e < e1; ++e) knn_one_event<CAP, DIMS>(p, e, blockIdx.y, gridDim.y, s_coord);
+    return;
+  }
+  if (blockIdx.y != 0 || total <= 0) return;
+  for (int t = 0; t < dims; ++t)
+    for (int c = tid; c < total; c += KNN_THREADS)
+      s_coord[t * chunk + c] = p.x[(int64_t)(lo0 + c) * p.ldx + p.cols[t]];
+  __syncthreads();
+  for (int qbase = 0; qbase < total; qbase += KNN_THREADS / 2) {
+    const int q = qbase + (tid >> 1), h = tid & 1;   // q: row of the group
+    const bool active = q < total;
+    int ev = e0;                                      // the event of row q
+    if (active)
+      while (p.ptr[ev + 1] - lo0 <= q) ++ev;
+    const int lo = active ? p.ptr[ev] - lo0 : 0;      // first row of that event in the group
+    const int n = active ? p.ptr[ev + 1] - lo0 - lo : 0;
+    float qc[QD];
+#pragma unroll
+    for (int t = 0; t < QD; ++t) qc[t] = (active && t < dims) ? s_coord[t * chunk + q] : 0.f;
+    TopList<CAP> top;
+    top.init();
+    const int mid = (n + 1) >> 1;
+    const int c0 = h ? mid : 0, c1 = h ? n : mid;     // candidate indices inside the event
+    for (int c = c0; c < c1; ++c) {
+      const uint32_t cd = knn_dist_bits<DIMS>(qc, s_coord, chunk, lo + c, dims);
+      if (cd < top.worst()) top.push(cd, c);
+    }
+#pragma unroll
+    for (int s = 0; s < CAP; ++s) {
+      const uint32_t od = __shfl_down_sync(0xffffffffu, top.d[s], 1);
+      const int oi = __shfl_down_sync(0xffffffffu, top.idx[s], 1);
+      if (h == 0) top.push(od, oi);
+    }
+    if (active && h == 0) knn_write_row<CAP>(p, top, lo0 + lo, q - lo);
+  }
+}
+
 // Runtime-capacity variant for large k (k+1 > 33): the list lives in local memory.
 constexpr int KNN_MAX_KK = 128;
 template <int DIMS>
@@ -323,7 +385,7 @@ static int launch_knn(const KnnParams& p, int64_t N, int64_t B, cudaStream_t st)
   // CTAs per event from the mean event size (the host knows N and B, not the largest event)
   int64_t split = ceil_div(ceil_div(N, B), (int64_t)KNN_THREADS);
   split = split < 1 ? 1 : (split > KNN_MAX_SPLIT ? KNN_MAX_SPLIT : split);
-  dim3 grid((unsigned)B, (unsigned)split), block(KNN_THREADS);
+  dim3 grid((unsigned)ceil_div(B, (int64_t)p.group), (unsigned)split), block(KNN_THREADS);
   switch (p.dims) {
     case 1: knn_kernel<CAP, 1><<<grid, block, smem, st>>>(p); break;
     case 2: knn_kernel<CAP, 2><<<grid, block, smem, st>>>(p); break;
@@ -502,6 +564,10 @@ extern "C" int gn_knn_graph(const float* x, int64_t ldx, const int32_t* cols, in
   for (int t = 0; t < dims; ++t)
     GN_CHECK_ARG(cols[t] >= 0 && cols[t] < ldx, "gn_knn_graph: column %d out of range", cols[t]);
   p.chunk = (KNN_SMEM_FLOATS / dims) & ~31;
+  // events per CTA: as many as fill the 64 query slots of a CTA at the mean event size
+  const int64_t mean_n = ceil_div(N, B);
+  p.group = mean_n >= 32 ? 1 : (int)(64 / (mean_n > 8 ? mean_n : 8));
+  p.B = B;
   cudaStream_t st = as_stream(stream);
   if (kk <= 9) launch_knn<9>(p, N, B, st);
   else if (kk <= 17) launch_knn<17>(p, N, B, st);

@@ -97,6 +97,25 @@ def test_scan_shapes_with_ties(counts, k):
     assert torch.equal(gpu_knn(x.contiguous(), k, batch), oracle.knn_graph(x, k, batch))
 
 
+@pytest.mark.parametrize("k", [2, 8])
+@pytest.mark.parametrize("lo,hi,outliers", [(1, 12, []), (2, 30, [70, 200]), (16, 16, []), (1, 3, [64, 65])])
+def test_small_events_share_a_cta(lo, hi, outliers, k):
+    """Mean event size below 32: several consecutive events are staged and searched by one CTA
+    (csrc/knn.cu, p.group > 1); an event above 64 pulses inside such a batch sends its group
+    down the one-event-at-a-time path.  Same (distance, index) order either way."""
+    g = torch.Generator().manual_seed(lo * 100 + hi + k)
+    counts = torch.randint(lo, hi + 1, (301,), generator=g)
+    for i, n in enumerate(outliers):
+        counts[37 + 50 * i] = n
+    n_all = int(counts.sum())
+    x = torch.round(torch.randn(n_all, 3, generator=g) * 2) / 2       # lattice: exact ties
+    fine = torch.rand(n_all, generator=g) < 0.5
+    x[fine] += torch.randn(int(fine.sum()), 3, generator=g) * 1e-3
+    batch = torch.repeat_interleave(torch.arange(len(counts)), counts)
+    assert n_all / len(counts) < 32
+    assert torch.equal(gpu_knn(x.contiguous(), k, batch), oracle.knn_graph(x, k, batch))
+
+
 def test_strided_latent_columns_via_ell():
     """The in-model call: columns of a wide row-major matrix, ELL output, no COO."""
     import graphnet_b200.ops as ops
