@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(256) edge_build_h_kernel(
     int64_t i = 0;
     if (e < E) {
       j = nbr[e];
-      i = e / KP;
+      i = (uint32_t)e / (uint32_t)KP;   // E < 2^31 (checked by the caller): 32-bit division
     }
     for (int pc = lane; pc < pieces; pc += 32) {
       float h[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -236,8 +236,10 @@ __global__ void __launch_bounds__(256) edge_grad_z_kernel(
   for (int r = warp; r < EB_ROWS; r += 8) {
     const int64_t e = e0 + r;
     const bool filled = e < E && nbr[e] >= 0;
-    const int64_t i = e < E ? e / KP : 0;
-    const int64_t mrow = (MASK && e < E) ? (e / used) * 64 + (e % used) : 0;
+    const uint32_t e32 = (uint32_t)e;   // E < 2^31 (checked by the caller): 32-bit divisions
+    const int64_t i = e < E ? e32 / (uint32_t)KP : 0;
+    const int64_t mrow =
+        (MASK && e < E) ? (int64_t)(e32 / (uint32_t)used) * 64 + (e32 % (uint32_t)used) : 0;
     for (int pc = lane; pc < pieces; pc += 32) {
       const int c = pc * 8;
       float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -781,6 +783,7 @@ extern "C" int gn_edge_build_h(const void* P, int64_t ldp, const void* Q, int64_
   if (rc != GN_OK) return rc;
   const int KP = graph->ell_stride;
   const int64_t E = N * KP;
+  GN_CHECK_ARG(E < INT32_MAX, "gn_edge_build_h: N * stride must fit int32");
   GN_CHECK_ARG(Kp >= 8 && Kp % 8 == 0 && ldp >= Kp && ldq >= Kp && ldp % 8 == 0 && ldq % 8 == 0 &&
                    (H == nullptr || (ldh >= Kp && ldh % 8 == 0)) && (HT == nullptr || ldht >= E),
                "gn_edge_build_h: Kp and the row strides must be multiples of 8");
@@ -809,6 +812,7 @@ extern "C" int gn_edge_grad_z(const void* Z, int64_t ldz, const float* dOut, int
   const int KP = graph->ell_stride;
   const int64_t E = N * KP;
   const int bw = (b + 7) & ~7;
+  GN_CHECK_ARG(E < INT32_MAX, "gn_edge_grad_z: N * stride must fit int32");
   GN_CHECK_ARG(b >= 2 && b % 2 == 0 && b <= 1024 && ldz >= bw && ldd >= bw && ldg >= bw &&
                    ldgt >= E && ldz % 8 == 0 && ldd % 4 == 0 && ldg % 8 == 0,
                "gn_edge_grad_z: rows must hold round_up(b, 8) columns; strides multiples of 8");
@@ -838,6 +842,7 @@ extern "C" int gn_edge_grad_z_mask(const uint32_t* relu_mask, int64_t mask_ld, c
   GN_CHECK_ARG(KP <= 64, "gn_edge_grad_z_mask: %d slots per node (max 64)", KP);
   const int used = (64 / KP) * KP;
   const int bw = (b + 7) & ~7;
+  GN_CHECK_ARG(E < INT32_MAX, "gn_edge_grad_z_mask: N * stride must fit int32");
   GN_CHECK_ARG(b >= 2 && b % 2 == 0 && b <= 256 && ldd >= bw && ldg >= bw && ldgt >= E &&
                    ldd % 4 == 0 && ldg % 8 == 0 && mask_ld >= ceil_div(E, (int64_t)used) * 64,
                "gn_edge_grad_z_mask: rows must hold round_up(b, 8) columns; strides multiples of 8");
