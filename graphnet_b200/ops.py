@@ -36,10 +36,15 @@ def _require_cuda(*tensors: Optional[Tensor]) -> torch.device:
     return dev
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream(dev: torch.device) -> C.c_void_p:
-    # the raw handle of torch's current stream (no Stream object per call)
-    return C.c_void_p(torch._C._cuda_getCurrentRawStream(dev.index if dev.index is not None
-                                                         else torch.cuda.current_device()))
+    # the raw handle of torch's current stream (no Stream object per call where torch offers it)
+    if _raw_stream is None:
+        return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    return C.c_void_p(_raw_stream(dev.index if dev.index is not None
+                                  else torch.cuda.current_device()))
 
 
 class _NoSwitch:
