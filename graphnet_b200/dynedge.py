@@ -426,6 +426,9 @@ class DynEdge(torch.nn.Module):
 
     validate_inputs: bool = True
     _last_flags: Optional[Tensor] = None
+    # k of the input graph built on the device when a batch carries no `edge_index`
+    # (None: the model's nb_neighbours, the pairing every reference example uses)
+    input_graph_neighbours: Optional[int] = None
 
     def _dispatch(self, data: Any, edge_index: Optional[Tensor]) -> Tensor:
         if (self.training and self.precision == "bf16" and torch.is_grad_enabled()
@@ -453,8 +456,19 @@ class DynEdge(torch.nn.Module):
         B = int(n_pulses.shape[0]) if n_pulses.dim() > 0 else 1
         n_pulses = n_pulses.reshape(-1)
         ptr, bflags = ops.batch_to_ptr(data.batch, B)
-        graph = ops.coo_to_csr(data.edge_index if edge_index is None else edge_index, N)
-        graph.flags |= bflags
+        if edge_index is None:
+            edge_index = getattr(data, "edge_index", None)
+        if edge_index is None:
+            # edges on the device: a batch that arrives without `edge_index`
+            # gets the graph the reference's KNNGraph would have built per event on the host
+            # (graphs/graphs.py:24-73: columns [0, 1, 2], k = nb_nearest_neighbours) from ONE
+            # launch, kept in the slot-table layout the kernels consume - no COO, no host sync
+            k = self.input_graph_neighbours or self._nb_neighbours
+            graph = ops.knn_graph_ell(x, k, ptr, [0, 1, 2])
+            graph.flags = bflags
+        else:
+            graph = ops.coo_to_csr(edge_index, N)
+            graph.flags |= bflags
         return x, n_pulses, ptr, graph, N, B
 
     @staticmethod

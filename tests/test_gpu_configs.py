@@ -289,3 +289,33 @@ def test_particlenet_matches_reference_golden_and_oracle():
     ms = ms.to(DEV).eval()
     want_nodes = particlenet_forward(sd, x, ei, b, skip_readout=True)
     assert ms(data).shape == want_nodes.shape and rel_l2(ms(data).cpu(), want_nodes) < 1e-4
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-6), ("bf16", 1e-6)])
+def test_batch_without_edge_index_gets_its_graph_on_the_device(precision, tol):
+    """a batch that carries no `edge_index` gets KNNGraph's per-event graph
+    (columns 0-2, k = nb_nearest_neighbours) from one device launch; same output as the batch
+    that brings the identical graph as an int64 COO tensor."""
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(40, 35.0, seed=17)
+    x, b, n = pb.x.to(DEV), pb.batch.to(DEV), pb.n_pulses.to(DEV)
+    ei = gb.knn_graph(x[:, :3].contiguous(), 8, b, num_events=40)
+    assert torch.equal(ei.cpu(), oracle.knn_graph(pb.x[:, :3], 8, pb.batch))
+    torch.manual_seed(4)
+    m = gb.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision=precision).to(DEV)
+    m.train(False)
+    with torch.no_grad():
+        want = m(gb.Data(x=x, edge_index=ei, batch=b, n_pulses=n))
+        got = m(gb.Data(x=x, batch=b, n_pulses=n))
+        assert rel_l2(got.cpu(), want.cpu()) < tol
+        m.input_graph_neighbours = 4          # another k for the input graph than for the layers
+        ei4 = gb.knn_graph(x[:, :3].contiguous(), 4, b, num_events=40)
+        assert rel_l2(m(gb.Data(x=x, batch=b, n_pulses=n)).cpu(),
+                      m(gb.Data(x=x, edge_index=ei4, batch=b, n_pulses=n)).cpu()) < tol
+    if precision == "bf16":                   # and the training path (no host sync for the graph)
+        m.input_graph_neighbours = None
+        m.train()
+        out = m(gb.Data(x=x, batch=b, n_pulses=n))
+        out.square().mean().backward()
+        assert all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in m.parameters())
