@@ -56,9 +56,14 @@ class KNNGraph:
         seed: Optional[int] = None,
         nb_nearest_neighbours: int = 8,
         columns: List[int] = [0, 1, 2],
+        distance_as_edge_feature: bool = False,
         device: str = "cuda",
         **kwargs: Any,
     ) -> None:
+        if distance_as_edge_feature:
+            # graphs.py:57-59 -> KNNDistanceEdges (undirected edges + a distance attribute):
+            # DynEdge reads neither; not part of this path
+            raise NotImplementedError("distance_as_edge_feature=True (KNNDistanceEdges) is not built")
         if node_definition is not None:
             raise NotImplementedError("only the default NodesAsPulses node definition is built")
         self._detector = detector
