@@ -416,6 +416,7 @@ def run_ours(args):
 
     # ---- roofline of the dominant kernel (conv layers 2-4 fused edge kernel), timed alone
     roof = dominant_kernel_roofline(backbone, data_dev, precision, N, E, dev, flush_buf)
+    roof_hbm = pooling_roofline(batch_dev, args.events, N, pools, dev, flush_buf)
 
     # BASELINE's metric is "inference+train": a short measurement of the training step (configs[2];
     # `--mode train` prints it as the main line) rides along; it can never cost the line above
@@ -466,6 +467,7 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roof(pk) if roof else None,
+        "roofline_hbm": roof_hbm(pk) if roof_hbm else None,
     }
     if ms_graph is not None:
         line["graph_replay"] = {"value": events_total * args.steps / (ms_graph * 1e-3), "unit": UNIT,
@@ -689,6 +691,41 @@ def dominant_kernel_roofline(backbone, data, precision, N, E, dev, flush_buf):
                 "executed_tflops": executed_flops / (ms * 1e-3) / 1e12,
                 "note": "achieved counts the reference's unfactored 2E(2d*a+a*b) FLOPs; the kernel "
                         "executes the factored form (executed_*)"}
+    return fill
+
+
+def pooling_roofline(batch_dev, num_events, N, pools, dev, flush_buf):
+    """The largest pure byte mover of the forward, `gn_segment_pool` (all schemes from one read of
+    the [N, 256] fp32 node matrix), timed alone with a flushed L2 against the measured HBM peak.
+    Algorithmic bytes: 4*N*256 in + 4*B*256*P out; DRAM traffic per launch from
+    the committed counters (profiles/r01_hbm_kernels.md: 63.0 MB at C2)."""
+    import graphnet_b200.ops as ops
+    try:
+        ptr, _ = ops.batch_to_ptr(batch_dev, num_events)
+        h = torch.randn(N, 256, device=dev)
+        out = torch.empty(num_events, 256 * len(pools), device=dev)
+        for _ in range(3):
+            ops.segment_pool(h, ptr, pools, out=out)
+        reps = 10
+        s = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+        for i in range(reps):
+            flush_buf.fill_(i)
+            s[i].record()
+            ops.segment_pool(h, ptr, pools, out=out)
+            e[i].record()
+        torch.cuda.synchronize(dev)
+        ms = sum(a.elapsed_time(b) for a, b in zip(s, e)) / reps
+    except Exception as exc:  # diagnostic; never lose the bench line
+        return lambda pk: {"error": repr(exc)}
+    nbytes = 4 * N * 256 + 4 * num_events * 256 * len(pools)
+
+    def fill(pk):
+        ach = nbytes / (ms * 1e-3) / 1e9
+        return {"bound": "hbm", "kernel": "gn::segment_pool_kernel<float,4> (min/max/mean/sum from one read)",
+                "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"],
+                "traffic": None, "peak_source": f"{pk['source']} copy bandwidth",
+                "ms_per_launch": ms, "algorithmic_mb_per_launch": nbytes / 1e6}
     return fill
 
 
