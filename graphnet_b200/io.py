@@ -226,10 +226,18 @@ class SQLitePulseSource:
         return out
 
     def batches(self, batch_size: int, shuffle: bool = False, seed: int = 0,
-                drop_last: bool = False) -> Iterator[PackedBatch]:
+                drop_last: bool = False, rank: int = 0, world_size: int = 1) -> Iterator[PackedBatch]:
+        """Batches of `batch_size` events.  With `world_size` > 1 every rank walks its own
+        contiguous share of the (optionally shuffled - same `seed` on all ranks) event list:
+        events are independent, so multi-GPU inference needs nothing else (sharding.py)."""
         ev = np.asarray(self._events, dtype=np.int64)
         if shuffle:
             ev = np.random.default_rng(seed).permutation(ev)
+        if world_size > 1:
+            assert 0 <= rank < world_size
+            lo = len(ev) * rank // world_size
+            hi = len(ev) * (rank + 1) // world_size
+            ev = ev[lo:hi]
         for i in range(0, len(ev), batch_size):
             chunk = ev[i:i + batch_size]
             if drop_last and len(chunk) < batch_size:

@@ -80,6 +80,19 @@ def test_batched_read_equals_per_event_reads(tmp_path, indexed):
     assert sorted(shuffled) == sorted(seen) and shuffled != seen
 
 
+def test_ranks_read_disjoint_shares(tmp_path):
+    path = str(tmp_path / "events.db")
+    ev_ids, per_event, _ = _make_db(path, [4, 6, 3, 9, 2, 5, 7, 8, 3, 4, 6])
+    src = SQLitePulseSource(path, "pulses", FEATURES_ICECUBE86)
+    for shuffle in (False, True):
+        shares = [[e for b in src.batches(2, shuffle=shuffle, seed=5, rank=r, world_size=3)
+                   for e in b.event_no.tolist()] for r in range(3)]
+        assert sorted(sum(shares, [])) == sorted(ev_ids)
+        assert max(len(s) for s in shares) - min(len(s) for s in shares) <= 1
+    one = [e for b in src.batches(2) for e in b.event_no.tolist()]
+    assert one == ev_ids
+
+
 def test_source_survives_pickling_without_connection(tmp_path):
     import pickle
     path = str(tmp_path / "events.db")
