@@ -68,6 +68,8 @@ def parse_args():
     ap.add_argument("--cpu-events", type=int, default=128,
                     help="events per CPU-baseline step (reference distribute step is O(N*B))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-riders", action="store_true",
+                    help="skip the fp32 / C4 / C5 / sharded-stream riders of the default line")
     ap.add_argument("--workload", default="c2", choices=["c2", "c4", "c5"],
                     help="c2: BASELINE configs[1] (default); c4: configs[3] shapes (IceCube-Upgrade "
                          "geometry, F=14, k=16, pools min/max/mean; use --events 256 --pulses 500); "
@@ -289,6 +291,144 @@ def algorithmic_flops_per_event_batch(N, E, F=7):
     return conv + post
 
 
+
+# --------------------------------------------------------------------------- #
+# riders: the other BASELINE configurations, a few steps each, in the same JSON line
+# --------------------------------------------------------------------------- #
+def _timed_steps(fn, steps, warmup, dev, world, flush_buf):
+    """`steps` calls of fn, CUDA events per step, L2 flushed in between; ms = max over ranks."""
+    import torch.distributed as dist
+    for _ in range(warmup):
+        fn()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    for i in range(steps):
+        flush_buf.fill_(i & 0xFF)
+        starts[i].record()
+        fn()
+        ends[i].record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    ms = sum(a.elapsed_time(b) for a, b in zip(starts, ends))
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def rider_infer(dev, world, rank, flush_buf, *, workload, events, pulses, precision, steps=5,
+                warmup=3):
+    """Inference events/s of one BASELINE configuration (inputs resident, every rank its own
+    batch, value = all ranks' events / max-over-ranks time)."""
+    import graphnet_b200 as g
+    from graphnet_b200.synthetic import make_pulse_batch
+    ns = argparse.Namespace(workload=workload, events=events, pulses=pulses, mode="infer")
+    det, knn_k, pools = workload_cfg(ns)
+    pb = make_pulse_batch(events, pulses, detector=det, seed=1234 + rank,
+                          fixed_pulses=int(pulses) if workload == "c5" else None)
+    x_dev, batch_dev, npulse_dev = pb.x.to(dev), pb.batch.to(dev), pb.n_pulses.to(dev)
+    ei_dev = g.knn_graph(x_dev[:, :3].contiguous(), knn_k, batch_dev, num_events=events)
+    N, E = x_dev.shape[0], ei_dev.shape[1]
+    torch.manual_seed(0)
+    backbone = g.DynEdge(x_dev.shape[1], nb_neighbours=knn_k, global_pooling_schemes=pools,
+                         precision=precision)
+    tasks = [g.EnergyReconstruction(hidden_size=backbone.nb_outputs, target_labels="energy",
+                                    loss_function=g.LogCoshLoss())]
+    if workload == "c5":
+        tasks.insert(0, g.DirectionReconstructionWithKappa(
+            hidden_size=backbone.nb_outputs, target_labels="direction",
+            loss_function=g.VonMisesFisher3DLoss()))
+    model = g.StandardModel(tasks=tasks, graph_definition=object(), gnn=backbone).to(dev)
+    model.inference()
+    model.train(False)
+    backbone.validate_inputs = False
+    data_dev = g.Data(x=x_dev, edge_index=ei_dev, batch=batch_dev, n_pulses=npulse_dev)
+    backbone.check_inputs(data_dev)
+    ms = _timed_steps(lambda: model(data_dev)[0], steps, warmup, dev, world, flush_buf)
+    out = {"workload": workload_name(ns), "value": events * world * steps / (ms * 1e-3),
+           "unit": UNIT, "n_gpus": world, "ms_per_step": ms / steps, "steps": steps,
+           "warmup": warmup, "dtype": "bf16" if precision == "bf16" else "f32",
+           "nodes_per_batch": N, "edges_per_batch": E,
+           "nodes_per_s": N * world * steps / (ms * 1e-3)}
+    if precision == "fp32" and workload == "c2":
+        roof = dominant_kernel_roofline(backbone, data_dev, "fp32", N, E, dev, flush_buf)
+        r = roof(peaks())
+        out["edge_kernel"] = {k_: r.get(k_) for k_ in ("kernel", "ms_per_launch", "achieved",
+                                                       "unit", "error") if k_ in r}
+    return out
+
+
+def rider_sharded(dev, world, rank, flush_buf, *, events_per_gpu=1024, steps=5, warmup=3):
+    """One RAGGED event stream (every rank holds the same host batch), split over the ranks by
+    `sharding.predict_sharded(balance="pulses")`: each rank copies and runs its contiguous share,
+    the per-event outputs come back with one NCCL all_gather.  Timed per step on the device:
+    H2D of the share + forward + all_gather; value = all events / max-over-ranks time."""
+    import numpy as np
+    import graphnet_b200 as g
+    from graphnet_b200.sharding import predict_sharded, shard_ranges
+    from graphnet_b200.synthetic import make_pulse_batch
+    B = events_per_gpu * world
+    rng = np.random.default_rng(99)
+    counts = np.exp(rng.uniform(np.log(8.0), np.log(400.0), size=B)).astype(np.int64)  # ~8..400
+    pb = make_pulse_batch(B, seed=4321, counts=counts)       # the same stream on every rank
+    host = g.Data(x=pb.x.pin_memory(), batch=pb.batch.pin_memory(),
+                  n_pulses=pb.n_pulses.pin_memory())
+    torch.manual_seed(0)
+    backbone = g.DynEdge(7, global_pooling_schemes=POOLS, precision="bf16")
+    task = g.EnergyReconstruction(hidden_size=backbone.nb_outputs, target_labels="energy",
+                                  loss_function=g.LogCoshLoss())
+    model = g.StandardModel(tasks=[task], graph_definition=object(), gnn=backbone).to(dev)
+    model.inference()
+    model.train(False)
+    backbone.validate_inputs = False
+    outs = []
+
+    def step():
+        outs[:] = [predict_sharded(model, host, device=dev, balance="pulses")]
+    ms = _timed_steps(step, steps, warmup, dev, world, flush_buf)
+    ranges = shard_ranges(pb.n_pulses, world, "pulses")
+    share = [int(pb.n_pulses[lo:hi].sum()) for lo, hi in ranges]
+    assert outs[0].shape[0] == B, outs[0].shape
+    return {"workload": f"one ragged stream of {B} events (8..400 pulses, log-uniform), "
+                        f"sharding.predict_sharded(balance='pulses'), input graph built on device",
+            "value": B * steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
+            "ms_per_step": ms / steps, "steps": steps, "events": B, "nodes": int(pb.x.shape[0]),
+            "events_per_rank": [hi - lo for lo, hi in ranges], "pulses_per_rank": share,
+            "collective": "all_gather of [B_local, 1] outputs (NCCL)" if world > 1 else "none",
+            "h2d_bytes_per_step_rank0": int(share[0] * (7 * 4 + 8) + (ranges[0][1] - ranges[0][0]) * 4)}
+
+
+RIDERS = (
+    ("fp32", dict(workload="c2", events=1024, pulses=60.0, precision="fp32")),
+    ("c4", dict(workload="c4", events=256, pulses=500.0, precision="bf16")),
+    ("c5_n16", dict(workload="c5", events=65536, pulses=16, precision="bf16")),
+    ("c5_n256", dict(workload="c5", events=4096, pulses=256, precision="bf16")),
+    ("c5_n2048", dict(workload="c5", events=512, pulses=2048, precision="bf16")),
+)
+
+
+def run_riders(dev, world, rank, flush_buf):
+    out = {}
+    for key, kw in RIDERS:
+        try:
+            out[key] = rider_infer(dev, world, rank, flush_buf, **kw)
+        except Exception as exc:  # noqa: BLE001 - a rider never costs the main line
+            out[key] = {"error": repr(exc)}
+        torch.cuda.synchronize(dev)
+        torch.cuda.empty_cache()
+    try:
+        out["sharded"] = rider_sharded(dev, world, rank, flush_buf)
+    except Exception as exc:  # noqa: BLE001
+        out["sharded"] = {"error": repr(exc)}
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(args):
     import torch.distributed as dist
     import graphnet_b200 as g
@@ -433,6 +573,10 @@ def run_ours(args):
     except Exception as exc:  # noqa: BLE001
         train = {"error": repr(exc)}
 
+    riders = None
+    if args.workload == "c2" and not args.no_riders:
+        riders = run_riders(dev, world, rank, flush_buf)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -478,6 +622,14 @@ def run_ours(args):
                                                 "steps", "gpu_launches")}
                          | {"e2e": train["e2e"], "workload": train["config"]["workload"]}
                          if "error" not in train else train)
+    if riders:
+        # BASELINE configs beside the headline one: C2 in fp32 (the reference's own arithmetic),
+        # C4, three points of the C5 sweep, and one event stream sharded over the ranks
+        c5 = {k_[3:]: v_ for k_, v_ in riders.items() if k_.startswith("c5_")}
+        line["fp32"] = riders.get("fp32")
+        line["c4"] = riders.get("c4")
+        line["c5"] = c5
+        line["sharded"] = riders.get("sharded")
     if world == 1 and not args.no_cpu_baseline and args.workload == "c2":
         v, cores, sec = cpu_reference_events_per_s(args.cpu_events, args.pulses, steps=10, warmup=2)
         line["cpu_baseline"] = {
@@ -638,15 +790,15 @@ def ncu_traffic_bytes(kernel_name):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the
     committed `ncu --set full` capture of this workload (profiles/r01_edge_kernel_ncu.json);
     None when the capture is of another kernel."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
-                        "r01_edge_kernel_ncu.json")
-    try:
-        with open(path) as f:
-            cap = json.load(f)
-    except (OSError, ValueError):
-        return None
-    if cap.get("kernel_prefix") and cap["kernel_prefix"] in kernel_name:
-        return cap.get("dram_bytes_per_launch")
+    for fname in ("r02_edge_kernel_ncu.json", "r01_edge_kernel_ncu.json"):
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", fname)
+        try:
+            with open(path) as f:
+                cap = json.load(f)
+        except (OSError, ValueError):
+            continue
+        if cap.get("kernel_prefix") and cap["kernel_prefix"] in kernel_name:
+            return cap.get("dram_bytes_per_launch")
     return None
 
 
@@ -675,22 +827,24 @@ def dominant_kernel_roofline(backbone, data, precision, N, E, dev, flush_buf):
             torch.cuda.synchronize(dev)
             ms = sum(a.elapsed_time(b) for a, b in zip(s, e)) / reps
             executed_flops = 2 * N * 256 * 672 + 2 * E * 336 * 256
-            name = "gn::linear_f32_kernel x2 + gn::edgeconv_f32_kernel (FFMA path)"
+            name = "gn::linear_f32_kernel x2 + gn::edgeconv_f32_kernel (fp32 path)"
     except Exception as exc:  # roofline is diagnostic; never lose the bench line
         return lambda pk: {"error": repr(exc)}
     algorithmic = 2 * E * (2 * 256 * 336 + 336 * 256)
 
     def fill(pk):
         peak = pk["bf16_tflops"]
-        ach = algorithmic / (ms * 1e-3) / 1e12
+        ach = executed_flops / (ms * 1e-3) / 1e12
         return {"bound": "tensor", "kernel": name, "achieved": ach, "peak": peak,
                 "unit": "TFLOP/s", "frac": ach / peak, "traffic": ncu_traffic_bytes(name),
                 "peak_source": f"{pk['source']} cuBLAS bf16 burst (kernel timed alone)",
-                "ms_per_launch": ms, "algorithmic_gflop_per_launch": algorithmic / 1e9,
-                "executed_gflop_per_launch": executed_flops / 1e9,
-                "executed_tflops": executed_flops / (ms * 1e-3) / 1e12,
-                "note": "achieved counts the reference's unfactored 2E(2d*a+a*b) FLOPs; the kernel "
-                        "executes the factored form (executed_*)"}
+                "ms_per_launch": ms, "executed_gflop_per_launch": executed_flops / 1e9,
+                "algorithmic_gflop_per_launch": algorithmic / 1e9,
+                "achieved_unfactored": algorithmic / (ms * 1e-3) / 1e12,
+                "note": "achieved / frac count the FLOPs the kernel issues (factored form: the "
+                        "first Linear is the node GEMM, this kernel runs 2*slots*Kp*b16 per node); "
+                        "achieved_unfactored counts the reference's 2E(2d*a+a*b) per SURVEY.md 8(d) "
+                        "and is not a utilisation"}
     return fill
 
 

@@ -11,6 +11,8 @@
 // (distance^2, index) total order falls out of the scan order plus a strict '<'
 // insertion.  Distances use __fsub_rn/__fmul_rn/__fadd_rn so nvcc cannot contract
 // them into FMAs: the rounding is that of the CPU reference.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace gn {
@@ -628,16 +630,20 @@ static __device__ __align__(256) int64_t g_static_scan_sums[STATIC_SCAN_MAX_BLOC
 // asked for, once per device, with that device current.
 static int static_scan_scratch(int64_t** out) {
   constexpr int MAX_DEVICES = 64;
-  static int64_t* addr[MAX_DEVICES] = {nullptr};
+  // several host threads may make their first call at once: the slots are atomics (all writers
+  // of a slot store the same address)
+  static std::atomic<int64_t*> addr[MAX_DEVICES];
   int dev = 0;
-  GN_CUDA(cudaGetDevice(&dev));
+  GN_CUDA(cudaGetDevice(&dev));   // the CURRENT device: it must be the one `stream` belongs to
   GN_CHECK_ARG(dev >= 0 && dev < MAX_DEVICES, "device ordinal %d not supported", dev);
-  if (addr[dev] == nullptr) {
+  int64_t* a = addr[dev].load(std::memory_order_acquire);
+  if (a == nullptr) {
     void* p = nullptr;
     GN_CUDA(cudaGetSymbolAddress(&p, g_static_scan_sums));
-    addr[dev] = reinterpret_cast<int64_t*>(p);
+    a = reinterpret_cast<int64_t*>(p);
+    addr[dev].store(a, std::memory_order_release);
   }
-  *out = addr[dev];
+  *out = a;
   return GN_OK;
 }
 

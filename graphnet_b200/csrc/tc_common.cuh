@@ -41,41 +41,35 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
                "r"(bytes)
                : "memory");
 }
-// Bounded spin: a protocol bug traps (sticky CUDA error) instead of hanging the GPU.
+// Bounded wait: a protocol bug traps (sticky CUDA error) instead of hanging the GPU.
+// try_wait is given a suspend-time hint: the warp sleeps IN HARDWARE until the phase flips (it is
+// woken at once then) or the hint runs out, instead of re-issuing try_wait + branch every ~40
+// cycles.  In the warp-specialised kernels several warps of a scheduler wait at any time; as
+// spinners they took most of its issue slots from the warps that had work (measured on the
+// CTA-pair edge kernel: the epilogue warps sharing a scheduler with spinning builders and the
+// MMA issuer ran 2-3x slower than their peers).
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
-  for (uint32_t it = 0; it < (1u << 24); ++it) {
+#pragma unroll 1
+  for (uint32_t it = 0; it < (1u << 16); ++it) {   // x 20 us: ~1.3 s, then trap
     uint32_t done;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(done)
-        : "r"(addr), "r"(parity)
+        : "r"(addr), "r"(parity), "r"(20000u)
         : "memory");
     if (done) return;
   }
   __trap();
 }
 
-// Same, for roles with slack: back off between polls so that the waiting warp does not compete
-// for issue slots with the warps on the critical path.
+// Same, for roles with slack (kept as a separate name; the hinted try_wait above already sleeps
+// in hardware).
 template <int SLEEP_NS = 200>
 __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
-  const uint32_t addr = smem_u32(bar);
-  for (uint32_t it = 0; it < (1u << 22); ++it) {
-    uint32_t done;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(addr), "r"(parity)
-        : "memory");
-    if (done) return;
-    __nanosleep(SLEEP_NS);
-  }
-  __trap();
+  mbar_wait(bar, parity);
 }
 
 // make generic-proxy shared-memory writes visible to the async proxy (TMA / tensor core)
@@ -179,6 +173,19 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32]) {
                  "+r"(r[31])
                :
                : "memory");
+}
+
+// registers -> TMEM: this warp's 32 lanes x 16 consecutive 32-bit columns
+__device__ __forceinline__ void tmem_st_32x32_x16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+      "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
 // -------------------------------------------------------------- descriptors

@@ -1,25 +1,19 @@
 // Fused EdgeConv message + aggregation on tcgen05 / TMEM (fp16 hidden layer, fp32 accumulate).
 //
-//   out[i] = sum_{j in N(i)} ReLU( W2 ReLU(P_i + Q_j) + b2 )
+//   out[i] = aggr_{j in N(i)} act( W2 act(P_i + Q_j) + b2 )
 //
 // with P = x (W1a-W1b)^T + b1 and Q = x W1b^T produced by the node GEMM (tc_linear.cu), so
 // that W1 [x_i, x_j - x_i] + b1 = P_i + Q_j.  Replaces torch_geometric EdgeConv.propagate +
-// torch_scatter sum as reached from components/layers.py:67 (MLP of dynedge.py:193-204,
-// aggr="add" dynedge.py:208).  The [E, a] hidden tensor and the [E, b] messages never
-// reach HBM: they live in shared memory / TMEM for the lifetime of one 128-edge tile.
+// torch_scatter as reached from components/layers.py:67 (MLP of dynedge.py:193-204,
+// aggr="add" dynedge.py:208).  The [E, a] hidden tensor and the [E, b] messages never reach
+// HBM: they live in shared memory / TMEM for the lifetime of one tile.  The kernel is in
+// tc_edge_pair.cuh (a CTA pair per TPC, tcgen05.mma.cta_group::2); this file holds its
+// parameter block, the layout helper for graphs that are not slot tables, and the C ABI.
 //
-// Persistent kernel, one CTA per SM, 19 warps:
-//   warp 0       tcgen05.mma issuer; owns TMEM (2 x 256 fp32 columns: double-buffered D) and
-//                loads the whole W2 (bf16, K padded, 64B-swizzled) into shared memory once by TMA
-//   warps 1-10   producers: gather P_i / Q_j rows (16-byte chunks, L2 resident), h = ReLU(P+Q)
-//                in packed fp16, written into the 64B-swizzled K-major A stage ring; one warp
-//                pair per stage, so five K-chunks are being gathered at any time
-//   warps 11-18  epilogue: TMEM -> registers, ReLU, reduce-scatter over the KP edge rows of a
-//                node with warp shuffles, store bf16 row slice (+ fp32 kNN coordinates)
-// Tile rows are ELL slots: row r of tile t is (node t*128/KP + r/KP, slot r%KP); empty slots are
-// all-zero A rows.  b2 is folded into the GEMM: P carries 1.0 in the two pad columns a, a+1 and
-// W2's columns a, a+1 hold b2 split into bf16 hi + lo parts, so an empty slot contributes
-// exactly 0 and the epilogue needs no bias add.
+// Tile rows are ELL slots: row r of tile t is (node t*NPT + r/KP, slot r%KP), KP slots per node;
+// empty slots are all-zero h rows.  b2 is folded into the GEMM: P carries 1.0 in the two pad
+// columns a, a+1 and W2's columns a, a+1 hold b2 split into fp16 hi + lo parts, so an empty
+// slot contributes exactly 0 and the epilogue needs no bias add.
 //
 // The hidden layer (P, Q, h, W2) is IEEE fp16 rather than bf16: same tensor-core rate, 3 more
 // mantissa bits, which matters because P_i + Q_j cancels (W1b (x_j - x_i) is small for near
@@ -32,28 +26,15 @@
 #include <cuda_fp16.h>
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "tc_common.cuh"
 
 namespace gn {
 namespace tc {
 
-constexpr int EK_ROWS = 128;
-constexpr int EK_KCH = 32;                       // K elements per stage (64-byte rows)
-constexpr int EK_STAGE_BYTES = EK_ROWS * 64;     // 8 KB
-constexpr int EK_STAGES = 5;
+constexpr int EK_KCH = 32;                       // hidden width is padded to a multiple of this
 constexpr int EK_MAX_CHUNKS = 11;                // hidden width (padded) <= 352
-constexpr int EK_PROD_WARPS = 2 * EK_STAGES;     // a pair of producer warps owns each stage
-constexpr int EK_EPI_WARPS = 8;
-constexpr int EK_THREADS = 32 * (1 + EK_PROD_WARPS + EK_EPI_WARPS);  // 544
-
-struct __align__(8) EdgeBarriers {
-  uint64_t full[EK_STAGES];
-  uint64_t empty[EK_STAGES];
-  uint64_t tmem_full[2];
-  uint64_t tmem_empty[2];
-  uint64_t w2_full;
-  uint32_t tmem_base;
-};
 
 struct EdgeParams {
   const __half* pmat;       // [N, ldp]: P = x (W1a-W1b)^T + b1  (+ the two "ones" columns)
@@ -75,30 +56,15 @@ struct EdgeParams {
   float* coords;            // [N, ncoord] fp32 copy of the columns selected by coord_mask, or null
   int ncoord;
   uint32_t coord_mask[8];
-  const void* w2;           // W2p [bnp, Kp] fp16 row-major (second-generation kernel reads it directly)
-  int use_ws;               // weight-stationary MMA form (collector re-use of the h chunk)
-  void* dbg;                // optional 8 x uint64 wait-time counters (GN_EDGE_DEBUG), else null
+  const void* w2;           // W2p [bnp, Kp] fp16 row-major
+  void* dbg;                // profiling builds: wait-time counters + timeline (GN_EDGE_DEBUG), else null
   uint32_t* relu_mask;      // training: [8][mask_ld] words, bit c of word (g, row) = [z(row, 32g+c) > 0]
   int64_t mask_ld;          // words per 32-channel group: >= tiles * 64
+  int act;                  // CTA-pair kernel: activation of both Linear layers (gn::Act)
+  int aggr;                 // CTA-pair kernel: 0 add, 1 mean, 2 max, 3 min
+  const int32_t* deg;       // slots in use per node (ELL graphs; mean / max / min need it)
+  const void* neg_row;      // CTA-pair kernel: 1 KB of fp16 -inf, read in place of Q_j by empty slots
 };
-
-__device__ __forceinline__ uint4 ldg16(const __half* p) {
-  return __ldg(reinterpret_cast<const uint4*>(p));
-}
-// Q rows are gathered ~k times each: ask L2 to keep them (evict_last) while the streamed
-// operands (P, outputs) pass through with normal priority.
-__device__ __forceinline__ uint64_t policy_evict_last() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ uint4 ldg16_keep(const __half* p, uint64_t pol) {
-  uint4 r;
-  asm volatile("ld.global.nc.L2::cache_hint.v4.b32 {%0, %1, %2, %3}, [%4], %5;"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p), "l"(pol));
-  return r;
-}
 
 __device__ __forceinline__ uint32_t relu_add_f16x2(uint32_t a, uint32_t b) {
   uint32_t r;  // one HFMA2.RELU: max(a * 1 + b, 0)
@@ -106,296 +72,23 @@ __device__ __forceinline__ uint32_t relu_add_f16x2(uint32_t a, uint32_t b) {
   return r;
 }
 
-__device__ __forceinline__ uint32_t pack2_16(float a, float b, bool f16) {
-  if (f16) {
-    __half2 h = __floats2half2_rn(fminf(a, 65504.f), fminf(b, 65504.f));  // inputs are >= 0
-    return *reinterpret_cast<uint32_t*>(&h);
-  }
-  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
-}
 __device__ __forceinline__ uint16_t pack1_16(float a, bool f16) {
   if (f16) {
-    __half h = __float2half_rn(fminf(a, 65504.f));
+    __half h = __float2half_rn(fmaxf(fminf(a, 65504.f), -65504.f));   // saturate, never inf
     return *reinterpret_cast<uint16_t*>(&h);
   }
   __nv_bfloat16 h = __float2bfloat16_rn(a);
   return *reinterpret_cast<uint16_t*>(&h);
 }
-__device__ __forceinline__ void red_add2_16(void* dst, float a, float b, bool f16) {
-  if (f16) atomicAdd(reinterpret_cast<__half2*>(dst), __floats2half2_rn(fminf(a, 65504.f), fminf(b, 65504.f)));
-  else atomicAdd(reinterpret_cast<__nv_bfloat162*>(dst), __floats2bfloat162_rn(a, b));
-}
 __device__ __forceinline__ void red_add1_16(void* dst, float a, bool f16) {
-  if (f16) atomicAdd(reinterpret_cast<__half*>(dst), __float2half_rn(fminf(a, 65504.f)));
+  if (f16) atomicAdd(reinterpret_cast<__half*>(dst),
+                     __float2half_rn(fmaxf(fminf(a, 65504.f), -65504.f)));
   else atomicAdd(reinterpret_cast<__nv_bfloat16*>(dst), __float2bfloat16_rn(a));
-}
-
-template <int KP>
-__global__ void __launch_bounds__(EK_THREADS, 1) edge_mlp_aggregate_kernel(
-    const __grid_constant__ CUtensorMap tmW2, const EdgeParams p) {
-  extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
-  const int w2_chunk_bytes = p.bnp * 64;
-  uint8_t* w2_smem = smem;
-  uint8_t* a_smem = smem + (size_t)p.nch * w2_chunk_bytes;
-  EdgeBarriers* bars = reinterpret_cast<EdgeBarriers*>(a_smem + EK_STAGES * EK_STAGE_BYTES);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  constexpr int NPT = EK_ROWS / KP;  // groups (nodes) per tile
-  const int nch = p.nch;
-  const int64_t num_groups = p.group_count ? (int64_t)__ldg(p.group_count) : p.N;
-  const int64_t num_tiles = (num_groups + NPT - 1) / NPT;
-  if ((int64_t)blockIdx.x >= num_tiles) return;  // uniform per CTA, before any barrier
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmW2);
-#pragma unroll
-    for (int s = 0; s < EK_STAGES; ++s) {
-      mbar_init(&bars->full[s], 2);  // the pair of producer warps that owns the stage
-      mbar_init(&bars->empty[s], 1);
-    }
-#pragma unroll
-    for (int b = 0; b < 2; ++b) {
-      mbar_init(&bars->tmem_full[b], 1);
-      mbar_init(&bars->tmem_empty[b], EK_EPI_WARPS);
-    }
-    mbar_init(&bars->w2_full, 1);
-    fence_mbar_init();
-  }
-  if (warp == 0) tmem_alloc<512>(&bars->tmem_base);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = bars->tmem_base;
-
-  if (warp == 0) {
-    // ================================================================ MMA issuer
-    if (elect_one()) {
-      mbar_arrive_expect_tx(&bars->w2_full, (uint32_t)(nch * w2_chunk_bytes));
-      for (int kc = 0; kc < nch; ++kc)
-        tma_load_2d(w2_smem + (size_t)kc * w2_chunk_bytes, &tmW2, &bars->w2_full, kc * EK_KCH, 0);
-    }
-    __syncwarp();
-    mbar_wait(&bars->w2_full, 0);
-    const uint32_t idesc = make_idesc_f16(EK_ROWS, p.bnp);
-    const uint32_t w2_addr = smem_u32(w2_smem);
-    const uint32_t a_addr = smem_u32(a_smem);
-    uint32_t g = 0;  // running stage counter
-    uint32_t it = 0;
-    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const uint32_t buf = it & 1;
-      mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
-      tc_fence_after();
-      const uint32_t tmem_d = tmem_base + buf * 256;
-      for (int kc = 0; kc < nch; ++kc, ++g) {
-        const uint32_t s = g % EK_STAGES;
-        mbar_wait(&bars->full[s], (g / EK_STAGES) & 1);
-        tc_fence_after();
-        if (elect_one()) {
-          const uint64_t adesc = make_kmajor_desc<64>(a_addr + s * EK_STAGE_BYTES);
-          const uint64_t bdesc = make_kmajor_desc<64>(w2_addr + kc * w2_chunk_bytes);
-#pragma unroll
-          for (int k2 = 0; k2 < EK_KCH / 16; ++k2)
-            mma_bf16_ss(tmem_d, adesc + (uint64_t)(k2 * 2), bdesc + (uint64_t)(k2 * 2), idesc,
-                        (kc | k2) != 0);
-          mma_commit(&bars->empty[s]);
-          if (kc == nch - 1) mma_commit(&bars->tmem_full[buf]);
-        }
-        __syncwarp();
-      }
-    }
-  } else if (warp <= EK_PROD_WARPS) {
-    // ================================================================= producers
-    // Stage s of the A ring is owned by the producer warp pair (2s, 2s+1): each warp builds 64
-    // of its 128 rows, and the five pairs work on five consecutive K-chunks concurrently.
-    // (fence.proxy.async waits for the issuing thread's outstanding global loads, so a warp
-    // cannot prefetch across its own fence - the overlap that hides the gather latency comes
-    // from the other pairs.  A pair only ever waits for the consumption of its own previous
-    // item, which keeps the mbarrier parity protocol one phase deep.)  Lane l owns the 16-byte
-    // chunk c = l & 3 of rows 64 half + (l >> 2) + 8 t, t = 0..7; rows are processed two at a
-    // time with the next pair's loads in flight.  The 8 rows of one load instruction belong to
-    // one node (KP = 8), so the P chunk is fetched once per instruction; Q rows are the gather.
-    const int pw = warp - 1;          // 0..9
-    const int owner = pw >> 1;        // stage owned by this warp's pair
-    const int half = pw & 1;
-    const int c = lane & 3;
-    const int rq = half * 64 + (lane >> 2);
-    const uint32_t a_addr = smem_u32(a_smem);
-    const int64_t my_tiles = (num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
-    const uint32_t total = (uint32_t)(my_tiles * nch);
-    const uint4 zero4 = make_uint4(0, 0, 0, 0);
-    const uint64_t pol = policy_evict_last();
-    const int64_t ell_len = num_groups * KP;
-    const uint32_t base = a_addr + owner * EK_STAGE_BYTES;
-
-    int32_t ids[8];       // neighbour ids of my 8 rows for the current item's tile
-    int32_t ids_nx[8];    // ... for my next item (prefetched)
-    auto fetch_ids = [&](uint32_t g, int32_t (&dst)[8]) {
-      const int64_t tile = blockIdx.x + (int64_t)(g / nch) * gridDim.x;
-#pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        const int64_t e = tile * EK_ROWS + rq + 8 * t;
-        dst[t] = (g < total && e < ell_len) ? __ldg(p.ell + e) : -1;
-      }
-    };
-    fetch_ids(owner, ids_nx);
-
-    for (uint32_t g = owner; g < total; g += EK_STAGES) {
-#pragma unroll
-      for (int t = 0; t < 8; ++t) ids[t] = ids_nx[t];
-      fetch_ids(g + EK_STAGES, ids_nx);
-      const int64_t tile = blockIdx.x + (int64_t)(g / nch) * gridDim.x;
-      const int kc = g % nch;
-      const __half* pbase = p.pmat + kc * EK_KCH + c * 8;
-      const __half* qbase = p.qmat + kc * EK_KCH + c * 8;
-
-      uint4 Pb[2][2], Qb[2][2];
-#define GN_EK_LOAD(BUF, S)                                                                 \
-  {                                                                                        \
-    _Pragma("unroll") for (int tt = 0; tt < 2; ++tt) {                                     \
-      const int t = 2 * (S) + tt;                                                          \
-      const int32_t j = ids[t];                                                            \
-      if (j >= 0) {                                                                        \
-        const int64_t grp = tile * NPT + (rq + 8 * t) / KP;                                \
-        const int64_t node = p.group_node ? (int64_t)__ldg(p.group_node + grp) : grp;      \
-        Pb[BUF][tt] = ldg16(pbase + node * p.ldp);                                         \
-        Qb[BUF][tt] = ldg16_keep(qbase + (int64_t)j * p.ldq, pol);                         \
-      } else {                                                                             \
-        Pb[BUF][tt] = zero4;                                                               \
-        Qb[BUF][tt] = zero4;                                                               \
-      }                                                                                    \
-    }                                                                                      \
-  }
-      GN_EK_LOAD(0, 0)
-      mbar_wait(&bars->empty[owner], ((g / EK_STAGES) & 1) ^ 1);
-#pragma unroll
-      for (int sb = 0; sb < 4; ++sb) {
-        if (sb + 1 < 4) {
-          if ((sb & 1) == 0) GN_EK_LOAD(1, sb + 1) else GN_EK_LOAD(0, sb + 1)
-        }
-#pragma unroll
-        for (int tt = 0; tt < 2; ++tt) {
-          const uint4 P = Pb[sb & 1][tt], Q = Qb[sb & 1][tt];
-          const int r = rq + 8 * (2 * sb + tt);
-          const uint32_t dst = base + (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4));
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst),
-                       "r"(relu_add_f16x2(P.x, Q.x)), "r"(relu_add_f16x2(P.y, Q.y)),
-                       "r"(relu_add_f16x2(P.z, Q.z)), "r"(relu_add_f16x2(P.w, Q.w))
-                       : "memory");
-        }
-      }
-#undef GN_EK_LOAD
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->full[owner]);
-    }
-  } else {
-    // ================================================================== epilogue
-    const int e = warp - (1 + EK_PROD_WARPS);  // 0..7
-    const int q = warp & 3;                    // TMEM lane quadrant of this warp
-    const int chalf = e >> 2;                  // which 128-column half
-    constexpr int CPL = 32 / KP;               // columns per lane after the reduce-scatter
-    const int coloff = (lane & (KP - 1)) * CPL;
-    uint32_t it = 0;
-    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const uint32_t buf = it & 1;
-      mbar_wait(&bars->tmem_full[buf], (it >> 1) & 1);
-      tc_fence_after();
-      const int64_t grp = tile * NPT + (q * 32 + lane) / KP;
-      const bool grp_ok = grp < num_groups;
-      const int64_t node = grp_ok ? (p.group_node ? (int64_t)__ldg(p.group_node + grp) : grp) : 0;
-#pragma unroll 1
-      for (int cc = 0; cc < 4; ++cc) {
-        const int c0 = chalf * 128 + cc * 32;
-        if (c0 >= p.bnp) break;
-        float v[32];
-        tmem_ld_32x32(tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
-        // reduce-scatter over the KP lanes (edge rows) of each node
-        int n = 32;
-#pragma unroll
-        for (int mask = KP / 2; mask >= 1; mask >>= 1) {
-          n >>= 1;
-          const bool up = (lane & mask) != 0;
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            if (i < n) {
-              const float send = up ? v[i] : v[i + n];
-              const float keep = up ? v[i + n] : v[i];
-              v[i] = keep + __shfl_xor_sync(0xffffffffu, send, mask);
-            }
-          }
-        }
-        const bool f16 = p.out_f16 != 0;
-        if (grp_ok && p.accumulate) {
-          const int col = c0 + coloff;
-          uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + node * p.ldo + col;
-#pragma unroll
-          for (int i = 0; i < CPL; i += 2) {
-            if (CPL >= 2 && col + i + 2 <= p.b) {
-              red_add2_16(dst + i, v[i], v[i + 1 < CPL ? i + 1 : i], f16);
-            } else {
-              if (col + i < p.b) red_add1_16(dst + i, v[i], f16);
-              if (i + 1 < CPL && col + i + 1 < p.b)
-                red_add1_16(dst + i + 1, v[i + 1 < CPL ? i + 1 : i], f16);
-            }
-          }
-          if (p.coords != nullptr) {
-#pragma unroll
-            for (int i = 0; i < CPL; ++i) {
-              const int cidx = col + i;
-              const uint32_t word = p.coord_mask[cidx >> 5];
-              if (cidx < p.b && ((word >> (cidx & 31)) & 1u)) {
-                int rank = __popc(word & ((1u << (cidx & 31)) - 1u));
-                for (int w = 0; w < (cidx >> 5); ++w) rank += __popc(p.coord_mask[w]);
-                atomicAdd(p.coords + node * p.ncoord + rank, v[i]);
-              }
-            }
-          }
-        } else if (grp_ok) {
-          const int col = c0 + coloff;
-          uint16_t* dst = reinterpret_cast<uint16_t*>(p.out) + node * p.ldo + col;
-          if (CPL == 4 && col + 4 <= p.b) {
-            uint2 u;
-            u.x = pack2_16(v[0], v[1], f16);
-            u.y = pack2_16(v[2], v[3], f16);
-            *reinterpret_cast<uint2*>(dst) = u;
-          } else {
-#pragma unroll
-            for (int i = 0; i < CPL; ++i)
-              if (col + i < p.b) dst[i] = pack1_16(v[i], f16);
-          }
-          if (p.coords != nullptr) {
-#pragma unroll
-            for (int i = 0; i < CPL; ++i) {
-              const int cidx = col + i;
-              const uint32_t word = p.coord_mask[cidx >> 5];
-              if (cidx < p.b && ((word >> (cidx & 31)) & 1u)) {
-                int rank = __popc(word & ((1u << (cidx & 31)) - 1u));
-                for (int w = 0; w < (cidx >> 5); ++w) rank += __popc(p.coord_mask[w]);
-                p.coords[node * p.ncoord + rank] = v[i];
-              }
-            }
-          }
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc<512>(tmem_base);
 }
 
 }  // namespace tc
 }  // namespace gn
-#include "tc_edge2.cuh"
-#include "tc_edge3.cuh"
+#include "tc_edge_pair.cuh"
 namespace gn {
 namespace tc {
 
@@ -440,11 +133,14 @@ static int64_t edge_overflow_cap(const gn_graph* graph, int64_t N, int slots) {
   return graph->num_edges / slots + 1;
 }
 
-// 8 wait-time counters, then a timeline of CTA 0: [warp 0..31][iteration 0..31][4 stamps]
-constexpr int EDGE_DBG_WORDS = 8 + 32 * 32 * 4;
+#ifdef GN_DEBUG_BUILD
+// profiling builds only (declared in include/graphnet_b200_debug.h): 8 wait-time counters, then a
+// timeline of cluster 0 - [CTA rank 0..1][warp 0..31][step 0..63][4 stamps], cycles since the
+// kernel's set-up barrier
+constexpr int EDGE_DBG_WORDS = 8 + 2 * 32 * 64 * 4;
 static __device__ unsigned long long g_edge_dbg[EDGE_DBG_WORDS];
 
-// diagnostic only (not part of include/graphnet_b200.h): copy out and clear the counters
+// copy out and clear the counters
 extern "C" int gn_debug_edge_counters(unsigned long long* host8) {
   GN_CUDA(cudaDeviceSynchronize());
   GN_CUDA(cudaMemcpyFromSymbol(host8, g_edge_dbg, 8 * sizeof(unsigned long long)));
@@ -452,7 +148,7 @@ extern "C" int gn_debug_edge_counters(unsigned long long* host8) {
   GN_CUDA(cudaMemcpyToSymbol(g_edge_dbg, zero, sizeof(zero)));
   return GN_OK;
 }
-// diagnostic only: the per-warp timeline of CTA 0 of the last launch (clock64 stamps)
+// the per-warp timeline of the last launch
 extern "C" int gn_debug_edge_trace(unsigned long long* host, int words) {
   GN_CUDA(cudaDeviceSynchronize());
   if (words > EDGE_DBG_WORDS - 8) words = EDGE_DBG_WORDS - 8;
@@ -460,19 +156,22 @@ extern "C" int gn_debug_edge_trace(unsigned long long* host, int words) {
                                8 * sizeof(unsigned long long)));
   return GN_OK;
 }
+#endif
 
-static bool edge_use_v2() {
-  // the third-generation kernel (tc_edge3.cuh) is opt-in until it beats the second
-  static const bool v3 = getenv("GN_EDGE_V3") != nullptr;
-  return !v3;
-}
-static bool edge_use_v1() {
-  static const bool v = getenv("GN_EDGE_V1") != nullptr;  // first-generation kernel (A/B runs)
-  return v;
-}
+// 1 KB of fp16 -inf (what an empty slot gathers instead of a neighbour row)
+#define GN_NI4 0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u
+#define GN_NI16 GN_NI4, GN_NI4, GN_NI4, GN_NI4
+#define GN_NI64 GN_NI16, GN_NI16, GN_NI16, GN_NI16
+static __device__ __align__(16) const uint32_t g_neg_inf_row[256] = {GN_NI64, GN_NI64, GN_NI64,
+                                                                      GN_NI64};
+#undef GN_NI4
+#undef GN_NI16
+#undef GN_NI64
+
 // an ELL graph whose stride is a supported slot count is consumed in place: no lists, no 2nd pass
+static bool edge_supported_slots(int s) { return s == 8 || s == 9 || s == 16 || s == 17 || s == 32; }
 static bool edge_direct_ell(const gn_graph* graph) {
-  return !edge_use_v1() && graph->ell_stride > 0 && tc::edge2_supported_slots(graph->ell_stride);
+  return graph->ell_stride > 0 && edge_supported_slots(graph->ell_stride);
 }
 
 extern "C" size_t gn_tc_edge_scratch_bytes(const gn_graph* graph, int64_t N, int slots) {
@@ -485,8 +184,8 @@ extern "C" size_t gn_tc_edge_scratch_bytes(const gn_graph* graph, int64_t N, int
 }
 
 extern "C" int64_t gn_tc_edge_relu_mask_ld(int64_t N, int slots) {
-  if (N <= 0 || !tc::edge2_supported_slots(slots)) return 0;
-  return ceil_div(N, (int64_t)(tc::E2_ROWS / slots)) * tc::E2_ROWS;
+  if (N <= 0 || !edge_supported_slots(slots)) return 0;
+  return ceil_div(N, (int64_t)(tc::E4_ROWS / slots)) * tc::E4_ROWS;
 }
 
 static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q, int64_t ldq,
@@ -502,10 +201,8 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
   GN_CHECK_ARG(Kp >= 32 && Kp % 32 == 0 && Kp <= tc::EK_MAX_CHUNKS * tc::EK_KCH,
                "gn_tc_edge_mlp_aggregate: padded hidden width %d not a multiple of 32 in [32,%d]",
                Kp, tc::EK_MAX_CHUNKS * tc::EK_KCH);
-  GN_CHECK_ARG(tc::edge2_supported_slots(slots),
+  GN_CHECK_ARG(edge_supported_slots(slots),
                "gn_tc_edge_mlp_aggregate: slots=%d (must be 8, 9, 16, 17 or 32)", slots);
-  GN_CHECK_ARG(!edge_use_v1() || slots == 8 || slots == 16 || slots == 32,
-               "gn_tc_edge_mlp_aggregate: the first-generation kernel takes 8, 16 or 32 slots");
   GN_CHECK_ARG(ldp >= Kp && ldq >= Kp && ldp % 8 == 0 && ldq % 8 == 0 && ldo % 4 == 0 && ldo >= b,
                "gn_tc_edge_mlp_aggregate: bad leading dimensions");
   GN_CHECK_ARG(ncoord >= 0 && ncoord <= 16, "gn_tc_edge_mlp_aggregate: ncoord=%d", ncoord);
@@ -537,9 +234,9 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
   const bool direct = edge_direct_ell(graph);
   if (direct) slots = graph->ell_stride;
   if (relu_mask != nullptr) {
-    if (!direct || !edge_use_v2()) {
+    if (!direct) {
       set_error("gn_tc_edge_mlp_aggregate_mask: needs an ELL graph with 8, 9, 16, 17 or 32 slots "
-                "per node and the default (second-generation) kernel");
+                "per node");
       return GN_ERR_UNSUPPORTED;
     }
     GN_CHECK_ARG(mask_ld >= gn_tc_edge_relu_mask_ld(N, slots),
@@ -557,23 +254,17 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
     GN_LAUNCH_CHECK();
   }
 
-  CUtensorMap tmW2;
-  if (edge_use_v1()) {
-    rc = make_tmap_f16_2d(&tmW2, W2p, (uint64_t)bnp, (uint64_t)Kp, (uint64_t)Kp, (uint32_t)bnp,
-                          tc::EK_KCH, 64);
-    if (rc != GN_OK) return rc;
-  }
-
   p.w2 = W2p;
+  p.act = ACT_RELU;
+  p.aggr = 0;
+  p.deg = direct ? graph->deg : nullptr;
   p.relu_mask = relu_mask;
   p.mask_ld = mask_ld;
-  // GN_EDGE_DEBUG=1: the second-generation kernel accumulates wait-time counters (tc_edge2.cuh)
-  // into g_edge_dbg, read back with the undeclared diagnostic export gn_debug_edge_counters()
-  static const bool dbg_on = getenv("GN_EDGE_DEBUG") != nullptr;
   p.dbg = nullptr;
-  static const bool ws_off = getenv("GN_EDGE_NO_WS") != nullptr;
-  p.use_ws = ws_off ? 0 : 1;
+#ifdef GN_DEBUG_BUILD   // GN_EDGE_DEBUG=1: wait-time counters and a timeline (graphnet_b200_debug.h)
+  static const bool dbg_on = getenv("GN_EDGE_DEBUG") != nullptr;
   if (dbg_on) GN_CUDA(cudaGetSymbolAddress(&p.dbg, g_edge_dbg));
+#endif
   p.pmat = reinterpret_cast<const __half*>(P);
   p.ldp = ldp;
   p.qmat = reinterpret_cast<const __half*>(Q);
@@ -588,16 +279,29 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
   p.ldo = ldo;
   p.coords = ncoord > 0 ? coords : nullptr;
   p.ncoord = ncoord;
-  const bool use_v1 = edge_use_v1();
-  const int npt = (use_v1 ? tc::EK_ROWS : tc::E2_ROWS) / slots;
+  const int npt = tc::E4_ROWS / slots;
 
   int dev = 0, sms = 0;
   GN_CUDA(cudaGetDevice(&dev));
-  GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const size_t smem1 = (size_t)p.nch * bnp * 64 + tc::EK_STAGES * tc::EK_STAGE_BYTES +
-                       sizeof(tc::EdgeBarriers) + 1024;
-  const bool use_v2 = edge_use_v2();
-  const size_t smem2 = use_v2 ? tc::edge2_smem_bytes(Kp, slots) : tc::edge3_smem_bytes(Kp);
+  {
+    static std::atomic<int> sm_count[64];   // per device, fetched once
+    sms = sm_count[dev & 63].load(std::memory_order_relaxed);
+    if (sms == 0) {
+      GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      sm_count[dev & 63].store(sms, std::memory_order_relaxed);
+    }
+  }
+  GN_CHECK_ARG(sms >= 2, "gn_tc_edge_mlp_aggregate: needs a CTA pair (>= 2 SMs)");
+  {   // a __device__ symbol has one address per device: looked up once
+    static std::atomic<void*> neg_row_addr[64];
+    void* nr = neg_row_addr[dev & 63].load(std::memory_order_relaxed);
+    if (nr == nullptr) {
+      GN_CUDA(cudaGetSymbolAddress(&nr, g_neg_inf_row));
+      neg_row_addr[dev & 63].store(nr, std::memory_order_relaxed);
+    }
+    p.neg_row = nr;
+  }
+  const size_t smem4 = tc::edge4_smem_bytes(Kp);
   for (int pass = 0; pass < 2; ++pass) {
     int64_t max_tiles;
     if (pass == 0) {
@@ -614,46 +318,40 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
       p.accumulate = 1;
       max_tiles = ceil_div(cap, npt);
     }
-    const unsigned grid = (unsigned)(max_tiles < sms ? max_tiles : sms);
-#define GN_EDGE_CASE1(KP_)                                                                       \
+    // CTA pairs: one cluster of 2 per TPC, a step = two 64-row tiles
+    const int64_t max_steps = (max_tiles + 1) / 2;
+    const unsigned grid4 = 2u * (unsigned)(max_steps < sms / 2 ? max_steps : sms / 2);
+  /* the opt-in to > 48 KB of dynamic shared memory is per function and device: once */
+#define GN_EDGE_LAUNCH4(KP_, ACC_, F16_)                                                         \
   {                                                                                              \
-    auto kern = tc::edge_mlp_aggregate_kernel<KP_>;                                              \
-    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1)); \
-    kern<<<grid, tc::EK_THREADS, smem1, st>>>(tmW2, p);                                          \
+    const bool mask_ = !(ACC_) && p.relu_mask != nullptr;                                        \
+    auto kern = mask_ ? tc::edge_mlp_aggregate_pair_kernel<KP_, false, F16_, false, true>        \
+                      : tc::edge_mlp_aggregate_pair_kernel<KP_, ACC_, F16_, false, false>;       \
+    static std::atomic<unsigned long long> ready_[2];                                            \
+    if (!((ready_[mask_].load(std::memory_order_relaxed) >> (dev & 63)) & 1ull)) {               \
+      GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,            \
+                                   (int)tc::edge4_smem_bytes(tc::EK_MAX_CHUNKS * tc::EK_KCH)));  \
+      ready_[mask_].fetch_or(1ull << (dev & 63), std::memory_order_relaxed);                     \
+    }                                                                                            \
+    kern<<<grid4, tc::E4_THREADS, smem4, st>>>(p);                                               \
   }
-#define GN_EDGE_LAUNCH2(KP_, ACC_, F16_)                                                         \
-  {                                                                                              \
-    auto kern = use_v2 ? tc::edge_mlp_aggregate_v2_kernel<KP_, ACC_, F16_>                       \
-                       : tc::edge_mlp_aggregate_v3_kernel<KP_, ACC_, F16_>;                      \
-    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2)); \
-    kern<<<grid, use_v2 ? tc::E2_THREADS : tc::E3_THREADS, smem2, st>>>(p);                      \
-  }
-#define GN_EDGE_CASE2(KP_)                                                                       \
+#define GN_EDGE_CASE4(KP_)                                                                       \
   {                                                                                              \
     if (p.accumulate) {                                                                          \
-      if (p.out_f16) GN_EDGE_LAUNCH2(KP_, true, true) else GN_EDGE_LAUNCH2(KP_, true, false)     \
+      if (p.out_f16) GN_EDGE_LAUNCH4(KP_, true, true) else GN_EDGE_LAUNCH4(KP_, true, false)     \
     } else {                                                                                     \
-      if (p.out_f16) GN_EDGE_LAUNCH2(KP_, false, true) else GN_EDGE_LAUNCH2(KP_, false, false)   \
+      if (p.out_f16) GN_EDGE_LAUNCH4(KP_, false, true) else GN_EDGE_LAUNCH4(KP_, false, false)   \
     }                                                                                            \
   }
-    if (use_v1) {
-      if (slots == 8) GN_EDGE_CASE1(8)
-      else if (slots == 16) GN_EDGE_CASE1(16)
-      else GN_EDGE_CASE1(32)
-    } else {
-      switch (slots) {
-        case 8: GN_EDGE_CASE2(8) break;
-        case 9: GN_EDGE_CASE2(9) break;
-        case 16: GN_EDGE_CASE2(16) break;
-        case 17: GN_EDGE_CASE2(17) break;
-        default: GN_EDGE_CASE2(32) break;
-      }
+    switch (slots) {
+      case 8: GN_EDGE_CASE4(8) break;
+      case 9: GN_EDGE_CASE4(9) break;
+      case 16: GN_EDGE_CASE4(16) break;
+      case 17: GN_EDGE_CASE4(17) break;
+      default: GN_EDGE_CASE4(32) break;
     }
-#undef GN_EDGE_CASE1
-#undef GN_EDGE_CASE2
-#undef GN_EDGE_LAUNCH2
-#define GN_EDGE_CASE(x)
-#undef GN_EDGE_CASE
+#undef GN_EDGE_CASE4
+#undef GN_EDGE_LAUNCH4
     GN_LAUNCH_CHECK();
   }
   return GN_OK;

@@ -168,8 +168,10 @@ __device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int
   }
 }
 
-// profiling runs (GN_TC_DEBUG=1): clock64 stamps of CTA 0, [warp 0..9][item 0..15][4]
+#ifdef GN_DEBUG_BUILD
+// profiling builds (GN_TC_DEBUG=1): clock64 stamps of CTA 0, [warp 0..9][item 0..15][4]
 __device__ unsigned long long g_lin_trace[10 * 16 * 4];
+#endif
 
 template <typename OutT, int ACT>
 __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
@@ -178,10 +180,14 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
     int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages, int splits,
     int accumulate, int coalesce_in, int wres) {
   const bool coalesce = coalesce_in != 0 && accumulate == 0;
+#ifdef GN_DEBUG_BUILD
   const bool traced = (coalesce_in & 4) && blockIdx.x == 0 && (threadIdx.x & 31) == 0;
   auto stamp = [&](uint32_t i, int k) {
     if (traced && i < 16) g_lin_trace[((threadIdx.x >> 5) * 16 + i) * 4 + k] = clock64();
   };
+#else
+  auto stamp = [](uint32_t, int) {};
+#endif
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -456,9 +462,14 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
                        (size_t)LIN_EPI_WARPS * LIN_SCR_BYTES + 16;
   // 16-byte stores need C rows and the tile's first column on 16-byte boundaries
   static const bool no_coalesce = getenv("GN_TC_NO_COALESCE") != nullptr;
+#ifdef GN_DEBUG_BUILD   // ablation / trace switches exist in profiling builds only
   static const bool hack_nostore = getenv("GN_TC_HACK_NOSTORE") != nullptr;
   static const bool dbg_trace = getenv("GN_TC_DEBUG") != nullptr;
   static const int hack_bits = getenv("GN_TC_HACK") ? atoi(getenv("GN_TC_HACK")) : 0;
+#else
+  constexpr bool hack_nostore = false, dbg_trace = false;
+  constexpr int hack_bits = 0;
+#endif
   const int coalesce = ((hack_nostore ? 3 : 1) | (dbg_trace ? 4 : 0) | (hack_bits & 24)) * (int)(!no_coalesce && (reinterpret_cast<uintptr_t>(C) % 16 == 0) &&
                        ((ldc * (int64_t)sizeof(OutT)) % 16 == 0) &&
                        ((BN * (int)sizeof(OutT)) % 16 == 0));
@@ -595,10 +606,13 @@ extern "C" int gn_tc_linear_accumulate(const void* A, int64_t lda, const void* W
                                      as_stream(stream), splits, 1);
 }
 
-// diagnostic only (not part of include/graphnet_b200.h): timeline of CTA 0 of the last tc_linear
+#ifdef GN_DEBUG_BUILD
+// profiling builds only (declared in include/graphnet_b200_debug.h): timeline of CTA 0 of the
+// last tc_linear launch
 extern "C" int gn_debug_linear_trace(unsigned long long* host, int words) {
   GN_CUDA(cudaDeviceSynchronize());
   if (words > 10 * 16 * 4) words = 10 * 16 * 4;
   GN_CUDA(cudaMemcpyFromSymbol(host, tc::g_lin_trace, words * sizeof(unsigned long long)));
   return GN_OK;
 }
+#endif

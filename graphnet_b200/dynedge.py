@@ -401,9 +401,17 @@ class DynEdge(torch.nn.Module):
         """
         if self._add_norm_layer and self.precision != "fp32":
             raise NotImplementedError("add_norm_layer=True runs on precision='fp32'")
-        training = (self.training and self.precision == "bf16" and torch.is_grad_enabled()
-                    and any(p.requires_grad for p in self.parameters()))
-        if not training:   # inference kernels allocate nothing for autograd
+        wants_grad = (self.training and torch.is_grad_enabled()
+                      and any(p.requires_grad for p in self.parameters()))
+        if wants_grad and self.precision != "bf16":
+            # the hand-written backward exists for the bf16 kernels only; returning an output
+            # without grad_fn here would let an optimizer step update the task heads while the
+            # backbone silently stays frozen
+            raise NotImplementedError(
+                f"DynEdge(precision={self.precision!r}) has no backward pass: train with "
+                "precision='bf16', or call model.eval() / wrap the call in torch.no_grad() for "
+                "inference")
+        if not wants_grad:   # inference kernels allocate nothing for autograd
             with torch.no_grad():
                 return self._forward_checked(data)
         return self._forward_checked(data)
@@ -434,8 +442,7 @@ class DynEdge(torch.nn.Module):
         if (self.training and self.precision == "bf16" and torch.is_grad_enabled()
                 and any(p.requires_grad for p in self.parameters())):
             # train mode with autograd recording: the forward that keeps what the hand-written
-            # backward needs (the fp32 / fp16 paths have no backward: their outputs carry no
-            # grad_fn, so `.backward()` on them fails loudly)
+            # backward needs (fp32 / fp16 never get here: `forward` raises for them)
             from .training import dynedge_train_forward
             if edge_index is not None:
                 data = _with_edge_index(data, edge_index)

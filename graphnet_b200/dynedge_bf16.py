@@ -278,6 +278,7 @@ def time_edge_kernel(model, data: Any, flush_buf: Tensor, layer: int = 1, reps: 
     ms = sum(a.elapsed_time(b_) for a, b_ in zip(s, e)) / reps
     E = int(ell.deg.sum().item())
     executed = 2.0 * (N * slots) * pk.Kp * pk.b16
-    name = (f"gn::tc::edge_mlp_aggregate_v2_kernel<{slots},false,{'true' if out.dtype == torch.float16 else 'false'}> "
-            "(tcgen05.mma.ws kind::f16, W2 resident in TMEM; one launch = one C-ABI call)")
+    name = (f"gn::tc::edge_mlp_aggregate_pair_kernel<{slots},false,{'true' if out.dtype == torch.float16 else 'false'},false,false> "
+            "(tcgen05.mma.cta_group::2 kind::f16, W2 split over the TMEM of a CTA pair; one launch = "
+            "one C-ABI call)")
     return ms, executed, name

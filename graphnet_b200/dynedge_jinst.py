@@ -50,8 +50,18 @@ class DynEdgeJINST(torch.nn.Module):
     def nb_outputs(self) -> int:
         return self._nb_outputs
 
-    @torch.no_grad()
     def forward(self, data: Any) -> Tensor:
+        if (self.training and torch.is_grad_enabled()
+                and any(p.requires_grad for p in self.parameters())):
+            # inference only: a silent forward without grad_fn would leave the backbone frozen
+            # while an optimizer updates the task heads
+            raise NotImplementedError(
+                "graphnet_b200.DynEdgeJINST has no backward pass: call model.eval() or wrap the "
+                "call in torch.no_grad()")
+        with torch.no_grad():
+            return self._forward(data)
+
+    def _forward(self, data: Any) -> Tensor:
         x = data.x
         if not x.is_cuda:
             raise RuntimeError("graphnet_b200.DynEdgeJINST needs CUDA tensors (no CPU fallback)")
@@ -61,8 +71,9 @@ class DynEdgeJINST(torch.nn.Module):
         l1, l3, l5 = self._dims
         n_pulses = data.n_pulses.reshape(-1)
         B = int(n_pulses.shape[0])
-        ptr, _ = ops.batch_to_ptr(data.batch, B)
+        ptr, bflags = ops.batch_to_ptr(data.batch, B)
         graph = ops.coo_to_csr(data.edge_index, N)
+        flags = graph.flags | bflags
         # homophily of x, y, z, t over the input graph (models/utils.py:17-33): columns F..F+3
         gv = ops.global_variables(x, graph, ptr, n_pulses)
         skip = torch.empty((N, l1 + 4 * l3), dtype=torch.float32, device=dev)
@@ -84,4 +95,12 @@ class DynEdgeJINST(torch.nn.Module):
         pooled[:, 4 * l5 + 1:4 * l5 + 4] = gv[:, F:F + 3]   # h_x, h_y, h_z
         pooled[:, 4 * l5 + 4] = n_pulses.to(torch.float32)
         torch.nn.functional.leaky_relu_(pooled, 0.01)
-        return ops.linear_f32(pooled, self.nn3.weight, self.nn3.bias, act="leaky_relu")
+        out = ops.linear_f32(pooled, self.nn3.weight, self.nn3.bias, act="leaky_relu")
+        if self.validate_inputs:
+            # one 4-byte device->host read per forward (as DynEdge): unsorted `batch`, edge targets
+            # out of order or ids out of range raise instead of producing garbage
+            from .dynedge import DynEdge
+            DynEdge._check_flags(int(flags.item()))
+        return out
+
+    validate_inputs: bool = True

@@ -188,7 +188,10 @@ def coo_to_csr(edge_index: Tensor, num_nodes: int) -> Graph:
     if ei.dtype != torch.int64:
         ei = ei.long()
     E = ei.shape[1]
-    rowptr = torch.empty(num_nodes + 1, dtype=torch.int32, device=dev)
+    # zero-filled: for an edge list with ids out of range the kernel flags the error and leaves
+    # part of rowptr unwritten - consumers launched before the flags are read must then see empty
+    # rows, not garbage offsets
+    rowptr = torch.zeros(num_nodes + 1, dtype=torch.int32, device=dev)
     col = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
     flags = torch.zeros(1, dtype=torch.int32, device=dev)
     maxdeg = torch.empty(1, dtype=torch.int32, device=dev)
@@ -241,6 +244,9 @@ def segment_pool(x: Tensor, ptr: Tensor, schemes: Sequence[str],
     if out is None:
         out = torch.empty((B, C_ * P), dtype=torch.float32, device=dev)
     assert out.dtype == torch.float32 and out.stride(1) == 1
+    # gn_segment_pool reads float32 or bfloat16 rows (no fp16 loader): anything else would be
+    # reinterpreted silently
+    assert x.dtype in (torch.float32, torch.bfloat16), f"segment_pool: unsupported dtype {x.dtype}"
     dt = DTYPE_BF16 if x.dtype == torch.bfloat16 else DTYPE_F32
     with _on(dev):
         check(_lib.load().gn_segment_pool(_ptr(x), dt, x.stride(0), C_, _ptr(ptr), B,
@@ -607,6 +613,9 @@ def segment_pool_backward(x: Tensor, ptr: Tensor, schemes: Sequence[str], pooled
     N, C_ = x.shape
     B = ptr.shape[0] - 1
     dX = torch.zeros((N, C_), dtype=torch.float32, device=dev)
+    # gn_segment_pool reads float32 or bfloat16 rows (no fp16 loader): anything else would be
+    # reinterpreted silently
+    assert x.dtype in (torch.float32, torch.bfloat16), f"segment_pool: unsupported dtype {x.dtype}"
     dt = DTYPE_BF16 if x.dtype == torch.bfloat16 else DTYPE_F32
     with _on(dev):
         check(_lib.load().gn_segment_pool_backward(

@@ -47,10 +47,12 @@ def take_events(data: Any, lo: int, hi: int) -> Data:
     batch = data.batch
     nlo = int(torch.searchsorted(batch, torch.tensor(lo, device=batch.device)))
     nhi = int(torch.searchsorted(batch, torch.tensor(hi, device=batch.device)))
-    ei = data.edge_index
-    keep = (ei[1] >= nlo) & (ei[1] < nhi)
-    return Data(x=data.x[nlo:nhi], batch=batch[nlo:nhi] - lo, n_pulses=data.n_pulses[lo:hi],
-                edge_index=ei[:, keep] - nlo)
+    sub = Data(x=data.x[nlo:nhi], batch=batch[nlo:nhi] - lo, n_pulses=data.n_pulses[lo:hi])
+    ei = getattr(data, "edge_index", None)
+    if ei is not None:   # a batch without edges gets its graph on the device (DynEdge._graph_inputs)
+        keep = (ei[1] >= nlo) & (ei[1] < nhi)
+        sub.edge_index = ei[:, keep] - nlo
+    return sub
 
 
 def gather_event_outputs(local: Tensor, counts: Sequence[int]) -> Tensor:

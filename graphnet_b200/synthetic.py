@@ -117,13 +117,19 @@ def make_pulse_batch(
     seed: int = 1234,
     fixed_pulses: Optional[int] = None,
     scale_m: float = 40.0,
+    counts: Optional[np.ndarray] = None,
 ) -> PulseBatch:
-    """Generate `num_events` standardised events (CPU tensors)."""
+    """Generate `num_events` standardised events (CPU tensors).
+
+    `counts` (optional, [num_events]) fixes the pulses of every event (ragged batches)."""
     rng = np.random.default_rng(seed)
     geo = icecube86_geometry() if detector == "icecube86" else upgrade_geometry()
     pos = np.stack([geo["x"], geo["y"], geo["z"]], axis=1)
     S = pos.shape[0]
-    if fixed_pulses is not None:
+    if counts is not None:
+        counts = np.maximum(2, np.asarray(counts, dtype=np.int64))
+        assert counts.shape == (num_events,)
+    elif fixed_pulses is not None:
         counts = np.full(num_events, int(fixed_pulses), dtype=np.int64)
     else:
         counts = np.maximum(2, rng.poisson(mean_pulses, size=num_events)).astype(np.int64)

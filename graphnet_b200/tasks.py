@@ -139,7 +139,9 @@ class StandardLearnedTask(torch.nn.Module):
 
     def forward(self, x: Tensor) -> Tensor:
         self._regularisation_loss = 0
-        if torch.is_grad_enabled() and (x.requires_grad or any(
+        # eval mode (model.train(False) / model.eval()) always takes the kernel path below, whether
+        # or not the caller wrapped the call in torch.no_grad(); the autograd branch is for training
+        if self.training and torch.is_grad_enabled() and (x.requires_grad or any(
                 p.requires_grad for p in self._affine.parameters())):
             # training: [B, hidden] -> [B, <=4]; autograd records these few element-wise torch
             # ops (the backbone's backward is the hand-written one, training.py)

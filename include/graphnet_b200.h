@@ -119,7 +119,8 @@ int gn_ell_row_offsets(const int32_t* deg, int64_t N, int64_t* rowptr,
  * needs only its input and output.  No counterpart in the reference.
  * Limit: N <= 4194304 nodes per call (larger N is rejected with GN_ERR_INVALID_ARGUMENT).
  * The first call on each device looks up the array's device address (cudaGetSymbolAddress);
- * make that first call before starting any stream capture.  All calls on a device share the
+ * make that first call before starting any stream capture.  The array is the CURRENT device's:
+ * the device that owns `stream` must be current when the call is made.  All calls on a device share the
  * array: calls whose kernels can overlap on the GPU (different streams) race - serialise them.
  * Nothing needs clearing between calls. */
 int gn_ell_row_offsets_noalloc(const int32_t* deg, int64_t N, int64_t* rowptr, void* stream);

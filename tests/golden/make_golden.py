@@ -20,6 +20,8 @@ prometheus  data/examples/sqlite/prometheus (50 events, 3-99 pulses, F=4),
             DynEdge(4) ctor defaults except pools=[min,max,mean,sum]; direction head.
 oscnext5_norm_gelu  the oscNext events through DynEdge(add_norm_layer=True,
             activation_layer="gelu") with 3-, 1- and 2-Linear EdgeConv MLPs.
+c2_1024_out / c4_256_out  BASELINE configs 2 and 4 at the benchmarked batch size (synthetic
+            events regenerated from the seed): outputs + per-event digests of the dynamic graphs.
 adversarial synthetic: events with n<k+1, all points identical, 2-pulse events,
             ties straddling the k+1 cut; DynEdge(7) node-level (no pooling).
 """
@@ -239,6 +241,55 @@ def run_particlenet_case(ref):
     print(f"oscnext5_particlenet: N={x.shape[0]} -> {os.path.getsize(path) / 1e3:.0f} kB")
 
 
+def graph_digest(ei, batch, ptr, num_events):
+    """Order-independent per-event digest of an edge list (int64 arithmetic wraps the same way
+    on CPU and GPU): events whose dynamic graphs equal the golden run's have equal digests."""
+    src, dst = ei[0], ei[1]
+    ev = batch[dst]
+    key = (src - ptr[ev]) * 4096 + (dst - ptr[ev]) + 1
+    h = key * 0x9E3779B97F4A7C1 + (key * key) * 0x85EBCA6B
+    out = torch.zeros(num_events, dtype=torch.int64)
+    out.index_add_(0, ev, h)
+    return out
+
+
+def run_fullsize_case(name, ref, events, pulses, detector, k, pools, seed=0, data_seed=5):
+    """BASELINE configs at the BENCHMARKED batch size (C2: 1024 x ~60 pulses, C4: 256 x ~500):
+    inputs are regenerated from the seed by the tests (graphnet_b200.synthetic), only the outputs
+    and per-event digests of the three dynamic graphs are stored."""
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(events, pulses, detector=detector, seed=data_seed)
+    x, batch, n_pulses = pb.x, pb.batch, pb.n_pulses
+    ei = oracle.knn_graph(x[:, :3], k, batch)
+    dyn_kwargs = dict(nb_neighbours=k, global_pooling_schemes=pools)
+    torch.manual_seed(seed)
+    model = ref.DynEdge(x.shape[1], **dyn_kwargs)
+    spec = oracle.DynEdgeSpec(nb_inputs=x.shape[1], **dyn_kwargs)
+    sd = {k_: v.detach().clone() for k_, v in model.state_dict().items()}
+    sd2 = oracle.init_dynedge_state_dict(spec, seed)
+    assert all(torch.equal(sd[k_], sd2[k_]) for k_ in sd) and set(sd) == set(sd2)
+    with torch.no_grad():
+        y = model(ref.Data(x=x, edge_index=ei, batch=batch, n_pulses=n_pulses))
+        y2, inter = oracle.dynedge_forward(spec, sd, x, ei, batch, n_pulses,
+                                           return_intermediates=True)
+    assert torch.equal(y, y2), "oracle restatement differs from the reference code"
+    ptr = pb.ptr
+    dig = torch.stack([graph_digest(inter["graphs"][i], batch, ptr, events) for i in (1, 2, 3)])
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(
+        path, out=y.numpy(), graph_digest=dig.numpy(), k=np.int64(k), seed=np.int64(seed),
+        data_seed=np.int64(data_seed), events=np.int64(events), pulses=np.float64(pulses),
+        detector=np.array(detector), dyn_kwargs=np.array(repr(dyn_kwargs)),
+        input_digest=np.array([float(x.double().sum()), float(x.shape[0]), float(ei.shape[1]),
+                               float(ei.double().sum())]))
+    print(f"{name}: N={x.shape[0]} B={events} E={ei.shape[1]} -> {os.path.getsize(path) / 1e3:.0f} kB")
+
+
+def run_fullsize_cases(ref):
+    run_fullsize_case("c2_1024_out", ref, 1024, 60.0, "icecube86", 8, ["min", "max", "mean", "sum"])
+    run_fullsize_case("c4_256_out", ref, 256, 500.0, "upgrade", 16, ["min", "max", "mean"], seed=1)
+
+
 def main():
     ref = refstub.load_reference()
     pools4 = ["min", "max", "mean", "sum"]
@@ -263,6 +314,7 @@ def main():
     run_particlenet_case(ref)
     x, b, n = adversarial_inputs()
     run_case("adversarial", ref, x, b, n, 8, dict(), None, seed=3)
+    run_fullsize_cases(ref)
     run_case("adversarial_k16_after", ref, x, b, n, 8,
              dict(nb_neighbours=16, global_pooling_schemes=["mean"],
                   add_global_variables_after_pooling=True,
@@ -278,5 +330,7 @@ if __name__ == "__main__":
         run_jinst_case(_ref)
     elif "--particlenet-only" in sys.argv:
         run_particlenet_case(refstub.load_reference())
+    elif "--fullsize-only" in sys.argv:
+        run_fullsize_cases(refstub.load_reference())
     else:
         main()

@@ -164,6 +164,7 @@ def test_forward_16bit_matches_golden(name, precision):
     spec = oracle.DynEdgeSpec(nb_inputs=g["x"].shape[1], **g["dyn_kwargs"])
     sd = oracle.init_dynedge_state_dict(spec, seed=int(g["seed"]))
     m = gb.DynEdge(g["x"].shape[1], precision=precision, **g["dyn_kwargs"])
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.load_state_dict(sd)
     m = m.to(DEV)
     data = gb.Data(x=g["x"].to(DEV), edge_index=g["edge_index"].to(DEV), batch=g["batch"].to(DEV),
@@ -196,6 +197,7 @@ def test_16bit_c2_batch_against_oracle(precision):
     sd = oracle.init_dynedge_state_dict(spec, seed=0)
     want = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
     m = gb.DynEdge(7, global_pooling_schemes=pools, precision=precision)
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.load_state_dict(sd)
     m = m.to(DEV)
     data = gb.Data(x=pb.x.to(DEV), edge_index=ei.to(DEV), batch=pb.batch.to(DEV),

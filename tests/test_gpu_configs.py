@@ -23,6 +23,7 @@ def _run(pb, ei, nb_inputs, k, pools, precision, seed=0):
     sd = oracle.init_dynedge_state_dict(spec, seed=seed)
     want = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
     m = gb.DynEdge(nb_inputs, nb_neighbours=k, global_pooling_schemes=pools, precision=precision)
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.load_state_dict(sd)
     m = m.to(DEV)
     data = gb.Data(x=pb.x.to(DEV), edge_index=ei.to(DEV), batch=pb.batch.to(DEV),
@@ -74,6 +75,7 @@ def test_c5_sweep_two_tasks(n):
     tasks = [gb.DirectionReconstructionWithKappa(hidden_size=128, loss_function=gb.VonMisesFisher3DLoss()),
              gb.EnergyReconstruction(hidden_size=128, loss_function=gb.LogCoshLoss())]
     m32 = gb.DynEdge(7, global_pooling_schemes=pools)
+    m32.eval()   # inference: the fp32 / fp16 paths have no backward
     m32.load_state_dict({k: v for k, v in m.state_dict().items()})
     model = gb.StandardModel(tasks=tasks, graph_definition=object(), gnn=m32).to(DEV)
     model.train(False)
@@ -99,6 +101,7 @@ def test_device_prefetcher_yields_every_batch_in_order():
         host.append(gb.Data(x=pb.x.pin_memory(), edge_index=ei.pin_memory(),
                             batch=pb.batch.pin_memory(), n_pulses=pb.n_pulses.pin_memory()))
     m = gb.DynEdge(7, global_pooling_schemes=["max"]).to(DEV)
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.train(False)
     got = []
     for d in DevicePrefetcher(host, DEV):
@@ -131,6 +134,7 @@ def test_add_norm_layer_matches_oracle(activation):
             sd[k] = sd[k] + 0.2 * torch.randn(sd[k].shape, generator=g)
     want = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
     m = gb.DynEdge(7, global_pooling_schemes=pools, add_norm_layer=True, activation_layer=activation)
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.load_state_dict(sd)
     m = m.to(DEV)
     m.train(False)
@@ -155,6 +159,7 @@ def test_deeper_edgeconv_mlps_fp32():
     sd = oracle.init_dynedge_state_dict(spec, seed=4)
     want = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
     m = gb.DynEdge(7, global_pooling_schemes=["max", "mean"], dynedge_layer_sizes=sizes)
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.load_state_dict(sd)
     m = m.to(DEV)
     m.train(False)
@@ -180,6 +185,7 @@ def test_graphed_inference_replays_bit_exact(precision):
         pytest.skip("the two synthetic batches differ in edge count")
     torch.manual_seed(4)
     backbone = gb.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision=precision)
+    backbone.eval()   # inference: the fp32 / fp16 paths have no backward
     task = gb.EnergyReconstruction(hidden_size=128, target_labels="energy", loss_function=gb.LogCoshLoss())
     model = gb.StandardModel(tasks=[task], graph_definition=object(), gnn=backbone).to(DEV)
     model.train(False)
@@ -211,6 +217,7 @@ def test_norm_gelu_deep_mlps_match_reference_golden():
     spec = oracle.DynEdgeSpec(nb_inputs=g["x"].shape[1], **g["dyn_kwargs"])
     sd = oracle.init_dynedge_state_dict(spec, seed=int(g["seed"]))
     m = gb.DynEdge(g["x"].shape[1], **g["dyn_kwargs"])
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.load_state_dict(sd)
     m = m.to(DEV)
     m.train(False)
@@ -232,6 +239,7 @@ def test_dynedge_jinst_matches_reference_golden_and_oracle():
     x, b, n, ei = (torch.from_numpy(z[k]) for k in ("x", "batch", "n_pulses", "edge_index"))
     sd = init_jinst_state_dict(x.shape[1], 4, seed=int(z["seed"]))
     m = gb.DynEdgeJINST(x.shape[1])
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.load_state_dict(sd)
     m = m.to(DEV)
     got = m(gb.Data(x=x.to(DEV), edge_index=ei.to(DEV), batch=b.to(DEV), n_pulses=n.to(DEV))).cpu()
@@ -304,6 +312,7 @@ def test_batch_without_edge_index_gets_its_graph_on_the_device(precision, tol):
     assert torch.equal(ei.cpu(), oracle.knn_graph(pb.x[:, :3], 8, pb.batch))
     torch.manual_seed(4)
     m = gb.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision=precision).to(DEV)
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.train(False)
     with torch.no_grad():
         want = m(gb.Data(x=x, edge_index=ei, batch=b, n_pulses=n))

@@ -15,6 +15,7 @@ def _model(g, precision="fp32"):
     spec = oracle.DynEdgeSpec(nb_inputs=g["x"].shape[1], **g["dyn_kwargs"])
     sd = oracle.init_dynedge_state_dict(spec, seed=int(g["seed"]))
     m = gb.DynEdge(g["x"].shape[1], precision=precision, **g["dyn_kwargs"])
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     m.load_state_dict(sd)
     return m.to(DEV), spec, sd
 
@@ -119,6 +120,7 @@ def test_standard_model_two_tasks_c5_shape():
     pools = ["min", "max", "mean"]
     torch.manual_seed(5)
     backbone = gb.DynEdge(7, global_pooling_schemes=pools)
+    backbone.eval()   # inference: the fp32 / fp16 paths have no backward
     tasks = [gb.DirectionReconstructionWithKappa(hidden_size=128, loss_function=gb.VonMisesFisher3DLoss()),
              gb.EnergyReconstruction(hidden_size=128, loss_function=gb.LogCoshLoss(),
                                      transform_prediction_and_target=lambda x: torch.log10(x))]
@@ -163,6 +165,7 @@ def test_knngraph_collate_then_forward():
     want = oracle.knn_graph(b.x.cpu()[:, :3], 8, b.batch.cpu())
     assert torch.equal(b.edge_index.cpu(), want)
     m = gb.DynEdge(7, global_pooling_schemes=["max"]).to(DEV)
+    m.eval()   # inference: the fp32 / fp16 paths have no backward
     out = m(b)
     spec = oracle.DynEdgeSpec(nb_inputs=7, global_pooling_schemes=["max"])
     y = oracle.dynedge_forward(spec, {k: v.cpu() for k, v in m.state_dict().items()}, b.x.cpu(),

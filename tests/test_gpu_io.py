@@ -28,6 +28,7 @@ def test_database_to_prediction(tmp_path):
     spec = oracle.DynEdgeSpec(nb_inputs=7, global_pooling_schemes=pools)
     sd = oracle.init_dynedge_state_dict(spec, seed=0)
     model = gb.DynEdge(7, global_pooling_schemes=pools).to(DEV)
+    model.eval()   # inference: the fp32 / fp16 paths have no backward
     model.load_state_dict(sd)
     model.train(False)
     seen = 0

@@ -219,3 +219,30 @@ def test_golden_heads_through_task_modules():
         t._affine.bias.data.copy_(g["head_bias"])
         got = t(g["out"].to(DEV)).cpu()
         assert torch.allclose(got, g["head_out"], rtol=1e-4, atol=1e-5)
+
+
+def test_eval_forward_runs_the_head_on_our_kernels():
+    """An eval-mode StandardModel forward (no torch.no_grad() around it, as bench.py calls it) must
+    run the task head through gn_linear_f32 + gn_task_head - no cuBLAS gemv, no eager softplus."""
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(8, 20.0, seed=2)
+    backbone = gb.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision="bf16")
+    task = gb.EnergyReconstruction(hidden_size=backbone.nb_outputs, target_labels="energy",
+                                   loss_function=gb.LogCoshLoss())
+    model = gb.StandardModel(tasks=[task], graph_definition=object(), gnn=backbone).to(DEV)
+    model.inference()
+    model.train(False)
+    data = gb.Data(x=pb.x.to(DEV), batch=pb.batch.to(DEV), n_pulses=pb.n_pulses.to(DEV))
+    model(data)   # warm-up (weight packing)
+    torch.cuda.synchronize()
+    from torch.profiler import ProfilerActivity, profile
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        pred = model(data)[0]
+        torch.cuda.synchronize()
+    names = [e.key for e in prof.key_averages()]
+    assert not pred.requires_grad
+    if names:   # CUPTI available
+        bad = [n for n in names if "gemv" in n.lower() or "softplus" in n.lower() or "gemm" in n.lower()]
+        assert not bad, bad
+        assert any("task_head_kernel" in n for n in names), names

@@ -101,3 +101,22 @@ def test_losses_match_oracle_on_cpu():
     p = torch.cat([v, kappa], 1)
     t = torch.nn.functional.normalize(torch.randn(50, 3), dim=1)
     assert torch.allclose(g.VonMisesFisher3DLoss()(p, t), ot.vmf3d_loss(p, t), rtol=1e-5)
+
+
+def test_train_mode_forward_without_backward_raises():
+    """precision='fp32' / 'fp16' (and DynEdgeJINST) have no backward pass: a train-mode forward with
+    autograd on must fail loudly instead of returning an output without grad_fn (an optimizer
+    would then update the task heads over a silently frozen backbone)."""
+    import graphnet_b200 as g
+    d = g.Data(x=torch.randn(6, 7), edge_index=torch.zeros(2, 0, dtype=torch.long),
+               batch=torch.zeros(6, dtype=torch.long), n_pulses=torch.tensor([6], dtype=torch.int32))
+    for prec in ("fp32", "fp16"):
+        m = g.DynEdge(7, precision=prec)
+        with pytest.raises(NotImplementedError, match="no backward"):
+            m(d)
+        m.eval()
+        with pytest.raises(RuntimeError, match="CUDA"):   # past the mode check: no CPU fallback
+            m(d)
+    j = g.DynEdgeJINST(7)
+    with pytest.raises(NotImplementedError, match="no backward"):
+        j(d)

@@ -43,12 +43,21 @@ def test_noalloc_row_offsets_match_twice_in_a_row():
         deg = torch.randint(0, 10, (N,), generator=g, dtype=torch.int32).to(DEV)
         want = _offsets_with_scratch(lib, deg)
         out = torch.full((N + 1,), -1, dtype=torch.int64, device=DEV)
-        before = torch.cuda.memory_allocated()
+        # the whole vector against an independent cumulative sum (not only the sibling scan)
+        ref = torch.zeros(N + 1, dtype=torch.int64, device=DEV)
+        ref[1:] = torch.cumsum(deg.to(torch.int64), 0)
+        torch.cuda.synchronize()
+        # the DEVICE's free memory, as the driver reports it: a cudaMalloc made inside the library
+        # would not show in torch's own counters (torch cannot see it), but it shows here
+        free_before, _ = torch.cuda.mem_get_info()
+        torch_before = torch.cuda.memory_allocated()
         assert _offsets_noalloc(lib, deg, out) == 0, lib.gn_last_error()
         torch.cuda.synchronize()
-        assert torch.cuda.memory_allocated() == before  # nothing came from torch's pool
+        free_after, _ = torch.cuda.mem_get_info()
+        assert free_after == free_before, "the call changed the device's free memory"
+        assert torch.cuda.memory_allocated() == torch_before  # nor anything from torch's pool
         assert torch.equal(out, want)  # integer result: bit-exact
-        assert int(out[-1]) == int(deg.sum())
+        assert torch.equal(out, ref)
     # and the smaller one again, after the large call
     deg = torch.randint(0, 10, (700,), generator=g, dtype=torch.int32).to(DEV)
     out = torch.empty(701, dtype=torch.int64, device=DEV)
