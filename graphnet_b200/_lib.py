@@ -61,6 +61,8 @@ SIGNATURES = {
     "gn_global_variables": (_int, [_p, _i64, _int, _gp, _p, _p, _i64, _i64, _p, _p, _i64, _int, _int,
                                    _p, _i64, _int, _int, _p]),
     "gn_segment_pool": (_int, [_p, _int, _i64, _int, _p, _i64, _hp, _int, _p, _i64, _p]),
+    "gn_tc_linear_pool": (_int, [_p, _i64, _p, _i64, _int, _p, _i64, _int, _int, _p, _p, _i64, _p, _p]),
+    "gn_pool_finalize": (_int, [_p, _p, _i64, _int, _hp, _int, _p, _i64, _p, _i64, C.c_float, _p]),
     "gn_linear_f32": (_int, [_p, _i64, _p, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),
     "gn_edgeconv_prepare_f32": (_int, [_p, _p, _int, _int, _int, _p, _p, _p]),
     "gn_edgeconv_f32": (_int, [_p, _i64, _int, _gp, _i64, _p, _p, _int, _p, _p, _int, _int, _int, _p, _p, _i64, _p]),

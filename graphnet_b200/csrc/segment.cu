@@ -11,6 +11,9 @@
 #include <cuda_fp16.h>
 #include <math.h>
 
+#include <algorithm>
+#include <atomic>
+
 #include "common.cuh"
 
 namespace gn {
@@ -176,9 +179,9 @@ __global__ void __launch_bounds__(POOL_COLS * POOL_ROWG) segment_pool_kernel(
   if (col_ok) {
     const T* base = x + (int64_t)lo * ldx + c;
     int r = rg;
-    // eight rows of this row group in flight per pass: an event of ~60 pulses is read in two
-    // dependent round trips to HBM instead of four
-    constexpr int UNR = 8;
+    // sixteen rows of this row group in flight per pass: an event of up to 64 pulses is read
+    // in ONE round trip to HBM (eight per pass needed two dependent ones)
+    constexpr int UNR = VEC == 4 ? 16 : 8;
     for (; r + (UNR - 1) * POOL_ROWG < n; r += UNR * POOL_ROWG) {
       float a[UNR][VEC];
 #pragma unroll
@@ -246,9 +249,60 @@ __global__ void __launch_bounds__(POOL_COLS * POOL_ROWG) segment_pool_kernel(
   }
 }
 
+// acc[4][B][C] (min bits / max bits / 64-bit fixed-point sum in units of 2^-32, as
+// gn_tc_linear_pool leaves them) -> the pooled row
+// of every event in the order of `sch`, plus (optionally) the scaled 16-bit copy the readout GEMM
+// reads.  An event without rows pools to 0 (torch_scatter).
+__global__ void pool_finalize_kernel(const float* __restrict__ acc, const int32_t* __restrict__ ptr,
+                                     int64_t B, int C, PoolSchemes sch, float* __restrict__ out,
+                                     int64_t ldo, __half* __restrict__ out16, int64_t ld16,
+                                     float scale16) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * C) return;
+  const int64_t e = i / C;
+  const int c = (int)(i - e * C);
+  const int n = ptr[e + 1] - ptr[e];
+  const int64_t plane = B * (int64_t)C;
+  float a = acc[i], b = acc[plane + i];
+  const float s = (float)((double)reinterpret_cast<const long long*>(acc + 2 * plane)[i] *
+                          (1.0 / 4294967296.0));
+  if (n == 0) { a = 0.f; b = 0.f; }
+  const float cnt = (float)max(n, 1);
+  for (int k = 0; k < sch.n; ++k) {
+    const float r = sch.s[k] == GN_POOL_MIN ? a
+                  : sch.s[k] == GN_POOL_MAX ? b
+                  : sch.s[k] == GN_POOL_SUM ? s : s / cnt;
+    out[e * ldo + (int64_t)k * C + c] = r;
+    if (out16 != nullptr)
+      out16[e * ld16 + (int64_t)k * C + c] =
+          __float2half_rn(fmaxf(fminf(r * scale16, 65504.f), -65504.f));
+  }
+}
+
 }  // namespace gn
 
 using namespace gn;
+
+extern "C" int gn_pool_finalize(const float* acc, const int32_t* ptr, int64_t B, int C,
+                                const int32_t* schemes, int num_schemes, float* out, int64_t ldo,
+                                void* out16, int64_t ld16, float scale16, void* stream) {
+  GN_CHECK_ARG(B >= 0 && C >= 1 && num_schemes >= 1 && num_schemes <= 8 && ldo >= (int64_t)C * num_schemes,
+               "gn_pool_finalize: bad sizes");
+  if (B == 0) return GN_OK;
+  GN_CHECK_ARG(acc && ptr && schemes && out, "gn_pool_finalize: null pointer");
+  GN_CHECK_ARG(out16 == nullptr || ld16 >= (int64_t)C * num_schemes, "gn_pool_finalize: bad ld16");
+  PoolSchemes sch;
+  sch.n = num_schemes;
+  for (int k = 0; k < num_schemes; ++k) {
+    GN_CHECK_ARG(schemes[k] >= 0 && schemes[k] <= 3, "gn_pool_finalize: unknown scheme %d", schemes[k]);
+    sch.s[k] = schemes[k];
+  }
+  const int64_t total = B * (int64_t)C;
+  pool_finalize_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, as_stream(stream)>>>(
+      acc, ptr, B, C, sch, out, ldo, reinterpret_cast<__half*>(out16), ld16, scale16);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
 
 extern "C" int gn_global_variables(const float* x, int64_t ldx, int F, const gn_graph* graph,
                                    const int32_t* ptr, const int32_t* n_pulses, int64_t N,

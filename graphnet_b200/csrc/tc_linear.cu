@@ -14,6 +14,8 @@
 #include <cuda_fp16.h>
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "tc_common.cuh"
 
 namespace gn {
@@ -173,12 +175,30 @@ __device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int
 __device__ unsigned long long g_lin_trace[10 * 16 * 4];
 #endif
 
-template <typename OutT, int ACT>
+// Segmented-pooling epilogue (POOL): instead of storing the [M, N] output, every column's min, max
+// and sum over the rows of one event (rows = nodes, sorted by event) go straight into
+// acc[3][B][N] - the [N, 256] post-processing output and the pooling kernel that re-read it
+// (63 MB each way at C2) disappear.  Values are >= 0 (ReLU), so their bit patterns order like
+// unsigned integers: min / max are plain atomicMin / atomicMax on uint32 (acc_min starts as
+// 0xFFFFFFFF, acc_max as 0).  The sum is accumulated in 64-bit FIXED POINT (units of 2^-32, every
+// element converted before it is added): integer addition is associative, so the result does not
+// depend on the order in which tiles, warps and atomics happen to run, nor on where an event's
+// rows fall relative to the 32-row chunks - the same event pools to the same bits in any batch.
+struct PoolEpilogue {
+  const int64_t* batch;   // [M] event id of every row, non-decreasing
+  const int32_t* ptr;     // [B + 1] first row of every event
+  float* acc;             // [4][B][N] words: min bits, max bits, sum (int64 fixed point: 2 planes)
+  int64_t B;
+};
+constexpr float POOL_FIX_SCALE = 4294967296.f;        // 2^32
+constexpr float POOL_FIX_MAX = 1073741824.f;          // elements are clamped to 2^30
+
+template <typename OutT, int ACT, bool POOL = false>
 __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
     int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages, int splits,
-    int accumulate, int coalesce_in, int wres) {
+    int accumulate, int coalesce_in, int wres, const PoolEpilogue pool) {
   const bool coalesce = coalesce_in != 0 && accumulate == 0;
 #ifdef GN_DEBUG_BUILD
   const bool traced = (coalesce_in & 4) && blockIdx.x == 0 && (threadIdx.x & 31) == 0;
@@ -361,6 +381,72 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
           v[j + 2] = activate<ACT>(v[j + 2] + b.z);
           v[j + 3] = activate<ACT>(v[j + 3] + b.w);
         }
+        if constexpr (POOL) {
+          // registers (lane = row) -> this warp's scratch; then lane = COLUMN walks the chunk's
+          // 32 rows (consecutive nodes) keeping min / max / sum of the current event and
+          // flushes them at every event boundary and at the end of the chunk
+          uint8_t* scr = s_scr + (warp - 2) * LIN_SCR_BYTES;
+          uint8_t* mine = scr + lane * LIN_SCR_PITCH;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(mine + j * 4) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          __syncwarp();
+          const int64_t node0 = m0 + q * 32;
+          const int rows = (int)min((int64_t)32, M - node0);
+          const int col = n + lane;
+          if (rows > 0) {
+            int64_t e = __ldg(pool.batch + node0);
+            const int64_t plane = pool.B * (int64_t)N;
+            const uint32_t col_addr = smem_u32(scr) + (uint32_t)lane * 4u;
+            auto ld_row = [&](int r) {   // this lane's column of scratch row r
+              float f;
+              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(f) : "r"(col_addr + (uint32_t)r * LIN_SCR_PITCH));
+              return f;
+            };
+            auto fix = [](float f) {     // fixed point, units of 2^-32
+              return (unsigned long long)__float2ll_rn(fminf(f, POOL_FIX_MAX) * POOL_FIX_SCALE);
+            };
+            int r = 0;
+            while (r < rows) {
+              // rows [r, rend) of the chunk belong to event e (events without rows are skipped)
+              int64_t end = __ldg(pool.ptr + e + 1);
+              while (node0 + r >= end && e + 1 < pool.B) { ++e; end = __ldg(pool.ptr + e + 1); }
+              const int rend = (int)min((int64_t)rows, end - node0);
+              // four independent chains (the row loop is latency bound otherwise)
+              float mn[4], mx[4];
+              unsigned long long sm[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) { mn[k] = __int_as_float(0x7f800000); mx[k] = 0.f; sm[k] = 0ull; }
+              for (; r + 4 <= rend; r += 4) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const float xv = ld_row(r + k);
+                  mn[k] = fminf(mn[k], xv);
+                  mx[k] = fmaxf(mx[k], xv);
+                  sm[k] += fix(xv);
+                }
+              }
+              for (; r < rend; ++r) {
+                const float xv = ld_row(r);
+                mn[0] = fminf(mn[0], xv);
+                mx[0] = fmaxf(mx[0], xv);
+                sm[0] += fix(xv);
+              }
+              if (col < N) {
+                float* a = pool.acc + e * N + col;
+                atomicMin(reinterpret_cast<unsigned int*>(a),
+                          __float_as_uint(fminf(fminf(mn[0], mn[1]), fminf(mn[2], mn[3]))));
+                atomicMax(reinterpret_cast<unsigned int*>(a + plane),
+                          __float_as_uint(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]))));
+                atomicAdd(reinterpret_cast<unsigned long long*>(pool.acc + 2 * plane) + e * N + col,
+                          (sm[0] + sm[1]) + (sm[2] + sm[3]));
+              }
+              if (r < rows) ++e;
+            }
+          }
+          __syncwarp();
+          return;
+        }
         if (row < M) {
           if constexpr (sizeof(OutT) == 4) {
             if (accumulate) {  // C += : fp32 reductions in L2 (split K, or adding onto a gradient)
@@ -453,7 +539,11 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
 template <typename OutT>
 static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, const float* bias,
                             void* C, int64_t ldc, int64_t M, int N, int K, int BN, int act,
-                            int ab_dtype, cudaStream_t st, int splits = 1, int accumulate = 0) {
+                            int ab_dtype, cudaStream_t st, int splits = 1, int accumulate = 0,
+                            const PoolEpilogue* pool_in = nullptr) {
+  PoolEpilogue pool;
+  memset(&pool, 0, sizeof(pool));
+  if (pool_in) pool = *pool_in;
   const uint32_t idesc =
       ab_dtype == GN_F16 ? make_idesc_f16(LIN_BM, BN) : make_idesc_bf16(LIN_BM, BN);
   const int num_n_tiles = (int)ceil_div(N, BN);
@@ -479,7 +569,14 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
   // weights-resident variant: one K-complete W tile per CTA + a ring of A-only stages (>= 4)
   int dev0 = 0, sms0 = 0;
   GN_CUDA(cudaGetDevice(&dev0));
-  GN_CUDA(cudaDeviceGetAttribute(&sms0, cudaDevAttrMultiProcessorCount, dev0));
+  {
+    static std::atomic<int> sm_count[64];   // per device, fetched once
+    sms0 = sm_count[dev0 & 63].load(std::memory_order_relaxed);
+    if (sms0 == 0) {
+      GN_CUDA(cudaDeviceGetAttribute(&sms0, cudaDevAttrMultiProcessorCount, dev0));
+      sm_count[dev0 & 63].store(sms0, std::memory_order_relaxed);
+    }
+  }
   static const bool no_wres = getenv("GN_TC_NO_WRES") != nullptr;
   const size_t w_bytes = (size_t)ceil_div(K, LIN_BK) * BN * LIN_BK * 2;
   int wres = 0;
@@ -492,9 +589,7 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
     smem = w_bytes + (size_t)stages * LIN_A_BYTES + fixed;
   }
   const int64_t num_tiles = ceil_div(M, LIN_BM) * num_n_tiles;
-  int dev = 0, sms = 0;
-  GN_CUDA(cudaGetDevice(&dev));
-  GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int dev = dev0, sms = sms0;
   const int nkb = (int)ceil_div(K, LIN_BK);
   if (splits == 0) {  // automatic: enough items to fill the machine, at least 4 K blocks each
     splits = (int)(sms / (num_tiles < sms ? num_tiles : sms));
@@ -505,13 +600,31 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
   const int64_t num_items = num_tiles * splits;
   unsigned grid = (unsigned)(num_items < sms ? num_items : sms);
   if (wres) grid = (unsigned)((sms / num_n_tiles) * num_n_tiles);
-#define GN_TC_LIN_CASE(A_)                                                                      \
+  /* the opt-in to > 48 KB of dynamic shared memory is per function and device: once */        \
+#define GN_TC_LIN_LAUNCH(KERN_)                                                                 \
   {                                                                                             \
-    auto kern = tc_linear_kernel<OutT, A_>;                                                     \
-    GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    auto kern = KERN_;                                                                          \
+    static std::atomic<unsigned long long> ready_;                                              \
+    if (!((ready_.load(std::memory_order_relaxed) >> (dev & 63)) & 1ull)) {                     \
+      GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
+                                   227 * 1024));                                                \
+      ready_.fetch_or(1ull << (dev & 63), std::memory_order_relaxed);                           \
+    }                                                                                           \
     kern<<<grid, LIN_THREADS, smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
                                           K, BN, num_n_tiles, num_tiles, idesc, stages, splits,  \
-                                          accumulate, coalesce, wres);                          \
+                                          accumulate, coalesce, wres, pool);                    \
+  }
+#define GN_TC_LIN_CASE(A_) GN_TC_LIN_LAUNCH((tc_linear_kernel<OutT, A_, false>))
+  if (pool.acc != nullptr) {
+    if constexpr (sizeof(OutT) == 4) {
+      if (act != GN_ACT_RELU) {
+        set_error("gn_tc_linear_pool: the pooling epilogue needs ReLU outputs");
+        return GN_ERR_UNSUPPORTED;
+      }
+      GN_TC_LIN_LAUNCH((tc_linear_kernel<float, ACT_RELU, true>))
+      GN_LAUNCH_CHECK();
+      return GN_OK;
+    }
   }
   switch (act) {
     case GN_ACT_NONE: GN_TC_LIN_CASE(ACT_NONE) break;
@@ -520,6 +633,7 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
     default: set_error("unknown activation %d", act); return GN_ERR_INVALID_ARGUMENT;
   }
 #undef GN_TC_LIN_CASE
+#undef GN_TC_LIN_LAUNCH
   GN_LAUNCH_CHECK();
   return GN_OK;
 }
@@ -584,6 +698,46 @@ extern "C" int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
     return tc::launch_tc_linear<__half>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype, st);
   return tc::launch_tc_linear<__nv_bfloat16>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype,
                                              st);
+}
+
+extern "C" int gn_tc_linear_pool(const void* A, int64_t lda, const void* W, int64_t ldw,
+                                 int ab_dtype, const float* bias, int64_t M, int N, int K,
+                                 const int64_t* batch, const int32_t* ptr, int64_t B, float* acc,
+                                 void* stream) {
+  GN_CHECK_ARG(M >= 0 && N >= 1 && K >= 1 && lda >= K && ldw >= K && B >= 0,
+               "gn_tc_linear_pool: bad sizes");
+  GN_CHECK_ARG(ab_dtype == GN_BF16 || ab_dtype == GN_F16, "gn_tc_linear_pool: bad ab_dtype");
+  GN_CHECK_ARG(N <= tc::LIN_MAX_N, "gn_tc_linear_pool: N=%d exceeds %d", N, tc::LIN_MAX_N);
+  if (B == 0) return GN_OK;
+  GN_CHECK_ARG(acc, "gn_tc_linear_pool: null pointer");
+  cudaStream_t st = as_stream(stream);
+  // identities of the three reductions: min over bit patterns of non-negative floats starts at
+  // 0xFFFFFFFF, max and sum at 0
+  const size_t plane = (size_t)B * (size_t)N * sizeof(float);
+  GN_CHECK_ARG((reinterpret_cast<uintptr_t>(acc) & 7) == 0 && (plane & 7) == 0,
+               "gn_tc_linear_pool: acc must be 8-byte aligned and B*N even");
+  GN_CUDA(cudaMemsetAsync(acc, 0xFF, plane, st));
+  GN_CUDA(cudaMemsetAsync(reinterpret_cast<uint8_t*>(acc) + plane, 0, 3 * plane, st));
+  if (M == 0) return GN_OK;
+  GN_CHECK_ARG(A && W && batch && ptr, "gn_tc_linear_pool: null pointer");
+  int BN = tc_pick_bn(N);
+  if (!tc_wres_fits(N, K, BN) && M >= 4096) {
+    const int bn2 = tc_pick_bn(N, 128);
+    if (tc_wres_fits(N, K, bn2)) BN = bn2;
+  }
+  CUtensorMap tmA, tmW;
+  auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
+  int rc = mk(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, tc::LIN_BM, tc::LIN_BK, 128);
+  if (rc != GN_OK) return rc;
+  rc = mk(&tmW, W, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)BN, tc::LIN_BK, 128);
+  if (rc != GN_OK) return rc;
+  tc::PoolEpilogue pe;
+  pe.batch = batch;
+  pe.ptr = ptr;
+  pe.acc = acc;
+  pe.B = B;
+  return tc::launch_tc_linear<float>(tmA, tmW, bias, acc, N, M, N, K, BN, GN_ACT_RELU, ab_dtype,
+                                     st, 1, 0, &pe);
 }
 
 extern "C" int gn_tc_linear_accumulate(const void* A, int64_t lda, const void* W, int64_t ldw,

@@ -194,27 +194,49 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
 
     packs = _post_pack(model, total, D0, widths, offs, io)
     h = skip
+    pools = model._global_pooling_schemes if not model._skip_readout else None
+    # inference: the last post-processing Linear + ReLU is fused with the global pooling (its
+    # [N, 256] output and the pooling kernel that re-read it never exist); training and
+    # return_intermediates keep the separate kernels (the backward pass needs that matrix)
+    fuse_pool = bool(pools) and save is None and not return_intermediates and \
+        isinstance(getattr(data, "batch", None), Tensor) and data.batch.dtype == torch.int64 \
+        and packs[-1][2] % 2 == 0
+    pooled = hb16 = None
     for i, (Wp, bias, n, K) in enumerate(packs):
         lastp = i + 1 == len(packs)
+        if lastp and fuse_pool:
+            P = len(pools)
+            extra = model._nb_global_variables if model._add_global_variables_after_pooling else 0
+            pooled = torch.empty((B, n * P + extra), dtype=torch.float32, device=dev)
+            want16 = (n * P + extra) % 8 == 0 and (n * P + extra) >= 256 and not extra
+            hb16 = (torch.empty((B, n * P), dtype=torch.float16, device=dev) if want16 else None)
+            ops.tc_linear_pool(h, Wp, bias, K, data.batch.contiguous(), ptr, pools, pooled,
+                               out16=hb16, scale16=1.0 / 64.0)
+            if extra:
+                pooled[:, n * P:] = gv
+            h = pooled
+            break
         out = torch.empty((N, n if lastp else _round_up(n, 8)),
                           dtype=torch.float32 if lastp else io, device=dev)
         ops.tc_linear_bf16(h, Wp, bias, out, K=K, act="relu")
         h = out
         if save is not None:
             save["post"].append(out)
-    inter["post"] = h
+    if pooled is None:
+        inter["post"] = h
 
     if not model._skip_readout:
-        if model._global_pooling_schemes:
-            P = len(model._global_pooling_schemes)
+        if pools and pooled is None:
+            P = len(pools)
             C_ = h.shape[1]
             extra = model._nb_global_variables if model._add_global_variables_after_pooling else 0
             pooled = torch.empty((B, C_ * P + extra), dtype=torch.float32, device=dev)
-            ops.segment_pool(h, ptr, model._global_pooling_schemes, out=pooled)
+            ops.segment_pool(h, ptr, pools, out=pooled)
             if extra:
                 pooled[:, C_ * P:] = gv
-            inter["pooled"] = pooled
             h = pooled
+        if pooled is not None:
+            inter["pooled"] = pooled
         ro, ract = _parse_mlp(model._readout)
         for ri, lin in enumerate(ro):
             hin = h
@@ -230,7 +252,8 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
                 Wb = getattr(model, key).get(
                     [lin.weight],
                     lambda: (lin.weight.detach().float() * 64.0).to(torch.float16).contiguous())
-                hb = ops.convert_scale_16(h, torch.float16, 1.0 / 64.0)
+                hb = hb16 if (ri == 0 and hb16 is not None) else \
+                    ops.convert_scale_16(h, torch.float16, 1.0 / 64.0)
                 out = torch.empty((M_, lin.out_features), dtype=torch.float32, device=dev)
                 bias = None if lin.bias is None else lin.bias.detach().float().contiguous()
                 h = ops.tc_linear_bf16(hb, Wb, bias, out, K=K_, act=ract)

@@ -359,6 +359,38 @@ def tc_linear_bf16(A: Tensor, W: Tensor, bias: Optional[Tensor], out: Tensor, K:
     return out
 
 
+def tc_linear_pool(A: Tensor, W: Tensor, bias: Optional[Tensor], K: int, batch: Tensor,
+                   ptr: Tensor, schemes: Sequence[str], out: Tensor,
+                   out16: Optional[Tensor] = None, scale16: float = 1.0) -> Tensor:
+    """out[e, s*C + c] = pool_s over the rows of event e of relu(A[:, :K] W[:, :K]^T + bias)[:, c]:
+    the last post-processing Linear fused with the global pooling (the [N, C] matrix is never
+    stored).  `out16` (optional, fp16): the same values times `scale16`."""
+    dev = _require_cuda(A, W, bias, batch, ptr, out, out16)
+    assert A.dtype == W.dtype and A.dtype in (torch.bfloat16, torch.float16)
+    assert A.stride(1) == 1 and W.stride(1) == 1 and out.stride(1) == 1
+    assert batch.dtype == torch.int64 and batch.is_contiguous() and ptr.dtype == torch.int32
+    M, C_ = A.shape[0], W.shape[0]
+    B = ptr.shape[0] - 1
+    P = len(schemes)
+    assert batch.shape[0] == M and out.dtype == torch.float32 and out.shape[0] == B
+    assert out.shape[1] >= C_ * P and A.shape[1] >= K and W.shape[1] >= K
+    if out16 is not None:
+        assert out16.dtype == torch.float16 and out16.stride(1) == 1 and out16.shape[1] >= C_ * P
+    assert (B * C_) % 2 == 0, "tc_linear_pool: B * C must be even (64-bit sum plane)"
+    acc = torch.empty((4, B, C_), dtype=torch.float32, device=dev)
+    lib = _lib.load()
+    with _on(dev):
+        check(lib.gn_tc_linear_pool(_ptr(A), A.stride(0), _ptr(W), W.stride(0), _DT[A.dtype],
+                                    _ptr(bias), M, C_, K, _ptr(batch), _ptr(ptr), B, _ptr(acc),
+                                    _stream(dev)), "gn_tc_linear_pool")
+        check(lib.gn_pool_finalize(_ptr(acc), _ptr(ptr), B, C_,
+                                   _host_i32([POOL[s] for s in schemes]), P, _ptr(out),
+                                   out.stride(0), _ptr(out16),
+                                   out16.stride(0) if out16 is not None else 0, float(scale16),
+                                   _stream(dev)), "gn_pool_finalize")
+    return out
+
+
 def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: int, W2p: Tensor,
                           b: int, out: Tensor, coords: Optional[Tensor],
                           coord_cols: Sequence[int], relu_mask: Optional[Tensor] = None) -> Tensor:

@@ -155,6 +155,24 @@ int gn_global_variables(const float* x, int64_t ldx, int F, const gn_graph* grap
                         int x0_dtype, void* x0b, int64_t ldx0b, int x0b_cols, int x0b_dtype,
                         void* stream);
 
+/* Last post-processing Linear + ReLU (dynedge.py:222-232, 332) fused with DynEdge._global_pooling
+ * (dynedge.py:252-265): relu(A[M,K] W[N,K]^T + bias) is never stored - the GEMM's epilogue reduces
+ * every column over the rows of each event and leaves acc[4][B][N] 32-bit words (min, max, and
+ * the sum as 64-bit fixed point, units of 2^-32: integer addition makes the result independent
+ * of execution order and of the batch an event sits in), which gn_pool_finalize turns into the
+ * pooled rows.  acc: 8-byte aligned, B*N even.  `batch` [M] int64 sorted (the reference's
+ * `data.batch`), `ptr` [B+1] from gn_batch_to_ptr.  acc is initialised by the call. */
+int gn_tc_linear_pool(const void* A, int64_t lda, const void* W, int64_t ldw, int ab_dtype,
+                      const float* bias, int64_t M, int N, int K, const int64_t* batch,
+                      const int32_t* ptr, int64_t B, float* acc, void* stream);
+
+/* acc[4][B][C] of gn_tc_linear_pool -> out[e, s*C + c] for each scheme in `schemes` (HOST array;
+ * the layout of gn_segment_pool, empty events give 0) and, if out16 is not NULL, the same values
+ * times scale16 as IEEE fp16 (the operand of the readout GEMM, dynedge.py:347-348). */
+int gn_pool_finalize(const float* acc, const int32_t* ptr, int64_t B, int C,
+                     const int32_t* schemes, int num_schemes, float* out, int64_t ldo,
+                     void* out16, int64_t ld16, float scale16, void* stream);
+
 /* DynEdge._global_pooling (dynedge.py:252-265): torch_scatter.scatter_{min,max,
  * sum,mean}(x, batch, dim=0) for each scheme in `schemes` (HOST array), results
  * concatenated along features: out[e, s*C + c].  Empty events give 0. */
