@@ -84,7 +84,7 @@ SIGNATURES = {
     "gn_segment_pool_backward": (_int, [_p, _int, _i64, _int, _p, _i64, _p, _int, _p, _i64, _p, _i64, _p, _i64, _p]),
     "gn_tc_edge_scratch_bytes": (_sz, [_gp, _i64, _int]),
     "gn_tc_edge_mlp_aggregate": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _int, _p, _int, _p, _i64, _int,
-                                        _p, _hp, _int, _p, _sz, _p]),
+                                        _p, _hp, _int, _p, _sz, _int, _int, _p]),
     "gn_tc_edge_relu_mask_ld": (_i64, [_i64, _int]),
     "gn_tc_edge_mlp_aggregate_mask": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _int, _p, _int, _p, _i64,
                                              _int, _p, _hp, _int, _p, _sz, _p, _i64, _p]),
@@ -93,7 +93,7 @@ SIGNATURES = {
     "gn_edge_grad_pq_gather": (_int, [_p, _i64, _p, _i64, _p, _i64, _int, _gp, _p, _i64, _i64, _p, _p, _p,
                                       _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p]),
     "gn_edgeconv_pack_tc": (_int, [_p, _p, _p, _p, _int, _int, _int, _int, _int, _p, _int, _p, _p, _p, _p, _p,
-                                   _p]),
+                                   _int, _p]),
     "gn_task_head": (_int, [_p, _i64, _int, _int, _p, _p]),
 }
 

@@ -535,6 +535,7 @@ struct PackParams {
   __half* W2p;
   __nv_bfloat16 *W2b, *W2bT;
   void* WpqT;  // same dtype as Wpq (16-bit only)
+  float ones_act;   // act(1.0) as the h builder computes it (fp16)
 };
 
 __device__ __forceinline__ void store_as(void* base, int64_t idx, int dtype, float v) {
@@ -567,7 +568,9 @@ __global__ void __launch_bounds__(256) edgeconv_pack_tc_kernel(PackParams p) {
         if (c < p.a) {
           h = __float2half_rn(p.W2[(int64_t)r * p.a + c]);
         } else if (p.b2 != nullptr && c < p.a + 2) {
-          const float bv = p.b2[r];
+          // h's "ones" columns hold act(1) (1 for ReLU / LeakyReLU, 0.8413 for GELU): the bias
+          // is divided by exactly that fp16 value, so that act(1) * (hi + lo) = b2
+          const float bv = p.b2[r] / p.ones_act;
           const __half hi = __float2half_rn(bv);
           h = c == p.a ? hi : __float2half_rn(bv - __half2float(hi));
         }
@@ -755,7 +758,9 @@ static int check_ell(const gn_graph* graph, const char* who) {
 extern "C" int gn_edgeconv_pack_tc(const float* W1, const float* b1, const float* W2,
                                    const float* b2, int d, int a, int b, int Kp, int Kd,
                                    void* Wpq, int wpq_dtype, float* bias_pq, void* W2p, void* W2b,
-                                   void* W2bT, void* WpqT, void* stream) {
+                                   void* W2bT, void* WpqT, int act, void* stream) {
+  GN_CHECK_ARG(act == GN_ACT_RELU || act == GN_ACT_LEAKY_RELU || act == GN_ACT_GELU,
+               "gn_edgeconv_pack_tc: activation %d (ReLU, LeakyReLU or GELU)", act);
   GN_CHECK_ARG(d >= 1 && a >= 1 && b >= 1 && Kp >= a + 2 && Kd >= d, "gn_edgeconv_pack_tc: bad sizes");
   GN_CHECK_ARG(W1 && W2 && Wpq && bias_pq && W2p, "gn_edgeconv_pack_tc: null pointer");
   GN_CHECK_ARG(wpq_dtype == GN_F32 || wpq_dtype == GN_BF16 || wpq_dtype == GN_F16,
@@ -770,6 +775,10 @@ extern "C" int gn_edgeconv_pack_tc(const float* W1, const float* b1, const float
   p.W2b = reinterpret_cast<__nv_bfloat16*>(W2b);
   p.W2bT = reinterpret_cast<__nv_bfloat16*>(W2bT);
   p.WpqT = WpqT;
+  // what the edge kernel's h builder makes of the "ones" columns: act(1.0), rounded to fp16
+  p.ones_act = act == GN_ACT_GELU
+                   ? __half2float(__float2half_rn(0.5f * (1.0f + erff(0.70710678118654752440f))))
+                   : 1.0f;
   const int64_t total = (int64_t)2 * Kp * Kd + (int64_t)p.b16 * Kp + 2 * Kp;
   edgeconv_pack_tc_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, as_stream(stream)>>>(p);
   GN_LAUNCH_CHECK();

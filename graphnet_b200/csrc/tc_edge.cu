@@ -194,7 +194,10 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
                                       int out_dtype, float* coords,
                                       const int32_t* coord_cols, int ncoord, void* scratch,
                                       size_t scratch_bytes, uint32_t* relu_mask, int64_t mask_ld,
-                                      void* stream) {
+                                      int act, int aggr, void* stream) {
+  GN_CHECK_ARG(act == GN_ACT_RELU || act == GN_ACT_LEAKY_RELU || act == GN_ACT_GELU,
+               "gn_tc_edge_mlp_aggregate: activation %d (ReLU, LeakyReLU or GELU)", act);
+  GN_CHECK_ARG(aggr >= GN_AGGR_ADD && aggr <= GN_AGGR_MIN, "gn_tc_edge_mlp_aggregate: aggr %d", aggr);
   GN_CHECK_ARG(out_dtype == GN_BF16 || out_dtype == GN_F16,
                "gn_tc_edge_mlp_aggregate: out_dtype must be GN_BF16 or GN_F16");
   GN_CHECK_ARG(N >= 0 && b >= 1 && b <= 256, "gn_tc_edge_mlp_aggregate: b=%d not in [1,256]", b);
@@ -255,9 +258,21 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
   }
 
   p.w2 = W2p;
-  p.act = ACT_RELU;
-  p.aggr = 0;
+  p.act = act;
+  p.aggr = aggr;
   p.deg = direct ? graph->deg : nullptr;
+  if (aggr != GN_AGGR_ADD && !direct) {
+    // mean / max / min need every in-edge of a node in ONE group of slots (an overflow group
+    // could only be combined with the first by a second reduction)
+    set_error("gn_tc_edge_mlp_aggregate: aggr != add needs an ELL graph with 8, 9, 16, 17 or 32 "
+              "slots per node (every kNN graph of this library)");
+    return GN_ERR_UNSUPPORTED;
+  }
+  if ((act != GN_ACT_RELU || aggr != GN_AGGR_ADD) && relu_mask != nullptr) {
+    set_error("gn_tc_edge_mlp_aggregate_mask: the training forward is ReLU + add only");
+    return GN_ERR_UNSUPPORTED;
+  }
+  const bool generic = act != GN_ACT_RELU || aggr != GN_AGGR_ADD;
   p.relu_mask = relu_mask;
   p.mask_ld = mask_ld;
   p.dbg = nullptr;
@@ -324,14 +339,15 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
   /* the opt-in to > 48 KB of dynamic shared memory is per function and device: once */
 #define GN_EDGE_LAUNCH4(KP_, ACC_, F16_)                                                         \
   {                                                                                              \
-    const bool mask_ = !(ACC_) && p.relu_mask != nullptr;                                        \
-    auto kern = mask_ ? tc::edge_mlp_aggregate_pair_kernel<KP_, false, F16_, false, true>        \
-                      : tc::edge_mlp_aggregate_pair_kernel<KP_, ACC_, F16_, false, false>;       \
-    static std::atomic<unsigned long long> ready_[2];                                            \
-    if (!((ready_[mask_].load(std::memory_order_relaxed) >> (dev & 63)) & 1ull)) {               \
+    const int var_ = generic ? 2 : (!(ACC_) && p.relu_mask != nullptr) ? 1 : 0;                  \
+    auto kern = var_ == 2 ? tc::edge_mlp_aggregate_pair_kernel<KP_, ACC_, F16_, true, false>     \
+              : var_ == 1 ? tc::edge_mlp_aggregate_pair_kernel<KP_, false, F16_, false, true>    \
+                          : tc::edge_mlp_aggregate_pair_kernel<KP_, ACC_, F16_, false, false>;   \
+    static std::atomic<unsigned long long> ready_[3];                                            \
+    if (!((ready_[var_].load(std::memory_order_relaxed) >> (dev & 63)) & 1ull)) {                \
       GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,            \
                                    (int)tc::edge4_smem_bytes(tc::EK_MAX_CHUNKS * tc::EK_KCH)));  \
-      ready_[mask_].fetch_or(1ull << (dev & 63), std::memory_order_relaxed);                     \
+      ready_[var_].fetch_or(1ull << (dev & 63), std::memory_order_relaxed);                      \
     }                                                                                            \
     kern<<<grid4, tc::E4_THREADS, smem4, st>>>(p);                                               \
   }
@@ -362,10 +378,10 @@ extern "C" int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* 
                                         const void* W2p, int b, void* out, int64_t ldo,
                                         int out_dtype, float* coords,
                                         const int32_t* coord_cols, int ncoord, void* scratch,
-                                        size_t scratch_bytes, void* stream) {
+                                        size_t scratch_bytes, int act, int aggr, void* stream) {
   return tc_edge_mlp_aggregate_impl(P, ldp, Q, ldq, Kp, graph, N, slots, W2p, b, out, ldo,
                                     out_dtype, coords, coord_cols, ncoord, scratch, scratch_bytes,
-                                    nullptr, 0, stream);
+                                    nullptr, 0, act, aggr, stream);
 }
 
 extern "C" int gn_tc_edge_mlp_aggregate_mask(const void* P, int64_t ldp, const void* Q,
@@ -378,6 +394,6 @@ extern "C" int gn_tc_edge_mlp_aggregate_mask(const void* P, int64_t ldp, const v
   GN_CHECK_ARG(relu_mask != nullptr, "gn_tc_edge_mlp_aggregate_mask: relu_mask is null");
   return tc_edge_mlp_aggregate_impl(P, ldp, Q, ldq, Kp, graph, N, slots, W2p, b, out, ldo,
                                     out_dtype, coords, coord_cols, ncoord, scratch, scratch_bytes,
-                                    relu_mask, mask_ld, stream);
+                                    relu_mask, mask_ld, GN_ACT_RELU, GN_AGGR_ADD, stream);
 }
 

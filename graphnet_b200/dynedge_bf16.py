@@ -41,7 +41,7 @@ class _ConvPack:
     """Repacked weights of one DynEdgeConv MLP for the tensor-core kernels."""
 
     def __init__(self, l1: torch.nn.Linear, l2: torch.nn.Linear, io_dtype: torch.dtype,
-                 first: bool, train: bool = False):
+                 first: bool, train: bool = False, act: str = "relu"):
         a, d2 = l1.weight.shape
         d = d2 // 2
         b = l2.weight.shape[0]
@@ -58,8 +58,9 @@ class _ConvPack:
         # weights (P = x Wp^T + bias_p, Q = x Wq^T), the two "ones" columns that carry b2 through
         # the second GEMM, W2p in fp16 (the hidden layer runs in fp16, see csrc/tc_edge.cu) and,
         # in training, the bf16 / transposed copies the backward GEMMs read
+        self.act = act
         packed = ops.edgeconv_pack_tc(l1.weight, l1.bias, l2.weight, l2.bias, Kp, Kd,
-                                      torch.float32 if first else io_dtype, train)
+                                      torch.float32 if first else io_dtype, train, act=act)
         self.Wpq, self.bias_pq, self.W2p, self.W2b, self.W2bT, self.WpqT = packed
         self.Wp, self.Wq = self.Wpq[:Kp], self.Wpq[Kp:]
         self.bias_p = self.bias_pq[:Kp]
@@ -71,17 +72,20 @@ def _io_dtype(model) -> torch.dtype:
 
 def _conv_pack(conv, io_dtype: torch.dtype, first: bool, train: bool = False) -> _ConvPack:
     linears, act = conv._mlp()
-    if act != "relu" or len(linears) != 2:
+    if act not in ("relu", "gelu", "leaky_relu") or len(linears) != 2:
         raise NotImplementedError(
-            "precision='bf16' supports Linear-ReLU-Linear-ReLU EdgeConv MLPs; use precision='fp32'")
-    if conv.aggr not in ("add", "sum"):
-        raise NotImplementedError("precision='bf16' supports aggr='add'; use precision='fp32'")
-    key = f"_cache_tc_{io_dtype}_{first}_{train}"
+            "the 16-bit path supports Linear-act-Linear-act EdgeConv MLPs with ReLU, GELU or "
+            "LeakyReLU; use precision='fp32'")
+    if conv.aggr not in ("add", "sum", "mean", "max", "min"):
+        raise NotImplementedError(f"aggr={conv.aggr!r}: add, mean, max or min")
+    if train and (act != "relu" or conv.aggr not in ("add", "sum")):
+        raise NotImplementedError("training runs on ReLU / aggr='add' EdgeConv layers")
+    key = f"_cache_tc_{io_dtype}_{first}_{train}_{act}"
     if not hasattr(conv, key):
         setattr(conv, key, _WeightCache())
     l1, l2 = linears
     params = [p for p in (l1.weight, l1.bias, l2.weight, l2.bias) if p is not None]
-    return getattr(conv, key).get(params, lambda: _ConvPack(l1, l2, io_dtype, first, train))
+    return getattr(conv, key).get(params, lambda: _ConvPack(l1, l2, io_dtype, first, train, act))
 
 
 def _skip_layout(model) -> Tuple[int, List[int], List[int], int]:
@@ -101,8 +105,8 @@ def _post_pack(model, total: int, D0: int, widths: List[int], offs: List[int],
     if not hasattr(model, key):
         setattr(model, key, _WeightCache())
     linears, act = _parse_mlp(model._post_processing)
-    if act != "relu":
-        raise NotImplementedError("precision='bf16' supports ReLU; use precision='fp32'")
+    if act not in ("relu", "gelu"):
+        raise NotImplementedError("the 16-bit path supports ReLU and GELU; use precision='fp32'")
     params = [p for lin in linears for p in (lin.weight, lin.bias) if p is not None]
 
     def build():
@@ -162,6 +166,15 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
         # two halves as strided matrices
         PQ = torch.empty((N, 2 * pk.Kp), dtype=torch.float16, device=dev)
         P, Q = PQ[:, :pk.Kp], PQ[:, pk.Kp:]
+        aggr = "add" if conv.aggr == "sum" else conv.aggr
+        if aggr != "add" and graph.ell_stride <= 0:
+            # mean / max / min take every in-edge of a node from one row of slots: the data set's
+            # edge_index (layer 1, CSR) goes to the slot-table layout if its degrees allow
+            if graph.max_degree is None or int(graph.max_degree.item()) > _slots(conv.nb_neighbors):
+                raise NotImplementedError(
+                    f"aggr={aggr!r} on the 16-bit path needs in-degrees <= "
+                    f"{_slots(conv.nb_neighbors)} (a kNN graph of the layer's k); use precision='fp32'")
+            graph = ops.csr_to_ell(graph, _slots(conv.nb_neighbors))
         if li == 0:
             ops.linear_f32(x0, pk.Wpq, pk.bias_pq, act="none", out=PQ)
         else:
@@ -184,7 +197,8 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
         coords = (torch.empty((N, len(cols)), dtype=torch.float32, device=dev)
                   if need_graph else None)
         ops.tc_edge_mlp_aggregate(P, Q, pk.Kp, graph, slots, pk.W2p, pk.b,
-                                  skip[:, offs[li]:], coords, cols, relu_mask=relu_mask)
+                                  skip[:, offs[li]:], coords, cols, relu_mask=relu_mask,
+                                  act=pk.act, aggr=aggr)
         if need_graph:
             graph = ops.knn_graph_ell(coords, conv.nb_neighbors, ptr, list(range(len(cols))))
             if return_intermediates:
@@ -193,12 +207,15 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
         off_in, d_in = offs[li], pk.b
 
     packs = _post_pack(model, total, D0, widths, offs, io)
+    pact = _parse_mlp(model._post_processing)[1]
+    if save is not None and pact != "relu":
+        raise NotImplementedError("training runs on ReLU post-processing layers")
     h = skip
     pools = model._global_pooling_schemes if not model._skip_readout else None
     # inference: the last post-processing Linear + ReLU is fused with the global pooling (its
     # [N, 256] output and the pooling kernel that re-read it never exist); training and
     # return_intermediates keep the separate kernels (the backward pass needs that matrix)
-    fuse_pool = bool(pools) and save is None and not return_intermediates and \
+    fuse_pool = bool(pools) and pact == "relu" and save is None and not return_intermediates and \
         isinstance(getattr(data, "batch", None), Tensor) and data.batch.dtype == torch.int64 \
         and packs[-1][2] % 2 == 0
     pooled = hb16 = None
@@ -218,7 +235,7 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
             break
         out = torch.empty((N, n if lastp else _round_up(n, 8)),
                           dtype=torch.float32 if lastp else io, device=dev)
-        ops.tc_linear_bf16(h, Wp, bias, out, K=K, act="relu")
+        ops.tc_linear_bf16(h, Wp, bias, out, K=K, act=pact)
         h = out
         if save is not None:
             save["post"].append(out)

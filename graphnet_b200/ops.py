@@ -393,8 +393,10 @@ def tc_linear_pool(A: Tensor, W: Tensor, bias: Optional[Tensor], K: int, batch: 
 
 def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: int, W2p: Tensor,
                           b: int, out: Tensor, coords: Optional[Tensor],
-                          coord_cols: Sequence[int], relu_mask: Optional[Tensor] = None) -> Tensor:
-    """out[i] = sum_j ReLU(W2 ReLU(P_i + Q_j) + b2) on tcgen05 (see include/graphnet_b200.h).
+                          coord_cols: Sequence[int], relu_mask: Optional[Tensor] = None,
+                          act: str = "relu", aggr: str = "add") -> Tensor:
+    """out[i] = aggr_j act(W2 act(P_i + Q_j) + b2) on tcgen05 (see include/graphnet_b200.h);
+    act in relu / gelu / leaky_relu, aggr in add / mean / max / min.
 
     `relu_mask` ([8, ld] int32 from `edge_relu_mask`, training): receives the ReLU bits of the
     second Linear for the backward pass (gn_tc_edge_mlp_aggregate_mask)."""
@@ -423,12 +425,13 @@ def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: in
             _ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp, C.byref(gs), N, slots, _ptr(W2p), b,
             _ptr(out), out.stride(0), _DT[out.dtype], _ptr(coords),
             _host_i32(coord_cols) if ncoord else None,
-            ncoord, _ptr(scratch), nbytes, _stream(dev)), "gn_tc_edge_mlp_aggregate")
+            ncoord, _ptr(scratch), nbytes, ACT[act], AGGR[aggr], _stream(dev)),
+            "gn_tc_edge_mlp_aggregate")
     return out
 
 
 def edgeconv_pack_tc(W1: Tensor, b1: Optional[Tensor], W2: Tensor, b2: Optional[Tensor], Kp: int,
-                     Kd: int, wpq_dtype: torch.dtype, train: bool):
+                     Kd: int, wpq_dtype: torch.dtype, train: bool, act: str = "relu"):
     """(Wpq, bias_pq, W2p, W2b, W2bT, WpqT) for the tensor-core EdgeConv kernels from the
     nn.Linear parameters, in one launch; the last three only when `train` (else None)."""
     dev = _require_cuda(W1, b1, W2, b2)
@@ -451,7 +454,8 @@ def edgeconv_pack_tc(W1: Tensor, b1: Optional[Tensor], W2: Tensor, b2: Optional[
     with _on(dev):
         check(_lib.load().gn_edgeconv_pack_tc(_ptr(W1), _ptr(b1), _ptr(W2), _ptr(b2), d, a, b, Kp,
                                               Kd, _ptr(Wpq), _DT[wpq_dtype], _ptr(bias), _ptr(W2p),
-                                              _ptr(W2b), _ptr(W2bT), _ptr(WpqT), _stream(dev)),
+                                              _ptr(W2b), _ptr(W2bT), _ptr(WpqT), ACT[act],
+                                              _stream(dev)),
               "gn_edgeconv_pack_tc")
     return Wpq, bias, W2p, W2b, W2bT, WpqT
 

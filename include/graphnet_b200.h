@@ -33,7 +33,7 @@ extern "C" {
 #define GN_ACT_NONE 0
 #define GN_ACT_RELU 1
 #define GN_ACT_GELU 2
-#define GN_ACT_LEAKY_RELU 3 /* torch.nn.LeakyReLU(), slope 0.01 (DynEdgeJINST; FFMA kernels only) */
+#define GN_ACT_LEAKY_RELU 3 /* torch.nn.LeakyReLU(), slope 0.01 (DynEdgeJINST) */
 
 /* aggregation of EdgeConv messages (components/layers.py:33; dynedge.py:208 uses ADD) */
 #define GN_AGGR_ADD 0
@@ -221,8 +221,11 @@ int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t ldw, int ab_
                  const float* bias, void* C, int64_t ldc, int c_dtype, int64_t M, int N, int K,
                  int act, void* stream);
 
-/* Second half of the fused EdgeConv (components/layers.py:67, aggr="add"):
- *   out[i] = sum_{j in N(i)} ReLU(W2 ReLU(P_i + Q_j) + b2)
+/* Second half of the fused EdgeConv (components/layers.py:30-36, :67):
+ *   out[i] = aggr_{j in N(i)} act(W2 act(P_i + Q_j) + b2)
+ * act = GN_ACT_RELU / GN_ACT_GELU (dynedge.py:161-168) / GN_ACT_LEAKY_RELU; aggr = GN_AGGR_ADD
+ * (DynEdge, dynedge.py:208), MEAN, MAX or MIN (DynEdgeConv(aggr=...), PyG semantics: a node without
+ * in-edges gets 0; these three need an ELL graph, i.e. any kNN graph of this library).
  * P [N, ldp] and Q [N, ldq] are fp16 (as written by gn_tc_linear / gn_linear_f32 with c_dtype
  * GN_F16), Kp columns each (Kp = hidden width a padded to a multiple of 32 with >= 2 pad
  * columns; P[:,a] = P[:,a+1] = 1, Q pads = 0).  Q is the gathered operand: keeping it in its
@@ -240,7 +243,7 @@ int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t 
                              void* out,
                              int64_t ldo, int out_dtype, float* coords,
                              const int32_t* coord_cols, int ncoord, void* scratch,
-                             size_t scratch_bytes, void* stream);
+                             size_t scratch_bytes, int act, int aggr, void* stream);
 
 /* Training forward of the same op: additionally records the ReLU pattern of the second Linear
  * (what torch autograd keeps as the saved output of the ReLU in PyG's EdgeConv.message,
@@ -327,10 +330,12 @@ int gn_relu_backward(const void* dY, int dy_dtype, int64_t ld_dy, const void* Y,
  * W1[:, :d] - W1[:, d:], rows Kp.. = W1[:, d:]; wpq_dtype GN_F32 for the first layer, else 16-bit),
  * bias_pq [2Kp] fp32 (b1, then the two "ones" columns), W2p [b16, Kp] fp16 (W2; columns a, a+1 =
  * b2 split in fp16 hi/lo).  Optional, for the backward pass: W2b = bf16(W2p), W2bT [Kp, b16] its
- * transpose, WpqT [Kd, 2Kp] the transpose of a 16-bit Wpq.  b1, b2 may be NULL (no bias). */
+ * transpose, WpqT [Kd, 2Kp] the transpose of a 16-bit Wpq.  b1, b2 may be NULL (no bias).
+ * `act` is the MLP's activation (GN_ACT_RELU / GELU / LEAKY_RELU): the "ones" columns pass
+ * through it in the edge kernel, so b2 is stored divided by act(1). */
 int gn_edgeconv_pack_tc(const float* W1, const float* b1, const float* W2, const float* b2, int d,
                         int a, int b, int Kp, int Kd, void* Wpq, int wpq_dtype, float* bias_pq,
-                        void* W2p, void* W2b, void* W2bT, void* WpqT, void* stream);
+                        void* W2p, void* W2b, void* W2bT, void* WpqT, int act, void* stream);
 
 /* Re-materialise the hidden activations of the EdgeConv message MLP (PyG EdgeConv.message,
  * components/layers.py:67) for every slot of an ELL graph (stride = slots per node, -1 = empty):

@@ -240,3 +240,75 @@ def test_fused_linear_pool_matches_linear_then_pool(pools):
         else:
             assert float((a - b).abs().max() / b.abs().max()) < 1e-5, s
     assert float((got16.float() - got * 0.25).abs().max()) <= float(got.abs().max()) * 0.25 * 2 ** -10
+
+
+@pytest.mark.parametrize("act,aggr", [("gelu", "add"), ("leaky_relu", "add"), ("relu", "max"),
+                                      ("relu", "mean"), ("relu", "min"), ("gelu", "max"),
+                                      ("leaky_relu", "mean")])
+def test_tc_edge_activations_and_aggregations(act, aggr):
+    """The tensor-core EdgeConv with the reference's other constructor options: GELU
+    (dynedge.py:161-168), LeakyReLU (dynedge_jinst.py) and DynEdgeConv(aggr="max" | "mean" | "min")
+    (layers.py:30-36), PyG semantics: a node without in-edges gets 0.  b2 rides through the "ones"
+    columns, which pass through the activation (packed as b2 / act(1))."""
+    import graphnet_b200.ops as ops
+    from graphnet_b200.dynedge_bf16 import _slots, _round_up
+    k, a, b = 8, 80, 96
+    x, batch, _ = random_events(30, 1, 40, seed=11)   # events of 1 pulse: nodes without in-edges
+    N, B = x.shape[0], 30
+    ptr, _ = ops.batch_to_ptr(batch.to(DEV), B)
+    ell = ops.knn_graph_ell(x.to(DEV), k, ptr, [0, 1, 2])
+    ei = oracle.knn_graph(x[:, :3], k, batch)
+    Kp = _round_up(a + 2, 32)
+    g = torch.Generator().manual_seed(5)
+    l1 = torch.nn.Linear(2 * 7, a)
+    l2 = torch.nn.Linear(a, b)
+    with torch.no_grad():
+        l2.bias.mul_(3.0)   # a bias that matters
+    Wpq, bias_pq, W2p, _, _, _ = ops.edgeconv_pack_tc(l1.weight.to(DEV), l1.bias.to(DEV), l2.weight.to(DEV),
+                                                      l2.bias.to(DEV), Kp, 7, torch.float32, False, act=act)
+    xin = torch.randn(N, 7, generator=g)
+    PQ = torch.empty(N, 2 * Kp, dtype=torch.float16, device=DEV)
+    ops.linear_f32(xin.to(DEV), Wpq, bias_pq, act="none", out=PQ)
+    out = torch.full((N, b), -3.0, dtype=torch.bfloat16, device=DEV)
+    coords = torch.empty(N, 3, device=DEV)
+    ops.tc_edge_mlp_aggregate(PQ[:, :Kp], PQ[:, Kp:], Kp, ell, _slots(k), W2p, b, out, coords, [0, 1, 2],
+                              act=act, aggr=aggr)
+    # reference: PyG EdgeConv on the same fp16-rounded P, Q with the true W2, b2
+    f = {"relu": torch.relu, "gelu": torch.nn.functional.gelu,
+         "leaky_relu": lambda t: torch.nn.functional.leaky_relu(t, 0.01)}[act]
+    P, Q = PQ[:, :a].float().cpu(), PQ[:, Kp:Kp + a].float().cpu()
+    src, dst = ei[0], ei[1]
+    h = f((P[dst] + Q[src]).to(torch.float16).float()).to(torch.float16).float()
+    msg = f(h @ l2.weight.detach().to(torch.float16).float().t() + l2.bias.detach())
+    want = torch.zeros(N, b)
+    if aggr in ("add", "mean"):
+        want.index_add_(0, dst, msg)
+        if aggr == "mean":
+            want /= torch.bincount(dst, minlength=N).clamp(min=1).unsqueeze(1)
+    else:
+        red = "amax" if aggr == "max" else "amin"
+        want = want.scatter_reduce(0, dst.unsqueeze(1).expand(-1, b), msg, red, include_self=False)
+    deg = torch.bincount(dst, minlength=N)
+    assert int((deg == 0).sum()) > 0, "the case must contain nodes without in-edges"
+    scale = want.abs().max()
+    assert float((out.float().cpu() - want).abs().max() / scale) < 1e-2
+    assert float((coords.cpu() - want[:, :3]).abs().max() / scale) < 2e-3
+    assert bool((out[deg.to(DEV) == 0] == 0).all())
+
+
+def test_dynedge_gelu_on_the_tensor_cores():
+    """DynEdge(activation_layer="gelu") (reference dynedge.py:161-168) in bf16 against the oracle."""
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    pb = make_pulse_batch(24, 40.0, seed=9)
+    ei = oracle.knn_graph(pb.x[:, :3], 8, pb.batch)
+    kw = dict(global_pooling_schemes=["min", "max", "mean", "sum"], activation_layer="gelu")
+    spec = oracle.DynEdgeSpec(nb_inputs=7, **kw)
+    sd = oracle.init_dynedge_state_dict(spec, seed=2)
+    want = oracle.dynedge_forward(spec, sd, pb.x, ei, pb.batch, pb.n_pulses)
+    m = gb.DynEdge(7, precision="bf16", **kw)
+    m.load_state_dict(sd)
+    m = m.to(DEV).eval()
+    got = m(gb.Data(x=pb.x.to(DEV), edge_index=ei.to(DEV), batch=pb.batch.to(DEV),
+                    n_pulses=pb.n_pulses.to(DEV)))
+    assert rel_l2(got.cpu(), want) < BF16_TOL
