@@ -175,6 +175,21 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32]) {
                : "memory");
 }
 
+// explicit shared-space accesses (a pointer carved out of dynamic shared memory through integer
+// alignment arithmetic is "generic" to the compiler, which then emits LD.E / ST.E)
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
 // registers -> TMEM: this warp's 32 lanes x 16 consecutive 32-bit columns
 __device__ __forceinline__ void tmem_st_32x32_x16(uint32_t taddr, const uint32_t (&r)[16]) {
   asm volatile(

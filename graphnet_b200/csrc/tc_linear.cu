@@ -79,14 +79,29 @@ namespace tc {
 constexpr int LIN_BM = 128;
 constexpr int LIN_BK = 64;        // 64 bf16 = one 128-byte swizzle row
 constexpr int LIN_STAGES = 8;     // capacity of the barrier arrays; the ring uses `stages` of them
-constexpr int LIN_EPI_WARPS = 8;
-constexpr int LIN_THREADS = 32 * (2 + LIN_EPI_WARPS);  // TMA + MMA + 8 epilogue warps
+// Epilogue warps: 16 for 16-bit outputs, 8 for fp32.  The epilogue of a 128 x BN tile (TMEM ->
+// registers -> bias / activation / pack -> scratch -> coalesced stores) is a long dependent
+// chain per warp; with eight warps (two per scheduler) it took ~3900 cycles per tile of the node
+// GEMMs against ~1400 of tensor work and paced the kernel (timeline of CTA 0, profiling build).
+// Sixteen warps halve the chunks per warp and give every scheduler four warps to interleave.
+// fp32 outputs keep eight: their scratch rows are twice as wide, and the shared memory is better
+// spent on the resident W tile.
+template <typename OutT>
+__host__ __device__ constexpr int lin_epi_warps() { return sizeof(OutT) == 4 ? 8 : 16; }
+template <typename OutT>
+__host__ __device__ constexpr int lin_threads() { return 32 * (2 + lin_epi_warps<OutT>()); }
 constexpr int LIN_MAX_N = 2048;   // bias staged in shared memory
 constexpr int LIN_A_BYTES = LIN_BM * LIN_BK * 2;  // 16 KB
 // per epilogue warp: a 32-row x 32-column chunk on its way from "lane = row" (tcgen05.ld) to
 // "lanes = consecutive 16-byte pieces of a row" (coalesced global stores); rows padded by 16 B
-constexpr int LIN_SCR_PITCH = 32 * 4 + 16;
-constexpr int LIN_SCR_BYTES = 32 * LIN_SCR_PITCH;  // 4608
+// fp32: rows of 128 B padded by 16 B.  16-bit: rows of 64 B, not padded, the 16-byte piece index
+// XOR-ed with (row >> 1) & 3 - conflict free both for the row-wise writes and for the reads
+// (the padded layout had 2-way conflicts on the 16-bit reads: 41 % of the kernel's wavefronts)
+template <typename OutT>
+__host__ __device__ constexpr int lin_scr_pitch() { return sizeof(OutT) == 4 ? 32 * 4 + 16 : 64; }
+template <typename OutT>
+__host__ __device__ constexpr int lin_scr_bytes() { return 32 * lin_scr_pitch<OutT>(); }
+constexpr int LIN_SCR_PITCH = 32 * 4 + 16;       // fp32 (the pooling epilogue reads it by column)
 
 struct __align__(16) LinBarriers {
   uint64_t full[LIN_STAGES];
@@ -194,16 +209,22 @@ constexpr float POOL_FIX_SCALE = 4294967296.f;        // 2^32
 constexpr float POOL_FIX_MAX = 1073741824.f;          // elements are clamped to 2^30
 
 template <typename OutT, int ACT, bool POOL = false>
-__global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
+__global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
     int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages, int splits,
     int accumulate, int coalesce_in, int wres, const PoolEpilogue pool) {
+  constexpr int LIN_EPI_WARPS = lin_epi_warps<OutT>();
+  constexpr int LIN_THREADS = lin_threads<OutT>();
+  constexpr int NPAR = LIN_EPI_WARPS / 4;          // warps sharing a TMEM lane quadrant
+  constexpr int SCR_PITCH = lin_scr_pitch<OutT>();
+  constexpr int SCR_BYTES = lin_scr_bytes<OutT>();
   const bool coalesce = coalesce_in != 0 && accumulate == 0;
 #ifdef GN_DEBUG_BUILD
   const bool traced = (coalesce_in & 4) && blockIdx.x == 0 && (threadIdx.x & 31) == 0;
   auto stamp = [&](uint32_t i, int k) {
-    if (traced && i < 16) g_lin_trace[((threadIdx.x >> 5) * 16 + i) * 4 + k] = clock64();
+    if (traced && i < 16 && (threadIdx.x >> 5) < 10)
+      g_lin_trace[((threadIdx.x >> 5) * 16 + i) * 4 + k] = clock64();
   };
 #else
   auto stamp = [](uint32_t, int) {};
@@ -224,7 +245,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
   const int stage_bytes = LIN_A_BYTES + (wres ? 0 : b_bytes);
   LinBarriers* bars = reinterpret_cast<LinBarriers*>(ring + stages * stage_bytes);
   float* s_bias = reinterpret_cast<float*>(bars + 1);  // [num_n_tiles * BN]
-  uint8_t* s_scr = reinterpret_cast<uint8_t*>(s_bias + num_n_tiles * BN);  // 8 x LIN_SCR_BYTES
+  uint8_t* s_scr = reinterpret_cast<uint8_t*>(s_bias + num_n_tiles * BN);  // one scratch per epilogue warp
   s_scr = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_scr) + 15) & ~uintptr_t(15));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -366,30 +387,32 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
       // the transpose and the stores.
       const uint32_t t_addr = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
       auto chunk_ok = [&](int c) { return c < BN && n0 + c < N; };
-      uint32_t ra[32], rb[32];
+      uint32_t ra[32];
+      [[maybe_unused]] uint32_t rb[32];
       auto process = [&](uint32_t (&raw)[32], const int c) {
         const int n = n0 + c;
         float v[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
-        const float4* b4 = reinterpret_cast<const float4*>(s_bias + n);
+        const uint32_t b4 = smem_u32(s_bias + n);
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
-          const float4 b = b4[j >> 2];  // same address in every lane: one broadcast wavefront
-          v[j] = activate<ACT>(v[j] + b.x);
-          v[j + 1] = activate<ACT>(v[j + 1] + b.y);
-          v[j + 2] = activate<ACT>(v[j + 2] + b.z);
-          v[j + 3] = activate<ACT>(v[j + 3] + b.w);
+          const uint4 b = lds128(b4 + j * 4);  // same address in every lane: one broadcast wavefront
+          v[j] = activate<ACT>(v[j] + __uint_as_float(b.x));
+          v[j + 1] = activate<ACT>(v[j + 1] + __uint_as_float(b.y));
+          v[j + 2] = activate<ACT>(v[j + 2] + __uint_as_float(b.z));
+          v[j + 3] = activate<ACT>(v[j + 3] + __uint_as_float(b.w));
         }
         if constexpr (POOL) {
           // registers (lane = row) -> this warp's scratch; then lane = COLUMN walks the chunk's
           // 32 rows (consecutive nodes) keeping min / max / sum of the current event and
           // flushes them at every event boundary and at the end of the chunk
-          uint8_t* scr = s_scr + (warp - 2) * LIN_SCR_BYTES;
-          uint8_t* mine = scr + lane * LIN_SCR_PITCH;
+          uint8_t* scr = s_scr + (warp - 2) * SCR_BYTES;
+          const uint32_t mine = smem_u32(scr) + (uint32_t)lane * SCR_PITCH;
 #pragma unroll
           for (int j = 0; j < 32; j += 4)
-            *reinterpret_cast<float4*>(mine + j * 4) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            sts128(mine + j * 4, make_uint4(__float_as_uint(v[j]), __float_as_uint(v[j + 1]),
+                                            __float_as_uint(v[j + 2]), __float_as_uint(v[j + 3])));
           __syncwarp();
           const int64_t node0 = m0 + q * 32;
           const int rows = (int)min((int64_t)32, M - node0);
@@ -466,13 +489,15 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
           // x 16 bytes
           constexpr int P = (32 * (int)sizeof(OutT)) / 16;   // pieces per 32-column row: 4 or 8
           constexpr int EPP = 16 / (int)sizeof(OutT);        // elements per piece
-          uint8_t* scr = s_scr + (warp - 2) * LIN_SCR_BYTES;
-          uint8_t* mine = scr + lane * LIN_SCR_PITCH;
+          const uint32_t scr = smem_u32(s_scr + (warp - 2) * SCR_BYTES);
+          const uint32_t mine = scr + (uint32_t)lane * SCR_PITCH;
           if constexpr (sizeof(OutT) == 4) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4)
-              *reinterpret_cast<float4*>(mine + j * 4) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              sts128(mine + j * 4, make_uint4(__float_as_uint(v[j]), __float_as_uint(v[j + 1]),
+                                              __float_as_uint(v[j + 2]), __float_as_uint(v[j + 3])));
           } else {
+            const int wsw = (lane >> 1) & 3;   // swizzle of this lane's row
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
               uint4 u;
@@ -480,7 +505,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
               u.y = pack2<OutT>(v[j + 2], v[j + 3]);
               u.z = pack2<OutT>(v[j + 4], v[j + 5]);
               u.w = pack2<OutT>(v[j + 6], v[j + 7]);
-              *reinterpret_cast<uint4*>(mine + j * 2) = u;
+              sts128(mine + (uint32_t)(((j >> 3) ^ wsw) << 4), u);
             }
           }
           __syncwarp();
@@ -491,7 +516,8 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
             const int r = i * (32 / P) + rsub;
             const int64_t grow = m0 + q * 32 + r;
             if (grow < M && piece * EPP < nv && !(coalesce_in & 2)) {
-              const uint4 u = *reinterpret_cast<const uint4*>(scr + r * LIN_SCR_PITCH + piece * 16);
+              const int psw = sizeof(OutT) == 4 ? piece : (piece ^ ((r >> 1) & 3));
+              const uint4 u = lds128(scr + (uint32_t)(r * SCR_PITCH + psw * 16));
               OutT* dst = C + grow * ldc + n + piece * EPP;
               if ((piece + 1) * EPP <= nv) {
                 *reinterpret_cast<uint4*>(dst) = u;
@@ -507,21 +533,34 @@ __global__ void __launch_bounds__(LIN_THREADS, 1) tc_linear_kernel(
         }
       };
       {
+        // this warp's chunks: c = par*32, + 32*NPAR, ...
+        constexpr int CSTEP = 32 * NPAR;
         int c = par * 32;
         if (chunk_ok(c) && !(coalesce_in & 16)) {   // (16: profiling without the epilogue body)
-          tmem_ld_32x32_issue(t_addr + (uint32_t)c, ra);
-          for (;;) {
-            tmem_ld_wait(ra);
-            const bool more1 = chunk_ok(c + 64);
-            if (more1) tmem_ld_32x32_issue(t_addr + (uint32_t)(c + 64), rb);
-            process(ra, c);
-            if (!more1) break;
-            tmem_ld_wait(rb);
-            const bool more2 = chunk_ok(c + 128);
-            if (more2) tmem_ld_32x32_issue(t_addr + (uint32_t)(c + 128), ra);
-            process(rb, c + 64);
-            if (!more2) break;
-            c += 128;
+          if constexpr (NPAR <= 2) {
+            // two register sets: the tcgen05.ld of the next chunk is in flight while this one
+            // is processed
+            tmem_ld_32x32_issue(t_addr + (uint32_t)c, ra);
+            for (;;) {
+              tmem_ld_wait(ra);
+              const bool more1 = chunk_ok(c + CSTEP);
+              if (more1) tmem_ld_32x32_issue(t_addr + (uint32_t)(c + CSTEP), rb);
+              process(ra, c);
+              if (!more1) break;
+              tmem_ld_wait(rb);
+              const bool more2 = chunk_ok(c + 2 * CSTEP);
+              if (more2) tmem_ld_32x32_issue(t_addr + (uint32_t)(c + 2 * CSTEP), ra);
+              process(rb, c + CSTEP);
+              if (!more2) break;
+              c += 2 * CSTEP;
+            }
+          } else {
+            // four warps per quadrant: the other warps of the scheduler cover the TMEM latency
+            for (; chunk_ok(c); c += CSTEP) {
+              tmem_ld_32x32_issue(t_addr + (uint32_t)c, ra);
+              tmem_ld_wait(ra);
+              process(ra, c);
+            }
           }
         }
       }
@@ -549,7 +588,7 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
   const int num_n_tiles = (int)ceil_div(N, BN);
   const size_t stage_bytes = (size_t)LIN_A_BYTES + (size_t)BN * LIN_BK * 2;
   const size_t fixed = sizeof(LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024 +
-                       (size_t)LIN_EPI_WARPS * LIN_SCR_BYTES + 16;
+                       (size_t)lin_epi_warps<OutT>() * lin_scr_bytes<OutT>() + 16;
   // 16-byte stores need C rows and the tile's first column on 16-byte boundaries
   static const bool no_coalesce = getenv("GN_TC_NO_COALESCE") != nullptr;
 #ifdef GN_DEBUG_BUILD   // ablation / trace switches exist in profiling builds only
@@ -610,7 +649,7 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
                                    227 * 1024));                                                \
       ready_.fetch_or(1ull << (dev & 63), std::memory_order_relaxed);                           \
     }                                                                                           \
-    kern<<<grid, LIN_THREADS, smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
+    kern<<<grid, lin_threads<OutT>(), smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
                                           K, BN, num_n_tiles, num_tiles, idesc, stages, splits,  \
                                           accumulate, coalesce, wres, pool);                    \
   }
@@ -640,15 +679,17 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
 
 }  // namespace tc
 
-static size_t tc_fixed_smem(int N, int BN) {
+static size_t tc_fixed_smem(int N, int BN, int out_bytes) {
   const int num_n_tiles = (N + BN - 1) / BN;
-  return sizeof(tc::LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024 +
-         (size_t)tc::LIN_EPI_WARPS * tc::LIN_SCR_BYTES + 16;
+  const size_t scr = out_bytes == 4
+                         ? (size_t)tc::lin_epi_warps<float>() * tc::lin_scr_bytes<float>()
+                         : (size_t)tc::lin_epi_warps<__half>() * tc::lin_scr_bytes<__half>();
+  return sizeof(tc::LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024 + scr + 16;
 }
 // does a K-complete W tile of width BN fit next to a ring of at least four A stages?
-static bool tc_wres_fits(int N, int K, int BN) {
+static bool tc_wres_fits(int N, int K, int BN, int out_bytes) {
   const size_t w_bytes = (size_t)ceil_div(K, tc::LIN_BK) * BN * tc::LIN_BK * 2;
-  return w_bytes + 4 * (size_t)tc::LIN_A_BYTES + tc_fixed_smem(N, BN) <= 227 * 1024;
+  return w_bytes + 4 * (size_t)tc::LIN_A_BYTES + tc_fixed_smem(N, BN, out_bytes) <= 227 * 1024;
 }
 
 int tc_pick_bn(int N, int bn_max_arg = 256) {
@@ -680,10 +721,11 @@ extern "C" int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
   GN_CHECK_ARG(c_dtype == GN_F32 || c_dtype == GN_BF16 || c_dtype == GN_F16,
                "gn_tc_linear: bad c_dtype");
   int BN = tc_pick_bn(N);
+  const int out_bytes = c_dtype == GN_F32 ? 4 : 2;
   // a narrower tile whose K-complete W fits in shared memory beats a wide one that streams W
-  if (!tc_wres_fits(N, K, BN) && M >= 4096) {
+  if (!tc_wres_fits(N, K, BN, out_bytes) && M >= 4096) {
     const int bn2 = tc_pick_bn(N, 128);
-    if (tc_wres_fits(N, K, bn2)) BN = bn2;
+    if (tc_wres_fits(N, K, bn2, out_bytes)) BN = bn2;
   }
   CUtensorMap tmA, tmW;
   auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
@@ -721,9 +763,9 @@ extern "C" int gn_tc_linear_pool(const void* A, int64_t lda, const void* W, int6
   if (M == 0) return GN_OK;
   GN_CHECK_ARG(A && W && batch && ptr, "gn_tc_linear_pool: null pointer");
   int BN = tc_pick_bn(N);
-  if (!tc_wres_fits(N, K, BN) && M >= 4096) {
+  if (!tc_wres_fits(N, K, BN, 4) && M >= 4096) {
     const int bn2 = tc_pick_bn(N, 128);
-    if (tc_wres_fits(N, K, bn2)) BN = bn2;
+    if (tc_wres_fits(N, K, bn2, 4)) BN = bn2;
   }
   CUtensorMap tmA, tmW;
   auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
