@@ -20,7 +20,7 @@ GN_OK = 0
 ACT = {"none": 0, "relu": 1, "gelu": 2, "leaky_relu": 3}
 AGGR = {"add": 0, "sum": 0, "mean": 1, "max": 2, "min": 3}
 POOL = {"min": 0, "max": 1, "sum": 2, "mean": 3}
-DTYPE_F32, DTYPE_BF16, DTYPE_F16 = 0, 1, 2
+DTYPE_F32, DTYPE_BF16, DTYPE_F16, DTYPE_BF16X3 = 0, 1, 2, 3
 HEAD = {
     "IdentityTask": 0,
     "EnergyReconstruction": 1,

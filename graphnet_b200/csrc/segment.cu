@@ -32,7 +32,15 @@ struct X0Out {
 
 __device__ __forceinline__ void store_x0(const X0Out& o, int64_t row, int c, float v) {
   if (o.dtype == GN_F32) reinterpret_cast<float*>(o.ptr)[row * o.ld + c] = v;
-  else if (o.dtype == GN_BF16)
+  else if (o.dtype == GN_BF16X3) {
+    // v = hi + lo to 16 mantissa bits; the row is [hi | lo | hi], each `cols` wide: against
+    // weights laid out as [W_hi | W_hi | W_lo] one bf16 GEMM gives hi W_hi + lo W_hi + hi W_lo
+    __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(o.ptr) + row * o.ld + c;
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    p[0] = hi;
+    p[o.cols] = __float2bfloat16_rn(v - __bfloat162float(hi));
+    p[2 * o.cols] = hi;
+  } else if (o.dtype == GN_BF16)
     reinterpret_cast<__nv_bfloat16*>(o.ptr)[row * o.ld + c] = __float2bfloat16_rn(v);
   else
     reinterpret_cast<__half*>(o.ptr)[row * o.ld + c] =
@@ -321,9 +329,10 @@ extern "C" int gn_global_variables(const float* x, int64_t ldx, int F, const gn_
   X0Out o0{x0, ldx0, x0_cols, x0_dtype}, o1{x0b, ldx0b, x0b_cols, x0b_dtype};
   for (const X0Out* o : {&o0, &o1}) {
     if (!o->ptr) continue;
-    GN_CHECK_ARG(o->cols >= F + F + 5 && o->ld >= o->cols,
-                 "gn_global_variables: x0 needs >= 2F+5 columns");
-    GN_CHECK_ARG(o->dtype == GN_F32 || o->dtype == GN_BF16 || o->dtype == GN_F16,
+    GN_CHECK_ARG(o->cols >= F + F + 5 && o->ld >= (o->dtype == GN_BF16X3 ? 3 : 1) * o->cols,
+                 "gn_global_variables: x0 needs >= 2F+5 columns (three times that for GN_BF16X3)");
+    GN_CHECK_ARG(o->dtype == GN_F32 || o->dtype == GN_BF16 || o->dtype == GN_F16 ||
+                     o->dtype == GN_BF16X3,
                  "gn_global_variables: bad x0 dtype");
   }
   const int threads = (N / (B > 0 ? B : 1)) > 128 ? GV_MAX_THREADS : GV_THREADS;

@@ -64,6 +64,22 @@ class _ConvPack:
         self.Wpq, self.bias_pq, self.W2p, self.W2b, self.W2bT, self.WpqT = packed
         self.Wp, self.Wq = self.Wpq[:Kp], self.Wpq[Kp:]
         self.bias_p = self.bias_pq[:Kp]
+        self._split = None
+
+    def split_weights(self, kc: int) -> Tensor:
+        """First layer: Wpq (fp32 [2Kp, d]) as bf16 [2Kp, 3*kc] = [W_hi | W_hi | W_lo], the partner
+        of a GN_BF16X3 input ([x_hi | x_lo | x_hi]); built once per weight version (plumbing)."""
+        if self._split is None or self._split.shape[1] != 3 * kc:
+            W = self.Wpq.float()
+            hi = W.to(torch.bfloat16)
+            lo = (W - hi.float()).to(torch.bfloat16)
+            out = torch.zeros((W.shape[0], 3 * kc), dtype=torch.bfloat16, device=W.device)
+            d = W.shape[1]
+            out[:, :d] = hi
+            out[:, kc:kc + d] = hi
+            out[:, 2 * kc:2 * kc + d] = lo
+            self._split = out.contiguous()
+        return self._split
 
 
 def _io_dtype(model) -> torch.dtype:
@@ -146,11 +162,20 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
     needs_zero = any(w % 8 for w in widths)
     skip = (torch.zeros if needs_zero else torch.empty)((N, total), dtype=io, device=dev)
     x0w = offs[0]
+    # inference: the first node GEMM runs on the tensor cores from a bf16 [hi | lo | hi] split of
+    # the fp32 input features (GN_BF16X3: 16 mantissa bits, no 8-bit rounding of the coordinates);
+    # training keeps the fp32 copy its weight-gradient kernel reads
+    x0_split = None
     if model._add_global_variables_after_pooling:
         gv = ops.global_variables(x, graph, ptr, n_pulses)
         skip[:, :x0w] = 0
         skip[:, :F] = x
         x0 = x
+    elif save is None:
+        x0 = None
+        x0_split = torch.empty((N, 3 * x0w), dtype=torch.bfloat16, device=dev)
+        gv = ops.global_variables(x, graph, ptr, n_pulses, x0=x0_split, x0_cols=x0w,
+                                  x0b=skip, x0b_cols=x0w, x0_split=True)
     else:
         x0 = torch.empty((N, D0), dtype=torch.float32, device=dev)
         gv = ops.global_variables(x, graph, ptr, n_pulses, x0=x0, x0_cols=D0,
@@ -175,7 +200,10 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
                     f"aggr={aggr!r} on the 16-bit path needs in-degrees <= "
                     f"{_slots(conv.nb_neighbors)} (a kNN graph of the layer's k); use precision='fp32'")
             graph = ops.csr_to_ell(graph, _slots(conv.nb_neighbors))
-        if li == 0:
+        if li == 0 and x0_split is not None:
+            ops.tc_linear_bf16(x0_split, pk.split_weights(x0w), pk.bias_pq, PQ, K=3 * x0w,
+                               act="none")
+        elif li == 0:
             ops.linear_f32(x0, pk.Wpq, pk.bias_pq, act="none", out=PQ)
         else:
             ops.tc_linear_bf16(skip[:, off_in:], pk.Wpq, pk.bias_pq, PQ, K=d_in, act="none")

@@ -16,7 +16,8 @@ import torch
 from torch import Tensor
 
 from . import _lib
-from ._lib import ACT, AGGR, DTYPE_BF16, DTYPE_F16, DTYPE_F32, HEAD, POOL, GnGraph, check
+from ._lib import (ACT, AGGR, DTYPE_BF16, DTYPE_BF16X3, DTYPE_F16, DTYPE_F32, HEAD, POOL, GnGraph,
+                   check)
 
 
 def _require_cuda(*tensors: Optional[Tensor]) -> torch.device:
@@ -208,8 +209,10 @@ _DT = {torch.float32: DTYPE_F32, torch.bfloat16: DTYPE_BF16, torch.float16: DTYP
 
 def global_variables(x: Tensor, graph: Graph, ptr: Tensor, n_pulses: Tensor,
                      x0: Optional[Tensor] = None, x0_cols: int = 0,
-                     x0b: Optional[Tensor] = None, x0b_cols: int = 0) -> Tensor:
-    """gv [B, F+5]; if `x0` (/`x0b`) is given also writes [:, :cols] = [x, gv[batch], 0...]."""
+                     x0b: Optional[Tensor] = None, x0b_cols: int = 0,
+                     x0_split: bool = False) -> Tensor:
+    """gv [B, F+5]; if `x0` (/`x0b`) is given also writes [:, :cols] = [x, gv[batch], 0...].
+    `x0_split`: x0 is a bf16 [N, 3*x0_cols] buffer that receives [hi | lo | hi] (GN_BF16X3)."""
     dev = _require_cuda(x, ptr, n_pulses, x0, x0b)
     assert x.dtype == torch.float32 and x.stride(1) == 1
     N, F = x.shape
@@ -225,6 +228,9 @@ def global_variables(x: Tensor, graph: Graph, ptr: Tensor, n_pulses: Tensor,
             outs.append((_DT[t.dtype], t.stride(0)))
         else:
             outs.append((DTYPE_F32, 0))
+    if x0_split:
+        assert x0 is not None and x0.dtype == torch.bfloat16 and x0.shape[1] >= 3 * x0_cols
+        outs[0] = (DTYPE_BF16X3, x0.stride(0))
     with _on(dev):
         check(_lib.load().gn_global_variables(
             _ptr(x), x.stride(0), F, C.byref(gs), _ptr(ptr), _ptr(n_pulses), N, B, _ptr(gv),

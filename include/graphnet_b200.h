@@ -51,6 +51,11 @@ extern "C" {
 #define GN_F32 0
 #define GN_BF16 1
 #define GN_F16 2
+/* gn_global_variables' x0 only: every value v as bf16 hi + lo (16 mantissa bits), rows laid out as
+ * [hi | lo | hi], each x0_cols wide (ld >= 3 x0_cols): one bf16 GEMM against [W_hi | W_hi | W_lo]
+ * then equals the fp32 product to ~2^-16 - the raw detector coordinates reach the first
+ * EdgeConv's node GEMM on the tensor cores without being rounded to 8 bits */
+#define GN_BF16X3 3
 
 /* task heads, models/task/reconstruction.py */
 #define GN_HEAD_IDENTITY 0
