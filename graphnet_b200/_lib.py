@@ -42,7 +42,40 @@ class GnGraph(C.Structure):
     ]
 
 
+GN_MAX_LAYERS, GN_MAX_DENSE = 8, 4
+
+
+class GnDynedgeConv(C.Structure):
+    _fields_ = [
+        ("Wpq", C.c_void_p), ("bias_pq", C.c_void_p), ("W2p", C.c_void_p),
+        ("d_in", C.c_int32), ("Kp", C.c_int32), ("b", C.c_int32), ("k", C.c_int32),
+        ("slots", C.c_int32), ("act", C.c_int32), ("off_in", C.c_int32), ("off_out", C.c_int32),
+        ("ncoord", C.c_int32), ("ldw", C.c_int32), ("coord_cols", C.c_int32 * 16),
+    ]
+
+
+class GnDynedgeDense(C.Structure):
+    _fields_ = [
+        ("W", C.c_void_p), ("bias", C.c_void_p),
+        ("n", C.c_int32), ("K", C.c_int32), ("act", C.c_int32), ("ldw", C.c_int32),
+        ("tc", C.c_int32), ("pad_", C.c_int32),
+    ]
+
+
+class GnDynedgePlan(C.Structure):
+    _fields_ = [
+        ("F", C.c_int32), ("x0w", C.c_int32), ("skip_cols", C.c_int32), ("io_dtype", C.c_int32),
+        ("n_conv", C.c_int32), ("n_post", C.c_int32), ("n_readout", C.c_int32),
+        ("n_pools", C.c_int32), ("input_k", C.c_int32), ("pad_", C.c_int32),
+        ("conv", GnDynedgeConv * GN_MAX_LAYERS),
+        ("post", GnDynedgeDense * GN_MAX_DENSE),
+        ("readout", GnDynedgeDense * GN_MAX_DENSE),
+        ("pools", C.c_int32 * 8),
+    ]
+
+
 _p, _i64, _i32, _int, _sz = C.c_void_p, C.c_int64, C.c_int32, C.c_int, C.c_size_t
+_pp = C.POINTER(GnDynedgePlan)
 _gp = C.POINTER(GnGraph)
 _hp = C.POINTER(C.c_int32)  # host int32 array
 
@@ -61,6 +94,8 @@ SIGNATURES = {
     "gn_global_variables": (_int, [_p, _i64, _int, _gp, _p, _p, _i64, _i64, _p, _p, _i64, _int, _int,
                                    _p, _i64, _int, _int, _p]),
     "gn_segment_pool": (_int, [_p, _int, _i64, _int, _p, _i64, _hp, _int, _p, _i64, _p]),
+    "gn_dynedge_infer16_workspace": (_sz, [_pp, _i64, _i64, _i64, _int]),
+    "gn_dynedge_infer16": (_int, [_pp, _p, _i64, _p, _p, _i64, _i64, _p, _i64, _p, _sz, _p, _i64, _p, _p]),
     "gn_tc_linear_pool": (_int, [_p, _i64, _p, _i64, _int, _p, _i64, _int, _int, _p, _p, _i64, _p, _p]),
     "gn_pool_finalize": (_int, [_p, _p, _i64, _int, _hp, _int, _p, _i64, _p, _i64, C.c_float, _p]),
     "gn_linear_f32": (_int, [_p, _i64, _p, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),

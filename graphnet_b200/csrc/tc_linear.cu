@@ -188,6 +188,8 @@ __device__ __forceinline__ void store_row32(OutT* dst, const float (&v)[32], int
 #ifdef GN_DEBUG_BUILD
 // profiling builds (GN_TC_DEBUG=1): clock64 stamps of CTA 0, [warp 0..9][item 0..15][4]
 __device__ unsigned long long g_lin_trace[10 * 16 * 4];
+// per ring stage g < 64 of CTA 0: [0] TMA issued, [1] MMA thread saw `full`, [2] commit issued
+__device__ unsigned long long g_lin_stage[3 * 64];
 #endif
 
 // Segmented-pooling epilogue (POOL): instead of storing the [M, N] output, every column's min, max
@@ -213,7 +215,7 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
     const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
     int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages, int splits,
-    int accumulate, int coalesce_in, int wres, const PoolEpilogue pool) {
+    int accumulate, int coalesce_in, int wres, int cshape, const PoolEpilogue pool) {
   constexpr int LIN_EPI_WARPS = lin_epi_warps<OutT>();
   constexpr int LIN_THREADS = lin_threads<OutT>();
   constexpr int NPAR = LIN_EPI_WARPS / 4;          // warps sharing a TMEM lane quadrant
@@ -226,8 +228,14 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
     if (traced && i < 16 && (threadIdx.x >> 5) < 10)
       g_lin_trace[((threadIdx.x >> 5) * 16 + i) * 4 + k] = clock64();
   };
+  uint32_t gstage = 0;
+  auto stage_stamp = [&](int k) {
+    if (traced && gstage < 64) g_lin_stage[k * 64 + gstage] = clock64();
+  };
 #else
   auto stamp = [](uint32_t, int) {};
+  [[maybe_unused]] uint32_t gstage = 0;
+  auto stage_stamp = [](int) {};
 #endif
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B swizzle atoms
@@ -253,13 +261,23 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
   for (int n = threadIdx.x; n < num_n_tiles * BN; n += LIN_THREADS)
     s_bias[n] = (bias != nullptr && n < N) ? bias[n] : 0.f;
 
+  // cluster of cn x cm CTAs (see LinPlan): rank = m_idx * cn + n_idx
+  const uint32_t cn = (uint32_t)cshape & 0xffu, cm = (uint32_t)cshape >> 8, csize = cn * cm;
+  const uint32_t crank = blockIdx.x % csize;   // == %cluster_ctarank of a 1-D cluster
+  const uint32_t n_idx = crank % cn, m_idx = crank / cn;
+  // CTAs that receive the A parts this CTA loads (its cluster row) and the W parts (its column);
+  // the same CTAs write into this one's ring, so a slot is free once all of them released it
+  const uint16_t mask_a = (uint16_t)(((1u << cn) - 1u) << (m_idx * cn));
+  uint16_t mask_w = 0;
+  for (uint32_t i = 0; i < cm; ++i) mask_w |= (uint16_t)(1u << (i * cn + n_idx));
+  const uint16_t mask_rel = (uint16_t)(mask_a | (wres ? 0 : mask_w));
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmW);
 #pragma unroll
     for (int s = 0; s < LIN_STAGES; ++s) {
       mbar_init(&bars->full[s], 1);
-      mbar_init(&bars->empty[s], 1);
+      mbar_init(&bars->empty[s], (uint32_t)__popc((unsigned)mask_rel));
     }
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
@@ -272,6 +290,7 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
   if (warp == 1) tmem_alloc<512>(&bars->tmem_base);
   tc_fence_before();
   __syncthreads();
+  if (csize > 1) cl_sync();   // every CTA's barriers exist before a peer signals them
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
 
@@ -279,104 +298,160 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
   // split fastest; consecutive tile ids share the A row block (n fastest), so concurrently
   // running CTAs hit the same A tile in L2.  splits > 1 (weight gradients: few tiles, K = rows of
   // the batch) gives every item the K blocks [kb0, kb1) and the epilogue adds with red.add.
-  const int64_t num_items = num_tiles * splits;
-  // i-th work item of this CTA -> (tile t, K split sp); false when the CTA is done
-  const int cta_n = blockIdx.x % num_n_tiles, cta_m0 = blockIdx.x / num_n_tiles;
-  const int cta_mstep = gridDim.x / num_n_tiles;           // wres: grid is a multiple of n tiles
-  const int64_t num_m_tiles = num_tiles / num_n_tiles;
-  auto work_item = [&](uint32_t i, int64_t& t, int& sp) -> bool {
-    if (wres) {
-      const int64_t mt = cta_m0 + (int64_t)i * cta_mstep;
-      if (mt >= num_m_tiles) return false;
-      t = mt * num_n_tiles + cta_n;
-      sp = 0;
-      return true;
+  //
+  // The three roles walk the same sequence, each in ONE thread (or one warp) of dependent
+  // instructions, so the walk must not divide: the item -> (m tile, n tile, split) map is advanced
+  // incrementally (the 64-bit divisions and the g % stages ring index of the first version cost
+  // ~1100 cycles per item and ~700 per stage in the producer and MMA threads - more than the
+  // tensor work of a node-GEMM tile - and paced the whole kernel).
+  struct Walk {
+    uint32_t mt, nt, sp;          // current item
+    uint32_t dm, dn, ds;          // gridDim.x in mixed radix (m tiles, n tiles, splits)
+    uint32_t nnt, nsp, nmt, off;
+    bool wres;
+    // cluster: cluster c takes the row-tile groups c, c + clusters, ...; CTA (m_idx, n_idx) of it
+    // the tile (group * cm + m_idx, n_idx).  Every CTA of a cluster walks the same number of items
+    // (a row tile past the end loads zeros and stores nothing).
+    __device__ __forceinline__ void init_cluster(uint32_t cta, uint32_t grid, uint32_t cn, uint32_t cm,
+                                                 uint32_t n_idx, uint32_t m_idx, uint32_t nmt_) {
+      const uint32_t csize = cn * cm;
+      nnt = cn; nsp = 1; nmt = nmt_; wres = false; off = m_idx;
+      nt = n_idx; mt = (cta / csize) * cm + m_idx; sp = 0;
+      dm = (grid / csize) * cm; dn = 0; ds = 0;
     }
-    const int64_t w = blockIdx.x + (int64_t)i * gridDim.x;
-    if (w >= num_items) return false;
-    t = w / splits;
-    sp = (int)(w % splits);
-    return true;
+    __device__ __forceinline__ void init(uint32_t cta, uint32_t grid, uint32_t nnt_, uint32_t nsp_,
+                                         uint32_t nmt_, bool wres_) {
+      nnt = nnt_; nsp = nsp_; nmt = nmt_; wres = wres_; off = 0;
+      if (wres) {                 // one n tile per CTA; the CTAs of an n tile stride over m
+        nt = cta % nnt; mt = cta / nnt; sp = 0;
+        dm = grid / nnt; dn = 0; ds = 0;
+      } else {
+        sp = cta % nsp; const uint32_t t = cta / nsp; nt = t % nnt; mt = t / nnt;
+        ds = grid % nsp; const uint32_t g = grid / nsp; dn = g % nnt; dm = g / nnt;
+      }
+    }
+    __device__ __forceinline__ bool valid() const { return mt - off < nmt; }
+    __device__ __forceinline__ void next() {
+      sp += ds;
+      if (sp >= nsp) { sp -= nsp; ++nt; }
+      nt += dn;
+      if (nt >= nnt) { nt -= nnt; ++mt; }
+      if (nt >= nnt) { nt -= nnt; ++mt; }   // (carry + dn can pass nnt twice)
+      mt += dm;
+    }
   };
+  const uint32_t num_m_tiles = (uint32_t)(num_tiles / num_n_tiles);
+  Walk walk;
+  if (csize > 1)
+    walk.init_cluster(blockIdx.x, gridDim.x, cn, cm, n_idx, m_idx, num_m_tiles);
+  else
+    walk.init(blockIdx.x, gridDim.x, (uint32_t)num_n_tiles, (uint32_t)splits, num_m_tiles, wres != 0);
+  // K blocks [kb0, kb1) of split sp (splits == 1: all of them)
+  auto k_range = [&](uint32_t sp, int& kb0, int& kb1) {
+    if (splits == 1) { kb0 = 0; kb1 = nk; return; }
+    kb0 = (int)(sp * (uint32_t)nk / (uint32_t)splits);
+    kb1 = (int)((sp + 1) * (uint32_t)nk / (uint32_t)splits);
+  };
+  const int cta_n = (int)walk.nt;   // (wres: the CTA's one column tile)
   if (warp == 0) {
     // ---------------------------------------------------------- TMA producer
     if (elect_one()) {
-      uint32_t g = 0;
       if (wres) {  // the CTA's W tile, once
         mbar_arrive_expect_tx(&bars->w_full, (uint32_t)(nk_all * b_bytes));
         for (int kb = 0; kb < nk_all; ++kb)
           tma_load_2d(w_res + kb * b_bytes, &tmW, &bars->w_full, kb * LIN_BK, cta_n * BN);
       }
-      int64_t t;
-      int sp;
-      for (uint32_t i = 0; work_item(i, t, sp); ++i) {
-        const int kb0 = (int)((int64_t)sp * nk / splits), kb1 = (int)((int64_t)(sp + 1) * nk / splits);
-        const int32_t m0 = (int32_t)((t / num_n_tiles) * LIN_BM);
-        const int32_t n0 = (int32_t)(t % num_n_tiles) * BN;
+      uint32_t s = 0, ph = 1;   // ring slot and the parity its `empty` barrier is waited with
+      const uint32_t ring_a = smem_u32(ring);
+      const uint32_t a_part_rows = LIN_BM / cn, a_part_bytes = a_part_rows * (LIN_BK * 2);
+      const uint32_t w_part_rows = (uint32_t)BN / cm, w_part_bytes = w_part_rows * (LIN_BK * 2);
+      for (uint32_t i = 0; walk.valid(); walk.next(), ++i) {
+        int kb0, kb1;
+        k_range(walk.sp, kb0, kb1);
+        const int32_t m0 = (int32_t)(walk.mt * LIN_BM);
+        const int32_t n0 = (int32_t)walk.nt * BN;
         stamp(i, 0);
-        for (int kb = kb0; kb < kb1; ++kb, ++g) {
-          const uint32_t s = g % stages;
-          mbar_wait(&bars->empty[s], ((g / stages) & 1) ^ 1);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&bars->empty[s], ph);
           if (kb == kb0) stamp(i, 1);
           if (kb == kb1 - 1) stamp(i, 2);
-          uint8_t* a_dst = ring + s * stage_bytes;
+          const uint32_t a_dst = ring_a + s * (uint32_t)stage_bytes;
           mbar_arrive_expect_tx(&bars->full[s], (uint32_t)stage_bytes);
-          tma_load_2d(a_dst, &tmA, &bars->full[s], kb * LIN_BK, m0);
-          if (!wres) tma_load_2d(a_dst + LIN_A_BYTES, &tmW, &bars->full[s], kb * LIN_BK, n0);
+          stage_stamp(0);
+          ++gstage;
+          if (cn > 1)   // this CTA's 128 / cn rows of the A tile, into every CTA of its row
+            tma_load_2d_mc(a_dst + n_idx * a_part_bytes, &tmA, &bars->full[s], kb * LIN_BK,
+                           m0 + (int32_t)(n_idx * a_part_rows), mask_a);
+          else
+            tma_load_2d_a(a_dst, &tmA, &bars->full[s], kb * LIN_BK, m0);
+          if (!wres) {
+            if (cm > 1)
+              tma_load_2d_mc(a_dst + LIN_A_BYTES + m_idx * w_part_bytes, &tmW, &bars->full[s],
+                             kb * LIN_BK, n0 + (int32_t)(m_idx * w_part_rows), mask_w);
+            else
+              tma_load_2d_a(a_dst + LIN_A_BYTES, &tmW, &bars->full[s], kb * LIN_BK, n0);
+          }
+          if (++s == (uint32_t)stages) { s = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    uint32_t g = 0;
+    // The whole warp walks the loop (every value in it is warp-uniform) and ONE elected lane
+    // issues: ptxas then keeps descriptors and addresses in uniform registers.  Under
+    // `if (lane == 0)` it cannot know that a single thread is active and wraps every tcgen05.mma
+    // in an ELECT / 5 x R2UR / branch loop (~70 cycles per instruction, measured).
     if (wres) {
       mbar_wait(&bars->w_full, 0);
       tc_fence_after();
     }
-    int64_t t;
-    int sp;
-    for (uint32_t it = 0; work_item(it, t, sp); ++it) {
-      const int kb0 = (int)((int64_t)sp * nk / splits), kb1 = (int)((int64_t)(sp + 1) * nk / splits);
+    uint32_t s = 0, ph = 0;
+    const uint32_t ring_a = smem_u32(ring), wres_a = smem_u32(w_res);
+    for (uint32_t it = 0; walk.valid(); walk.next(), ++it) {
+      int kb0, kb1;
+      k_range(walk.sp, kb0, kb1);
       const uint32_t buf = it & 1;
       stamp(it, 0);
       mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
       stamp(it, 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + buf * 256;
-      for (int kb = kb0; kb < kb1; ++kb, ++g) {
-        const uint32_t s = g % stages;
-        mbar_wait(&bars->full[s], (g / stages) & 1);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&bars->full[s], ph);
+        stage_stamp(1);
         if (kb == kb0) stamp(it, 2);
         if (kb == kb1 - 1) stamp(it, 3);
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t a_addr = smem_u32(ring + s * stage_bytes);
-          const uint32_t b_addr = wres ? smem_u32(w_res + kb * b_bytes) : a_addr + LIN_A_BYTES;
+          const uint32_t a_addr = ring_a + s * (uint32_t)stage_bytes;
+          const uint32_t b_addr = wres ? wres_a + (uint32_t)(kb * b_bytes) : a_addr + LIN_A_BYTES;
           const uint64_t adesc = make_kmajor_desc<128>(a_addr);
           const uint64_t bdesc = make_kmajor_desc<128>(b_addr);
-#pragma unroll
-          for (int k4 = 0; k4 < LIN_BK / 16; ++k4) {
-            if (coalesce_in & 8) break;   // profiling: no tensor work, data path only
+          if (!(coalesce_in & 8)) {   // (8: profiling without tensor work, data path only)
             // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4) units
-            mma_bf16_ss(tmem_d, adesc + (uint64_t)(k4 * 2), bdesc + (uint64_t)(k4 * 2), idesc,
-                        ((kb - kb0) | k4) != 0);
+            mma_bf16_ss(tmem_d, adesc, bdesc, idesc, kb != kb0);
+            mma_bf16_ss(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
+            mma_bf16_ss(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
+            mma_bf16_ss(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
           }
-          mma_commit(&bars->empty[s]);
+          if (csize > 1) mma_commit_mc(&bars->empty[s], mask_rel);
+          else mma_commit(&bars->empty[s]);
           if (kb == kb1 - 1) mma_commit(&bars->tmem_full[buf]);
         }
         __syncwarp();
+        stage_stamp(2);
+        ++gstage;
+        if (++s == (uint32_t)stages) { s = 0; ph ^= 1; }
       }
     }
   } else {
     // -------------------------------------------------------------- epilogue
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
     const int par = (warp - 2) >> 2;  // the two warps of a quadrant take alternate 32-col chunks
-    int64_t t;
-    int sp;
-    for (uint32_t it = 0; work_item(it, t, sp); ++it) {
+    for (uint32_t it = 0; walk.valid(); walk.next(), ++it) {
       const uint32_t buf = it & 1;
-      const int64_t m0 = (t / num_n_tiles) * LIN_BM;
-      const int n0 = (int)(t % num_n_tiles) * BN;
+      const int64_t m0 = (int64_t)walk.mt * LIN_BM;
+      const int n0 = (int)walk.nt * BN;
       stamp(it, 0);
       mbar_wait(&bars->tmem_full[buf], (it >> 1) & 1);
       stamp(it, 1);
@@ -572,23 +647,144 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
   }
   tc_fence_before();
   __syncthreads();
+  if (csize > 1) cl_sync();   // no CTA leaves while a peer may still signal its barriers
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
+// largest tile width <= bn_max (multiple of 16) that minimises padding
+static int tc_pick_bn(int N, int bn_max_arg = 256) {
+  static const char* env = getenv("GN_TC_BN_MAX");
+  const int bn_max = env ? atoi(env) : bn_max_arg;
+  int best = bn_max, best_waste = 1 << 30;
+  for (int bn = bn_max; bn >= 64; bn -= 16) {
+    int tiles = (N + bn - 1) / bn;
+    int waste = tiles * bn - N;
+    if (waste < best_waste) { best = bn; best_waste = waste; }
+  }
+  return best;
+}
+
 template <typename OutT>
-static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, const float* bias,
-                            void* C, int64_t ldc, int64_t M, int N, int K, int BN, int act,
-                            int ab_dtype, cudaStream_t st, int splits = 1, int accumulate = 0,
-                            const PoolEpilogue* pool_in = nullptr) {
+static size_t lin_fixed_smem(int N, int BN) {
+  const int num_n_tiles = (N + BN - 1) / BN;
+  return sizeof(LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024 +
+         (size_t)lin_epi_warps<OutT>() * lin_scr_bytes<OutT>() + 16;
+}
+// does a K-complete W tile of width BN fit next to a ring of at least four A stages?
+template <typename OutT>
+static bool lin_wres_fits(int N, int K, int BN) {
+  const size_t w_bytes = (size_t)ceil_div(K, LIN_BK) * BN * LIN_BK * 2;
+  return w_bytes + 4 * (size_t)LIN_A_BYTES + lin_fixed_smem<OutT>(N, BN) <= 227 * 1024;
+}
+
+// How one GEMM runs: tile width, whether the W tile stays in shared memory, and the cluster.
+//
+// Cluster (cn x cm CTAs = the cn column tiles of cm consecutive row tiles): every stage of A is
+// fetched ONCE per cluster row - each of the cn CTAs loads 128 / cn of its rows and the TMA unit
+// multicasts them into all cn - and every streamed stage of W once per cluster column.  Without it
+// each CTA pulls whole A and W tiles through L2 for itself: 4 x 31 MB of A for the node GEMMs of
+// C2, 266 MB of A + 351 MB of W for the first post-processing GEMM, and the kernels ran at the
+// L2 -> SM throughput limit (the loads alone, no tensor work, no epilogue, took 2/3 of their time).
+struct LinPlan {
+  int BN, wres, cn, cm, stages, num_n_tiles;
+  size_t smem;
+};
+
+template <typename OutT>
+static LinPlan lin_plan(int64_t M, int N, int K, int splits, int accumulate, int sms) {
+  static const bool no_wres = getenv("GN_TC_NO_WRES") != nullptr;
+  static const int max_cluster = getenv("GN_TC_MAX_CLUSTER") ? atoi(getenv("GN_TC_MAX_CLUSTER")) : 4;
+  LinPlan p;
+  memset(&p, 0, sizeof(p));
+  p.cn = p.cm = 1;
+  int BN = tc_pick_bn(N);
+  const bool plain = splits == 1 && !accumulate;
+  // a narrower tile whose K-complete W fits in shared memory beats a wide one that streams W
+  if (plain && !lin_wres_fits<OutT>(N, K, BN) && M >= 4096) {
+    const int bn2 = tc_pick_bn(N, 128);
+    if (lin_wres_fits<OutT>(N, K, bn2)) BN = bn2;
+  }
+  int nnt = (int)ceil_div(N, BN);
+  const int64_t m_tiles = ceil_div(M, LIN_BM);
+  if (plain && !no_wres && nnt <= sms && lin_wres_fits<OutT>(N, K, BN) &&
+      m_tiles >= 2 * (sms / nnt)) {
+    p.wres = 1;
+    // (no cluster here: with W resident only A streams, and multicasting it between the column
+    // tiles of a row made the node GEMMs of C2 slower, 38 vs 34 us in the running step - their
+    // pace is set by the MMA / epilogue contention for shared memory, not by L2 traffic)
+    static const bool wres_cluster = getenv("GN_TC_WRES_CLUSTER") != nullptr;
+    if (wres_cluster && (nnt == 2 || nnt == 4) && nnt <= max_cluster) p.cn = nnt;
+  } else if (plain && M >= 4096 && max_cluster >= 2) {
+    // W streams: share it between cm row tiles, and A between the column tiles.  Parts of a W
+    // stage must start on a swizzle atom (8 rows): pick the tile width accordingly.
+    for (int bn = 256; bn >= 64; bn -= 16) {
+      const int t = (N + bn - 1) / bn;
+      if (t != 1 && t != 2 && t != 4) continue;
+      if (t > max_cluster) continue;
+      const int cm = max_cluster / t;          // 1, 2 or 4
+      if ((bn / cm) % 8) continue;
+      const int waste = t * bn - N;
+      if (waste * 16 > N) continue;            // at most ~6 % padded columns
+      BN = bn; nnt = t; p.cn = t; p.cm = cm;
+      break;
+    }
+  }
+  p.BN = BN;
+  p.num_n_tiles = nnt;
+  const size_t fixed = lin_fixed_smem<OutT>(N, BN);
+  const size_t b_bytes = (size_t)BN * LIN_BK * 2;
+  const size_t w_bytes = (size_t)ceil_div(K, LIN_BK) * b_bytes;
+  const size_t stage_bytes = (size_t)LIN_A_BYTES + (p.wres ? 0 : b_bytes);
+  const size_t avail = 227 * 1024 - fixed - (p.wres ? w_bytes : 0);
+  int stages = (int)(avail / stage_bytes);   // as deep as shared memory allows
+  p.stages = stages > LIN_STAGES ? LIN_STAGES : stages;
+  p.smem = (p.wres ? w_bytes : 0) + (size_t)p.stages * stage_bytes + fixed;
+  return p;
+}
+
+template <typename OutT>
+static int launch_tc_linear(const void* A, int64_t lda, const void* W, int64_t ldw,
+                            const float* bias, void* C, int64_t ldc, int64_t M, int N, int K,
+                            int act, int ab_dtype, cudaStream_t st, int splits = 1,
+                            int accumulate = 0, const PoolEpilogue* pool_in = nullptr) {
   PoolEpilogue pool;
   memset(&pool, 0, sizeof(pool));
   if (pool_in) pool = *pool_in;
+  int dev = 0, sms = 0;
+  GN_CUDA(cudaGetDevice(&dev));
+  {
+    static std::atomic<int> sm_count[64];   // per device, fetched once
+    sms = sm_count[dev & 63].load(std::memory_order_relaxed);
+    if (sms == 0) {
+      GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      sm_count[dev & 63].store(sms, std::memory_order_relaxed);
+    }
+  }
+  const int nkb = (int)ceil_div(K, LIN_BK);
+  LinPlan pl = lin_plan<OutT>(M, N, K, splits == 1 ? 1 : 2, accumulate, sms);
+  const int BN = pl.BN, num_n_tiles = pl.num_n_tiles;
+  const int64_t num_m_tiles = ceil_div(M, LIN_BM);
+  const int64_t num_tiles = num_m_tiles * num_n_tiles;
+  if (splits == 0) {  // automatic: enough items to fill the machine, at least 4 K blocks each
+    splits = (int)(sms / (num_tiles < sms ? num_tiles : sms));
+    if (splits > nkb / 4) splits = nkb / 4;
+  }
+  if (splits > nkb) splits = nkb;
+  if (splits < 1) splits = 1;
+#ifdef GN_DEBUG_BUILD
+  {
+    static const int cap = getenv("GN_TC_STAGES") ? atoi(getenv("GN_TC_STAGES")) : 0;
+    if (cap > 0 && cap < pl.stages) pl.stages = cap;
+  }
+#endif
+  CUtensorMap tmA, tmW;
+  auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
+  int rc = mk(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, LIN_BM / pl.cn, LIN_BK, 128);
+  if (rc != GN_OK) return rc;
+  rc = mk(&tmW, W, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)(BN / pl.cm), LIN_BK, 128);
+  if (rc != GN_OK) return rc;
   const uint32_t idesc =
       ab_dtype == GN_F16 ? make_idesc_f16(LIN_BM, BN) : make_idesc_bf16(LIN_BM, BN);
-  const int num_n_tiles = (int)ceil_div(N, BN);
-  const size_t stage_bytes = (size_t)LIN_A_BYTES + (size_t)BN * LIN_BK * 2;
-  const size_t fixed = sizeof(LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024 +
-                       (size_t)lin_epi_warps<OutT>() * lin_scr_bytes<OutT>() + 16;
   // 16-byte stores need C rows and the tile's first column on 16-byte boundaries
   static const bool no_coalesce = getenv("GN_TC_NO_COALESCE") != nullptr;
 #ifdef GN_DEBUG_BUILD   // ablation / trace switches exist in profiling builds only
@@ -599,59 +795,64 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
   constexpr bool hack_nostore = false, dbg_trace = false;
   constexpr int hack_bits = 0;
 #endif
-  const int coalesce = ((hack_nostore ? 3 : 1) | (dbg_trace ? 4 : 0) | (hack_bits & 24)) * (int)(!no_coalesce && (reinterpret_cast<uintptr_t>(C) % 16 == 0) &&
-                       ((ldc * (int64_t)sizeof(OutT)) % 16 == 0) &&
-                       ((BN * (int)sizeof(OutT)) % 16 == 0));
-  int stages = (int)((227 * 1024 - fixed) / stage_bytes);  // as deep as shared memory allows
-  stages = stages > LIN_STAGES ? LIN_STAGES : stages;
-  size_t smem = (size_t)stages * stage_bytes + fixed;
-  // weights-resident variant: one K-complete W tile per CTA + a ring of A-only stages (>= 4)
-  int dev0 = 0, sms0 = 0;
-  GN_CUDA(cudaGetDevice(&dev0));
-  {
-    static std::atomic<int> sm_count[64];   // per device, fetched once
-    sms0 = sm_count[dev0 & 63].load(std::memory_order_relaxed);
-    if (sms0 == 0) {
-      GN_CUDA(cudaDeviceGetAttribute(&sms0, cudaDevAttrMultiProcessorCount, dev0));
-      sm_count[dev0 & 63].store(sms0, std::memory_order_relaxed);
-    }
-  }
-  static const bool no_wres = getenv("GN_TC_NO_WRES") != nullptr;
-  const size_t w_bytes = (size_t)ceil_div(K, LIN_BK) * BN * LIN_BK * 2;
-  int wres = 0;
-  if (!no_wres && splits == 1 && !accumulate && num_n_tiles <= sms0 &&
-      w_bytes + 4 * (size_t)LIN_A_BYTES + fixed <= 227 * 1024 &&
-      ceil_div(M, LIN_BM) >= 2 * (sms0 / num_n_tiles)) {
-    wres = 1;
-    stages = (int)((227 * 1024 - fixed - w_bytes) / LIN_A_BYTES);
-    stages = stages > LIN_STAGES ? LIN_STAGES : stages;
-    smem = w_bytes + (size_t)stages * LIN_A_BYTES + fixed;
-  }
-  const int64_t num_tiles = ceil_div(M, LIN_BM) * num_n_tiles;
-  const int dev = dev0, sms = sms0;
-  const int nkb = (int)ceil_div(K, LIN_BK);
-  if (splits == 0) {  // automatic: enough items to fill the machine, at least 4 K blocks each
-    splits = (int)(sms / (num_tiles < sms ? num_tiles : sms));
-    if (splits > nkb / 4) splits = nkb / 4;
-  }
-  if (splits > nkb) splits = nkb;
-  if (splits < 1) splits = 1;
+  const int coalesce = ((hack_nostore ? 3 : 1) | (dbg_trace ? 4 : 0) | (hack_bits & 24)) *
+                       (int)(!no_coalesce && (reinterpret_cast<uintptr_t>(C) % 16 == 0) &&
+                             ((ldc * (int64_t)sizeof(OutT)) % 16 == 0) &&
+                             ((BN * (int)sizeof(OutT)) % 16 == 0));
+  const int csize = pl.cn * pl.cm;
   const int64_t num_items = num_tiles * splits;
-  unsigned grid = (unsigned)(num_items < sms ? num_items : sms);
-  if (wres) grid = (unsigned)((sms / num_n_tiles) * num_n_tiles);
-  /* the opt-in to > 48 KB of dynamic shared memory is per function and device: once */        \
+  const int wres = pl.wres, stages = pl.stages, cshape = pl.cn | (pl.cm << 8);
+  const size_t smem = pl.smem;
+  /* per kernel instantiation and device, once: the opt-in to > 48 KB of dynamic shared memory   \
+     and how many clusters of each size the device holds at a time (a persistent kernel must not  \
+     launch more: GPCs whose SM count is not a multiple of the cluster leave SMs out) */          \
 #define GN_TC_LIN_LAUNCH(KERN_)                                                                 \
   {                                                                                             \
     auto kern = KERN_;                                                                          \
     static std::atomic<unsigned long long> ready_;                                              \
+    static std::atomic<int> max_clusters_[64][9];                                               \
     if (!((ready_.load(std::memory_order_relaxed) >> (dev & 63)) & 1ull)) {                     \
       GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
                                    227 * 1024));                                                \
       ready_.fetch_or(1ull << (dev & 63), std::memory_order_relaxed);                           \
     }                                                                                           \
-    kern<<<grid, lin_threads<OutT>(), smem, st>>>(tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
-                                          K, BN, num_n_tiles, num_tiles, idesc, stages, splits,  \
-                                          accumulate, coalesce, wres, pool);                    \
+    cudaLaunchConfig_t cfg;                                                                     \
+    memset(&cfg, 0, sizeof(cfg));                                                               \
+    cudaLaunchAttribute attr[1];                                                                \
+    attr[0].id = cudaLaunchAttributeClusterDimension;                                           \
+    attr[0].val.clusterDim.x = (unsigned)csize;                                                 \
+    attr[0].val.clusterDim.y = 1;                                                               \
+    attr[0].val.clusterDim.z = 1;                                                               \
+    cfg.blockDim = dim3(lin_threads<OutT>());                                                   \
+    cfg.dynamicSmemBytes = smem;                                                                \
+    cfg.stream = st;                                                                            \
+    cfg.attrs = attr;                                                                           \
+    cfg.numAttrs = 1;                                                                           \
+    unsigned grid;                                                                              \
+    if (csize > 1) {                                                                            \
+      int ncl = max_clusters_[dev & 63][csize].load(std::memory_order_relaxed);                 \
+      if (ncl == 0) {                                                                           \
+        cfg.gridDim = dim3((unsigned)(sms / csize * csize));                                    \
+        cfg.dynamicSmemBytes = 227 * 1024;                                                      \
+        GN_CUDA(cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg));                              \
+        cfg.dynamicSmemBytes = smem;                                                            \
+        if (ncl < 1) {                                                                          \
+          set_error("gn_tc_linear: no cluster of %d CTAs fits on this device", csize);          \
+          return GN_ERR_UNSUPPORTED;                                                            \
+        }                                                                                       \
+        max_clusters_[dev & 63][csize].store(ncl, std::memory_order_relaxed);                   \
+      }                                                                                         \
+      const int64_t supers = ceil_div(num_m_tiles, pl.cm);                                      \
+      grid = (unsigned)((supers < ncl ? supers : ncl) * csize);                                 \
+    } else if (wres) {                                                                          \
+      grid = (unsigned)((sms / num_n_tiles) * num_n_tiles);                                     \
+    } else {                                                                                    \
+      grid = (unsigned)(num_items < sms ? num_items : sms);                                     \
+    }                                                                                           \
+    cfg.gridDim = dim3(grid);                                                                   \
+    GN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
+                               K, BN, num_n_tiles, num_tiles, idesc, stages, splits,             \
+                               accumulate, coalesce, wres, cshape, pool));                      \
   }
 #define GN_TC_LIN_CASE(A_) GN_TC_LIN_LAUNCH((tc_linear_kernel<OutT, A_, false>))
   if (pool.acc != nullptr) {
@@ -678,33 +879,6 @@ static int launch_tc_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
 }
 
 }  // namespace tc
-
-static size_t tc_fixed_smem(int N, int BN, int out_bytes) {
-  const int num_n_tiles = (N + BN - 1) / BN;
-  const size_t scr = out_bytes == 4
-                         ? (size_t)tc::lin_epi_warps<float>() * tc::lin_scr_bytes<float>()
-                         : (size_t)tc::lin_epi_warps<__half>() * tc::lin_scr_bytes<__half>();
-  return sizeof(tc::LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024 + scr + 16;
-}
-// does a K-complete W tile of width BN fit next to a ring of at least four A stages?
-static bool tc_wres_fits(int N, int K, int BN, int out_bytes) {
-  const size_t w_bytes = (size_t)ceil_div(K, tc::LIN_BK) * BN * tc::LIN_BK * 2;
-  return w_bytes + 4 * (size_t)tc::LIN_A_BYTES + tc_fixed_smem(N, BN, out_bytes) <= 227 * 1024;
-}
-
-int tc_pick_bn(int N, int bn_max_arg = 256) {
-  // largest tile width <= 256 (multiple of 16) that minimises padding
-  static const char* env = getenv("GN_TC_BN_MAX");
-  const int bn_max = env ? atoi(env) : bn_max_arg;
-  int best = bn_max, best_waste = 1 << 30;
-  for (int bn = bn_max; bn >= 64; bn -= 16) {
-    int tiles = (N + bn - 1) / bn;
-    int waste = tiles * bn - N;
-    if (waste < best_waste) { best = bn; best_waste = waste; }
-  }
-  return best;
-}
-
 }  // namespace gn
 
 using namespace gn;
@@ -720,25 +894,12 @@ extern "C" int gn_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
   GN_CHECK_ARG(N <= tc::LIN_MAX_N, "gn_tc_linear: N=%d exceeds %d", N, tc::LIN_MAX_N);
   GN_CHECK_ARG(c_dtype == GN_F32 || c_dtype == GN_BF16 || c_dtype == GN_F16,
                "gn_tc_linear: bad c_dtype");
-  int BN = tc_pick_bn(N);
-  const int out_bytes = c_dtype == GN_F32 ? 4 : 2;
-  // a narrower tile whose K-complete W fits in shared memory beats a wide one that streams W
-  if (!tc_wres_fits(N, K, BN, out_bytes) && M >= 4096) {
-    const int bn2 = tc_pick_bn(N, 128);
-    if (tc_wres_fits(N, K, bn2, out_bytes)) BN = bn2;
-  }
-  CUtensorMap tmA, tmW;
-  auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
-  int rc = mk(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, tc::LIN_BM, tc::LIN_BK, 128);
-  if (rc != GN_OK) return rc;
-  rc = mk(&tmW, W, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)BN, tc::LIN_BK, 128);
-  if (rc != GN_OK) return rc;
   cudaStream_t st = as_stream(stream);
   if (c_dtype == GN_F32)
-    return tc::launch_tc_linear<float>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype, st);
+    return tc::launch_tc_linear<float>(A, lda, W, ldw, bias, C, ldc, M, N, K, act, ab_dtype, st);
   if (c_dtype == GN_F16)
-    return tc::launch_tc_linear<__half>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype, st);
-  return tc::launch_tc_linear<__nv_bfloat16>(tmA, tmW, bias, C, ldc, M, N, K, BN, act, ab_dtype,
+    return tc::launch_tc_linear<__half>(A, lda, W, ldw, bias, C, ldc, M, N, K, act, ab_dtype, st);
+  return tc::launch_tc_linear<__nv_bfloat16>(A, lda, W, ldw, bias, C, ldc, M, N, K, act, ab_dtype,
                                              st);
 }
 
@@ -762,23 +923,12 @@ extern "C" int gn_tc_linear_pool(const void* A, int64_t lda, const void* W, int6
   GN_CUDA(cudaMemsetAsync(reinterpret_cast<uint8_t*>(acc) + plane, 0, 3 * plane, st));
   if (M == 0) return GN_OK;
   GN_CHECK_ARG(A && W && batch && ptr, "gn_tc_linear_pool: null pointer");
-  int BN = tc_pick_bn(N);
-  if (!tc_wres_fits(N, K, BN, 4) && M >= 4096) {
-    const int bn2 = tc_pick_bn(N, 128);
-    if (tc_wres_fits(N, K, bn2, 4)) BN = bn2;
-  }
-  CUtensorMap tmA, tmW;
-  auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
-  int rc = mk(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, tc::LIN_BM, tc::LIN_BK, 128);
-  if (rc != GN_OK) return rc;
-  rc = mk(&tmW, W, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)BN, tc::LIN_BK, 128);
-  if (rc != GN_OK) return rc;
   tc::PoolEpilogue pe;
   pe.batch = batch;
   pe.ptr = ptr;
   pe.acc = acc;
   pe.B = B;
-  return tc::launch_tc_linear<float>(tmA, tmW, bias, acc, N, M, N, K, BN, GN_ACT_RELU, ab_dtype,
+  return tc::launch_tc_linear<float>(A, lda, W, ldw, bias, acc, N, M, N, K, GN_ACT_RELU, ab_dtype,
                                      st, 1, 0, &pe);
 }
 
@@ -791,15 +941,8 @@ extern "C" int gn_tc_linear_accumulate(const void* A, int64_t lda, const void* W
   GN_CHECK_ARG(A && W && C, "gn_tc_linear_accumulate: null pointer");
   GN_CHECK_ARG(ab_dtype == GN_BF16 || ab_dtype == GN_F16, "gn_tc_linear_accumulate: bad ab_dtype");
   GN_CHECK_ARG(N <= tc::LIN_MAX_N, "gn_tc_linear_accumulate: N=%d exceeds %d", N, tc::LIN_MAX_N);
-  const int BN = tc_pick_bn(N);
-  CUtensorMap tmA, tmW;
-  auto mk = ab_dtype == GN_F16 ? make_tmap_f16_2d : make_tmap_bf16_2d;
-  int rc = mk(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, tc::LIN_BM, tc::LIN_BK, 128);
-  if (rc != GN_OK) return rc;
-  rc = mk(&tmW, W, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, (uint32_t)BN, tc::LIN_BK, 128);
-  if (rc != GN_OK) return rc;
-  return tc::launch_tc_linear<float>(tmA, tmW, nullptr, C, ldc, M, N, K, BN, GN_ACT_NONE, ab_dtype,
-                                     as_stream(stream), splits, 1);
+  return tc::launch_tc_linear<float>(A, lda, W, ldw, nullptr, C, ldc, M, N, K, GN_ACT_NONE,
+                                     ab_dtype, as_stream(stream), splits, 1);
 }
 
 #ifdef GN_DEBUG_BUILD
@@ -809,6 +952,12 @@ extern "C" int gn_debug_linear_trace(unsigned long long* host, int words) {
   GN_CUDA(cudaDeviceSynchronize());
   if (words > 10 * 16 * 4) words = 10 * 16 * 4;
   GN_CUDA(cudaMemcpyFromSymbol(host, tc::g_lin_trace, words * sizeof(unsigned long long)));
+  return GN_OK;
+}
+extern "C" int gn_debug_linear_stages(unsigned long long* host, int words) {
+  GN_CUDA(cudaDeviceSynchronize());
+  if (words > 3 * 64) words = 3 * 64;
+  GN_CUDA(cudaMemcpyFromSymbol(host, tc::g_lin_stage, words * sizeof(unsigned long long)));
   return GN_OK;
 }
 #endif

@@ -433,6 +433,9 @@ class DynEdge(torch.nn.Module):
         return out
 
     validate_inputs: bool = True
+    # 16-bit inference: enqueue the whole forward from ONE C-ABI call (csrc/forward.cu) where the
+    # model's shape allows; False keeps the call-by-call Python sequence (same kernels, same bits)
+    native_driver: bool = True
     _last_flags: Optional[Tensor] = None
     # k of the input graph built on the device when a batch carries no `edge_index`
     # (None: the model's nb_neighbours, the pairing every reference example uses)

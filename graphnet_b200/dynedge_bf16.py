@@ -15,6 +15,7 @@ version on the device with torch ops - plumbing, not the timed path.
 
 from __future__ import annotations
 
+import ctypes as C
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -149,9 +150,153 @@ def _post_pack(model, total: int, D0: int, widths: List[int], offs: List[int],
     return getattr(model, key).get(params, build)
 
 
+class _NativePlan:
+    """`gn_dynedge_plan` of a model (csrc/forward.cu) plus the tensors its pointers refer to."""
+
+    def __init__(self, model, io: torch.dtype):
+        from . import _lib
+        D0, widths, offs, total = _skip_layout(model)
+        convs = list(model._conv_layers)
+        posts = _post_pack(model, total, D0, widths, offs, io)
+        pact = _parse_mlp(model._post_processing)[1]
+        ro, ract = _parse_mlp(model._readout)
+        pools = model._global_pooling_schemes
+        if len(convs) > _lib.GN_MAX_LAYERS or len(posts) > _lib.GN_MAX_DENSE or len(ro) != 1 \
+                or pact != "relu" or not pools or posts[-1][2] % 2:
+            raise NotImplementedError("outside the native driver's shapes")
+        plan = _lib.GnDynedgePlan()
+        keep: List[Any] = []
+        x0w = offs[0]
+        plan.F, plan.x0w, plan.skip_cols = model._nb_inputs, x0w, total
+        plan.io_dtype = ops._DT[io]
+        plan.n_conv, plan.n_post, plan.n_readout, plan.n_pools = len(convs), len(posts), 1, len(pools)
+        plan.input_k = model.input_graph_neighbours or model._nb_neighbours
+        off_in, d_in = 0, D0
+        for li, conv in enumerate(convs):
+            if conv.aggr not in ("add", "sum"):
+                raise NotImplementedError("native driver: aggr='add'")
+            pk = _conv_pack(conv, io, first=(li == 0))
+            assert pk.d == d_in
+            W = pk.split_weights(x0w) if li == 0 else pk.Wpq
+            cols = sorted(ops._columns(conv.features_subset, pk.b))
+            if len(cols) > 16:
+                raise NotImplementedError("native driver: at most 16 kNN columns")
+            c = plan.conv[li]
+            c.Wpq, c.bias_pq, c.W2p = W.data_ptr(), pk.bias_pq.data_ptr(), pk.W2p.data_ptr()
+            c.d_in, c.Kp, c.b, c.k = d_in, pk.Kp, pk.b, conv.nb_neighbors
+            c.slots, c.act = _slots(conv.nb_neighbors), ops.ACT[pk.act]
+            c.off_in, c.off_out, c.ncoord, c.ldw = off_in, offs[li], len(cols), W.stride(0)
+            for t, col in enumerate(cols):
+                c.coord_cols[t] = col
+            keep += [pk, W]
+            off_in, d_in = offs[li], pk.b
+        for i, (Wp, bias, n, K) in enumerate(posts):
+            d = plan.post[i]
+            d.W, d.bias = Wp.data_ptr(), 0 if bias is None else bias.data_ptr()
+            d.n, d.K, d.act, d.ldw, d.tc = n, K, ops.ACT[pact], Wp.stride(0), 1
+            keep += [Wp, bias]
+        lin = ro[0]
+        K_ = posts[-1][2] * len(pools)
+        if lin.in_features != K_:
+            raise NotImplementedError("native driver: readout width")
+        tc = K_ % 8 == 0 and K_ >= 256 and ract in ("relu", "none")
+        if tc:  # fp16 operands, weights times 2^6 and the pooled input times 2^-6 (exact)
+            Wr = (lin.weight.detach().float() * 64.0).to(torch.float16).contiguous()
+        else:
+            Wr = lin.weight.detach().float().contiguous()
+        br = None if lin.bias is None else lin.bias.detach().float().contiguous()
+        d = plan.readout[0]
+        d.W, d.bias = Wr.data_ptr(), 0 if br is None else br.data_ptr()
+        d.n, d.K, d.act, d.ldw, d.tc = lin.out_features, K_, ops.ACT[ract], Wr.stride(0), int(tc)
+        keep += [Wr, br]
+        for i, s in enumerate(pools):
+            plan.pools[i] = ops.POOL[s]
+        self.plan, self.keep, self.n_out = plan, keep, lin.out_features
+        self.ws_bytes: Dict[Tuple[int, int, int, bool, int], int] = {}
+
+
+def _native_plan(model, io: torch.dtype):
+    """The cached plan, or None when the model is outside what csrc/forward.cu drives (the Python
+    sequence below then runs the same kernels one call at a time)."""
+    key = f"_cache_native_{io}"
+    cache = model.__dict__.get(key)
+    if cache is None:
+        cache = _WeightCache()
+        model.__dict__[key] = cache
+    if model._add_global_variables_after_pooling or model._skip_readout:
+        return None
+    params = list(model.parameters())
+
+    def build():
+        try:
+            return _NativePlan(model, io)
+        except NotImplementedError:
+            return None
+    return cache.get(params, build)
+
+
+def _forward_native(model, np_: _NativePlan, data: Any, edge_index: Optional[Tensor]) -> Tensor:
+    """One C-ABI call (gn_dynedge_infer16) enqueues the whole forward over one workspace."""
+    from . import _lib
+    x = data.x
+    if not x.is_cuda:
+        raise RuntimeError("graphnet_b200.DynEdge needs CUDA tensors (no CPU fallback)")
+    dev = x.device
+    if x.dtype != torch.float32 or x.stride(1) != 1:
+        x = x.float().contiguous()
+    N = x.shape[0]
+    assert x.shape[1] == model._nb_inputs, \
+        f"expected {model._nb_inputs} input features, got {x.shape[1]}"
+    n_pulses = data.n_pulses.reshape(-1)
+    B = n_pulses.shape[0]
+    if n_pulses.dtype != torch.int32 or not n_pulses.is_contiguous():
+        n_pulses = n_pulses.to(torch.int32).contiguous()
+    batch = data.batch
+    if not batch.is_contiguous():
+        batch = batch.contiguous()
+    assert batch.shape[0] == N
+    if edge_index is None:
+        edge_index = getattr(data, "edge_index", None)
+    E = 0
+    if edge_index is not None:
+        assert edge_index.dim() == 2 and edge_index.shape[0] == 2
+        if edge_index.dtype != torch.int64 or not edge_index.is_contiguous():
+            edge_index = edge_index.long().contiguous()
+        E = edge_index.shape[1]
+    lib = _lib.load()
+    # (not a weight: may be changed between calls)
+    input_k = model.input_graph_neighbours or model._nb_neighbours
+    np_.plan.input_k = input_k
+    plan = C.byref(np_.plan)
+    wkey = (N, B, E, edge_index is not None, input_k)
+    nbytes = np_.ws_bytes.get(wkey)
+    if nbytes is None:
+        nbytes = int(lib.gn_dynedge_infer16_workspace(plan, N, B, E, int(edge_index is not None)))
+        if len(np_.ws_bytes) > 4096:
+            np_.ws_bytes.clear()
+        np_.ws_bytes[wkey] = nbytes
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    out = torch.empty((B, np_.n_out), dtype=torch.float32, device=dev)
+    flags = torch.empty(1, dtype=torch.int32, device=dev)
+    with ops._on(dev):
+        ops.check(lib.gn_dynedge_infer16(
+            plan, x.data_ptr(), x.stride(0), batch.data_ptr(), n_pulses.data_ptr(), N, B,
+            None if edge_index is None else edge_index.data_ptr(), E, ws.data_ptr(), nbytes,
+            out.data_ptr(), out.stride(0), flags.data_ptr(), ops._stream(dev)),
+            "gn_dynedge_infer16")
+    model._last_flags = flags
+    return out
+
+
 def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
                  return_intermediates: bool = False, save: Optional[Dict[str, Any]] = None):
     """`save` (training): receives the tensors the backward pass needs (training.py)."""
+    if save is None and not return_intermediates and getattr(model, "native_driver", True) and \
+            isinstance(getattr(data, "batch", None), Tensor) and data.batch.dtype == torch.int64 \
+            and data.x.shape[0] > 0 and data.n_pulses.numel() > 0:
+        np_ = _native_plan(model, _io_dtype(model))
+        if np_ is not None:
+            return _forward_native(model, np_, data, edge_index)
     x, n_pulses, ptr, graph, N, B = model._graph_inputs(data, edge_index)
     model._last_flags = graph.flags
     dev = x.device

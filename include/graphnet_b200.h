@@ -143,6 +143,57 @@ int gn_ell_to_coo(const int32_t* nbr, int32_t stride, const int32_t* deg,
 int gn_coo_to_csr(const int64_t* edge_index, int64_t E, int64_t N, int32_t* rowptr,
                   int32_t* col, int32_t* flags, int32_t* max_degree, void* stream);
 
+/* ---- whole forward pass, one call ------------------------------------------ */
+
+/* The 16-bit inference forward of DynEdge (gnn/dynedge.py:296-350: global variables, EdgeConv
+ * layers with dynamic kNN graphs, skip-cat, post-processing MLP, global pooling, one readout
+ * layer) enqueued by ONE call over a caller-provided workspace - the same kernels, in the same
+ * order, as the per-operator entry points below.  The plan holds the repacked weights
+ * (gn_edgeconv_pack_tc layouts) and the architecture; all pointers are device pointers that must
+ * stay valid while a call is in flight. */
+#define GN_MAX_LAYERS 8
+#define GN_MAX_DENSE 4
+typedef struct gn_dynedge_conv {
+  const void* Wpq;      /* node GEMM: layer 0 [2Kp, 3*x0w] bf16 [W_hi | W_hi | W_lo]; else [2Kp, ldw] */
+  const float* bias_pq; /* [2Kp] */
+  const void* W2p;      /* [b16, Kp] fp16 */
+  int32_t d_in, Kp, b, k, slots, act, off_in, off_out, ncoord, ldw;
+  int32_t coord_cols[16]; /* columns of this layer's output the next kNN graph is built on */
+} gn_dynedge_conv;
+typedef struct gn_dynedge_dense {
+  const void* W;        /* [n, ldw]: io_dtype (post-processing), fp16 x 64 (readout, tc = 1) or fp32 */
+  const float* bias;
+  int32_t n, K, act, ldw, tc, pad_;
+} gn_dynedge_dense;
+typedef struct gn_dynedge_plan {
+  int32_t F;            /* input features; D0 = 2F + 5 */
+  int32_t x0w;          /* D0 rounded up to 8 */
+  int32_t skip_cols;    /* columns of the skip-cat buffer */
+  int32_t io_dtype;     /* GN_BF16 or GN_F16 */
+  int32_t n_conv, n_post, n_readout, n_pools;
+  int32_t input_k;      /* k of the input graph built when edge_index is NULL */
+  int32_t pad_;
+  gn_dynedge_conv conv[GN_MAX_LAYERS];
+  gn_dynedge_dense post[GN_MAX_DENSE];
+  gn_dynedge_dense readout[GN_MAX_DENSE];
+  int32_t pools[8];     /* GN_POOL_* in output order */
+} gn_dynedge_plan;
+
+/* Bytes of workspace gn_dynedge_infer16 needs for a batch of N nodes, B events and (when the data
+ * set's edge_index is passed) E edges. */
+size_t gn_dynedge_infer16_workspace(const gn_dynedge_plan* plan, int64_t N, int64_t B, int64_t E,
+                                    int has_edge_index);
+
+/* x [N, ldx] fp32, batch [N] int64 sorted, n_pulses [B] int32, edge_index [2, E] int64 grouped by
+ * target or NULL (then KNNGraph's graph on columns 0-2 with plan->input_k neighbours is built on
+ * the device); out [B, ldo] fp32 = readout output; flags: device int32 receiving the GN_FLAG_*
+ * bits of the input checks.  workspace: 256-byte aligned, >= gn_dynedge_infer16_workspace bytes. */
+int gn_dynedge_infer16(const gn_dynedge_plan* plan, const float* x, int64_t ldx,
+                       const int64_t* batch, const int32_t* n_pulses, int64_t N, int64_t B,
+                       const int64_t* edge_index, int64_t E, void* workspace,
+                       size_t workspace_bytes, float* out, int64_t ldo, int32_t* flags,
+                       void* stream);
+
 /* ---- per-event summary features ----------------------------------------- */
 
 /* DynEdge._calculate_global_variables (models/gnn/dynedge.py:267-294) with

@@ -24,6 +24,10 @@ int gn_debug_edge_trace(unsigned long long* host, int words);
  * [warp 0..9][item 0..15][4 stamps] (clock64). */
 int gn_debug_linear_trace(unsigned long long* host, int words);
 
+/* Same launch, per ring stage g < 64 of CTA 0: [0][g] TMA issued, [1][g] the MMA thread saw the
+ * stage full, [2][g] its commit (slot release) issued. */
+int gn_debug_linear_stages(unsigned long long* host, int words);
+
 #ifdef __cplusplus
 }
 #endif

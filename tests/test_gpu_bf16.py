@@ -20,7 +20,11 @@ def rel_l2(a, b):
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 256, 64), (300, 704, 19), (1000, 352, 1088), (77, 336, 256),
-                                   (4096, 256, 336), (129, 320, 24), (5, 16, 8)])
+                                   (4096, 256, 336), (129, 320, 24), (5, 16, 8),
+                                   # large M: clusters with TMA multicast (4 x 1 with W resident,
+                                   # 2 x 2 and 1 x 4 with W streamed), ragged last row tiles
+                                   (20001, 704, 256), (20001, 336, 1088), (9999, 130, 72),
+                                   (12289, 256, 336)])
 @pytest.mark.parametrize("act,out_dtype", [("none", torch.bfloat16), ("relu", torch.float32),
                                            ("none", torch.float16)])
 def test_tc_linear(M, N, K, act, out_dtype):
@@ -312,3 +316,54 @@ def test_dynedge_gelu_on_the_tensor_cores():
     got = m(gb.Data(x=pb.x.to(DEV), edge_index=ei.to(DEV), batch=pb.batch.to(DEV),
                     n_pulses=pb.n_pulses.to(DEV)))
     assert rel_l2(got.cpu(), want) < BF16_TOL
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp16"])
+@pytest.mark.parametrize("with_edges", [True, False])
+@pytest.mark.parametrize("kw", [
+    dict(global_pooling_schemes=["min", "max", "mean", "sum"]),
+    dict(global_pooling_schemes=["mean"], nb_neighbours=4, features_subset=[0, 1, 2, 3],
+         dynedge_layer_sizes=[(64, 128), (168, 128)], post_processing_layer_sizes=[168, 128],
+         readout_layer_sizes=[64]),
+    dict(global_pooling_schemes=["max", "sum"], dynedge_layer_sizes=[(40, 50), (62, 100)],
+         post_processing_layer_sizes=[96, 64, 32], readout_layer_sizes=[48]),
+])
+def test_native_driver_equals_python_sequence(precision, with_edges, kw):
+    """gn_dynedge_infer16 (csrc/forward.cu: one C-ABI call enqueues the whole forward) against the
+    Python sequence of the same entry points: same kernels on the same inputs -> same bits."""
+    import graphnet_b200 as gb
+    x, batch, counts = random_events(37, 1, 90, seed=5)
+    m = gb.DynEdge(7, precision=precision, **kw)
+    m = m.to(DEV).eval()
+    ei = None
+    if with_edges:
+        ei = gb.knn_graph(x[:, :3].contiguous().to(DEV), kw.get("nb_neighbours", 8), batch.to(DEV),
+                          num_events=37)
+    data = gb.Data(x=x.to(DEV), edge_index=ei, batch=batch.to(DEV), n_pulses=counts.to(DEV))
+    from graphnet_b200 import dynedge_bf16
+    assert dynedge_bf16._native_plan(m, dynedge_bf16._io_dtype(m)) is not None
+    got = m(data)
+    flags = int(m._last_flags.item())
+    m.native_driver = False
+    want = m(data)
+    assert flags == int(m._last_flags.item()) == 0
+    assert got.shape == want.shape and torch.equal(got, want)
+    # the flags word reports what the separate calls report
+    m.native_driver = True
+    bad = gb.Data(x=x.to(DEV), edge_index=ei, batch=batch.flip(0).contiguous().to(DEV),
+                  n_pulses=counts.to(DEV))
+    with pytest.raises(ValueError):
+        m(bad)
+
+
+def test_native_driver_declines_what_it_does_not_drive():
+    import graphnet_b200 as gb
+    from graphnet_b200 import dynedge_bf16
+    for kw in (dict(global_pooling_schemes=None), dict(add_global_variables_after_pooling=True,
+                                                       global_pooling_schemes=["max"]),
+               dict(global_pooling_schemes=["max"], readout_layer_sizes=[64, 32])):
+        m = gb.DynEdge(7, precision="bf16", **kw).to(DEV).eval()
+        assert dynedge_bf16._native_plan(m, torch.bfloat16) is None
+        x, batch, counts = random_events(5, 3, 30, seed=1)
+        out = m(gb.Data(x=x.to(DEV), batch=batch.to(DEV), n_pulses=counts.to(DEV)))
+        assert torch.isfinite(out).all()
