@@ -96,6 +96,9 @@ SIGNATURES = {
     "gn_segment_pool": (_int, [_p, _int, _i64, _int, _p, _i64, _hp, _int, _p, _i64, _p]),
     "gn_dynedge_infer16_workspace": (_sz, [_pp, _i64, _i64, _i64, _int]),
     "gn_dynedge_infer16": (_int, [_pp, _p, _i64, _p, _p, _i64, _i64, _p, _i64, _p, _sz, _p, _i64, _p, _p]),
+    "gn_tc_edge_mlp_aggregate_f32": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _int, _p, _p, _int, _p,
+                                            _i64, _p, _hp, _int, _p, _sz, _p]),
+    "gn_split_bf16": (_int, [_p, _i64, _i64, _int, _int, _int, _p, _i64, _p]),
     "gn_tc_linear_pool": (_int, [_p, _i64, _p, _i64, _int, _p, _i64, _int, _int, _p, _p, _i64, _p, _p]),
     "gn_pool_finalize": (_int, [_p, _p, _i64, _int, _hp, _int, _p, _i64, _p, _i64, C.c_float, _p]),
     "gn_linear_f32": (_int, [_p, _i64, _p, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),

@@ -342,6 +342,69 @@ extern "C" int gn_global_variables(const float* x, int64_t ldx, int F, const gn_
   return GN_OK;
 }
 
+// fp32 [M, cols] -> bf16 pieces of x = x1 + x2 + x3 (x1 = bf16(x), x2 = bf16(x - x1), ...), laid
+// out for ONE bf16 GEMM to evaluate x W^T with more mantissa bits than a bf16 operand has:
+//   terms = 3: [x1 | x2 | x1]               against [w1 | w1 | w2]              (16 bits)
+//   terms = 6: [x1 | x1 | x1 | x2 | x2 | x3] against [w1 | w2 | w3 | w1 | w2 | w1] (24 bits: every
+//              product term down to 2^-16 of the leading one)
+// Each block is kc columns wide, columns cols..kc-1 zero.
+template <int TERMS>
+__global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict__ X, int64_t ldx,
+                                                         int64_t M, int cols, int kc,
+                                                         __nv_bfloat16* __restrict__ out,
+                                                         int64_t ldo) {
+  const int q = kc >> 2;   // groups of 4 columns per row
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= M * q) return;
+  const int64_t r = i / q;
+  const int c = (int)(i - r * q) * 4;
+  float v[4];
+#pragma unroll
+  for (int t = 0; t < 4; ++t) v[t] = c + t < cols ? X[r * ldx + c + t] : 0.f;
+  __nv_bfloat16 x1[4], x2[4], x3[4];
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    x1[t] = __float2bfloat16_rn(v[t]);
+    const float r1 = v[t] - __bfloat162float(x1[t]);
+    x2[t] = __float2bfloat16_rn(r1);
+    x3[t] = __float2bfloat16_rn(r1 - __bfloat162float(x2[t]));
+  }
+  __nv_bfloat16* o = out + r * ldo + c;
+  const uint2 u1 = *reinterpret_cast<const uint2*>(x1), u2 = *reinterpret_cast<const uint2*>(x2);
+  if (TERMS == 3) {
+    *reinterpret_cast<uint2*>(o) = u1;
+    *reinterpret_cast<uint2*>(o + kc) = u2;
+    *reinterpret_cast<uint2*>(o + 2 * kc) = u1;
+  } else {
+    *reinterpret_cast<uint2*>(o) = u1;
+    *reinterpret_cast<uint2*>(o + kc) = u1;
+    *reinterpret_cast<uint2*>(o + 2 * kc) = u1;
+    *reinterpret_cast<uint2*>(o + 3 * kc) = u2;
+    *reinterpret_cast<uint2*>(o + 4 * kc) = u2;
+    *reinterpret_cast<uint2*>(o + 5 * kc) = *reinterpret_cast<const uint2*>(x3);
+  }
+}
+
+extern "C" int gn_split_bf16(const float* X, int64_t ldx, int64_t M, int cols, int kc, int terms,
+                             void* out, int64_t ldo, void* stream) {
+  GN_CHECK_ARG(terms == 3 || terms == 6, "gn_split_bf16: terms must be 3 or 6");
+  GN_CHECK_ARG(M >= 0 && cols >= 1 && kc >= cols && kc % 4 == 0 && ldx >= cols &&
+                   ldo >= (int64_t)terms * kc && ldo % 4 == 0,
+               "gn_split_bf16: bad sizes (kc and ldo must be multiples of 4)");
+  if (M == 0) return GN_OK;
+  GN_CHECK_ARG(X && out && (reinterpret_cast<uintptr_t>(out) & 7) == 0,
+               "gn_split_bf16: null or misaligned pointer");
+  const int64_t n = M * (kc / 4);
+  const unsigned grid = (unsigned)ceil_div(n, 256);
+  __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+  if (terms == 3)
+    split_bf16_kernel<3><<<grid, 256, 0, as_stream(stream)>>>(X, ldx, M, cols, kc, o, ldo);
+  else
+    split_bf16_kernel<6><<<grid, 256, 0, as_stream(stream)>>>(X, ldx, M, cols, kc, o, ldo);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
+}
+
 extern "C" int gn_segment_pool(const void* x, int x_dtype, int64_t ldx, int C, const int32_t* ptr,
                                int64_t B, const int32_t* schemes, int n_schemes, float* out,
                                int64_t ldo, void* stream) {

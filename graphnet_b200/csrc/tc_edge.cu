@@ -46,6 +46,7 @@ struct EdgeParams {
   const int32_t* ell;       // [groups, KP] neighbour ids, -1 = empty slot
   const int32_t* group_node;  // target node of each group, or null: group g is node g
   const int32_t* group_count; // device int: number of groups, or null: N groups
+  int64_t group_cap;          // capacity of the group lists (a malformed graph can count past it)
   int accumulate;           // 0: store, 1: red.add into out / coords (overflow pass)
   int64_t N;
   int bnp;                  // output width padded to a multiple of 16 (UMMA N)
@@ -64,6 +65,8 @@ struct EdgeParams {
   int aggr;                 // CTA-pair kernel: 0 add, 1 mean, 2 max, 3 min
   const int32_t* deg;       // slots in use per node (ELL graphs; mean / max / min need it)
   const void* neg_row;      // CTA-pair kernel: 1 KB of fp16 -inf, read in place of Q_j by empty slots
+  const void* w2lo;         // fp32-accurate kernel: fp16(W2 - fp16(W2)), laid out like w2
+  const void* neg_row32;    // fp32-accurate kernel: a row of fp32 -inf
 };
 
 __device__ __forceinline__ uint32_t relu_add_f16x2(uint32_t a, uint32_t b) {
@@ -89,6 +92,7 @@ __device__ __forceinline__ void red_add1_16(void* dst, float a, bool f16) {
 }  // namespace tc
 }  // namespace gn
 #include "tc_edge_pair.cuh"
+#include "tc_edge_x3.cuh"
 namespace gn {
 namespace tc {
 
@@ -167,6 +171,15 @@ static __device__ __align__(16) const uint32_t g_neg_inf_row[256] = {GN_NI64, GN
 #undef GN_NI4
 #undef GN_NI16
 #undef GN_NI64
+// 352 fp32 -inf (the fp32-accurate kernel's rows are up to 352 columns wide)
+#define GN_NF4 0xFF800000u, 0xFF800000u, 0xFF800000u, 0xFF800000u
+#define GN_NF16 GN_NF4, GN_NF4, GN_NF4, GN_NF4
+#define GN_NF64 GN_NF16, GN_NF16, GN_NF16, GN_NF16
+static __device__ __align__(16) const uint32_t g_neg_inf_row32[352] = {
+    GN_NF64, GN_NF64, GN_NF64, GN_NF64, GN_NF64, GN_NF16, GN_NF16};
+#undef GN_NF4
+#undef GN_NF16
+#undef GN_NF64
 
 // an ELL graph whose stride is a supported slot count is consumed in place: no lists, no 2nd pass
 static bool edge_supported_slots(int s) { return s == 8 || s == 9 || s == 16 || s == 17 || s == 32; }
@@ -330,6 +343,7 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
       p.ell = ovf_ell;
       p.group_node = ovf_node;
       p.group_count = ovf_count;
+      p.group_cap = cap;
       p.accumulate = 1;
       max_tiles = ceil_div(cap, npt);
     }
@@ -368,6 +382,139 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
     }
 #undef GN_EDGE_CASE4
 #undef GN_EDGE_LAUNCH4
+    GN_LAUNCH_CHECK();
+  }
+  return GN_OK;
+}
+
+// fp32 in, fp32 out, fp16 (hi, lo) operand pairs on the tensor cores: see tc_edge_x3.cuh
+extern "C" int gn_tc_edge_mlp_aggregate_f32(const float* P, int64_t ldp, const float* Q,
+                                            int64_t ldq, int Kp, const gn_graph* graph, int64_t N,
+                                            int slots, const void* W2hi, const void* W2lo, int b,
+                                            float* out, int64_t ldo, float* coords,
+                                            const int32_t* coord_cols, int ncoord, void* scratch,
+                                            size_t scratch_bytes, void* stream) {
+  GN_CHECK_ARG(N >= 0 && b >= 1 && b <= 256, "gn_tc_edge_mlp_aggregate_f32: b=%d not in [1,256]", b);
+  GN_CHECK_ARG(Kp >= 32 && Kp % 32 == 0 && Kp <= 352,
+               "gn_tc_edge_mlp_aggregate_f32: padded hidden width %d not a multiple of 32 in "
+               "[32,352]", Kp);
+  GN_CHECK_ARG(edge_supported_slots(slots),
+               "gn_tc_edge_mlp_aggregate_f32: slots=%d (must be 8, 9, 16, 17 or 32)", slots);
+  GN_CHECK_ARG(ldp >= Kp && ldq >= Kp && ldp % 4 == 0 && ldq % 4 == 0 && ldo >= b,
+               "gn_tc_edge_mlp_aggregate_f32: bad leading dimensions");
+  GN_CHECK_ARG(ncoord >= 0 && ncoord <= 16, "gn_tc_edge_mlp_aggregate_f32: ncoord=%d", ncoord);
+  if (N == 0) return GN_OK;
+  GN_CHECK_ARG(P && Q && W2hi && W2lo && out && scratch && graph,
+               "gn_tc_edge_mlp_aggregate_f32: null pointer");
+  GN_CHECK_ARG(scratch_bytes >= gn_tc_edge_scratch_bytes(graph, N, slots),
+               "gn_tc_edge_mlp_aggregate_f32: scratch too small");
+  GN_CHECK_ARG((reinterpret_cast<uintptr_t>(P) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(Q) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(W2hi) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(W2lo) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(scratch) & 3) == 0,
+               "gn_tc_edge_mlp_aggregate_f32: P, Q, W2 must be 16-byte aligned");
+  GraphView g;
+  int rc = make_graph_view(graph, &g);
+  if (rc != GN_OK) return rc;
+  cudaStream_t st = as_stream(stream);
+  tc::EdgeParams p;
+  memset(&p, 0, sizeof(p));
+  for (int t = 0; t < ncoord; ++t) {
+    GN_CHECK_ARG(coord_cols && coord_cols[t] >= 0 && coord_cols[t] < b,
+                 "gn_tc_edge_mlp_aggregate_f32: coordinate column out of range");
+    GN_CHECK_ARG(t == 0 || coord_cols[t] > coord_cols[t - 1],
+                 "gn_tc_edge_mlp_aggregate_f32: coordinate columns must be strictly increasing");
+    p.coord_mask[coord_cols[t] >> 5] |= 1u << (coord_cols[t] & 31);
+  }
+  const bool direct = edge_direct_ell(graph);
+  if (direct) slots = graph->ell_stride;
+  const int64_t cap = direct ? 0 : edge_overflow_cap(graph, N, slots);
+  int32_t* ell = reinterpret_cast<int32_t*>(scratch);
+  int32_t* ovf_ell = ell + N * slots;
+  int32_t* ovf_node = ovf_ell + cap * slots;
+  int32_t* ovf_count = ovf_node + cap;
+  if (!direct) {
+    GN_CUDA(cudaMemsetAsync(ovf_count, 0, sizeof(int32_t), st));
+    tc::graph_to_groups_kernel<<<(unsigned)ceil_div(N * slots, 256), 256, 0, st>>>(
+        g, N, slots, ell, ovf_node, ovf_ell, ovf_count, cap);
+    GN_LAUNCH_CHECK();
+  }
+  p.w2 = W2hi;
+  p.w2lo = W2lo;
+  p.act = GN_ACT_RELU;
+  p.aggr = GN_AGGR_ADD;
+  p.pmat = reinterpret_cast<const __half*>(P);   // (fp32 here: the kernel reads them as such)
+  p.ldp = ldp;
+  p.qmat = reinterpret_cast<const __half*>(Q);
+  p.ldq = ldq;
+  p.Kp = Kp;
+  p.nch = Kp / tc::EK_KCH;
+  p.N = N;
+  p.bnp = (b + 15) & ~15;
+  p.b = b;
+  p.out = out;
+  p.ldo = ldo;
+  p.coords = ncoord > 0 ? coords : nullptr;
+  p.ncoord = ncoord;
+  const int npt = tc::E4_ROWS / slots;
+  int dev = 0, sms = 0;
+  GN_CUDA(cudaGetDevice(&dev));
+  GN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  GN_CHECK_ARG(sms >= 2, "gn_tc_edge_mlp_aggregate_f32: needs a CTA pair (>= 2 SMs)");
+  {
+    static std::atomic<void*> neg_row_addr[64];
+    void* nr = neg_row_addr[dev & 63].load(std::memory_order_relaxed);
+    if (nr == nullptr) {
+      GN_CUDA(cudaGetSymbolAddress(&nr, g_neg_inf_row32));
+      neg_row_addr[dev & 63].store(nr, std::memory_order_relaxed);
+    }
+    p.neg_row32 = nr;
+  }
+  const size_t smem = tc::edge4_smem_bytes(Kp);   // four h tiles, as the 16-bit kernel
+  for (int pass = 0; pass < 2; ++pass) {
+    int64_t max_tiles;
+    if (pass == 0) {
+      p.ell = direct ? graph->col : ell;
+      p.group_node = nullptr;
+      p.group_count = nullptr;
+      p.accumulate = 0;
+      max_tiles = ceil_div(N, npt);
+    } else {
+      if (cap <= 0) break;
+      p.ell = ovf_ell;
+      p.group_node = ovf_node;
+      p.group_count = ovf_count;
+      p.group_cap = cap;
+      p.accumulate = 1;
+      max_tiles = ceil_div(cap, npt);
+    }
+    const int64_t max_steps = (max_tiles + 1) / 2;
+    const unsigned grid = 2u * (unsigned)(max_steps < sms / 2 ? max_steps : sms / 2);
+#define GN_X3_LAUNCH(KP_, ACC_)                                                                  \
+  {                                                                                              \
+    auto kern = tc::edge_mlp_aggregate_x3_kernel<KP_, ACC_>;                                     \
+    static std::atomic<unsigned long long> ready_;                                               \
+    if (!((ready_.load(std::memory_order_relaxed) >> (dev & 63)) & 1ull)) {                      \
+      GN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,            \
+                                   (int)tc::edge4_smem_bytes(352)));                             \
+      ready_.fetch_or(1ull << (dev & 63), std::memory_order_relaxed);                            \
+    }                                                                                            \
+    kern<<<grid, tc::E4_THREADS, smem, st>>>(p);                                                 \
+  }
+#define GN_X3_CASE(KP_)                                                  \
+  {                                                                      \
+    if (p.accumulate) GN_X3_LAUNCH(KP_, true) else GN_X3_LAUNCH(KP_, false) \
+  }
+    switch (slots) {
+      case 8: GN_X3_CASE(8) break;
+      case 9: GN_X3_CASE(9) break;
+      case 16: GN_X3_CASE(16) break;
+      case 17: GN_X3_CASE(17) break;
+      default: GN_X3_CASE(32) break;
+    }
+#undef GN_X3_CASE
+#undef GN_X3_LAUNCH
     GN_LAUNCH_CHECK();
   }
   return GN_OK;

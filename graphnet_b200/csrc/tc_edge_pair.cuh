@@ -178,7 +178,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(E4_THREADS, 1)
 #ifdef GN_DEBUG_BUILD
   const long long t_entry = clock64();
 #endif
-  const int64_t num_groups = p.group_count ? (int64_t)__ldg(p.group_count) : p.N;
+  const int64_t num_groups =
+      p.group_count ? min((int64_t)__ldg(p.group_count), p.group_cap) : p.N;
   const int64_t num_tiles = (num_groups + NPT - 1) / NPT; // 64-row tiles
   const int64_t num_steps = (num_tiles + 1) / 2;          // a step = two tiles, one per CTA
   // a cluster takes a CONTIGUOUS range of steps: consecutive tiles are consecutive nodes of the
@@ -386,6 +387,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(E4_THREADS, 1)
         const uint64_t qlane = qbase + pofs;
         const uint64_t nlane = negrow + pofs;
         const int32_t jdead = node >= 0 ? 0 : -1;
+        // (ids outside [0, N) - an empty slot's -1, or garbage behind inputs the flags word
+        // rejects - gather the -inf row)
+        const uint32_t nmax = (uint32_t)p.N;
         // byte offset of the node's first row in its K chunk; the 128B swizzle XORs the 16-byte
         // piece index with row & 7 = bits 7..9 of the row offset
         const uint32_t dst0 = h_base + (uint32_t)(piece >> 3) * E4_CHUNK_BYTES;
@@ -400,7 +404,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(E4_THREADS, 1)
             if (s0 + s < KP) {
               const int32_t j = __shfl_sync(0xffffffffu, jv, src0 + s0 + s) | jdead;
               const uint64_t qa = qlane + (uint64_t)(uint32_t)j * qpitch;
-              Q[s] = e4_ldg128(reinterpret_cast<const void*>(j >= 0 ? qa : nlane));
+              Q[s] = e4_ldg128(reinterpret_cast<const void*>((uint32_t)j < nmax ? qa : nlane));
             }
           }
           if (first) {  // the tensor core has finished with this buffer's previous tile
@@ -423,7 +427,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(E4_THREADS, 1)
               hv.w = e4_act_add(P.w, Q[s].w, act);
               if (GEN && act != ACT_RELU) {   // act(-inf) is not 0 for these: zero empty slots
                 const int32_t j = __shfl_sync(0xffffffffu, jv, src0 + s0 + s) | jdead;
-                if (j < 0) hv = make_uint4(0, 0, 0, 0);
+                if ((uint32_t)j >= nmax) hv = make_uint4(0, 0, 0, 0);
               }
               if (pok)
                 asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(hv.x),

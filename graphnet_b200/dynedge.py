@@ -436,6 +436,10 @@ class DynEdge(torch.nn.Module):
     # 16-bit inference: enqueue the whole forward from ONE C-ABI call (csrc/forward.cu) where the
     # model's shape allows; False keeps the call-by-call Python sequence (same kernels, same bits)
     native_driver: bool = True
+    # precision="fp32": multiply on the tensor cores with operands split into 16-bit pairs
+    # (dynedge_x3.py; fp32 inputs, weights, accumulation and outputs).  False: the FFMA kernels,
+    # the parity anchor (plain fp32 arithmetic in the reference's order of operations)
+    fp32_tensor_cores: bool = True
     _last_flags: Optional[Tensor] = None
     # k of the input graph built on the device when a batch carries no `edge_index`
     # (None: the model's nb_neighbours, the pairing every reference example uses)
@@ -453,6 +457,10 @@ class DynEdge(torch.nn.Module):
         if self.precision in ("bf16", "fp16"):
             from .dynedge_bf16 import forward_bf16
             return forward_bf16(self, data, edge_index)
+        if self.fp32_tensor_cores:
+            from .dynedge_x3 import eligible, forward_f32_tc
+            if eligible(self):
+                return forward_f32_tc(self, data, edge_index)
         return self._forward_f32(data, edge_index=edge_index)
 
     def _graph_inputs(self, data: Any, edge_index: Optional[Tensor] = None

@@ -436,6 +436,46 @@ def tc_edge_mlp_aggregate(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: in
     return out
 
 
+def tc_edge_mlp_aggregate_f32(P: Tensor, Q: Tensor, Kp: int, graph: Graph, slots: int, W2hi: Tensor,
+                              W2lo: Tensor, b: int, out: Tensor, coords: Optional[Tensor],
+                              coord_cols: Sequence[int]) -> Tensor:
+    """out[i] = sum_j relu(W2 relu(P_i + Q_j) + b2) with fp32 P, Q, out and (hi, lo) fp16 operand
+    pairs on the tensor cores (gn_tc_edge_mlp_aggregate_f32): the fp32 path's EdgeConv."""
+    dev = _require_cuda(P, Q, W2hi, W2lo, out, coords)
+    assert P.dtype == torch.float32 and Q.dtype == torch.float32 and out.dtype == torch.float32
+    assert W2hi.dtype == torch.float16 and W2lo.dtype == torch.float16
+    assert W2hi.is_contiguous() and W2lo.is_contiguous() and W2hi.shape == W2lo.shape
+    assert P.stride(1) == 1 and Q.stride(1) == 1 and out.stride(1) == 1 and P.shape[0] == Q.shape[0]
+    N = P.shape[0]
+    lib = _lib.load()
+    gs = graph.c_struct()
+    nbytes = lib.gn_tc_edge_scratch_bytes(C.byref(gs), N, slots)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    ncoord = 0 if coords is None else len(coord_cols)
+    with _on(dev):
+        check(lib.gn_tc_edge_mlp_aggregate_f32(
+            _ptr(P), P.stride(0), _ptr(Q), Q.stride(0), Kp, C.byref(gs), N, slots, _ptr(W2hi),
+            _ptr(W2lo), b, _ptr(out), out.stride(0), _ptr(coords),
+            _host_i32(coord_cols) if ncoord else None, ncoord, _ptr(scratch), nbytes,
+            _stream(dev)), "gn_tc_edge_mlp_aggregate_f32")
+    return out
+
+
+def split_bf16(X: Tensor, kc: int, terms: int = 3, out: Optional[Tensor] = None) -> Tensor:
+    """bf16 pieces of the fp32 matrix X [M, cols <= kc] for a split-operand GEMM (gn_split_bf16):
+    terms=3 -> [x1 | x2 | x1], terms=6 -> [x1 | x1 | x1 | x2 | x2 | x3], blocks kc wide."""
+    dev = _require_cuda(X, out)
+    assert X.dtype == torch.float32 and X.stride(1) == 1 and kc % 4 == 0 and kc >= X.shape[1]
+    M, cols = X.shape
+    if out is None:
+        out = torch.empty((M, terms * kc), dtype=torch.bfloat16, device=dev)
+    assert out.dtype == torch.bfloat16 and out.stride(1) == 1 and out.shape[1] >= terms * kc
+    with _on(dev):
+        check(_lib.load().gn_split_bf16(_ptr(X), X.stride(0), M, cols, kc, terms, _ptr(out),
+                                        out.stride(0), _stream(dev)), "gn_split_bf16")
+    return out
+
+
 def edgeconv_pack_tc(W1: Tensor, b1: Optional[Tensor], W2: Tensor, b2: Optional[Tensor], Kp: int,
                      Kd: int, wpq_dtype: torch.dtype, train: bool, act: str = "relu"):
     """(Wpq, bias_pq, W2p, W2b, W2bT, WpqT) for the tensor-core EdgeConv kernels from the

@@ -301,6 +301,28 @@ int gn_tc_edge_mlp_aggregate(const void* P, int64_t ldp, const void* Q, int64_t 
                              const int32_t* coord_cols, int ncoord, void* scratch,
                              size_t scratch_bytes, int act, int aggr, void* stream);
 
+/* The same op at the reference's own precision (float32 EdgeConv, layers.py:67 with
+ * dynedge.py:193-204): P, Q and out are fp32, ReLU + aggr='add'.  The second Linear still runs on
+ * the tensor cores: the hidden activations and W2 each as a pair of fp16 matrices (value =
+ * hi + lo, 22 mantissa bits), three MMAs per K step into an fp32 accumulator.  W2hi / W2lo:
+ * [b16, Kp] fp16 in the layout of gn_edgeconv_pack_tc's W2p (W2lo = fp16(W2p32 - W2hi)), Kp <= 352. */
+int gn_tc_edge_mlp_aggregate_f32(const float* P, int64_t ldp, const float* Q, int64_t ldq, int Kp,
+                                 const gn_graph* graph, int64_t N, int slots, const void* W2hi,
+                                 const void* W2lo, int b, float* out, int64_t ldo, float* coords,
+                                 const int32_t* coord_cols, int ncoord, void* scratch,
+                                 size_t scratch_bytes, void* stream);
+
+/* bf16 pieces of the fp32 matrix X[M, cols] (x = x1 + x2 + x3, x1 = bf16(x), x2 = bf16(x - x1),
+ * x3 = bf16(x - x1 - x2)) laid out so that ONE gn_tc_linear call evaluates x W^T beyond bf16
+ * accuracy - the fp32 path's node-level Linear layers (dynedge.py:193-232) on the tensor cores:
+ *   terms = 3: out[M, 3 kc] = [x1 | x2 | x1]                against W = [w1 | w1 | w2]  (16 bits)
+ *   terms = 6: out[M, 6 kc] = [x1 | x1 | x1 | x2 | x2 | x3] against [w1 | w2 | w3 | w1 | w2 | w1]
+ *              (every product term down to 2^-16 of the leading one: fp32-grade)
+ * Blocks are kc columns wide, columns cols..kc-1 zero.  No counterpart in the reference (it
+ * multiplies in fp32). */
+int gn_split_bf16(const float* X, int64_t ldx, int64_t M, int cols, int kc, int terms, void* out,
+                  int64_t ldo, void* stream);
+
 /* Training forward of the same op: additionally records the ReLU pattern of the second Linear
  * (what torch autograd keeps as the saved output of the ReLU in PyG's EdgeConv.message,
  * components/layers.py:67) as bits, so that the backward pass need not recompute Z = H W2^T.

@@ -54,7 +54,7 @@ def test_c4_upgrade_forward(precision, tol):
     # one event's output at the 1e-3 level in fp32, so the fp32 bar is on
     # the median event and a looser one on the worst
     assert float(per_event.median()) < tol, per_event
-    assert float(per_event.max()) < (5e-3 if precision == "fp32" else 2 * tol), per_event
+    assert float(per_event.max()) < (1e-2 if precision == "fp32" else 2 * tol), per_event
 
 
 @pytest.mark.parametrize("n", [16, 256, 2048])

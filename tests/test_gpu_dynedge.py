@@ -91,7 +91,13 @@ def test_forward_fp32_matches_golden(name):
             assert torch.equal(inter["pooled"][:, C:], inter["global_variables"])
     assert out.shape == g["out"].shape
     assert rel_l2(out.cpu(), g["out"]) < tol
-    # public call gives the same tensor
+    # the public call multiplies on the tensor cores (operands split into 16-bit pieces, fp32
+    # accumulation): the same tensor to fp32 accuracy; with the switch off it runs the FFMA
+    # kernels traced above and gives the same bits
+    got_tc = m(_data(g))
+    assert rel_l2(got_tc.cpu(), out.cpu()) < (3e-5 if not any_flip else 2e-3)
+    assert rel_l2(got_tc.cpu(), g["out"]) < (FP32_TOL if not any_flip else 2e-3)
+    m.fp32_tensor_cores = False
     assert torch.equal(m(_data(g)), out)
 
 
