@@ -352,7 +352,8 @@ def rider_infer(dev, world, rank, flush_buf, *, workload, events, pulses, precis
     ms = _timed_steps(lambda: model(data_dev)[0], steps, warmup, dev, world, flush_buf)
     out = {"workload": workload_name(ns), "value": events * world * steps / (ms * 1e-3),
            "unit": UNIT, "n_gpus": world, "ms_per_step": ms / steps, "steps": steps,
-           "warmup": warmup, "dtype": "bf16" if precision == "bf16" else "f32",
+           "warmup": warmup, "dtype": "bf16" if precision == "bf16" else
+           "f32 (tensor cores: 16-bit operand pieces summing to the fp32 operands, fp32 accumulate)",
            "nodes_per_batch": N, "edges_per_batch": E,
            "nodes_per_s": N * world * steps / (ms * 1e-3)}
     if precision == "fp32" and workload == "c2":
@@ -810,24 +811,8 @@ def dominant_kernel_roofline(backbone, data, precision, N, E, dev, flush_buf):
             from graphnet_b200.dynedge_bf16 import time_edge_kernel
             ms, executed_flops, name = time_edge_kernel(backbone, data, flush_buf)
         else:
-            conv = backbone._conv_layers[1]
-            x = torch.randn(N, 256, device=dev)
-            graph = ops.coo_to_csr(data.edge_index, N)
-            out = torch.empty(N, 256, device=dev)
-            for _ in range(3):
-                conv._conv_f32(x, graph, out=out)
-            reps = 5
-            s = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
-            e = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
-            for i in range(reps):
-                flush_buf.fill_(i)
-                s[i].record()
-                conv._conv_f32(x, graph, out=out)
-                e[i].record()
-            torch.cuda.synchronize(dev)
-            ms = sum(a.elapsed_time(b) for a, b in zip(s, e)) / reps
-            executed_flops = 2 * N * 256 * 672 + 2 * E * 336 * 256
-            name = "gn::linear_f32_kernel x2 + gn::edgeconv_f32_kernel (fp32 path)"
+            from graphnet_b200.dynedge_x3 import time_edge_kernel_f32
+            ms, executed_flops, name = time_edge_kernel_f32(backbone, data, flush_buf)
     except Exception as exc:  # roofline is diagnostic; never lose the bench line
         return lambda pk: {"error": repr(exc)}
     algorithmic = 2 * E * (2 * 256 * 336 + 336 * 256)

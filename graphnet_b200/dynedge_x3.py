@@ -179,3 +179,38 @@ def forward_f32_tc(model, data: Any, edge_index: Optional[Tensor] = None) -> Ten
     for lin in ro:
         out = ops.linear_f32(out, lin.weight, lin.bias, act=ract)
     return out
+
+
+def time_edge_kernel_f32(model, data: Any, flush_buf: Tensor, layer: int = 1, reps: int = 5):
+    """CUDA-event time of the fp32 edge kernel of conv `layer` alone (bench.py's fp32 rider)."""
+    pack = _x3_pack(model)
+    assert pack is not None
+    x, n_pulses, ptr, graph, N, B = model._graph_inputs(data, None)
+    dev = x.device
+    cv = pack.convs[layer]
+    pk = cv["pk"]
+    g = torch.Generator(device=dev).manual_seed(0)
+    PQ = torch.randn((N, 2 * pk.Kp), generator=g, device=dev) * 0.5
+    out = torch.empty((N, pk.b), dtype=torch.float32, device=dev)
+    coords = torch.empty((N, 3), dtype=torch.float32, device=dev)
+    ell = ops.knn_graph_ell(x, cv["k"], ptr, [0, 1, 2])
+    slots = _slots(cv["k"])
+
+    def run():
+        ops.tc_edge_mlp_aggregate_f32(PQ[:, :pk.Kp], PQ[:, pk.Kp:], pk.Kp, ell, slots, cv["W2hi"],
+                                      cv["W2lo"], pk.b, out, coords, [0, 1, 2])
+    for _ in range(3):
+        run()
+    s = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+    e = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+    for i in range(reps):
+        flush_buf.fill_(i)
+        s[i].record()
+        run()
+        e[i].record()
+    torch.cuda.synchronize(dev)
+    ms = sum(a.elapsed_time(b_) for a, b_ in zip(s, e)) / reps
+    executed = 3 * 2.0 * (N * slots) * pk.Kp * pk.b16     # three MMAs per K step
+    name = (f"gn::tc::edge_mlp_aggregate_x3_kernel<{slots},false> (fp32 P / Q / out; three "
+            "tcgen05.mma.cta_group::2 kind::f16 per K step on fp16 (hi, lo) operand pairs)")
+    return ms, executed, name
