@@ -2,7 +2,7 @@
 ncu launch list (cold caches, serialised) these are the times the kernels take inside the running
 step, with the caches in the state the previous kernel left them.
 
-    python tools/insitu_kernels.py [events] [mean_pulses] [precision]
+    python tools/insitu_kernels.py [events] [mean_pulses] [precision] [c2|c4]
 """
 import collections
 import os
@@ -18,12 +18,15 @@ from graphnet_b200.synthetic import make_pulse_batch  # noqa: E402
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 mean = float(sys.argv[2]) if len(sys.argv) > 2 else 60.0
 prec = sys.argv[3] if len(sys.argv) > 3 else "bf16"
+c4 = len(sys.argv) > 4 and sys.argv[4] == "c4"
+k = 16 if c4 else 8
 dev = torch.device("cuda:0")
-pb = make_pulse_batch(B, mean, seed=1234)
+pb = make_pulse_batch(B, mean, seed=1234, detector="upgrade" if c4 else "icecube86")
 x, batch, npulse = pb.x.to(dev), pb.batch.to(dev), pb.n_pulses.to(dev)
-ei = g.knn_graph(x[:, :3].contiguous(), 8, batch, num_events=B)
+ei = g.knn_graph(x[:, :3].contiguous(), k, batch, num_events=B)
 torch.manual_seed(0)
-m = g.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision=prec).to(dev).eval()
+pools = ["min", "max", "mean"] if c4 else ["min", "max", "mean", "sum"]
+m = g.DynEdge(x.shape[1], nb_neighbours=k, global_pooling_schemes=pools, precision=prec).to(dev).eval()
 m.validate_inputs = False
 data = g.Data(x=x, edge_index=ei, batch=batch, n_pulses=npulse)
 for _ in range(10):
