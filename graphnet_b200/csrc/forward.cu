@@ -8,7 +8,10 @@
 // costs ~0.56 ms of host time per forward (~45 launches through ctypes, ~30 torch.empty calls),
 // which is no less than the kernels themselves take on a B200 (0.64 ms at C2) - the step followed
 // the host.  From C++ the pass is enqueued in ~0.1 ms.
+#include <stdlib.h>
 #include <string.h>
+
+#include <mutex>
 
 #include "common.cuh"
 
@@ -103,11 +106,12 @@ extern "C" size_t gn_dynedge_infer16_workspace(const gn_dynedge_plan* plan, int6
   return b.total;
 }
 
-extern "C" int gn_dynedge_infer16(const gn_dynedge_plan* pl, const float* x, int64_t ldx,
-                                  const int64_t* batch, const int32_t* n_pulses, int64_t N,
-                                  int64_t B, const int64_t* edge_index, int64_t E, void* workspace,
-                                  size_t workspace_bytes, float* out, int64_t ldo, int32_t* flags,
-                                  void* stream) {
+// every launch of the forward, in order, on `stream`
+static int enqueue_forward(const gn_dynedge_plan* pl, const float* x, int64_t ldx,
+                           const int64_t* batch, const int32_t* n_pulses, int64_t N, int64_t B,
+                           const int64_t* edge_index, int64_t E, void* workspace,
+                           size_t workspace_bytes, float* out, int64_t ldo, int32_t* flags,
+                           void* stream) {
   GN_CHECK_ARG(pl && x && batch && n_pulses && out && flags && workspace,
                "gn_dynedge_infer16: null pointer");
   GN_CHECK_ARG(pl->n_conv >= 1 && pl->n_conv <= GN_MAX_LAYERS && pl->n_post >= 1 &&
@@ -221,5 +225,84 @@ extern "C" int gn_dynedge_infer16(const gn_dynedge_plan* pl, const float* x, int
                          GN_F32, B, ro.n, ro.K, ro.act, stream));
   }
 #undef GN_TRY
+  return GN_OK;
+}
+
+// The launches above leave ~2 us of idle GPU between consecutive kernels (58 us of a 0.67 ms step at
+// C2).  A CUDA graph removes those gaps, but a captured graph is only good for the shapes and
+// pointers it was captured with, and a batch of events has a different N every time.  So every
+// call CAPTURES the launch sequence (on a private stream: nothing runs, and the caller's stream may
+// be the legacy default stream, which cannot capture) and folds it into the cached executable
+// graph with cudaGraphExecUpdate - same topology, new kernel parameters, grids and memset sizes -
+// then launches that on the caller's stream.  A change of topology (another model, edge_index
+// present or not) re-instantiates.  GN_NO_GRAPH=1, or a caller stream that is itself capturing:
+// direct launches.
+namespace {
+struct GraphCache {
+  std::mutex mu;
+  cudaStream_t cap = nullptr;
+  cudaGraphExec_t exec = nullptr;
+};
+GraphCache g_graphs[64];
+}  // namespace
+
+extern "C" int gn_dynedge_infer16(const gn_dynedge_plan* pl, const float* x, int64_t ldx,
+                                  const int64_t* batch, const int32_t* n_pulses, int64_t N,
+                                  int64_t B, const int64_t* edge_index, int64_t E, void* workspace,
+                                  size_t workspace_bytes, float* out, int64_t ldo, int32_t* flags,
+                                  void* stream) {
+  static const bool no_graph = getenv("GN_NO_GRAPH") != nullptr;
+  cudaStream_t st = as_stream(stream);
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (!no_graph) GN_CUDA(cudaStreamIsCapturing(st, &cs));
+  if (no_graph || cs != cudaStreamCaptureStatusNone)
+    return enqueue_forward(pl, x, ldx, batch, n_pulses, N, B, edge_index, E, workspace,
+                           workspace_bytes, out, ldo, flags, stream);
+  int dev = 0;
+  GN_CUDA(cudaGetDevice(&dev));
+  GraphCache& gc = g_graphs[dev & 63];
+  std::lock_guard<std::mutex> lock(gc.mu);
+  if (gc.cap == nullptr) GN_CUDA(cudaStreamCreateWithFlags(&gc.cap, cudaStreamNonBlocking));
+  GN_CUDA(cudaStreamBeginCapture(gc.cap, cudaStreamCaptureModeThreadLocal));
+  const int rc = enqueue_forward(pl, x, ldx, batch, n_pulses, N, B, edge_index, E, workspace,
+                                 workspace_bytes, out, ldo, flags, gc.cap);
+  cudaGraph_t graph = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture(gc.cap, &graph);
+  if (rc == GN_ERR_INVALID_ARGUMENT || rc == GN_ERR_UNSUPPORTED) {   // the message is already set
+    if (graph) cudaGraphDestroy(graph);
+    (void)cudaGetLastError();
+    return rc;
+  }
+  if (rc != GN_OK || ce != cudaSuccess || graph == nullptr) {
+    // something in the sequence cannot be captured here (e.g. the first launch of a kernel the
+    // driver has not loaded yet): run this call directly - it also serves as the warm-up
+    if (graph) cudaGraphDestroy(graph);
+    (void)cudaGetLastError();
+    return enqueue_forward(pl, x, ldx, batch, n_pulses, N, B, edge_index, E, workspace,
+                           workspace_bytes, out, ldo, flags, stream);
+  }
+  if (gc.exec != nullptr) {
+    cudaGraphExecUpdateResultInfo info;
+    if (cudaGraphExecUpdate(gc.exec, graph, &info) != cudaSuccess) {
+      (void)cudaGetLastError();          // another topology: build a new executable graph
+      cudaGraphExecDestroy(gc.exec);
+      gc.exec = nullptr;
+    }
+  }
+  if (gc.exec == nullptr) {
+    const cudaError_t ie = cudaGraphInstantiate(&gc.exec, graph, 0);
+    if (ie != cudaSuccess) {
+      cudaGraphDestroy(graph);
+      gc.exec = nullptr;
+      set_error("gn_dynedge_infer16: cudaGraphInstantiate failed: %s", cudaGetErrorString(ie));
+      return GN_ERR_CUDA;
+    }
+  }
+  const cudaError_t le = cudaGraphLaunch(gc.exec, st);
+  cudaGraphDestroy(graph);
+  if (le != cudaSuccess) {
+    set_error("gn_dynedge_infer16: cudaGraphLaunch failed: %s", cudaGetErrorString(le));
+    return GN_ERR_CUDA;
+  }
   return GN_OK;
 }
