@@ -9,7 +9,7 @@ is testable) where torch_geometric is absent.
 
 from __future__ import annotations
 
-from typing import Any, Dict, Iterable, List
+from typing import Any, Dict, Iterable, List, Optional
 
 import torch
 from torch import Tensor
@@ -120,3 +120,48 @@ class DevicePrefetcher:
                 v.record_stream(cur)
         self._preload()
         return dev
+
+
+class ResultReader:
+    """Device -> host read of per-batch results, awaited ONE batch behind the launches.
+
+    `push(tensors)` copies the tensors of the batch just enqueued into pinned host buffers on the
+    current stream (asynchronously) and returns the host copies of the PREVIOUS batch, waiting
+    only for that batch's copy event: the host enqueues batch i+1 while the device still works on
+    batch i, instead of idling the device for the host's launch time after every blocking read.
+    `flush()` returns the last batch.  Two sets of pinned buffers are reused alternately: the
+    tensors a call returns stay valid until the next call but one.
+    """
+
+    def __init__(self) -> None:
+        self._slots: List[Optional[tuple]] = [None, None]   # (host tensors, event)
+        self._i = 0
+        self._pending: Optional[int] = None
+
+    def _host_like(self, slot: int, tensors: List[Tensor]) -> List[Tensor]:
+        cur = self._slots[slot]
+        if cur is not None and len(cur[0]) == len(tensors) and all(
+                h.shape == t.shape and h.dtype == t.dtype for h, t in zip(cur[0], tensors)):
+            return cur[0]
+        return [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in tensors]
+
+    def _take(self, slot: int) -> List[Tensor]:
+        host, event = self._slots[slot]
+        event.synchronize()
+        return host
+
+    def push(self, tensors: List[Tensor]) -> Optional[List[Tensor]]:
+        slot = self._i & 1
+        host = self._host_like(slot, tensors)
+        for h, t in zip(host, tensors):
+            h.copy_(t, non_blocking=True)
+        event = torch.cuda.Event()
+        event.record()
+        self._slots[slot] = (host, event)
+        prev, self._pending = self._pending, slot
+        self._i += 1
+        return None if prev is None else self._take(prev)
+
+    def flush(self) -> Optional[List[Tensor]]:
+        prev, self._pending = self._pending, None
+        return None if prev is None else self._take(prev)

@@ -128,3 +128,23 @@ class StandardModel(torch.nn.Module):
         self.train(False)
         per_batch = [self(b) for b in batches]
         return [torch.cat([pb[i] for pb in per_batch], dim=0) for i in range(len(self._tasks))]
+
+    def predict_to_host(self, host_batches: Iterable[Any], device: Any) -> List[Tensor]:
+        """`predict` for a stream of HOST batches (pinned memory), results on the host: the copy
+        of batch i+1 runs under batch i's kernels (`DevicePrefetcher`) and the read of batch i's
+        predictions is awaited after batch i+1 has been enqueued (`ResultReader`) - the device
+        never waits for the host between batches.  Same values as `predict`."""
+        from .data import DevicePrefetcher, ResultReader
+        self.inference()
+        self.train(False)
+        reader = ResultReader()
+        outs: List[List[Tensor]] = []
+        with torch.no_grad():
+            for b in DevicePrefetcher(host_batches, device):
+                done = reader.push(self(b))
+                if done is not None:
+                    outs.append([t.clone() for t in done])
+            done = reader.flush()
+            if done is not None:
+                outs.append([t.clone() for t in done])
+        return [torch.cat([o[i] for o in outs], dim=0) for i in range(len(self._tasks))]

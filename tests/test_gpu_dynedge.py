@@ -180,3 +180,24 @@ def test_knngraph_collate_then_forward():
     # single-event call path of the reference (graph_definition.py:127-137)
     one = kg(events[2], FEATURES_ICECUBE86)
     assert torch.equal(one.edge_index.cpu(), oracle.knn_graph(one.x.cpu()[:, :3], 8, None))
+
+
+def test_predict_to_host_equals_predict():
+    """The pipelined host loop (prefetched copies, results read one batch behind) returns what
+    `predict` computes on device batches."""
+    import graphnet_b200 as gb
+    from graphnet_b200.synthetic import make_pulse_batch
+    torch.manual_seed(3)
+    backbone = gb.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision="bf16")
+    task = gb.EnergyReconstruction(hidden_size=backbone.nb_outputs, target_labels="energy",
+                                   loss_function=gb.LogCoshLoss())
+    model = gb.StandardModel(tasks=[task], graph_definition=object(), gnn=backbone).to(DEV)
+    host = []
+    for seed in range(5):
+        pb = make_pulse_batch(12 + seed, 25.0, seed=seed)
+        host.append(gb.Data(x=pb.x.pin_memory(), batch=pb.batch.pin_memory(),
+                            n_pulses=pb.n_pulses.pin_memory()))
+    want = model.predict([h.to(DEV) for h in host])
+    got = model.predict_to_host(host, DEV)
+    assert len(got) == 1 and got[0].device.type == "cpu"
+    assert torch.equal(got[0], want[0].cpu())
