@@ -43,7 +43,8 @@ struct EdgeParams {
   int64_t ldq;
   int Kp;                   // padded hidden width, multiple of 32
   int nch;                  // Kp / 32
-  const int32_t* ell;       // [groups, KP] neighbour ids, -1 = empty slot
+  const int32_t* ell;       // [groups, ell_ld] neighbour ids (the first KP of a row are used), -1 = empty slot
+  int64_t ell_ld;
   const int32_t* group_node;  // target node of each group, or null: group g is node g
   const int32_t* group_count; // device int: number of groups, or null: N groups
   int64_t group_cap;          // capacity of the group lists (a malformed graph can count past it)
@@ -127,6 +128,30 @@ __global__ void graph_to_groups_kernel(GraphView g, int64_t N, int KP, int32_t* 
   }
 }
 
+// Slot table with MORE entries per row than the kernel's slot count (a kNN graph, stride k + 1, run
+// with KP = k slots: a row holds k + 1 neighbours only where more than k points coincide with the
+// query, so nearly every tile row carries an edge instead of 1 in k + 1 staying empty): the table is
+// read in place, and the entries beyond KP go to the overflow group list.
+__global__ void ell_overflow_kernel(const int32_t* __restrict__ nbr, int32_t stride,
+                                    const int32_t* __restrict__ deg, int64_t N, int KP,
+                                    int32_t* __restrict__ ovf_node, int32_t* __restrict__ ovf_ell,
+                                    int32_t* __restrict__ ovf_count, int64_t ovf_cap) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const int cnt = min(max(deg[i], 0), stride);
+  if (cnt <= KP) return;
+  const int extra = (cnt - 1) / KP;
+  const int base = atomicAdd(ovf_count, extra);
+  for (int e = 0; e < extra; ++e) {
+    if (base + e >= ovf_cap) break;
+    ovf_node[base + e] = (int32_t)i;
+    for (int t = 0; t < KP; ++t) {
+      const int slot = (e + 1) * KP + t;
+      ovf_ell[(int64_t)(base + e) * KP + t] = slot < cnt ? nbr[i * stride + slot] : -1;
+    }
+  }
+}
+
 }  // namespace tc
 }  // namespace gn
 
@@ -181,19 +206,69 @@ static __device__ __align__(16) const uint32_t g_neg_inf_row32[352] = {
 #undef GN_NF16
 #undef GN_NF64
 
-// an ELL graph whose stride is a supported slot count is consumed in place: no lists, no 2nd pass
+// How the kernels get at a graph's in-edges:
+//   EDGE_DIRECT   an ELL graph whose stride is a supported slot count, run with that many slots:
+//                 consumed in place, no lists, no second pass;
+//   EDGE_INPLACE  an ELL graph run with FEWER slots than its stride: the first `slots` entries of
+//                 every row in place, the rest through the overflow list (ell_overflow_kernel);
+//   EDGE_GROUPS   anything else (CSR, odd strides): graph_to_groups_kernel copies the rows.
+enum EdgeMode { EDGE_DIRECT, EDGE_INPLACE, EDGE_GROUPS };
 static bool edge_supported_slots(int s) { return s == 8 || s == 9 || s == 16 || s == 17 || s == 32; }
-static bool edge_direct_ell(const gn_graph* graph) {
-  return graph->ell_stride > 0 && edge_supported_slots(graph->ell_stride);
+static EdgeMode edge_mode(const gn_graph* graph, int slots) {
+  if (graph->ell_stride > slots && edge_supported_slots(slots)) return EDGE_INPLACE;
+  if (graph->ell_stride > 0 && edge_supported_slots(graph->ell_stride)) return EDGE_DIRECT;
+  return EDGE_GROUPS;
 }
 
 extern "C" size_t gn_tc_edge_scratch_bytes(const gn_graph* graph, int64_t N, int slots) {
   if (!graph || slots <= 0) return 0;
-  if (edge_direct_ell(graph)) return 16;
+  const EdgeMode mode = edge_mode(graph, slots);
+  if (mode == EDGE_DIRECT) return 16;
   const int64_t n = N > 0 ? N : 1;
   const int64_t cap = edge_overflow_cap(graph, n, slots);
-  // ell [N, slots] + ovf_ell [cap, slots] + ovf_node [cap] + counter (16-byte padded)
-  return (size_t)(n * slots + cap * slots + cap + 4) * sizeof(int32_t);
+  // [ell [N, slots]] + ovf_ell [cap, slots] + ovf_node [cap] + counter (16-byte padded)
+  return (size_t)((mode == EDGE_GROUPS ? n * slots : 0) + cap * slots + cap + 4) * sizeof(int32_t);
+}
+
+// the group lists of one call, carved from the caller's scratch and filled on `st`
+struct EdgeLists {
+  EdgeMode mode;
+  int slots;                 // slots the kernels run with
+  const int32_t* ell;        // pass 1: [N, ell_ld]
+  int64_t ell_ld;
+  int32_t *ovf_ell, *ovf_node, *ovf_count;
+  int64_t cap;
+};
+static int edge_prepare_lists(const gn_graph* graph, const GraphView& g, int64_t N, int slots,
+                              void* scratch, cudaStream_t st, EdgeLists* L) {
+  L->mode = edge_mode(graph, slots);
+  L->slots = L->mode == EDGE_DIRECT ? graph->ell_stride : slots;
+  L->cap = L->mode == EDGE_DIRECT ? 0 : edge_overflow_cap(graph, N, slots);
+  int32_t* base = reinterpret_cast<int32_t*>(scratch);
+  int32_t* ell_copy = base;
+  L->ovf_ell = base + (L->mode == EDGE_GROUPS ? N * slots : 0);
+  L->ovf_node = L->ovf_ell + L->cap * slots;
+  L->ovf_count = L->ovf_node + L->cap;
+  if (L->mode == EDGE_GROUPS) {
+    L->ell = ell_copy;
+    L->ell_ld = slots;
+    GN_CUDA(cudaMemsetAsync(L->ovf_count, 0, sizeof(int32_t), st));
+    tc::graph_to_groups_kernel<<<(unsigned)ceil_div(N * slots, 256), 256, 0, st>>>(
+        g, N, slots, ell_copy, L->ovf_node, L->ovf_ell, L->ovf_count, L->cap);
+    GN_LAUNCH_CHECK();
+  } else {
+    L->ell = graph->col;
+    L->ell_ld = graph->ell_stride;
+    if (L->mode == EDGE_INPLACE) {
+      GN_CHECK_ARG(graph->deg != nullptr, "gn_tc_edge_mlp_aggregate: ELL graph without deg");
+      GN_CUDA(cudaMemsetAsync(L->ovf_count, 0, sizeof(int32_t), st));
+      tc::ell_overflow_kernel<<<(unsigned)ceil_div(N, 256), 256, 0, st>>>(
+          graph->col, graph->ell_stride, graph->deg, N, slots, L->ovf_node, L->ovf_ell,
+          L->ovf_count, L->cap);
+      GN_LAUNCH_CHECK();
+    }
+  }
+  return GN_OK;
 }
 
 extern "C" int64_t gn_tc_edge_relu_mask_ld(int64_t N, int slots) {
@@ -247,7 +322,11 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
                  "gn_tc_edge_mlp_aggregate: coordinate columns must be strictly increasing");
     p.coord_mask[coord_cols[t] >> 5] |= 1u << (coord_cols[t] & 31);
   }
-  const bool direct = edge_direct_ell(graph);
+  if (relu_mask != nullptr || aggr != GN_AGGR_ADD) {
+    // every in-edge of a node in ONE row of slots: run with the table's own stride
+    if (graph->ell_stride > 0 && edge_supported_slots(graph->ell_stride)) slots = graph->ell_stride;
+  }
+  const bool direct = edge_mode(graph, slots) == EDGE_DIRECT;
   if (direct) slots = graph->ell_stride;
   if (relu_mask != nullptr) {
     if (!direct) {
@@ -258,17 +337,10 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
     GN_CHECK_ARG(mask_ld >= gn_tc_edge_relu_mask_ld(N, slots),
                  "gn_tc_edge_mlp_aggregate_mask: mask_ld=%lld too small", (long long)mask_ld);
   }
-  const int64_t cap = direct ? 0 : edge_overflow_cap(graph, N, slots);
-  int32_t* ell = reinterpret_cast<int32_t*>(scratch);
-  int32_t* ovf_ell = ell + N * slots;
-  int32_t* ovf_node = ovf_ell + cap * slots;
-  int32_t* ovf_count = ovf_node + cap;
-  if (!direct) {
-    GN_CUDA(cudaMemsetAsync(ovf_count, 0, sizeof(int32_t), st));
-    tc::graph_to_groups_kernel<<<(unsigned)ceil_div(N * slots, 256), 256, 0, st>>>(
-        g, N, slots, ell, ovf_node, ovf_ell, ovf_count, cap);
-    GN_LAUNCH_CHECK();
-  }
+  EdgeLists L;
+  rc = edge_prepare_lists(graph, g, N, slots, scratch, st, &L);
+  if (rc != GN_OK) return rc;
+  const int64_t cap = L.cap;
 
   p.w2 = W2p;
   p.act = act;
@@ -333,16 +405,18 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
   for (int pass = 0; pass < 2; ++pass) {
     int64_t max_tiles;
     if (pass == 0) {
-      p.ell = direct ? graph->col : ell;
+      p.ell = L.ell;
+      p.ell_ld = L.ell_ld;
       p.group_node = nullptr;
       p.group_count = nullptr;
       p.accumulate = 0;
       max_tiles = ceil_div(N, npt);
     } else {
       if (cap <= 0) break;
-      p.ell = ovf_ell;
-      p.group_node = ovf_node;
-      p.group_count = ovf_count;
+      p.ell = L.ovf_ell;
+      p.ell_ld = slots;
+      p.group_node = L.ovf_node;
+      p.group_count = L.ovf_count;
       p.group_cap = cap;
       p.accumulate = 1;
       max_tiles = ceil_div(cap, npt);
@@ -427,19 +501,11 @@ extern "C" int gn_tc_edge_mlp_aggregate_f32(const float* P, int64_t ldp, const f
                  "gn_tc_edge_mlp_aggregate_f32: coordinate columns must be strictly increasing");
     p.coord_mask[coord_cols[t] >> 5] |= 1u << (coord_cols[t] & 31);
   }
-  const bool direct = edge_direct_ell(graph);
-  if (direct) slots = graph->ell_stride;
-  const int64_t cap = direct ? 0 : edge_overflow_cap(graph, N, slots);
-  int32_t* ell = reinterpret_cast<int32_t*>(scratch);
-  int32_t* ovf_ell = ell + N * slots;
-  int32_t* ovf_node = ovf_ell + cap * slots;
-  int32_t* ovf_count = ovf_node + cap;
-  if (!direct) {
-    GN_CUDA(cudaMemsetAsync(ovf_count, 0, sizeof(int32_t), st));
-    tc::graph_to_groups_kernel<<<(unsigned)ceil_div(N * slots, 256), 256, 0, st>>>(
-        g, N, slots, ell, ovf_node, ovf_ell, ovf_count, cap);
-    GN_LAUNCH_CHECK();
-  }
+  EdgeLists L;
+  rc = edge_prepare_lists(graph, g, N, slots, scratch, st, &L);
+  if (rc != GN_OK) return rc;
+  slots = L.slots;
+  const int64_t cap = L.cap;
   p.w2 = W2hi;
   p.w2lo = W2lo;
   p.act = GN_ACT_RELU;
@@ -475,16 +541,18 @@ extern "C" int gn_tc_edge_mlp_aggregate_f32(const float* P, int64_t ldp, const f
   for (int pass = 0; pass < 2; ++pass) {
     int64_t max_tiles;
     if (pass == 0) {
-      p.ell = direct ? graph->col : ell;
+      p.ell = L.ell;
+      p.ell_ld = L.ell_ld;
       p.group_node = nullptr;
       p.group_count = nullptr;
       p.accumulate = 0;
       max_tiles = ceil_div(N, npt);
     } else {
       if (cap <= 0) break;
-      p.ell = ovf_ell;
-      p.group_node = ovf_node;
-      p.group_count = ovf_count;
+      p.ell = L.ovf_ell;
+      p.ell_ld = slots;
+      p.group_node = L.ovf_node;
+      p.group_count = L.ovf_count;
       p.group_cap = cap;
       p.accumulate = 1;
       max_tiles = ceil_div(cap, npt);

@@ -358,7 +358,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(E4_THREADS, 1)
       else { nn = t_ - NPT; sl = lane; }
       const int64_t grp = tile * NPT + nn;
       if (nn < NPT && grp < num_groups) {
-        if (sl < KP) j_nx = e4_ldg32(p.ell + grp * KP + sl);
+        if (sl < KP) j_nx = e4_ldg32(p.ell + grp * p.ell_ld + sl);
         n_nx = p.group_node ? e4_ldg32(p.group_node + grp) : (int32_t)grp;
       }
     };

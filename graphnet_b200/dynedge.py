@@ -440,6 +440,9 @@ class DynEdge(torch.nn.Module):
     # (dynedge_x3.py; fp32 inputs, weights, accumulation and outputs).  False: the FFMA kernels,
     # the parity anchor (plain fp32 arithmetic in the reference's order of operations)
     fp32_tensor_cores: bool = True
+    # 16-bit inference: run the edge kernel with k slots per node instead of k + 1 (see
+    # dynedge_bf16._slots_min: pays off only where coincident kNN coordinates are rare)
+    min_edge_slots: bool = False
     _last_flags: Optional[Tensor] = None
     # k of the input graph built on the device when a batch carries no `edge_index`
     # (None: the model's nb_neighbours, the pairing every reference example uses)

@@ -38,6 +38,20 @@ def _slots(k: int) -> int:
     return 32
 
 
+def _slots_min(k: int) -> int:
+    """`DynEdge.min_edge_slots = True` (inference, aggr='add'): the smallest supported slot count
+    >= k.  A kNN row holds k + 1 neighbours only where more than k points coincide with the query;
+    those entries go through the kernel's overflow pass and every tile row carries an edge (k = 16:
+    4 nodes per 64-row tile instead of 3, k = 8: 8 instead of 7).  Measured at C2 / C4: the main
+    pass gets 7 % / 25 % shorter, but a layer whose kNN columns are tied for most nodes (ReLU-dead
+    coordinate columns of a randomly initialised model: 59 % of the nodes of one C2 layer) pays
+    4 x for its overflow pass - off by default."""
+    for s in (8, 9, 16, 17, 32):
+        if s >= k:
+            return s
+    return 32
+
+
 class _ConvPack:
     """Repacked weights of one DynEdgeConv MLP for the tensor-core kernels."""
 
@@ -184,7 +198,8 @@ class _NativePlan:
             c = plan.conv[li]
             c.Wpq, c.bias_pq, c.W2p = W.data_ptr(), pk.bias_pq.data_ptr(), pk.W2p.data_ptr()
             c.d_in, c.Kp, c.b, c.k = d_in, pk.Kp, pk.b, conv.nb_neighbors
-            c.slots, c.act = _slots(conv.nb_neighbors), ops.ACT[pk.act]
+            c.slots = (_slots_min if model.min_edge_slots else _slots)(conv.nb_neighbors)
+            c.act = ops.ACT[pk.act]
             c.off_in, c.off_out, c.ncoord, c.ldw = off_in, offs[li], len(cols), W.stride(0)
             for t, col in enumerate(cols):
                 c.coord_cols[t] = col
@@ -218,7 +233,7 @@ class _NativePlan:
 def _native_plan(model, io: torch.dtype):
     """The cached plan, or None when the model is outside what csrc/forward.cu drives (the Python
     sequence below then runs the same kernels one call at a time)."""
-    key = f"_cache_native_{io}"
+    key = f"_cache_native_{io}_{int(model.min_edge_slots)}"
     cache = model.__dict__.get(key)
     if cache is None:
         cache = _WeightCache()
@@ -352,7 +367,8 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
             ops.linear_f32(x0, pk.Wpq, pk.bias_pq, act="none", out=PQ)
         else:
             ops.tc_linear_bf16(skip[:, off_in:], pk.Wpq, pk.bias_pq, PQ, K=d_in, act="none")
-        slots = _slots(conv.nb_neighbors)
+        slots = _slots_min(conv.nb_neighbors) if (model.min_edge_slots and save is None
+                                                  and aggr == "add") else _slots(conv.nb_neighbors)
         relu_mask = None
         if save is not None:
             if graph.ell_stride <= 0 and graph.max_degree is not None and \
@@ -474,7 +490,7 @@ def time_edge_kernel(model, data: Any, flush_buf: Tensor, layer: int = 1, reps: 
     out = torch.empty((N, pk.b), dtype=_io_dtype(model), device=dev)
     coords = torch.empty((N, 3), dtype=torch.float32, device=dev)
     ell = ops.knn_graph_ell(x, conv.nb_neighbors, ptr, [0, 1, 2])
-    slots = _slots(conv.nb_neighbors)
+    slots = (_slots_min if model.min_edge_slots else _slots)(conv.nb_neighbors)
 
     def run():
         ops.tc_edge_mlp_aggregate(P, Q, pk.Kp, ell, slots, pk.W2p, pk.b, out, coords, [0, 1, 2])

@@ -98,10 +98,15 @@ def _edge_reference(pq, Kp, ei, W2p, b, N):
     return torch.zeros(N, b).index_add_(0, dst, msg)
 
 
+@pytest.mark.parametrize("min_slots", [False, True])
 @pytest.mark.parametrize("k,a,b", [(8, 336, 256), (8, 128, 256), (16, 336, 256), (4, 40, 48), (8, 62, 256)])
-def test_tc_edge_mlp_aggregate(k, a, b):
+def test_tc_edge_mlp_aggregate(k, a, b, min_slots):
+    """min_slots: k slots for a table of stride k + 1 (read in place, the k+1-th neighbours of
+    coincident pulses through the overflow pass) - how the inference forward runs it."""
     import graphnet_b200.ops as ops
-    from graphnet_b200.dynedge_bf16 import _slots, _round_up
+    from graphnet_b200.dynedge_bf16 import _slots_min, _round_up
+    from graphnet_b200.dynedge_bf16 import _slots as _slots_full
+    _slots = _slots_min if min_slots else _slots_full
     x, batch, _ = random_events(40, 1, 70, seed=k + a)
     # one more event of 40 coincident pulses: its later nodes keep k+1 in-edges (overflow path)
     stack = torch.randn(40, x.shape[1])
@@ -367,3 +372,19 @@ def test_native_driver_declines_what_it_does_not_drive():
         x, batch, counts = random_events(5, 3, 30, seed=1)
         out = m(gb.Data(x=x.to(DEV), batch=batch.to(DEV), n_pulses=counts.to(DEV)))
         assert torch.isfinite(out).all()
+
+
+def test_min_edge_slots_gives_the_same_forward():
+    """k slots + overflow pass instead of k + 1 slots: same sums up to the 16-bit rounding of the
+    one extra add an overflowing node gets."""
+    import graphnet_b200 as gb
+    x, batch, counts = random_events(30, 1, 80, seed=11)
+    torch.manual_seed(2)
+    m = gb.DynEdge(7, global_pooling_schemes=["max", "sum"], precision="bf16").to(DEV).eval()
+    data = gb.Data(x=x.to(DEV), batch=batch.to(DEV), n_pulses=counts.to(DEV))
+    want = m(data)
+    m.min_edge_slots = True
+    got = m(data)
+    assert rel_l2(got, want) < 1e-2
+    m.native_driver = False
+    assert torch.equal(m(data), got)

@@ -18,10 +18,13 @@ def _w2_pair(W2p32):
     return hi.contiguous(), lo.contiguous()
 
 
+@pytest.mark.parametrize("min_slots", [False, True])
 @pytest.mark.parametrize("k,a,b", [(8, 336, 256), (8, 128, 256), (16, 336, 256), (4, 40, 48), (8, 62, 130)])
-def test_tc_edge_mlp_aggregate_f32(k, a, b):
+def test_tc_edge_mlp_aggregate_f32(k, a, b, min_slots):
     import graphnet_b200.ops as ops
-    from graphnet_b200.dynedge_bf16 import _slots, _round_up
+    from graphnet_b200.dynedge_bf16 import _slots_min, _round_up
+    from graphnet_b200.dynedge_bf16 import _slots as _slots_full
+    _slots = _slots_min if min_slots else _slots_full
     x, batch, _ = random_events(40, 1, 70, seed=k + a)
     stack = torch.randn(40, x.shape[1])   # 40 coincident pulses: k+1 in-edges (overflow groups)
     stack[:, :3] = 0.125
