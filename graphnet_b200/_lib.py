@@ -99,6 +99,7 @@ SIGNATURES = {
     "gn_tc_edge_mlp_aggregate_f32": (_int, [_p, _i64, _p, _i64, _int, _gp, _i64, _int, _p, _p, _int, _p,
                                             _i64, _p, _hp, _int, _p, _sz, _p]),
     "gn_split_bf16": (_int, [_p, _i64, _i64, _int, _int, _int, _p, _i64, _p]),
+    "gn_split_bf16_both": (_int, [_p, _i64, _i64, _int, _int, _p, _i64, _p, _i64, _p]),
     "gn_tc_linear_pool": (_int, [_p, _i64, _p, _i64, _int, _p, _i64, _int, _int, _p, _p, _i64, _p, _p]),
     "gn_pool_finalize": (_int, [_p, _p, _i64, _int, _hp, _int, _p, _i64, _p, _i64, C.c_float, _p]),
     "gn_linear_f32": (_int, [_p, _i64, _p, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),

@@ -238,10 +238,16 @@ static int enqueue_forward(const gn_dynedge_plan* pl, const float* x, int64_t ld
 // present or not) re-instantiates.  GN_NO_GRAPH=1, or a caller stream that is itself capturing:
 // direct launches.
 namespace {
+struct GraphSlot {
+  const void* plan = nullptr;     // key: the caller's plan object and whether it brings edges
+  bool has_edges = false;
+  cudaGraphExec_t exec = nullptr;
+};
 struct GraphCache {
   std::mutex mu;
   cudaStream_t cap = nullptr;
-  cudaGraphExec_t exec = nullptr;
+  GraphSlot slots[4];             // a few models per device, replaced round robin
+  int next = 0;
 };
 GraphCache g_graphs[64];
 }  // namespace
@@ -281,24 +287,35 @@ extern "C" int gn_dynedge_infer16(const gn_dynedge_plan* pl, const float* x, int
     return enqueue_forward(pl, x, ldx, batch, n_pulses, N, B, edge_index, E, workspace,
                            workspace_bytes, out, ldo, flags, stream);
   }
-  if (gc.exec != nullptr) {
+  GraphSlot* slot = nullptr;
+  for (GraphSlot& c : gc.slots)
+    if (c.exec != nullptr && c.plan == pl && c.has_edges == (edge_index != nullptr)) slot = &c;
+  if (slot == nullptr) {
+    slot = &gc.slots[gc.next];
+    gc.next = (gc.next + 1) % 4;
+    if (slot->exec != nullptr) cudaGraphExecDestroy(slot->exec);
+    slot->exec = nullptr;
+    slot->plan = pl;
+    slot->has_edges = edge_index != nullptr;
+  }
+  if (slot->exec != nullptr) {
     cudaGraphExecUpdateResultInfo info;
-    if (cudaGraphExecUpdate(gc.exec, graph, &info) != cudaSuccess) {
+    if (cudaGraphExecUpdate(slot->exec, graph, &info) != cudaSuccess) {
       (void)cudaGetLastError();          // another topology: build a new executable graph
-      cudaGraphExecDestroy(gc.exec);
-      gc.exec = nullptr;
+      cudaGraphExecDestroy(slot->exec);
+      slot->exec = nullptr;
     }
   }
-  if (gc.exec == nullptr) {
-    const cudaError_t ie = cudaGraphInstantiate(&gc.exec, graph, 0);
+  if (slot->exec == nullptr) {
+    const cudaError_t ie = cudaGraphInstantiate(&slot->exec, graph, 0);
     if (ie != cudaSuccess) {
       cudaGraphDestroy(graph);
-      gc.exec = nullptr;
+      slot->exec = nullptr;
       set_error("gn_dynedge_infer16: cudaGraphInstantiate failed: %s", cudaGetErrorString(ie));
       return GN_ERR_CUDA;
     }
   }
-  const cudaError_t le = cudaGraphLaunch(gc.exec, st);
+  const cudaError_t le = cudaGraphLaunch(slot->exec, st);
   cudaGraphDestroy(graph);
   if (le != cudaSuccess) {
     set_error("gn_dynedge_infer16: cudaGraphLaunch failed: %s", cudaGetErrorString(le));

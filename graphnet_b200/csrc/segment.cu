@@ -348,11 +348,14 @@ extern "C" int gn_global_variables(const float* x, int64_t ldx, int F, const gn_
 //   terms = 6: [x1 | x1 | x1 | x2 | x2 | x3] against [w1 | w2 | w3 | w1 | w2 | w1] (24 bits: every
 //              product term down to 2^-16 of the leading one)
 // Each block is kc columns wide, columns cols..kc-1 zero.
+// TERMS = 9: both layouts from one read (out: 3 terms, out6: 6 terms)
 template <int TERMS>
 __global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict__ X, int64_t ldx,
                                                          int64_t M, int cols, int kc,
                                                          __nv_bfloat16* __restrict__ out,
-                                                         int64_t ldo) {
+                                                         int64_t ldo,
+                                                         __nv_bfloat16* __restrict__ out6 = nullptr,
+                                                         int64_t ldo6 = 0) {
   const int q = kc >> 2;   // groups of 4 columns per row
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= M * q) return;
@@ -371,11 +374,13 @@ __global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict
   }
   __nv_bfloat16* o = out + r * ldo + c;
   const uint2 u1 = *reinterpret_cast<const uint2*>(x1), u2 = *reinterpret_cast<const uint2*>(x2);
-  if (TERMS == 3) {
+  if (TERMS == 3 || TERMS == 9) {
     *reinterpret_cast<uint2*>(o) = u1;
     *reinterpret_cast<uint2*>(o + kc) = u2;
     *reinterpret_cast<uint2*>(o + 2 * kc) = u1;
-  } else {
+    if (TERMS == 9) o = out6 + r * ldo6 + c;
+  }
+  if (TERMS == 6 || TERMS == 9) {
     *reinterpret_cast<uint2*>(o) = u1;
     *reinterpret_cast<uint2*>(o + kc) = u1;
     *reinterpret_cast<uint2*>(o + 2 * kc) = u1;
@@ -383,6 +388,25 @@ __global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict
     *reinterpret_cast<uint2*>(o + 4 * kc) = u2;
     *reinterpret_cast<uint2*>(o + 5 * kc) = *reinterpret_cast<const uint2*>(x3);
   }
+}
+
+extern "C" int gn_split_bf16_both(const float* X, int64_t ldx, int64_t M, int cols, int kc,
+                                  void* out3, int64_t ldo3, void* out6, int64_t ldo6,
+                                  void* stream) {
+  GN_CHECK_ARG(M >= 0 && cols >= 1 && kc >= cols && kc % 4 == 0 && ldx >= cols &&
+                   ldo3 >= 3 * (int64_t)kc && ldo3 % 4 == 0 && ldo6 >= 6 * (int64_t)kc &&
+                   ldo6 % 4 == 0,
+               "gn_split_bf16_both: bad sizes (kc and the leading dimensions must be multiples of 4)");
+  if (M == 0) return GN_OK;
+  GN_CHECK_ARG(X && out3 && out6 && (reinterpret_cast<uintptr_t>(out3) & 7) == 0 &&
+                   (reinterpret_cast<uintptr_t>(out6) & 7) == 0,
+               "gn_split_bf16_both: null or misaligned pointer");
+  const int64_t n = M * (kc / 4);
+  split_bf16_kernel<9><<<(unsigned)ceil_div(n, 256), 256, 0, as_stream(stream)>>>(
+      X, ldx, M, cols, kc, reinterpret_cast<__nv_bfloat16*>(out3), ldo3,
+      reinterpret_cast<__nv_bfloat16*>(out6), ldo6);
+  GN_LAUNCH_CHECK();
+  return GN_OK;
 }
 
 extern "C" int gn_split_bf16(const float* X, int64_t ldx, int64_t M, int cols, int kc, int terms,

@@ -140,9 +140,9 @@ def forward_f32_tc(model, data: Any, edge_index: Optional[Tensor] = None) -> Ten
     xl = torch.empty((N, x0w), dtype=torch.float32, device=dev)     # layer input, fp32
     ops.global_variables(x, graph, ptr, n_pulses, x0=S, x0_cols=x0w, x0b=xl, x0b_cols=x0w,
                          x0_split=True)
+    A6 = ops.split_bf16(xl, x0w, terms=6)
     for li, cv in enumerate(pack.convs):
         pk, kc = cv["pk"], cv["kc"]
-        A6 = ops.split_bf16(xl, kc, terms=6)
         PQ = torch.empty((N, 2 * pk.Kp), dtype=torch.float32, device=dev)
         ops.tc_linear_bf16(A6, cv["Wpq6"], pk.bias_pq, PQ, K=6 * kc, act="none")
         last = li + 1 == len(pack.convs)
@@ -151,8 +151,10 @@ def forward_f32_tc(model, data: Any, edge_index: Optional[Tensor] = None) -> Ten
         coords = None if last else torch.empty((N, len(cols)), dtype=torch.float32, device=dev)
         ops.tc_edge_mlp_aggregate_f32(PQ[:, :pk.Kp], PQ[:, pk.Kp:], pk.Kp, graph, _slots(cv["k"]),
                                       cv["W2hi"], cv["W2lo"], pk.b, xl, coords, cols)
-        ops.split_bf16(xl, _round_up(pk.b, 8), terms=3, out=S[:, 3 * offs[li]:])
-        if not last:
+        if last:
+            ops.split_bf16(xl, _round_up(pk.b, 8), terms=3, out=S[:, 3 * offs[li]:])
+        else:   # three terms for the post-processing MLP, six for the next node GEMM: one read
+            A6 = ops.split_bf16_both(xl, _round_up(pk.b, 8), S[:, 3 * offs[li]:])
             graph = ops.knn_graph_ell(coords, cv["k"], ptr, list(range(len(cols))))
     h16 = S
     pools = model._global_pooling_schemes if not model._skip_readout else None

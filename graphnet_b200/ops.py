@@ -476,6 +476,22 @@ def split_bf16(X: Tensor, kc: int, terms: int = 3, out: Optional[Tensor] = None)
     return out
 
 
+def split_bf16_both(X: Tensor, kc: int, out3: Tensor, out6: Optional[Tensor] = None) -> Tensor:
+    """Three-term pieces of X into `out3` and six-term pieces into `out6` (returned) from one read."""
+    dev = _require_cuda(X, out3, out6)
+    assert X.dtype == torch.float32 and X.stride(1) == 1 and kc % 4 == 0 and kc >= X.shape[1]
+    M, cols = X.shape
+    if out6 is None:
+        out6 = torch.empty((M, 6 * kc), dtype=torch.bfloat16, device=dev)
+    for o, t in ((out3, 3), (out6, 6)):
+        assert o.dtype == torch.bfloat16 and o.stride(1) == 1 and o.shape[1] >= t * kc
+    with _on(dev):
+        check(_lib.load().gn_split_bf16_both(_ptr(X), X.stride(0), M, cols, kc, _ptr(out3),
+                                             out3.stride(0), _ptr(out6), out6.stride(0),
+                                             _stream(dev)), "gn_split_bf16_both")
+    return out6
+
+
 def edgeconv_pack_tc(W1: Tensor, b1: Optional[Tensor], W2: Tensor, b2: Optional[Tensor], Kp: int,
                      Kd: int, wpq_dtype: torch.dtype, train: bool, act: str = "relu"):
     """(Wpq, bias_pq, W2p, W2b, W2bT, WpqT) for the tensor-core EdgeConv kernels from the

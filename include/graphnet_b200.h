@@ -322,6 +322,10 @@ int gn_tc_edge_mlp_aggregate_f32(const float* P, int64_t ldp, const float* Q, in
  * multiplies in fp32). */
 int gn_split_bf16(const float* X, int64_t ldx, int64_t M, int cols, int kc, int terms, void* out,
                   int64_t ldo, void* stream);
+/* Both layouts from one read of X: out3 as terms = 3, out6 as terms = 6 (a layer output feeds the
+ * post-processing MLP with three terms and the next layer's node GEMM with six). */
+int gn_split_bf16_both(const float* X, int64_t ldx, int64_t M, int cols, int kc, void* out3,
+                       int64_t ldo3, void* out6, int64_t ldo6, void* stream);
 
 /* Training forward of the same op: additionally records the ReLU pattern of the second Linear
  * (what torch autograd keeps as the saved output of the ReLU in PyG's EdgeConv.message,

@@ -165,3 +165,14 @@ def test_fp32_forward_on_tensor_cores_matches_the_ffma_anchor(with_edges, kw):
     else:                      # node-level output: rows of an event whose graph flipped differ
         err = (got - want).norm(dim=1) / want.norm(dim=1).clamp(min=1e-20)
         assert float(err.median()) < 3e-5, float(err.median())
+
+
+def test_split_bf16_both_equals_the_two_separate_layouts():
+    import graphnet_b200.ops as ops
+    X = torch.randn(501, 130, generator=torch.Generator().manual_seed(4)).to(DEV) * 7.0
+    kc = 136
+    out3 = torch.zeros(501, 3 * kc + 8, dtype=torch.bfloat16, device=DEV)
+    out6 = ops.split_bf16_both(X, kc, out3)
+    assert torch.equal(out3[:, :3 * kc], ops.split_bf16(X, kc, terms=3))
+    assert torch.equal(out6, ops.split_bf16(X, kc, terms=6))
+    assert bool((out3[:, 3 * kc:] == 0).all())
