@@ -870,6 +870,7 @@ static int launch_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
     case GN_ACT_NONE: GN_TC_LIN_CASE(ACT_NONE) break;
     case GN_ACT_RELU: GN_TC_LIN_CASE(ACT_RELU) break;
     case GN_ACT_GELU: GN_TC_LIN_CASE(ACT_GELU) break;
+    case GN_ACT_LEAKY_RELU: GN_TC_LIN_CASE(ACT_LEAKY_RELU) break;
     default: set_error("unknown activation %d", act); return GN_ERR_INVALID_ARGUMENT;
   }
 #undef GN_TC_LIN_CASE

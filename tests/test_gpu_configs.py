@@ -254,6 +254,32 @@ def test_dynedge_jinst_matches_reference_golden_and_oracle():
     assert float(per_event.median()) < 1e-4 and float(per_event.max()) < 5e-3, per_event
 
 
+@pytest.mark.parametrize("precision", ["bf16", "fp16"])
+def test_dynedge_jinst_on_the_tensor_cores(precision):
+    """DynEdgeJINST(precision="bf16" | "fp16"): LeakyReLU EdgeConv layers on the tcgen05 kernels,
+    against the golden of the reference's own dynedge_jinst.py and a larger oracle batch."""
+    import os
+    import numpy as np
+    import graphnet_b200 as gb
+    from oracle.dynedge_jinst import init_jinst_state_dict, jinst_forward
+    from graphnet_b200.synthetic import make_pulse_batch
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "oscnext5_jinst.npz"))
+    x, b, n, ei = (torch.from_numpy(z[k]) for k in ("x", "batch", "n_pulses", "edge_index"))
+    sd = init_jinst_state_dict(x.shape[1], 4, seed=int(z["seed"]))
+    m = gb.DynEdgeJINST(x.shape[1], precision=precision)
+    m.eval()
+    m.load_state_dict(sd)
+    m = m.to(DEV)
+    got = m(gb.Data(x=x.to(DEV), edge_index=ei.to(DEV), batch=b.to(DEV), n_pulses=n.to(DEV))).cpu()
+    assert rel_l2(got, torch.from_numpy(z["out"])) < 2e-2
+    pb = make_pulse_batch(24, 40.0, seed=90)
+    ei2 = oracle.knn_graph(pb.x[:, :3], 8, pb.batch)
+    want = jinst_forward(sd, pb.x, ei2, pb.batch, pb.n_pulses)
+    got2 = m(gb.Data(x=pb.x.to(DEV), edge_index=ei2.to(DEV), batch=pb.batch.to(DEV),
+                     n_pulses=pb.n_pulses.to(DEV))).cpu()
+    assert rel_l2(got2, want) < 2e-2
+
+
 def test_particlenet_matches_reference_golden_and_oracle():
     """ParticleNeT (gnn/particlenet.py) in eval mode - BatchNorm folded into the
     Linear layers, aggr="mean", 3-Linear EdgeConv MLPs, dynamic or static graphs - on the fp32
