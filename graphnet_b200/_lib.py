@@ -15,6 +15,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libgraphnet_b200.so")
 if os.environ.get("GN_B200_DEBUG_LIB"):   # profiling build (__graft_entry__.build_debug)
     LIB_PATH = os.path.join(_HERE, "csrc", "libgraphnet_b200_dbg.so")
+if os.environ.get("GN_B200_LIB"):         # an explicitly named build (A/B measurements)
+    LIB_PATH = os.environ["GN_B200_LIB"]
 
 GN_OK = 0
 ACT = {"none": 0, "relu": 1, "gelu": 2, "leaky_relu": 3}

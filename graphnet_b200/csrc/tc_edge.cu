@@ -307,6 +307,7 @@ static int tc_edge_mlp_aggregate_impl(const void* P, int64_t ldp, const void* Q,
                (reinterpret_cast<uintptr_t>(out) & 7) == 0 &&
                (reinterpret_cast<uintptr_t>(scratch) & 3) == 0,
                "gn_tc_edge_mlp_aggregate: P, Q must be 16-byte and out 8-byte aligned");
+  GN_CHECK_ARG(N * 33 < (int64_t)1 << 31, "gn_tc_edge_mlp_aggregate: N too large (32-bit slot offsets)");
   GraphView g;
   int rc = make_graph_view(graph, &g);
   if (rc != GN_OK) return rc;
@@ -488,6 +489,8 @@ extern "C" int gn_tc_edge_mlp_aggregate_f32(const float* P, int64_t ldp, const f
                (reinterpret_cast<uintptr_t>(W2lo) & 15) == 0 &&
                (reinterpret_cast<uintptr_t>(scratch) & 3) == 0,
                "gn_tc_edge_mlp_aggregate_f32: P, Q, W2 must be 16-byte aligned");
+  GN_CHECK_ARG(N * 33 < (int64_t)1 << 31,
+               "gn_tc_edge_mlp_aggregate_f32: N too large (32-bit slot offsets)");
   GraphView g;
   int rc = make_graph_view(graph, &g);
   if (rc != GN_OK) return rc;

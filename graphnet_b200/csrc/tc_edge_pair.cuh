@@ -358,7 +358,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(E4_THREADS, 1)
       else { nn = t_ - NPT; sl = lane; }
       const int64_t grp = tile * NPT + nn;
       if (nn < NPT && grp < num_groups) {
-        if (sl < KP) j_nx = e4_ldg32(p.ell + grp * p.ell_ld + sl);
+        // (32-bit offset: a table has fewer than 2^31 entries)
+        if (sl < KP) j_nx = e4_ldg32(p.ell + ((int32_t)grp * (int32_t)p.ell_ld + sl));
         n_nx = p.group_node ? e4_ldg32(p.group_node + grp) : (int32_t)grp;
       }
     };

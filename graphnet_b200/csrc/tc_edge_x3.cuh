@@ -184,7 +184,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(E4_THREADS, 1)
       const int64_t tile = 2 * (step0 + it_) + rank;
       const int64_t grp = tile * NPT + t_ / nblk;
       if (grp < num_groups) {
-        if (lane < KP) j_nx = e4_ldg32(p.ell + grp * p.ell_ld + lane);
+        if (lane < KP) j_nx = e4_ldg32(p.ell + ((int32_t)grp * (int32_t)p.ell_ld + lane));
         n_nx = p.group_node ? e4_ldg32(p.group_node + grp) : (int32_t)grp;
       }
     };

@@ -250,7 +250,11 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
   // L2->SM limit with the tensor pipe 27 % busy.
   uint8_t* w_res = smem;                                   // [nk_all][BN x 128 B] when wres
   uint8_t* ring = smem + (wres ? nk_all * b_bytes : 0);
-  const int stage_bytes = LIN_A_BYTES + (wres ? 0 : b_bytes);
+  // K blocks (64 columns) per ring stage: two when W is resident - half as many barrier
+  // hand-shakes per tile for the two single threads that pace the kernel
+  const int kpb = (int)(((uint32_t)cshape >> 16) & 0xffu);
+  const int kb_bytes = LIN_A_BYTES + (wres ? 0 : b_bytes);   // one K block of a stage
+  const int stage_bytes = kpb * kb_bytes;
   LinBarriers* bars = reinterpret_cast<LinBarriers*>(ring + stages * stage_bytes);
   float* s_bias = reinterpret_cast<float*>(bars + 1);  // [num_n_tiles * BN]
   uint8_t* s_scr = reinterpret_cast<uint8_t*>(s_bias + num_n_tiles * BN);  // one scratch per epilogue warp
@@ -262,7 +266,7 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
     s_bias[n] = (bias != nullptr && n < N) ? bias[n] : 0.f;
 
   // cluster of cn x cm CTAs (see LinPlan): rank = m_idx * cn + n_idx
-  const uint32_t cn = (uint32_t)cshape & 0xffu, cm = (uint32_t)cshape >> 8, csize = cn * cm;
+  const uint32_t cn = (uint32_t)cshape & 0xffu, cm = ((uint32_t)cshape >> 8) & 0xffu, csize = cn * cm;
   const uint32_t crank = blockIdx.x % csize;   // == %cluster_ctarank of a 1-D cluster
   const uint32_t n_idx = crank % cn, m_idx = crank / cn;
   // CTAs that receive the A parts this CTA loads (its cluster row) and the W parts (its column);
@@ -371,25 +375,29 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
         const int32_t m0 = (int32_t)(walk.mt * LIN_BM);
         const int32_t n0 = (int32_t)walk.nt * BN;
         stamp(i, 0);
-        for (int kb = kb0; kb < kb1; ++kb) {
+        for (int kb = kb0; kb < kb1; kb += kpb) {
+          const int nb = min(kpb, kb1 - kb);
           mbar_wait(&bars->empty[s], ph);
           if (kb == kb0) stamp(i, 1);
-          if (kb == kb1 - 1) stamp(i, 2);
-          const uint32_t a_dst = ring_a + s * (uint32_t)stage_bytes;
-          mbar_arrive_expect_tx(&bars->full[s], (uint32_t)stage_bytes);
+          if (kb + nb >= kb1) stamp(i, 2);
+          mbar_arrive_expect_tx(&bars->full[s], (uint32_t)(nb * kb_bytes));
           stage_stamp(0);
           ++gstage;
-          if (cn > 1)   // this CTA's 128 / cn rows of the A tile, into every CTA of its row
-            tma_load_2d_mc(a_dst + n_idx * a_part_bytes, &tmA, &bars->full[s], kb * LIN_BK,
-                           m0 + (int32_t)(n_idx * a_part_rows), mask_a);
-          else
-            tma_load_2d_a(a_dst, &tmA, &bars->full[s], kb * LIN_BK, m0);
-          if (!wres) {
-            if (cm > 1)
-              tma_load_2d_mc(a_dst + LIN_A_BYTES + m_idx * w_part_bytes, &tmW, &bars->full[s],
-                             kb * LIN_BK, n0 + (int32_t)(m_idx * w_part_rows), mask_w);
+          for (int j = 0; j < nb; ++j) {
+            const uint32_t a_dst = ring_a + s * (uint32_t)stage_bytes + (uint32_t)(j * kb_bytes);
+            const int32_t k0 = (kb + j) * LIN_BK;
+            if (cn > 1)   // this CTA's 128 / cn rows of the A tile, into every CTA of its row
+              tma_load_2d_mc(a_dst + n_idx * a_part_bytes, &tmA, &bars->full[s], k0,
+                             m0 + (int32_t)(n_idx * a_part_rows), mask_a);
             else
-              tma_load_2d_a(a_dst + LIN_A_BYTES, &tmW, &bars->full[s], kb * LIN_BK, n0);
+              tma_load_2d_a(a_dst, &tmA, &bars->full[s], k0, m0);
+            if (!wres) {
+              if (cm > 1)
+                tma_load_2d_mc(a_dst + LIN_A_BYTES + m_idx * w_part_bytes, &tmW, &bars->full[s],
+                               k0, n0 + (int32_t)(m_idx * w_part_rows), mask_w);
+              else
+                tma_load_2d_a(a_dst + LIN_A_BYTES, &tmW, &bars->full[s], k0, n0);
+            }
           }
           if (++s == (uint32_t)stages) { s = 0; ph ^= 1; }
         }
@@ -416,27 +424,31 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
       stamp(it, 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + buf * 256;
-      for (int kb = kb0; kb < kb1; ++kb) {
+      for (int kb = kb0; kb < kb1; kb += kpb) {
+        const int nb = min(kpb, kb1 - kb);
         mbar_wait(&bars->full[s], ph);
         stage_stamp(1);
         if (kb == kb0) stamp(it, 2);
-        if (kb == kb1 - 1) stamp(it, 3);
+        if (kb + nb >= kb1) stamp(it, 3);
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t a_addr = ring_a + s * (uint32_t)stage_bytes;
-          const uint32_t b_addr = wres ? wres_a + (uint32_t)(kb * b_bytes) : a_addr + LIN_A_BYTES;
-          const uint64_t adesc = make_kmajor_desc<128>(a_addr);
-          const uint64_t bdesc = make_kmajor_desc<128>(b_addr);
-          if (!(coalesce_in & 8)) {   // (8: profiling without tensor work, data path only)
-            // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4) units
-            mma_bf16_ss(tmem_d, adesc, bdesc, idesc, kb != kb0);
-            mma_bf16_ss(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
-            mma_bf16_ss(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
-            mma_bf16_ss(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
+          for (int j = 0; j < nb; ++j) {
+            const uint32_t a_addr = ring_a + s * (uint32_t)stage_bytes + (uint32_t)(j * kb_bytes);
+            const uint32_t b_addr =
+                wres ? wres_a + (uint32_t)((kb + j) * b_bytes) : a_addr + LIN_A_BYTES;
+            const uint64_t adesc = make_kmajor_desc<128>(a_addr);
+            const uint64_t bdesc = make_kmajor_desc<128>(b_addr);
+            if (!(coalesce_in & 8)) {   // (8: profiling without tensor work, data path only)
+              // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4) units
+              mma_bf16_ss(tmem_d, adesc, bdesc, idesc, kb + j != kb0);
+              mma_bf16_ss(tmem_d, adesc + 2, bdesc + 2, idesc, 1);
+              mma_bf16_ss(tmem_d, adesc + 4, bdesc + 4, idesc, 1);
+              mma_bf16_ss(tmem_d, adesc + 6, bdesc + 6, idesc, 1);
+            }
           }
           if (csize > 1) mma_commit_mc(&bars->empty[s], mask_rel);
           else mma_commit(&bars->empty[s]);
-          if (kb == kb1 - 1) mma_commit(&bars->tmem_full[buf]);
+          if (kb + nb >= kb1) mma_commit(&bars->tmem_full[buf]);
         }
         __syncwarp();
         stage_stamp(2);
@@ -686,7 +698,7 @@ static bool lin_wres_fits(int N, int K, int BN) {
 // C2, 266 MB of A + 351 MB of W for the first post-processing GEMM, and the kernels ran at the
 // L2 -> SM throughput limit (the loads alone, no tensor work, no epilogue, took 2/3 of their time).
 struct LinPlan {
-  int BN, wres, cn, cm, stages, num_n_tiles;
+  int BN, wres, cn, cm, kpb, stages, num_n_tiles;
   size_t smem;
 };
 
@@ -734,8 +746,10 @@ static LinPlan lin_plan(int64_t M, int N, int K, int splits, int accumulate, int
   const size_t fixed = lin_fixed_smem<OutT>(N, BN);
   const size_t b_bytes = (size_t)BN * LIN_BK * 2;
   const size_t w_bytes = (size_t)ceil_div(K, LIN_BK) * b_bytes;
-  const size_t stage_bytes = (size_t)LIN_A_BYTES + (p.wres ? 0 : b_bytes);
   const size_t avail = 227 * 1024 - fixed - (p.wres ? w_bytes : 0);
+  static const bool no_kpb2 = getenv("GN_TC_KPB1") != nullptr;
+  p.kpb = (p.wres && !no_kpb2 && ceil_div(K, LIN_BK) >= 2 && avail >= 3 * 2 * (size_t)LIN_A_BYTES) ? 2 : 1;
+  const size_t stage_bytes = (size_t)p.kpb * ((size_t)LIN_A_BYTES + (p.wres ? 0 : b_bytes));
   int stages = (int)(avail / stage_bytes);   // as deep as shared memory allows
   p.stages = stages > LIN_STAGES ? LIN_STAGES : stages;
   p.smem = (p.wres ? w_bytes : 0) + (size_t)p.stages * stage_bytes + fixed;
@@ -801,7 +815,7 @@ static int launch_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
                              ((BN * (int)sizeof(OutT)) % 16 == 0));
   const int csize = pl.cn * pl.cm;
   const int64_t num_items = num_tiles * splits;
-  const int wres = pl.wres, stages = pl.stages, cshape = pl.cn | (pl.cm << 8);
+  const int wres = pl.wres, stages = pl.stages, cshape = pl.cn | (pl.cm << 8) | (pl.kpb << 16);
   const size_t smem = pl.smem;
   /* per kernel instantiation and device, once: the opt-in to > 48 KB of dynamic shared memory   \
      and how many clusters of each size the device holds at a time (a persistent kernel must not  \
