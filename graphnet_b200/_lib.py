@@ -102,6 +102,9 @@ SIGNATURES = {
                                             _i64, _p, _hp, _int, _p, _sz, _p]),
     "gn_split_bf16": (_int, [_p, _i64, _i64, _int, _int, _int, _p, _i64, _p]),
     "gn_split_bf16_both": (_int, [_p, _i64, _i64, _int, _int, _p, _i64, _p, _i64, _p]),
+    "gn_graph_capture_begin": (_int, [C.POINTER(C.c_void_p)]),
+    "gn_graph_capture_launch": (_int, [_p, _p]),
+    "gn_graph_capture_abort": (_int, []),
     "gn_tc_linear_pool": (_int, [_p, _i64, _p, _i64, _int, _p, _i64, _int, _int, _p, _p, _i64, _p, _p]),
     "gn_pool_finalize": (_int, [_p, _p, _i64, _int, _hp, _int, _p, _i64, _p, _i64, C.c_float, _p]),
     "gn_linear_f32": (_int, [_p, _i64, _p, _p, _p, _i64, _int, _i64, _int, _int, _int, _p]),

@@ -323,3 +323,93 @@ extern "C" int gn_dynedge_infer16(const gn_dynedge_plan* pl, const float* x, int
   }
   return GN_OK;
 }
+
+// The same mechanism for a launch sequence the CALLER composes from this library's entry points
+// (the fp32 forward of dynedge_x3.py, any pipeline of gn_* calls): between
+// gn_graph_capture_begin and gn_graph_capture_launch every call must be given the returned stream;
+// nothing runs until the launch, which folds the captured sequence into the executable graph
+// cached under `key` (cudaGraphExecUpdate; instantiated on first use or when the topology
+// changed) and launches it on `stream`.  One capture per device at a time (the pair holds a
+// per-device lock).  gn_graph_capture_launch returns GN_ERR_UNSUPPORTED when the sequence could
+// not be captured (e.g. first launch of a kernel the driver had not loaded): the caller then
+// issues the same calls directly.
+extern "C" int gn_graph_capture_begin(void** capture_stream) {
+  GN_CHECK_ARG(capture_stream != nullptr, "gn_graph_capture_begin: null pointer");
+  int dev = 0;
+  GN_CUDA(cudaGetDevice(&dev));
+  GraphCache& gc = g_graphs[dev & 63];
+  gc.mu.lock();
+  cudaError_t e = cudaSuccess;
+  if (gc.cap == nullptr) e = cudaStreamCreateWithFlags(&gc.cap, cudaStreamNonBlocking);
+  // (relaxed mode: the caller's allocator may call cudaMalloc between the launches; the capture
+  // stream is private, nothing else can depend on it)
+  if (e == cudaSuccess) e = cudaStreamBeginCapture(gc.cap, cudaStreamCaptureModeRelaxed);
+  if (e != cudaSuccess) {
+    gc.mu.unlock();
+    set_error("gn_graph_capture_begin: %s", cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return GN_ERR_CUDA;
+  }
+  *capture_stream = gc.cap;
+  return GN_OK;
+}
+
+static int graph_capture_finish(const void* key, cudaStream_t st, bool launch) {
+  int dev = 0;
+  GN_CUDA(cudaGetDevice(&dev));
+  GraphCache& gc = g_graphs[dev & 63];
+  cudaGraph_t graph = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture(gc.cap, &graph);
+  int rc = GN_OK;
+  if (!launch || ce != cudaSuccess || graph == nullptr) {
+    if (graph) cudaGraphDestroy(graph);
+    (void)cudaGetLastError();
+    if (launch) {
+      set_error("gn_graph_capture_launch: the sequence could not be captured (%s)",
+                cudaGetErrorString(ce));
+      rc = GN_ERR_UNSUPPORTED;
+    }
+    gc.mu.unlock();
+    return rc;
+  }
+  GraphSlot* slot = nullptr;
+  for (GraphSlot& c : gc.slots)
+    if (c.exec != nullptr && c.plan == key && !c.has_edges) slot = &c;
+  if (slot == nullptr) {
+    slot = &gc.slots[gc.next];
+    gc.next = (gc.next + 1) % 4;
+    if (slot->exec != nullptr) cudaGraphExecDestroy(slot->exec);
+    slot->exec = nullptr;
+    slot->plan = key;
+    slot->has_edges = false;
+  }
+  if (slot->exec != nullptr) {
+    cudaGraphExecUpdateResultInfo info;
+    if (cudaGraphExecUpdate(slot->exec, graph, &info) != cudaSuccess) {
+      (void)cudaGetLastError();
+      cudaGraphExecDestroy(slot->exec);
+      slot->exec = nullptr;
+    }
+  }
+  cudaError_t e = cudaSuccess;
+  if (slot->exec == nullptr) e = cudaGraphInstantiate(&slot->exec, graph, 0);
+  if (e == cudaSuccess) e = cudaGraphLaunch(slot->exec, st);
+  cudaGraphDestroy(graph);
+  if (e != cudaSuccess) {
+    if (slot->exec) cudaGraphExecDestroy(slot->exec);
+    slot->exec = nullptr;
+    set_error("gn_graph_capture_launch: %s", cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    rc = GN_ERR_CUDA;
+  }
+  gc.mu.unlock();
+  return rc;
+}
+
+extern "C" int gn_graph_capture_launch(const void* key, void* stream) {
+  return graph_capture_finish(key, as_stream(stream), true);
+}
+
+extern "C" int gn_graph_capture_abort(void) {
+  return graph_capture_finish(nullptr, nullptr, false);
+}

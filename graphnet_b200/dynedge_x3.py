@@ -132,55 +132,65 @@ def forward_f32_tc(model, data: Any, edge_index: Optional[Tensor] = None) -> Ten
     dev = x.device
     F = model._nb_inputs
     assert x.shape[1] == F, f"expected {F} input features, got {x.shape[1]}"
-    offs, total = pack.offs, pack.total
-    x0w = offs[0]
-    # S: every layer's features as bf16 [hi | lo | hi] triplets, [x0 | conv1 | conv2 | ...]; the
-    # node GEMM of a layer reads its own triplet, the post-processing MLP the whole row
-    S = torch.empty((N, 3 * total), dtype=torch.bfloat16, device=dev)
-    xl = torch.empty((N, x0w), dtype=torch.float32, device=dev)     # layer input, fp32
-    ops.global_variables(x, graph, ptr, n_pulses, x0=S, x0_cols=x0w, x0b=xl, x0b_cols=x0w,
-                         x0_split=True)
-    A6 = ops.split_bf16(xl, x0w, terms=6)
-    for li, cv in enumerate(pack.convs):
-        pk, kc = cv["pk"], cv["kc"]
-        PQ = torch.empty((N, 2 * pk.Kp), dtype=torch.float32, device=dev)
-        ops.tc_linear_bf16(A6, cv["Wpq6"], pk.bias_pq, PQ, K=6 * kc, act="none")
-        last = li + 1 == len(pack.convs)
-        cols = cv["cols"]
-        xl = torch.empty((N, pk.b), dtype=torch.float32, device=dev)
-        coords = None if last else torch.empty((N, len(cols)), dtype=torch.float32, device=dev)
-        ops.tc_edge_mlp_aggregate_f32(PQ[:, :pk.Kp], PQ[:, pk.Kp:], pk.Kp, graph, _slots(cv["k"]),
-                                      cv["W2hi"], cv["W2lo"], pk.b, xl, coords, cols)
-        if last:
-            ops.split_bf16(xl, _round_up(pk.b, 8), terms=3, out=S[:, 3 * offs[li]:])
-        else:   # three terms for the post-processing MLP, six for the next node GEMM: one read
-            A6 = ops.split_bf16_both(xl, _round_up(pk.b, 8), S[:, 3 * offs[li]:])
-            graph = ops.knn_graph_ell(coords, cv["k"], ptr, list(range(len(cols))))
-    h16 = S
-    pools = model._global_pooling_schemes if not model._skip_readout else None
+    n_pulses = n_pulses.to(torch.int32).contiguous()   # (torch kernels stay outside the capture)
     batch = getattr(data, "batch", None)
-    fuse_pool = bool(pools) and isinstance(batch, Tensor) and batch.dtype == torch.int64 \
-        and pack.post[-1][2] % 2 == 0
-    h = pooled = None
-    for i, (Wp, bias, n, K) in enumerate(pack.post):
-        lastp = i + 1 == len(pack.post)
-        if lastp and fuse_pool:
-            pooled = torch.empty((B, n * len(pools)), dtype=torch.float32, device=dev)
-            ops.tc_linear_pool(h16, Wp, bias, K, batch.contiguous(), ptr, pools, pooled)
-            break
-        h = torch.empty((N, n), dtype=torch.float32, device=dev)
-        ops.tc_linear_bf16(h16, Wp, bias, h, K=K, act="relu")
-        if not lastp:
-            h16 = ops.split_bf16(h, _round_up(n, 8), terms=3)
-    if model._skip_readout:
-        return h
-    if pools and pooled is None:
-        pooled = ops.segment_pool(h, ptr, pools)
-    out = pooled if pooled is not None else h
-    ro, ract = _parse_mlp(model._readout)
-    for lin in ro:
-        out = ops.linear_f32(out, lin.weight, lin.bias, act=ract)
-    return out
+    if isinstance(batch, Tensor):
+        batch = batch.contiguous()
+
+    def body() -> Tensor:
+        # only this library's launches and torch.empty from here on: ops.run_captured replays
+        # them as one CUDA graph (no idle GPU between the ~35 kernels)
+        g = graph
+        offs, total = pack.offs, pack.total
+        x0w = offs[0]
+        # S: every layer's features as bf16 [hi | lo | hi] triplets, [x0 | conv1 | conv2 | ...]; the
+        # node GEMM of a layer reads its own triplet, the post-processing MLP the whole row
+        S = torch.empty((N, 3 * total), dtype=torch.bfloat16, device=dev)
+        xl = torch.empty((N, x0w), dtype=torch.float32, device=dev)     # layer input, fp32
+        ops.global_variables(x, g, ptr, n_pulses, x0=S, x0_cols=x0w, x0b=xl, x0b_cols=x0w,
+                             x0_split=True)
+        A6 = ops.split_bf16(xl, x0w, terms=6)
+        for li, cv in enumerate(pack.convs):
+            pk, kc = cv["pk"], cv["kc"]
+            PQ = torch.empty((N, 2 * pk.Kp), dtype=torch.float32, device=dev)
+            ops.tc_linear_bf16(A6, cv["Wpq6"], pk.bias_pq, PQ, K=6 * kc, act="none")
+            last = li + 1 == len(pack.convs)
+            cols = cv["cols"]
+            xl = torch.empty((N, pk.b), dtype=torch.float32, device=dev)
+            coords = None if last else torch.empty((N, len(cols)), dtype=torch.float32, device=dev)
+            ops.tc_edge_mlp_aggregate_f32(PQ[:, :pk.Kp], PQ[:, pk.Kp:], pk.Kp, g, _slots(cv["k"]),
+                                          cv["W2hi"], cv["W2lo"], pk.b, xl, coords, cols)
+            if last:
+                ops.split_bf16(xl, _round_up(pk.b, 8), terms=3, out=S[:, 3 * offs[li]:])
+            else:   # three terms for the post-processing MLP, six for the next node GEMM: one read
+                A6 = ops.split_bf16_both(xl, _round_up(pk.b, 8), S[:, 3 * offs[li]:])
+                g = ops.knn_graph_ell(coords, cv["k"], ptr, list(range(len(cols))))
+        h16 = S
+        pools = model._global_pooling_schemes if not model._skip_readout else None
+        fuse_pool = bool(pools) and isinstance(batch, Tensor) and batch.dtype == torch.int64 \
+            and pack.post[-1][2] % 2 == 0
+        h = pooled = None
+        for i, (Wp, bias, n, K) in enumerate(pack.post):
+            lastp = i + 1 == len(pack.post)
+            if lastp and fuse_pool:
+                pooled = torch.empty((B, n * len(pools)), dtype=torch.float32, device=dev)
+                ops.tc_linear_pool(h16, Wp, bias, K, batch, ptr, pools, pooled)
+                break
+            h = torch.empty((N, n), dtype=torch.float32, device=dev)
+            ops.tc_linear_bf16(h16, Wp, bias, h, K=K, act="relu")
+            if not lastp:
+                h16 = ops.split_bf16(h, _round_up(n, 8), terms=3)
+        if model._skip_readout:
+            return h
+        if pools and pooled is None:
+            pooled = ops.segment_pool(h, ptr, pools)
+        out = pooled if pooled is not None else h
+        ro, ract = _parse_mlp(model._readout)
+        for lin in ro:
+            out = ops.linear_f32(out, lin.weight, lin.bias, act=ract)
+        return out
+
+    return ops.run_captured(id(pack), dev, body)
 
 
 def time_edge_kernel_f32(model, data: Any, flush_buf: Tensor, layer: int = 1, reps: int = 5):

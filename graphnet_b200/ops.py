@@ -9,8 +9,10 @@ Every wrapper refuses CPU tensors - there is no CPU path.
 from __future__ import annotations
 
 import ctypes as C
+import os
+import threading
 from dataclasses import dataclass
-from typing import List, Optional, Sequence, Tuple, Union
+from typing import Any, Callable, List, Optional, Sequence, Tuple, Union
 
 import torch
 from torch import Tensor
@@ -38,10 +40,14 @@ def _require_cuda(*tensors: Optional[Tensor]) -> torch.device:
 
 
 _raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_capture = threading.local()   # .stream: the library's capture stream while run_captured is active
 
 
 def _stream(dev: torch.device) -> C.c_void_p:
     # the raw handle of torch's current stream (no Stream object per call where torch offers it)
+    cap = getattr(_capture, "stream", None)
+    if cap is not None:
+        return C.c_void_p(cap)
     if _raw_stream is None:
         return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     return C.c_void_p(_raw_stream(dev.index if dev.index is not None
@@ -64,6 +70,35 @@ def _on(dev: torch.device):
     if dev.index is None or dev.index == torch.cuda.current_device():
         return _NO_SWITCH
     return torch.cuda.device(dev)
+
+
+def run_captured(key: int, dev: torch.device, fn: Callable[[], Any]) -> Any:
+    """Run `fn` - a sequence of this module's calls on `dev` and `torch.empty` allocations, NO
+    torch kernels - with every launch captured and replayed as one executable CUDA graph on the
+    current stream (gn_graph_capture_begin / _launch: the graph cached under `key` is updated
+    with this call's parameters, so shapes may change from call to call).  No idle GPU between
+    the kernels.  Falls back to running `fn` directly when capturing is not possible (the
+    current stream is itself capturing, GN_NO_GRAPH=1, or the driver refuses the capture)."""
+    if os.environ.get("GN_NO_GRAPH") or getattr(_capture, "stream", None) is not None or \
+            torch.cuda.is_current_stream_capturing():
+        return fn()
+    lib = _lib.load()
+    with _on(dev):
+        real = _stream(dev)
+        handle = C.c_void_p()
+        if lib.gn_graph_capture_begin(C.byref(handle)) != 0:
+            return fn()
+        _capture.stream = handle.value
+        try:
+            out = fn()
+        except BaseException:
+            _capture.stream = None
+            lib.gn_graph_capture_abort()
+            raise
+        _capture.stream = None
+        if lib.gn_graph_capture_launch(C.c_void_p(key), real) != 0:
+            return fn()      # not capturable here (first use of a kernel): direct launches
+    return out
 
 
 def _ptr(t: Optional[Tensor]) -> C.c_void_p:

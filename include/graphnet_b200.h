@@ -491,6 +491,19 @@ int gn_segment_pool_backward(const void* x, int x_dtype, int64_t ldx, int C, con
 int gn_csr_to_ell(const int32_t* rowptr, const int32_t* col, int64_t N, int stride, int32_t* nbr,
                   int32_t* deg, int32_t* flags, void* stream);
 
+/* Launch sequences composed by the caller, without idle GPU between the kernels: every gn_* call
+ * between gn_graph_capture_begin and gn_graph_capture_launch is given the stream `begin` returns
+ * (a private stream in capture mode: nothing runs); `launch` folds the captured sequence into the
+ * executable CUDA graph cached under `key` (cudaGraphExecUpdate: same topology, new parameters -
+ * batches of any size; instantiated on first use or when the topology changed) and launches it on
+ * `stream`.  Only this library's calls (and no allocation, no synchronisation) may happen in
+ * between; one capture per device at a time.  `launch` returns GN_ERR_UNSUPPORTED when the
+ * sequence could not be captured: issue the same calls directly then.  `abort` drops a capture.
+ * gn_dynedge_infer16 does this internally.  No counterpart in the reference. */
+int gn_graph_capture_begin(void** capture_stream);
+int gn_graph_capture_launch(const void* key, void* stream);
+int gn_graph_capture_abort(void);
+
 #ifdef __cplusplus
 }
 #endif
