@@ -388,3 +388,45 @@ def test_min_edge_slots_gives_the_same_forward():
     assert rel_l2(got, want) < 1e-2
     m.native_driver = False
     assert torch.equal(m(data), got)
+
+
+def test_graph_updating_driver_over_changing_batches_streams_and_models():
+    """gn_dynedge_infer16 re-captures every call and updates one cached executable graph: batches
+    of different sizes, with and without edge_index, on a side stream, two models alternating -
+    every result must equal the call-by-call sequence on the same inputs."""
+    import graphnet_b200 as gb
+    torch.manual_seed(7)
+    m1 = gb.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision="bf16").to(DEV).eval()
+    m2 = gb.DynEdge(7, global_pooling_schemes=["mean"], nb_neighbours=4, precision="fp16",
+                    dynedge_layer_sizes=[(64, 128), (168, 128)], post_processing_layer_sizes=[168, 128],
+                    readout_layer_sizes=[64]).to(DEV).eval()
+    batches = []
+    for seed, (nev, lo, hi) in enumerate([(1, 40, 40), (50, 1, 30), (9, 100, 300), (3, 1, 3), (50, 1, 30)]):
+        x, batch, counts = random_events(nev, lo, hi, seed=20 + seed)
+        d = gb.Data(x=x.to(DEV), batch=batch.to(DEV), n_pulses=counts.to(DEV))
+        if seed % 2:
+            d.edge_index = gb.knn_graph(x[:, :3].contiguous().to(DEV), 8, batch.to(DEV), num_events=nev)
+        batches.append(d)
+    side = torch.cuda.Stream()
+    got = []
+    for rep in range(2):
+        for i, d in enumerate(batches):
+            for m in (m1, m2):
+                if (i + rep) % 2:
+                    side.wait_stream(torch.cuda.current_stream())
+                    with torch.cuda.stream(side):
+                        got.append(m(d))
+                    torch.cuda.current_stream().wait_stream(side)
+                else:
+                    got.append(m(d))
+    torch.cuda.synchronize()
+    want = []
+    for m in (m1, m2):
+        m.native_driver = False
+    for rep in range(2):
+        for d in batches:
+            for m in (m1, m2):
+                want.append(m(d))
+    assert len(got) == len(want)
+    for a, b in zip(got, want):
+        assert a.shape == b.shape and torch.equal(a, b)

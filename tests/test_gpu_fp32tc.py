@@ -176,3 +176,33 @@ def test_split_bf16_both_equals_the_two_separate_layouts():
     assert torch.equal(out3[:, :3 * kc], ops.split_bf16(X, kc, terms=3))
     assert torch.equal(out6, ops.split_bf16(X, kc, terms=6))
     assert bool((out3[:, 3 * kc:] == 0).all())
+
+
+def test_run_captured_replays_and_falls_back():
+    """ops.run_captured: the fp32 forward as one updated CUDA graph gives the same bits as direct
+    launches (GN_NO_GRAPH), for changing batch sizes; an exception inside the captured function
+    leaves the library usable."""
+    import os
+    import graphnet_b200 as gb
+    import graphnet_b200.ops as ops
+    torch.manual_seed(3)
+    m = gb.DynEdge(7, global_pooling_schemes=["min", "max", "mean", "sum"], precision="fp32").to(DEV).eval()
+    datas = []
+    for seed, (nev, lo, hi) in enumerate([(12, 5, 60), (1, 33, 33), (30, 1, 20)]):
+        x, batch, counts = random_events(nev, lo, hi, seed=40 + seed)
+        datas.append(gb.Data(x=x.to(DEV), batch=batch.to(DEV), n_pulses=counts.to(DEV)))
+    got = [m(d) for d in datas + datas]
+    os.environ["GN_NO_GRAPH"] = "1"
+    try:
+        want = [m(d) for d in datas + datas]
+    finally:
+        del os.environ["GN_NO_GRAPH"]
+    for a, b in zip(got, want):
+        assert torch.equal(a, b)
+
+    def boom():
+        ops.split_bf16(torch.ones(4, 8, device=DEV), 8)
+        raise RuntimeError("inside the capture")
+    with pytest.raises(RuntimeError, match="inside the capture"):
+        ops.run_captured(12345, torch.device(DEV), boom)
+    assert torch.equal(m(datas[0]), want[0])
