@@ -213,7 +213,7 @@ constexpr float POOL_FIX_MAX = 1073741824.f;          // elements are clamped to
 template <typename OutT, int ACT, bool POOL = false>
 __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
     const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-    const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
+    const __grid_constant__ CUtensorMap tmC, const float* __restrict__ bias, OutT* __restrict__ C, int64_t ldc, int64_t M, int N, int K,
     int BN, int num_n_tiles, int64_t num_tiles, uint32_t idesc, int stages, int splits,
     int accumulate, int coalesce_in, int wres, int cshape, const PoolEpilogue pool) {
   constexpr int LIN_EPI_WARPS = lin_epi_warps<OutT>();
@@ -258,7 +258,8 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
   LinBarriers* bars = reinterpret_cast<LinBarriers*>(ring + stages * stage_bytes);
   float* s_bias = reinterpret_cast<float*>(bars + 1);  // [num_n_tiles * BN]
   uint8_t* s_scr = reinterpret_cast<uint8_t*>(s_bias + num_n_tiles * BN);  // one scratch per epilogue warp
-  s_scr = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_scr) + 15) & ~uintptr_t(15));
+  // (512-byte aligned: a 16-bit scratch is a 64B-swizzled TMA store box)
+  s_scr = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_scr) + 511) & ~uintptr_t(511));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = (K + LIN_BK - 1) / LIN_BK;
@@ -595,8 +596,22 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
               sts128(mine + (uint32_t)(((j >> 3) ^ wsw) << 4), u);
             }
           }
-          __syncwarp();
           const int nv = min(N - n, BN - c);                 // valid columns of this chunk
+          if constexpr (sizeof(OutT) == 2) {
+            // the scratch IS a 64B-swizzled [32 rows x 64 bytes] box: a full chunk leaves as one
+            // TMA store (rows beyond M are clipped by the unit) - no read-back, no per-lane stores
+            if ((coalesce_in & 32) && BN - c >= 32) {
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                if (!(coalesce_in & 2)) tma_store_2d(&tmC, scr, n, (int32_t)(m0 + q * 32));
+                tma_store_wait_read();     // (the next chunk rewrites the scratch)
+              }
+              __syncwarp();
+              return;
+            }
+          }
+          __syncwarp();
           const int piece = lane % P, rsub = lane / P;
 #pragma unroll
           for (int i = 0; i < P; ++i) {
@@ -657,6 +672,7 @@ __global__ void __launch_bounds__(lin_threads<OutT>(), 1) tc_linear_kernel(
       stamp(it, 2);
     }
   }
+  if (warp >= 2 && lane == 0) tma_store_wait_all();
   tc_fence_before();
   __syncthreads();
   if (csize > 1) cl_sync();   // no CTA leaves while a peer may still signal its barriers
@@ -680,7 +696,7 @@ template <typename OutT>
 static size_t lin_fixed_smem(int N, int BN) {
   const int num_n_tiles = (N + BN - 1) / BN;
   return sizeof(LinBarriers) + (size_t)num_n_tiles * BN * sizeof(float) + 32 + 1024 +
-         (size_t)lin_epi_warps<OutT>() * lin_scr_bytes<OutT>() + 16;
+         (size_t)lin_epi_warps<OutT>() * lin_scr_bytes<OutT>() + 512;
 }
 // does a K-complete W tile of width BN fit next to a ring of at least four A stages?
 template <typename OutT>
@@ -799,6 +815,8 @@ static int launch_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
   if (rc != GN_OK) return rc;
   const uint32_t idesc =
       ab_dtype == GN_F16 ? make_idesc_f16(LIN_BM, BN) : make_idesc_bf16(LIN_BM, BN);
+  CUtensorMap tmC = tmA;      // (only read by 16-bit outputs with TMA stores)
+  bool tma_store = false;
   // 16-byte stores need C rows and the tile's first column on 16-byte boundaries
   static const bool no_coalesce = getenv("GN_TC_NO_COALESCE") != nullptr;
 #ifdef GN_DEBUG_BUILD   // ablation / trace switches exist in profiling builds only
@@ -813,6 +831,15 @@ static int launch_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
                        (int)(!no_coalesce && (reinterpret_cast<uintptr_t>(C) % 16 == 0) &&
                              ((ldc * (int64_t)sizeof(OutT)) % 16 == 0) &&
                              ((BN * (int)sizeof(OutT)) % 16 == 0));
+  if (sizeof(OutT) == 2 && coalesce != 0 && splits == 1 && !accumulate) {
+    static const bool no_tma_store = getenv("GN_TC_NO_TMASTORE") != nullptr;
+    if (!no_tma_store) {
+      // C as a [M, N] tensor of 16-bit elements, boxes of 32 rows x 32 columns, 64B swizzle
+      rc = make_tmap_f16_2d(&tmC, C, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 32, 32, 64);
+      if (rc != GN_OK) return rc;
+      tma_store = true;
+    }
+  }
   const int csize = pl.cn * pl.cm;
   const int64_t num_items = num_tiles * splits;
   const int wres = pl.wres, stages = pl.stages, cshape = pl.cn | (pl.cm << 8) | (pl.kpb << 16);
@@ -864,9 +891,9 @@ static int launch_tc_linear(const void* A, int64_t lda, const void* W, int64_t l
       grid = (unsigned)(num_items < sms ? num_items : sms);                                     \
     }                                                                                           \
     cfg.gridDim = dim3(grid);                                                                   \
-    GN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
+    GN_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, tmC, bias, reinterpret_cast<OutT*>(C), ldc, M, N, \
                                K, BN, num_n_tiles, num_tiles, idesc, stages, splits,             \
-                               accumulate, coalesce, wres, cshape, pool));                      \
+                               accumulate, coalesce | (tma_store ? 32 : 0), wres, cshape, pool)); \
   }
 #define GN_TC_LIN_CASE(A_) GN_TC_LIN_LAUNCH((tc_linear_kernel<OutT, A_, false>))
   if (pool.acc != nullptr) {
