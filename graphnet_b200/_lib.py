@@ -102,6 +102,7 @@ SIGNATURES = {
                                             _i64, _p, _hp, _int, _p, _sz, _p]),
     "gn_split_bf16": (_int, [_p, _i64, _i64, _int, _int, _int, _p, _i64, _p]),
     "gn_split_bf16_both": (_int, [_p, _i64, _i64, _int, _int, _p, _i64, _p, _i64, _p]),
+    "gn_zero": (_int, [_p, _sz, _p]),
     "gn_graph_capture_begin": (_int, [C.POINTER(C.c_void_p)]),
     "gn_graph_capture_launch": (_int, [_p, _p]),
     "gn_graph_capture_abort": (_int, []),

@@ -1028,6 +1028,13 @@ extern "C" int gn_outer_accumulate_f32(const float* G, int64_t ldg, int cols, co
   return GN_OK;
 }
 
+extern "C" int gn_zero(void* p, size_t bytes, void* stream) {
+  if (bytes == 0) return GN_OK;
+  GN_CHECK_ARG(p != nullptr, "gn_zero: null pointer");
+  GN_CUDA(cudaMemsetAsync(p, 0, bytes, as_stream(stream)));
+  return GN_OK;
+}
+
 extern "C" int gn_convert_scale_16(const float* X, int64_t ldx, void* out, int out_dtype,
                                    int64_t ldo, int64_t M, int N, float scale, void* stream) {
   GN_CHECK_ARG(M >= 0 && N >= 1 && ldx >= N && ldo >= N, "gn_convert_scale_16: bad sizes");

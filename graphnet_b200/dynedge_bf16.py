@@ -303,8 +303,45 @@ def _forward_native(model, np_: _NativePlan, data: Any, edge_index: Optional[Ten
     return out
 
 
+def _readout_weight(model, ri: int, lin) -> Tensor:
+    """fp16 copy of a readout Linear's weight times 2^6 (per parameter version)."""
+    key = f"_cache_readout_{ri}"
+    if not hasattr(model, key):
+        setattr(model, key, _WeightCache())
+    return getattr(model, key).get(
+        [lin.weight],
+        lambda: (lin.weight.detach().float() * 64.0).to(torch.float16).contiguous())
+
+
+def prepare_training(model, data: Any):
+    """Everything of the training forward that is NOT a launch of this library: the batch's graph
+    inputs (tensor fills inside), the data set's CSR graph as a slot table (one device -> host
+    read), the weight repacks of this parameter version (tensor ops on a cache miss, i.e. every
+    step).  `forward_bf16(..., save=..., prep=...)` is launches and `torch.empty` only after this
+    and can replay as one updated CUDA graph (`ops.run_captured`)."""
+    x, n_pulses, ptr, graph, N, B = model._graph_inputs(data, None)
+    io = _io_dtype(model)
+    convs = list(model._conv_layers)
+    for li, conv in enumerate(convs):
+        _conv_pack(conv, io, first=(li == 0), train=True)
+    D0, widths, offs, total = _skip_layout(model)
+    _post_pack(model, total, D0, widths, offs, io)
+    if not model._skip_readout:
+        for ri, lin in enumerate(_parse_mlp(model._readout)[0]):
+            _readout_weight(model, ri, lin)
+    slots = _slots(convs[0].nb_neighbors)
+    if graph.ell_stride <= 0 and graph.max_degree is not None and \
+            int(graph.max_degree.item()) <= slots:
+        flags = graph.flags
+        graph = ops.csr_to_ell(graph, slots)
+        graph.flags = flags
+    n_pulses = n_pulses.to(torch.int32).contiguous()
+    return x, n_pulses, ptr, graph, N, B
+
+
 def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
-                 return_intermediates: bool = False, save: Optional[Dict[str, Any]] = None):
+                 return_intermediates: bool = False, save: Optional[Dict[str, Any]] = None,
+                 prep: Optional[tuple] = None):
     """`save` (training): receives the tensors the backward pass needs (training.py)."""
     if save is None and not return_intermediates and getattr(model, "native_driver", True) and \
             isinstance(getattr(data, "batch", None), Tensor) and data.batch.dtype == torch.int64 \
@@ -312,7 +349,8 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
         np_ = _native_plan(model, _io_dtype(model))
         if np_ is not None:
             return _forward_native(model, np_, data, edge_index)
-    x, n_pulses, ptr, graph, N, B = model._graph_inputs(data, edge_index)
+    x, n_pulses, ptr, graph, N, B = prep if prep is not None else \
+        model._graph_inputs(data, edge_index)
     model._last_flags = graph.flags
     dev = x.device
     F = model._nb_inputs
@@ -320,7 +358,8 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
     io = _io_dtype(model)
     D0, widths, offs, total = _skip_layout(model)
     needs_zero = any(w % 8 for w in widths)
-    skip = (torch.zeros if needs_zero else torch.empty)((N, total), dtype=io, device=dev)
+    skip = ops.zeros((N, total), io, dev) if needs_zero else \
+        torch.empty((N, total), dtype=io, device=dev)
     x0w = offs[0]
     # inference: the first node GEMM runs on the tensor cores from a bf16 [hi | lo | hi] split of
     # the fp32 input features (GN_BF16X3: 16 mantissa bits, no 8-bit rounding of the coordinates);
@@ -452,12 +491,7 @@ def forward_bf16(model, data: Any, edge_index: Optional[Tensor] = None,
                 # fp32 accumulate and output) - the FFMA kernel needs 35 us for it, this 10
                 # fp16 operands, the input scaled by 2^-6 and the weights by 2^6 (exact): 11
                 # mantissa bits and head-room for sum-pooled values up to 4e6
-                key = f"_cache_readout_{ri}"
-                if not hasattr(model, key):
-                    setattr(model, key, _WeightCache())
-                Wb = getattr(model, key).get(
-                    [lin.weight],
-                    lambda: (lin.weight.detach().float() * 64.0).to(torch.float16).contiguous())
+                Wb = _readout_weight(model, ri, lin)
                 hb = hb16 if (ri == 0 and hb16 is not None) else \
                     ops.convert_scale_16(h, torch.float16, 1.0 / 64.0)
                 out = torch.empty((M_, lin.out_features), dtype=torch.float32, device=dev)

@@ -101,6 +101,16 @@ def run_captured(key: int, dev: torch.device, fn: Callable[[], Any]) -> Any:
     return out
 
 
+def zeros(shape, dtype: torch.dtype, device: torch.device) -> Tensor:
+    """`torch.zeros` whose fill is a launch of this library on the current (or capture) stream -
+    inside `run_captured` a torch fill kernel would run before the captured launches do."""
+    t = torch.empty(shape, dtype=dtype, device=device)
+    with _on(t.device):
+        check(_lib.load().gn_zero(C.c_void_p(t.data_ptr()), t.numel() * t.element_size(),
+                                  _stream(t.device)), "gn_zero")
+    return t
+
+
 def _ptr(t: Optional[Tensor]) -> C.c_void_p:
     return C.c_void_p(0 if t is None else t.data_ptr())
 
@@ -745,7 +755,7 @@ def segment_pool_backward(x: Tensor, ptr: Tensor, schemes: Sequence[str], pooled
     assert pooled.stride(1) == 1 and d_pooled.stride(1) == 1
     N, C_ = x.shape
     B = ptr.shape[0] - 1
-    dX = torch.zeros((N, C_), dtype=torch.float32, device=dev)
+    dX = zeros((N, C_), torch.float32, dev)
     # gn_segment_pool reads float32 or bfloat16 rows (no fp16 loader): anything else would be
     # reinterpreted silently
     assert x.dtype in (torch.float32, torch.bfloat16), f"segment_pool: unsupported dtype {x.dtype}"

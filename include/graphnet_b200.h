@@ -491,6 +491,11 @@ int gn_segment_pool_backward(const void* x, int x_dtype, int64_t ldx, int C, con
 int gn_csr_to_ell(const int32_t* rowptr, const int32_t* col, int64_t N, int stride, int32_t* nbr,
                   int32_t* deg, int32_t* flags, void* stream);
 
+/* Zero `bytes` bytes at p on `stream` (the accumulators of gn_tc_linear_accumulate,
+ * gn_colsum_accumulate, ... inside a captured launch sequence, where the caller's own fill kernels
+ * would run out of order). */
+int gn_zero(void* p, size_t bytes, void* stream);
+
 /* Launch sequences composed by the caller, without idle GPU between the kernels: every gn_* call
  * between gn_graph_capture_begin and gn_graph_capture_launch is given the stream `begin` returns
  * (a private stream in capture mode: nothing runs); `launch` folds the captured sequence into the
