@@ -42,12 +42,16 @@ def shard_ranges(n_pulses: Tensor, world_size: int, balance: str = "pulses") -> 
     return [(bounds[r], bounds[r + 1]) for r in range(world_size)]
 
 
-def take_events(data: Any, lo: int, hi: int) -> Data:
-    """The sub-batch holding events [lo, hi) of a collated batch (host or device tensors)."""
+def take_events(data: Any, lo: int, hi: int, rebase: bool = True) -> Data:
+    """The sub-batch holding events [lo, hi) of a collated batch (host or device tensors).
+    `rebase=False` leaves `batch` (and `edge_index`) as views with the parent's numbering - the
+    caller subtracts `lo` (`sub.node_offset` for edges) after the copy to the device, so that
+    pinned host tensors stay pinned views and the copy stays asynchronous."""
     batch = data.batch
     nlo = int(torch.searchsorted(batch, torch.tensor(lo, device=batch.device)))
     nhi = int(torch.searchsorted(batch, torch.tensor(hi, device=batch.device)))
-    sub = Data(x=data.x[nlo:nhi], batch=batch[nlo:nhi] - lo, n_pulses=data.n_pulses[lo:hi])
+    b = batch[nlo:nhi]
+    sub = Data(x=data.x[nlo:nhi], batch=b - lo if rebase else b, n_pulses=data.n_pulses[lo:hi])
     ei = getattr(data, "edge_index", None)
     if ei is not None:   # a batch without edges gets its graph on the device (DynEdge._graph_inputs)
         keep = (ei[1] >= nlo) & (ei[1] < nhi)
@@ -76,9 +80,14 @@ def predict_sharded(model: Callable[[Any], Tensor], data: Any, device: torch.dev
     rank = dist.get_rank() if dist.is_initialized() else 0
     ranges = shard_ranges(data.n_pulses, world, balance)
     lo, hi = ranges[rank]
-    sub = take_events(data, lo, hi)
-    if device is not None:
-        sub = sub.to(device)
+    if device is not None and getattr(data, "edge_index", None) is None:
+        # views of the (pinned) host tensors, copied asynchronously, re-numbered on the device
+        sub = take_events(data, lo, hi, rebase=False).to(device, non_blocking=True)
+        sub.batch = sub.batch - lo
+    else:
+        sub = take_events(data, lo, hi)
+        if device is not None:
+            sub = sub.to(device)
     out = model(sub)
     if isinstance(out, (list, tuple)):
         out = out[0]
